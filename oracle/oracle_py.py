@@ -1,0 +1,219 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes access to oracle/libptoracle.so (plain-C restatement) and, when it
+has been built, oracle/_ref/libptref.so (the unmodified reference + shims).  Imported by tests/,
+__graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs only."""
+import ctypes as C
+import os
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "libptoracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libptref.so")
+
+_f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+_i32p = np.ctypeslib.ndpointer(dtype=np.int32, flags="C_CONTIGUOUS")
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+
+
+class OrScene(C.Structure):
+    _fields_ = [("n_tri", C.c_int), ("verts9", C.c_void_p), ("planes4", C.c_void_p), ("squares", C.c_void_p),
+                ("mat_ids", C.c_void_p), ("n_mat", C.c_int), ("mats10", C.c_void_p)]
+
+
+class OrConfig(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("max_depth", C.c_int),
+                ("eps", C.c_float), ("error", C.c_float), ("seed", C.c_uint32),
+                ("s_begin", C.c_int), ("s_step", C.c_int)]
+
+
+def _load(path):
+    if not os.path.exists(path):
+        raise FileNotFoundError(f"{path} missing: run `make -C oracle`")
+    return C.CDLL(path)
+
+
+class Oracle:
+    """The plain-C restatement.  A scene is a dict of float32/int32 arrays:
+    verts (n,9), planes (n,4), squares (n,), mat_ids (n,), mats (m,10)."""
+
+    def __init__(self):
+        L = self.lib = _load(ORACLE_SO)
+        L.or_render_accum.restype = C.c_ulonglong
+        L.or_render_accum.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_int, C.POINTER(C.c_double)]
+        L.or_intersect.argtypes = [C.POINTER(OrScene), C.c_float, _f32p, C.c_long, _i32p, _f32p, C.c_int]
+        L.or_triangle_setup.argtypes = [_f32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_float)]
+        L.or_primary_ray.argtypes = [C.POINTER(OrConfig), C.c_int, C.c_int, C.c_int, _f32p, _f32p]
+        L.or_trace_path.restype = C.c_int
+        L.or_trace_path.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+        L.or_resolve.argtypes = [_f32p, _i32p, C.c_long, _f32p]
+        L.or_libm_sincos.argtypes = [_f32p, C.c_long, _f32p, _f32p]
+        L.or_max_threads.restype = C.c_int
+
+    @staticmethod
+    def scene_struct(sc):
+        keep = {k: np.ascontiguousarray(sc[k], dtype=(np.int32 if k == "mat_ids" else np.float32))
+                for k in ("verts", "planes", "squares", "mat_ids", "mats")}
+        s = OrScene(int(keep["verts"].shape[0]), keep["verts"].ctypes.data, keep["planes"].ctypes.data,
+                    keep["squares"].ctypes.data, keep["mat_ids"].ctypes.data, int(keep["mats"].shape[0]),
+                    keep["mats"].ctypes.data)
+        s._keep = keep
+        return s
+
+    @staticmethod
+    def config(width, height, spp, max_depth=8, eps=1e-4, error=-1.0, seed=42, s_begin=0, s_step=1):
+        return OrConfig(width, height, spp, max_depth, eps, error, seed, s_begin, s_step)
+
+    def max_threads(self):
+        return int(self.lib.or_max_threads())
+
+    def triangle_setup(self, verts9, vn=None):
+        v = np.ascontiguousarray(verts9, np.float32).reshape(-1, 9)
+        n = v.shape[0]
+        planes = np.zeros((n, 4), np.float32)
+        squares = np.zeros(n, np.float32)
+        sq = C.c_float()
+        zero = np.zeros(3, np.float32)
+        for i in range(n):
+            has = vn is not None and vn[i] is not None
+            self.lib.or_triangle_setup(v[i].copy(), int(has), np.ascontiguousarray(vn[i], np.float32) if has else zero,
+                                       planes[i], C.byref(sq))
+            squares[i] = sq.value
+        return planes, squares
+
+    def intersect(self, sc, rays6, eps=1e-4, threads=0):
+        rays6 = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = rays6.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        s = self.scene_struct(sc)
+        self.lib.or_intersect(C.byref(s), eps, rays6, n, ids, t, threads or self.max_threads())
+        return ids, t
+
+    def primary_ray(self, cfg, x, y, s):
+        o = np.zeros(3, np.float32)
+        d = np.zeros(3, np.float32)
+        self.lib.or_primary_ray(C.byref(cfg), x, y, s, o, d)
+        return o, d
+
+    def render_accum(self, sc, cfg, threads=0):
+        """-> (sum[H,W,3], sum2[H,W,3], count[H,W] int32, segments, seconds)"""
+        H, W = cfg.height, cfg.width
+        sm = np.zeros((H, W, 3), np.float32)
+        s2 = np.zeros((H, W, 3), np.float32)
+        cnt = np.zeros((H, W), np.int32)
+        sec = C.c_double()
+        s = self.scene_struct(sc)
+        segs = self.lib.or_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data,
+                                        threads or self.max_threads(), C.byref(sec))
+        return sm, s2, cnt, int(segs), sec.value
+
+    def trace_path(self, sc, cfg, x, y, s, max_seg=64):
+        rec = np.zeros((max_seg, 9), np.float32)
+        st = self.scene_struct(sc)
+        n = self.lib.or_trace_path(C.byref(st), C.byref(cfg), x, y, s, max_seg, rec)
+        return rec[:min(n, max_seg)], n
+
+    def resolve(self, sm, cnt):
+        rgb = np.zeros_like(sm)
+        self.lib.or_resolve(np.ascontiguousarray(sm), np.ascontiguousarray(cnt), cnt.size, rgb)
+        return rgb
+
+    def libm_sincos(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        s = np.empty_like(x)
+        c = np.empty_like(x)
+        self.lib.or_libm_sincos(x, x.size, s, c)
+        return s, c
+
+    def philox(self, ctr, key):
+        out = (C.c_uint32 * 4)()
+        self.lib.or_philox((C.c_uint32 * 4)(*ctr), (C.c_uint32 * 2)(*key), out)
+        return [int(v) for v in out]
+
+
+class Reference:
+    """oracle/_ref/libptref.so: the reference's own Scene/Triangle/Material/Ray code (global scene)."""
+
+    def __init__(self):
+        L = self.lib = _load(REF_SO)
+        L.ref_set_config.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_char_p]
+        L.ref_scene_load_obj.restype = C.c_int
+        L.ref_scene_load_obj.argtypes = [C.c_char_p, C.c_char_p]
+        L.ref_scene_from_arrays.restype = C.c_int
+        L.ref_scene_from_arrays.argtypes = [C.c_int, _f32p, C.c_void_p, C.c_void_p, _i32p, C.c_int, _f32p]
+        L.ref_scene_size.restype = C.c_int
+        L.ref_scene_dump.argtypes = [_f32p, _f32p, _f32p]
+        L.ref_intersect.argtypes = [_f32p, C.c_long, _i32p, _f32p, C.c_int]
+        L.ref_primary_ray.argtypes = [C.c_uint, C.c_int, C.c_int, C.c_int, _f32p, _f32p]
+        L.ref_render_accum.restype = C.c_ulonglong
+        L.ref_render_accum.argtypes = [C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_void_p, C.POINTER(C.c_double)]
+        L.ref_trace_path.restype = C.c_int
+        L.ref_trace_path.argtypes = [C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_max_threads.restype = C.c_int
+        self.cfg = None
+
+    @staticmethod
+    def available():
+        return os.path.exists(REF_SO)
+
+    def max_threads(self):
+        return int(self.lib.ref_max_threads())
+
+    def set_config(self, width, height, spp, max_depth=8, eps=1e-4, error=-1.0, skybox=""):
+        self.cfg = (width, height, spp, max_depth)
+        self.lib.ref_set_config(width, height, spp, max_depth, eps, error, skybox.encode())
+
+    def load_obj(self, model_path, model_name):
+        if not model_path.endswith("/"):
+            model_path += "/"
+        return self.lib.ref_scene_load_obj(model_path.encode(), model_name.encode())
+
+    def from_arrays(self, verts, mat_ids, mats, vn=None, has_vn=None):
+        verts = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        mat_ids = np.ascontiguousarray(mat_ids, np.int32)
+        mats = np.ascontiguousarray(mats, np.float32).reshape(-1, 10)
+        hv = vp = None
+        if vn is not None:
+            vn = np.ascontiguousarray(vn, np.float32).reshape(-1, 3)
+            has_vn = np.ascontiguousarray(has_vn if has_vn is not None else np.ones(len(vn)), np.uint8)
+            hv, vp = has_vn.ctypes.data, vn.ctypes.data
+        return self.lib.ref_scene_from_arrays(verts.shape[0], verts, hv, vp, mat_ids, mats.shape[0], mats)
+
+    def dump(self):
+        n = self.lib.ref_scene_size()
+        planes = np.zeros((n, 4), np.float32)
+        verts = np.zeros((n, 9), np.float32)
+        squares = np.zeros(n, np.float32)
+        self.lib.ref_scene_dump(planes, verts, squares)
+        return planes, verts, squares
+
+    def intersect(self, rays6, threads=0):
+        rays6 = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = rays6.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        self.lib.ref_intersect(rays6, n, ids, t, threads or self.max_threads())
+        return ids, t
+
+    def primary_ray(self, seed, x, y, s):
+        o = np.zeros(3, np.float32)
+        d = np.zeros(3, np.float32)
+        self.lib.ref_primary_ray(seed, x, y, s, o, d)
+        return o, d
+
+    def render_accum(self, seed=42, s_begin=0, s_end=None, s_step=1, threads=0, accumulate=False):
+        W, H, spp, _ = self.cfg
+        s_end = spp if s_end is None else s_end
+        sm = np.zeros((H, W, 3), np.float32)
+        s2 = np.zeros((H, W, 3), np.float32)
+        cnt = np.zeros((H, W), np.int32)
+        sec = C.c_double()
+        segs = self.lib.ref_render_accum(seed, s_begin, s_end, s_step, threads or self.max_threads(), int(accumulate),
+                                         sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data, C.byref(sec))
+        return sm, s2, cnt, int(segs), sec.value
+
+    def trace_path(self, seed, x, y, s, max_seg=64):
+        rec = np.zeros((max_seg, 9), np.float32)
+        n = self.lib.ref_trace_path(seed, x, y, s, max_seg, rec)
+        return rec[:min(n, max_seg)], n
