@@ -1,0 +1,156 @@
+/* pt_render.h — C-ABI of the B200-native render loop.
+ *
+ * Drop-in boundary for the per-pixel sample loop of the reference renderer
+ * (Andareon/Path-Tracing, main.cpp:107-160: adaptive-skip test, jittered primary ray,
+ * `while (ray.IsValid()) scene.TraceRay(ray)`), i.e. Scene::TraceRay (scene.cpp:113-157),
+ * Triangle::Intersect (triangles.h:48-73), Material::Process + the Factory closures
+ * (material.h:36-106) and Ray::Reflect / IsValid (ray.h:45-56).
+ *
+ * The reference has no FFI for this path: the loop is inline in main().  These entry points are what a
+ * maintainer would bind in its place.  Plain pointers and sizes only; no C++ or
+ * torch types.  All functions return 0 on success or a PT_E* code; pt_last_error() gives the text.
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with PT_ENODEVICE.
+ */
+#ifndef PT_RENDER_H
+#define PT_RENDER_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* error codes */
+enum {
+    PT_OK = 0,
+    PT_EINVAL = 1,    /* bad argument (null pointer, non-positive size, index out of range) */
+    PT_ENODEVICE = 2, /* no usable CUDA device */
+    PT_ECUDA = 3,     /* a CUDA runtime call or kernel failed */
+    PT_ENCCL = 4,     /* NCCL unavailable or a collective failed */
+    PT_ENOMEM = 5
+};
+
+/* Scene: what Scene::LoadModel / AddTriangle built (scene.cpp:26-111), as plain data.
+ * The reference hides material parameters inside std::function closures (material.h:58-106) and keeps a
+ * Material copy in every Triangle (triangles.h:22); here they are arrays.
+ *   vertices  n×9  Triangle::vertices_ (v0 v1 v2), triangles.h:23
+ *   planes    n×4  Triangle::plane_ = (unit normal, -n·v0) after SetNormal (triangles.h:40-44), including the
+ *                  `vn` override of scene.cpp:102-104
+ *   squares   n    Triangle::square = |AB×AC| (triangles.h:35)
+ *   material_ids n index into materials (the `usemtl <int>` of scene.cpp:105-106)
+ *   materials m×10 MaterialCharacteristics: Ke[3] Kd[3] Ks[3] Ns (material.h:22-28)
+ *   sky_*     optional equirect skybox image, 24-bit BGR rows top-down as bitmap_image holds it
+ *             (scene.cpp:20-22,126-154); sky_bgr == NULL means Config::skybox is empty
+ * planes/squares may be NULL: they are then derived on the device from the vertices with the constructor's
+ * arithmetic (triangles.h:27-44, geometric normal, no `vn` override). */
+typedef struct PtScene {
+    int32_t n_triangles;
+    const float *vertices;
+    const float *planes;
+    const float *squares;
+    const int32_t *material_ids;
+    int32_t n_materials;
+    const float *materials;
+    int32_t sky_width, sky_height;
+    const uint8_t *sky_bgr;
+} PtScene;
+
+/* intersector modes */
+enum {
+    PT_ISECT_REFERENCE = 0, /* plane + area-sum test with absolute eps, triangles.h:48-73 (parity mode, default) */
+    PT_ISECT_WATERTIGHT = 1 /* watertight Möller–Trumbore-style edge test (north_star's throughput intersector) */
+};
+/* acceleration modes */
+enum {
+    PT_ACCEL_AUTO = 0,  /* brute force from shared memory for tiny scenes, LBVH otherwise */
+    PT_ACCEL_BRUTE = 1, /* every triangle in index order, as scene.cpp:114-120 */
+    PT_ACCEL_LBVH = 2
+};
+
+/* Config: the fields of the reference's Config singleton that the loop reads (config.h:10,16-29), followed by
+ * extensions that default (0) to the reference's behaviour. */
+typedef struct PtConfig {
+    int32_t width, height;       /* config.h:16-17 */
+    int32_t rays_per_pixel;      /* config.h:18 */
+    int32_t max_ray_reflections; /* config.h:19 */
+    float eps;                   /* config.h:22 */
+    float error;                 /* config.h:23; < 0 disables the adaptive rule of main.cpp:118-125 */
+    uint32_t seed;               /* config.h:10 / getSeed() config.h:101-104 */
+    /* ---- extensions ---- */
+    int32_t sample_begin; /* first sample index traced by this call (spp partition across GPUs) */
+    int32_t sample_step;  /* stride between sample indices; 0 is read as 1 */
+    int32_t intersector;  /* PT_ISECT_* */
+    int32_t accel;        /* PT_ACCEL_* */
+    int32_t rr_depth;     /* Russian roulette from this bounce on; 0 = off (the reference has none) */
+    int32_t n_gpus;       /* pt_render only: 0/1 = current device; N>1 = split samples over N devices of this
+                             process and sum with one NCCL reduce */
+    int32_t device;       /* first CUDA device ordinal */
+    int32_t reserved[4];
+} PtConfig;
+
+/* Statistics of the last render on a scene handle. */
+typedef struct PtStats {
+    uint64_t segments;        /* committed TraceRay-equivalents (what the reference's loop would have traced) */
+    uint64_t segments_traced; /* traced on the device, including speculative samples the adaptive rule discarded */
+    uint64_t nodes_visited;   /* BVH nodes fetched (0 unless the scene was built with counters on) */
+    uint64_t tris_tested;     /* triangle tests run */
+    float kernel_ms;          /* device time of the render kernel(s), CUDA events */
+    float build_ms;           /* device time of the LBVH build */
+    float upload_ms;
+    int32_t n_nodes;          /* BVH nodes in use */
+    int32_t n_large;          /* triangles kept out of the BVH and tested from shared memory */
+    int32_t accel;            /* PT_ACCEL_* actually used */
+    int32_t launches;         /* kernels launched by the last call */
+} PtStats;
+
+typedef struct PtDeviceScene PtDeviceScene; /* opaque: device-resident SoA triangles, materials, LBVH */
+
+/* ---- the drop-in entry point -------------------------------------------------------------------------
+ * Replaces the loop main.cpp:107-160.  rgb = height*width*3 floats, row-major ((y*W)+x)*3, holding the value
+ * the reference feeds to pow(·,gamma)*255 (main.cpp:179-182): color_map/samples_count, 0 where the count
+ * is 0.  Blocking.  Uploads the scene, builds the LBVH, renders, reduces (n_gpus>1), downloads. */
+int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb);
+
+/* Same, returning the three accumulators of main.cpp:94-99 instead of the resolved image, row-major [y][x]:
+ * sum3 = color_map, sum2_3 = color2_map (H*W*3 floats each), count = samples_count (H*W int32).
+ * Any of the three may be NULL. */
+int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count);
+
+/* ---- device-resident API (what bench.py / a multi-process host drives) ------------------------------- */
+/* Upload + SoA repack + LBVH build on the current device.  `flags` bit 0: keep traversal counters. */
+int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_t flags, PtDeviceScene **out);
+void pt_scene_destroy(PtDeviceScene *ds);
+/* Render into DEVICE buffers (float sum3[H*W*3], float sum2_3[H*W*3], int32 count[H*W]; NULL allowed) on
+ * `stream` (a cudaStream_t, 0 = default stream).  Asynchronous with respect to the host. */
+int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                           int32_t *d_count, void *stream);
+/* rgb = sum/count on the device (main.cpp:179-182 without the gamma); buffers are device pointers. */
+int pt_resolve_device(const float *d_sum3, const int32_t *d_count, int64_t n_pixels, float *d_rgb, void *stream);
+/* Statistics of the last render on this handle (synchronises the device). */
+int pt_scene_stats(PtDeviceScene *ds, PtStats *out);
+
+/* Nearest hit on an explicit ray set, exactly the loop scene.cpp:114-120: rays6 = n×(ox,oy,oz,dx,dy,dz) HOST
+ * floats; the direction is normalised as Ray's constructor does (ray.h:21-25).  tri_id[i] = index in the
+ * caller's triangle order, -1 on a miss; t[i] = hit distance, +inf on a miss. */
+int pt_intersect(const PtScene *scene, const PtConfig *cfg, const float *rays6, int64_t n, int32_t *tri_id, float *t);
+int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const float *rays6, int64_t n, int32_t *tri_id,
+                       float *t);
+
+/* Triangle constructor arithmetic (triangles.h:27-44 + scene.cpp:102-104) for n triangles on the device:
+ * vertices n×9, vn n×3 with has_vn n bytes (both may be NULL) -> planes n×4, squares n.  HOST pointers. */
+int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float *vn, int64_t n, float *planes,
+                      float *squares);
+
+/* Device building blocks exposed for the parity tests (HOST pointers). */
+int pt_philox(const uint32_t *ctr4, const uint32_t *key2, int64_t n, uint32_t *out4);
+int pt_sincos(const float *x, int64_t n, float *s, float *c);
+int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
+
+const char *pt_last_error(void);
+int pt_device_count(void);
+const char *pt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PT_RENDER_H */

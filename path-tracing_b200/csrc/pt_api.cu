@@ -1,0 +1,443 @@
+// pt_api.cu — the C-ABI of include/pt_render.h: scene upload + SoA repack + LBVH build, render, intersect.
+// Compiled for sm_100a only, with -fmad=false (see pt_math.cuh).  There is no CPU path in this library.
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+#include <vector>
+
+#include "../../include/pt_render.h"
+#include "pt_bvh.cuh"
+#include "pt_kernels.cuh"
+
+using namespace ptd;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define CK(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(e_ == cudaErrorMemoryAllocation ? PT_ENOMEM : PT_ECUDA, "%s:%d %s: %s", __FILE__, \
+                        __LINE__, #call, cudaGetErrorString(e_));                                        \
+    } while (0)
+
+int check_device() {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        return fail(PT_ENODEVICE, "no CUDA device (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "count 0" : cudaGetErrorString(e));
+    }
+    return PT_OK;
+}
+
+inline int blocks_for(long long n, int bs) { return (int)((n + bs - 1) / bs); }
+
+template <class T>
+struct DevBuf {  // RAII device allocation
+    T *p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc((void **)&p, (n ? n : 1) * sizeof(T)); }
+    T *release() { T *q = p; p = nullptr; return q; }
+};
+
+}  // namespace
+
+struct PtDeviceScene {
+    int device = 0;
+    int n_tri = 0, n_mat = 0;
+    float4 *tris = nullptr;
+    float4 *nodes = nullptr;
+    float4 *mats = nullptr;
+    unsigned long long *stats = nullptr;  // 4 counters
+    SceneView view{};
+    bool counters = false;
+    int n_nodes = 0;
+    float build_ms = 0.f, upload_ms = 0.f, kernel_ms = 0.f;
+    int launches = 0;
+    int accel = PT_ACCEL_BRUTE;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    bool timed = false;
+};
+
+static int validate_scene(const PtScene *s) {
+    if (!s) return fail(PT_EINVAL, "scene is NULL");
+    if (s->n_triangles < 0 || s->n_materials < 0) return fail(PT_EINVAL, "negative sizes");
+    if (s->n_triangles > 0x0fffffff) return fail(PT_EINVAL, "too many triangles (max 2^28-1)");
+    if (s->n_triangles > 0 && (!s->vertices || !s->material_ids || !s->materials || s->n_materials <= 0))
+        return fail(PT_EINVAL, "vertices, material_ids and materials are required");
+    if ((s->planes == nullptr) != (s->squares == nullptr))
+        return fail(PT_EINVAL, "planes and squares must both be given or both be NULL");
+    for (int i = 0; i < s->n_triangles; ++i)
+        if (s->material_ids[i] < 0 || s->material_ids[i] >= s->n_materials)
+            return fail(PT_EINVAL, "material id %d of triangle %d out of range [0,%d)", s->material_ids[i], i,
+                        s->n_materials);
+    return PT_OK;
+}
+
+static int validate_config(const PtConfig *c) {
+    if (!c) return fail(PT_EINVAL, "config is NULL");
+    if (c->width <= 0 || c->height <= 0) return fail(PT_EINVAL, "width/height must be positive");
+    if ((long long)c->width * c->height > 0x7fffffffLL) return fail(PT_EINVAL, "image too large");
+    if (c->rays_per_pixel < 0 || c->max_ray_reflections < 0) return fail(PT_EINVAL, "negative spp / depth");
+    if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
+    if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
+    if (c->rr_depth != 0) return fail(PT_EINVAL, "Russian roulette not available in this build");
+    return PT_OK;
+}
+
+extern "C" const char *pt_last_error(void) { return g_err; }
+extern "C" const char *pt_version(void) { return "path-tracing_b200 0.1 (sm_100a)"; }
+extern "C" int pt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
+    if (!ds) return;
+    cudaFree(ds->tris);
+    cudaFree(ds->nodes);
+    cudaFree(ds->mats);
+    cudaFree(ds->stats);
+    if (ds->ev0) cudaEventDestroy(ds->ev0);
+    if (ds->ev1) cudaEventDestroy(ds->ev1);
+    delete ds;
+}
+
+extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_t flags, PtDeviceScene **out) {
+    if (!out) return fail(PT_EINVAL, "out is NULL");
+    *out = nullptr;
+    int rc;
+    if ((rc = validate_scene(scene)) || (rc = check_device())) return rc;
+    const float eps = cfg ? cfg->eps : 1e-4f;
+    const int want = cfg ? cfg->accel : PT_ACCEL_AUTO;
+    const int n = scene->n_triangles, m = scene->n_materials;
+
+    PtDeviceScene *ds = new PtDeviceScene;
+    struct Guard { PtDeviceScene *p; ~Guard() { if (p) pt_scene_destroy(p); } } guard{ds};
+    CK(cudaGetDevice(&ds->device));
+    ds->n_tri = n;
+    ds->n_mat = m;
+    ds->counters = (flags & 1) != 0;
+    CK(cudaEventCreate(&ds->ev0));
+    CK(cudaEventCreate(&ds->ev1));
+    cudaEvent_t e0, e1, e2;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1)); CK(cudaEventCreate(&e2));
+    struct EvGuard { cudaEvent_t a, b, c; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); } } evg{e0, e1, e2};
+
+    // ---- upload the caller's arrays (AoS as the loader produced them) ----
+    DevBuf<float> d_verts, d_squares, d_mats10;
+    DevBuf<float4> d_planes;
+    DevBuf<int> d_matid;
+    CK(cudaEventRecord(e0));
+    CK(d_verts.alloc(9 * (size_t)n)); CK(d_planes.alloc(n)); CK(d_squares.alloc(n)); CK(d_matid.alloc(n));
+    CK(d_mats10.alloc(10 * (size_t)m));
+    if (n) {
+        CK(cudaMemcpyAsync(d_verts.p, scene->vertices, 9 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMemcpyAsync(d_matid.p, scene->material_ids, (size_t)n * sizeof(int), cudaMemcpyHostToDevice));
+        if (scene->planes) {
+            CK(cudaMemcpyAsync(d_planes.p, scene->planes, 4 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+            CK(cudaMemcpyAsync(d_squares.p, scene->squares, (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+        }
+    }
+    if (m) CK(cudaMemcpyAsync(d_mats10.p, scene->materials, 10 * (size_t)m * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaEventRecord(e1));
+
+    int launches = 0;
+    if (n && !scene->planes) {
+        k_triangle_setup<<<blocks_for(n, 256), 256>>>(d_verts.p, nullptr, nullptr, n, d_planes.p, d_squares.p);
+        ++launches;
+    }
+    CK(cudaMalloc((void **)&ds->mats, (m ? 2 * (size_t)m : 1) * sizeof(float4)));
+    if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, m, ds->mats); ++launches; }
+    CK(cudaMalloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
+    CK(cudaMalloc((void **)&ds->stats, 4 * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long)));
+
+    const bool brute = want == PT_ACCEL_BRUTE || (want == PT_ACCEL_AUTO && n <= kBruteMax) || n == 0;
+    SceneView v{};
+    v.n_tri = n;
+    v.counters = nullptr;
+    if (brute) {
+        if (n) { k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nullptr, n, ds->tris); ++launches; }
+        v.brute = 1;
+        v.n_bvh = 0; v.n_large = 0; v.root = kRefEmpty;
+        ds->accel = PT_ACCEL_BRUTE;
+    } else {
+        // ---- LBVH ----
+        DevBuf<BuildScratch> d_scr;
+        DevBuf<float4> box_lo, box_hi, node_lo, node_hi;
+        DevBuf<uint64_t> keys, keys2;
+        DevBuf<int> vals, vals2, parent, flags;
+        DevBuf<int2> children, range;
+        DevBuf<unsigned char> tmp;
+        CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
+        CK(vals.alloc(n)); CK(vals2.alloc(n));
+        k_init_scratch<<<1, 1>>>(d_scr.p);
+        k_vertex_bounds<<<std::min(blocks_for(n, 256), 1184), 256>>>(d_verts.p, n, d_scr.p);
+        k_tri_boxes_keys<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, n, eps, d_scr.p, box_lo.p,
+                                                      box_hi.p, keys.p, vals.p, 1);
+        launches += 3;
+        size_t tmp_bytes = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys2.p, vals.p, vals2.p, n));
+        CK(tmp.alloc(tmp_bytes));
+        CK(cub::DeviceRadixSort::SortPairs(tmp.p, tmp_bytes, keys.p, keys2.p, vals.p, vals2.p, n));
+        launches += 8;  // CUB's histogram + onesweep passes for 64-bit keys
+        BuildScratch scr;
+        CK(cudaMemcpy(&scr, d_scr.p, sizeof scr, cudaMemcpyDeviceToHost));
+        const int n_large = std::min(scr.n_large, kMaxLarge);
+        const int nb = n - n_large;
+        v.brute = 0; v.n_bvh = nb; v.n_large = n_large;
+        k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, vals2.p, n, ds->tris);
+        ++launches;
+        if (nb == 0) {
+            v.root = kRefEmpty;
+        } else if (nb <= kLeafMax) {
+            v.root = leaf_ref(0, nb);
+        } else {
+            CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb)); CK(children.alloc(nb)); CK(range.alloc(nb));
+            CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
+            CK(cudaMalloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
+            CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
+            k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
+            k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
+            k_emit_nodes<<<blocks_for(nb - 1, 256), 256>>>(nb, children.p, range.p, vals2.p, box_lo.p, box_hi.p, node_lo.p, node_hi.p, ds->nodes);
+            launches += 3;
+            v.root = 0;
+            ds->n_nodes = nb - 1;
+        }
+        ds->accel = PT_ACCEL_LBVH;
+        CK(cudaDeviceSynchronize());  // scratch buffers are freed on scope exit
+    }
+    CK(cudaEventRecord(e2));
+    CK(cudaEventSynchronize(e2));
+    CK(cudaGetLastError());
+    CK(cudaEventElapsedTime(&ds->upload_ms, e0, e1));
+    CK(cudaEventElapsedTime(&ds->build_ms, e1, e2));
+    v.tris = ds->tris;
+    v.nodes = ds->nodes;
+    v.mats = ds->mats;
+    ds->view = v;
+    ds->launches = launches;
+    guard.p = nullptr;
+    *out = ds;
+    return PT_OK;
+}
+
+static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum2, int *d_count,
+                                unsigned long long *stats) {
+    RenderParams rp{};
+    rp.W = cfg->width; rp.H = cfg->height;
+    rp.spp = cfg->rays_per_pixel;
+    rp.s_begin = cfg->sample_begin;
+    rp.s_step = cfg->sample_step > 0 ? cfg->sample_step : 1;
+    rp.max_depth = cfg->max_ray_reflections;
+    rp.eps = cfg->eps; rp.error = cfg->error;
+    rp.seed = cfg->seed;
+    rp.sum3 = d_sum3; rp.sum2_3 = d_sum2; rp.count = d_count;
+    rp.stats = stats;
+    return rp;
+}
+
+extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                                      int32_t *d_count, void *stream) {
+    if (!ds) return fail(PT_EINVAL, "scene handle is NULL");
+    int rc;
+    if ((rc = validate_config(cfg))) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long), st));
+    const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, ds->stats);
+    const int tiles = ((rp.W + kTileW - 1) / kTileW) * ((rp.H + kTileH - 1) / kTileH);
+    CK(cudaEventRecord(ds->ev0, st));
+    if (ds->counters) k_render<true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+    else k_render<false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ds->ev1, st));
+    ds->timed = true;
+    ds->launches = 1;
+    return PT_OK;
+}
+
+extern "C" int pt_resolve_device(const float *d_sum3, const int32_t *d_count, int64_t n_pixels, float *d_rgb,
+                                 void *stream) {
+    if (!d_sum3 || !d_count || !d_rgb || n_pixels < 0) return fail(PT_EINVAL, "bad resolve arguments");
+    if (n_pixels == 0) return PT_OK;
+    k_resolve<<<blocks_for(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(d_sum3, d_count, n_pixels, d_rgb);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
+extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
+    if (!ds || !out) return fail(PT_EINVAL, "NULL argument");
+    memset(out, 0, sizeof *out);
+    unsigned long long st[4] = {0, 0, 0, 0};
+    if (ds->timed) {
+        CK(cudaEventSynchronize(ds->ev1));
+        CK(cudaEventElapsedTime(&ds->kernel_ms, ds->ev0, ds->ev1));
+    }
+    CK(cudaMemcpy(st, ds->stats, sizeof st, cudaMemcpyDeviceToHost));
+    out->segments = st[0]; out->segments_traced = st[1]; out->nodes_visited = st[2]; out->tris_tested = st[3];
+    out->kernel_ms = ds->kernel_ms; out->build_ms = ds->build_ms; out->upload_ms = ds->upload_ms;
+    out->n_nodes = ds->n_nodes; out->n_large = ds->view.n_large; out->accel = ds->accel;
+    out->launches = ds->launches;
+    return PT_OK;
+}
+
+extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const float *rays6, int64_t n,
+                                  int32_t *tri_id, float *t) {
+    if (!ds || !rays6 || !tri_id || !t || n < 0) return fail(PT_EINVAL, "bad intersect arguments");
+    if (n == 0) return PT_OK;
+    const float eps = cfg ? cfg->eps : 1e-4f;
+    DevBuf<float> d_rays, d_t;
+    DevBuf<int> d_ids;
+    CK(d_rays.alloc(6 * (size_t)n)); CK(d_t.alloc(n)); CK(d_ids.alloc(n));
+    CK(cudaMemcpy(d_rays.p, rays6, 6 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemset(ds->stats, 0, 4 * sizeof(unsigned long long)));
+    const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 32);
+    CK(cudaEventRecord(ds->ev0));
+    if (ds->counters) k_intersect<true><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+    else k_intersect<false><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ds->ev1));
+    ds->timed = true;
+    ds->launches = 1;
+    CK(cudaMemcpy(tri_id, d_ids.p, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(t, d_t.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_intersect(const PtScene *scene, const PtConfig *cfg, const float *rays6, int64_t n, int32_t *tri_id,
+                            float *t) {
+    PtDeviceScene *ds = nullptr;
+    int rc = pt_scene_create(scene, cfg, 0, &ds);
+    if (rc) return rc;
+    rc = pt_scene_intersect(ds, cfg, rays6, n, tri_id, t);
+    pt_scene_destroy(ds);
+    return rc;
+}
+
+extern "C" int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count) {
+    int rc;
+    if ((rc = validate_config(cfg))) return rc;
+    if ((rc = validate_scene(scene))) return rc;
+    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "n_gpus > 1: use pt_render (in-process NCCL) or one process per GPU");
+    if ((rc = check_device())) return rc;
+    CK(cudaSetDevice(cfg->device));
+    PtDeviceScene *ds = nullptr;
+    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
+    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    const size_t px = (size_t)cfg->width * cfg->height;
+    DevBuf<float> d_sum, d_sum2;
+    DevBuf<int> d_cnt;
+    CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px));
+    if ((rc = pt_scene_render_device(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, nullptr))) return rc;
+    CK(cudaDeviceSynchronize());
+    if (sum3) CK(cudaMemcpy(sum3, d_sum.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
+    if (sum2_3) CK(cudaMemcpy(sum2_3, d_sum2.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
+    if (count) CK(cudaMemcpy(count, d_cnt.p, px * sizeof(int), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) {
+    int rc;
+    if (!rgb) return fail(PT_EINVAL, "rgb is NULL");
+    if ((rc = validate_config(cfg))) return rc;
+    if ((rc = validate_scene(scene))) return rc;
+    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
+    if ((rc = check_device())) return rc;
+    CK(cudaSetDevice(cfg->device));
+    PtDeviceScene *ds = nullptr;
+    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
+    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    const size_t px = (size_t)cfg->width * cfg->height;
+    DevBuf<float> d_sum, d_rgb;
+    DevBuf<int> d_cnt;
+    CK(d_sum.alloc(3 * px)); CK(d_rgb.alloc(3 * px)); CK(d_cnt.alloc(px));
+    if ((rc = pt_scene_render_device(ds, cfg, d_sum.p, nullptr, d_cnt.p, nullptr))) return rc;
+    if ((rc = pt_resolve_device(d_sum.p, d_cnt.p, (int64_t)px, d_rgb.p, nullptr))) return rc;
+    CK(cudaMemcpy(rgb, d_rgb.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+// ---- building blocks exposed for parity tests ---------------------------------------------------------------
+extern "C" int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float *vn, int64_t n,
+                                 float *planes, float *squares) {
+    if (!vertices || !planes || !squares || n < 0 || n > 0x7fffffff) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    if (n == 0) return PT_OK;
+    DevBuf<float> d_v, d_vn, d_s;
+    DevBuf<uint8_t> d_h;
+    DevBuf<float4> d_p;
+    CK(d_v.alloc(9 * (size_t)n)); CK(d_p.alloc(n)); CK(d_s.alloc(n));
+    CK(cudaMemcpy(d_v.p, vertices, 9 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+    const bool hv = has_vn && vn;
+    if (hv) {
+        CK(d_vn.alloc(3 * (size_t)n)); CK(d_h.alloc(n));
+        CK(cudaMemcpy(d_vn.p, vn, 3 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_h.p, has_vn, (size_t)n, cudaMemcpyHostToDevice));
+    }
+    k_triangle_setup<<<blocks_for(n, 256), 256>>>(d_v.p, hv ? d_h.p : nullptr, hv ? d_vn.p : nullptr, (int)n, d_p.p, d_s.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(planes, d_p.p, 4 * (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(squares, d_s.p, (size_t)n * sizeof(float), cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_philox(const uint32_t *ctr4, const uint32_t *key2, int64_t n, uint32_t *out4) {
+    if (!ctr4 || !key2 || !out4 || n < 0) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    if (n == 0) return PT_OK;
+    DevBuf<uint32_t> c, k, o;
+    CK(c.alloc(4 * (size_t)n)); CK(k.alloc(2 * (size_t)n)); CK(o.alloc(4 * (size_t)n));
+    CK(cudaMemcpy(c.p, ctr4, 16 * (size_t)n, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(k.p, key2, 8 * (size_t)n, cudaMemcpyHostToDevice));
+    k_philox<<<blocks_for(n, 256), 256>>>(c.p, k.p, n, o.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out4, o.p, 16 * (size_t)n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_sincos(const float *x, int64_t n, float *s, float *c) {
+    if (!x || !s || !c || n < 0) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    if (n == 0) return PT_OK;
+    DevBuf<float> dx, dsn, dcs;
+    CK(dx.alloc(n)); CK(dsn.alloc(n)); CK(dcs.alloc(n));
+    CK(cudaMemcpy(dx.p, x, 4 * (size_t)n, cudaMemcpyHostToDevice));
+    k_sincos<<<blocks_for(n, 256), 256>>>(dx.p, n, dsn.p, dcs.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(s, dsn.p, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(c, dcs.p, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6) {
+    if (!cfg || !xys3 || !rays6 || n < 0 || cfg->width <= 0 || cfg->height <= 0) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    if (n == 0) return PT_OK;
+    DevBuf<int> dx;
+    DevBuf<float> dr;
+    CK(dx.alloc(3 * (size_t)n)); CK(dr.alloc(6 * (size_t)n));
+    CK(cudaMemcpy(dx.p, xys3, 12 * (size_t)n, cudaMemcpyHostToDevice));
+    k_primary_rays<<<blocks_for(n, 256), 256>>>(cfg->width, cfg->height, cfg->seed, dx.p, n, dr.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(rays6, dr.p, 24 * (size_t)n, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}

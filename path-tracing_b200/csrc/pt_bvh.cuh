@@ -1,0 +1,302 @@
+// pt_bvh.cuh — SoA repack + GPU LBVH build (Morton codes -> radix sort -> Karras 2012 hierarchy -> bottom-up fit).
+//
+// The reference has no acceleration structure (scene.cpp:114-120 tests every triangle); the LBVH must therefore
+// return exactly the brute-force answer of the reference's intersector.  That intersector (triangles.h:48-73) is
+// NOT a geometric triangle test: it accepts a plane hit point P when  |PA x PB| + |PA x PC| + |PC x PB| <= S + eps
+// with an ABSOLUTE eps, and the plane may come from a rounded `vn` (scene.cpp:102-104).  The accepted set is the
+// convex "lens" { P : g(P) <= S + eps },  g = sum of the three parallelogram areas.  Its in-plane cross-section is
+// the hexagon with vertices  v_k + (v_k - v_j) * eps/(2S)  (k != j)  — a triangle with 0.01-long edges is dilated by
+// a quarter of its size at eps = 1e-4 — and its height over the geometric plane is at most
+// sqrt(2 S eps + eps^2) / (|AB| + |BC| + |CA|).  Leaf boxes bound that set (tri_bounds below), not the triangle.
+#pragma once
+#include <cub/cub.cuh>
+#include <float.h>
+#include "pt_math.cuh"
+#include "pt_scene.cuh"
+
+namespace ptd {
+
+// ---- Triangle constructor arithmetic, triangles.h:27-44 (+ `vn` override, scene.cpp:102-104) -------------------
+__device__ __forceinline__ void triangle_setup(V3 v0, V3 v1, V3 v2, bool has_vn, V3 vn, float4 *plane, float *square) {
+    const V3 AB = v1 - v0, AC = v2 - v0;
+    const V3 c = cross3(AB, AC);
+    V3 n = normalize3(c);     // SetNormal(cross(AB, AC))
+    *square = length3(c);     // ParallelogramSquare(AB, AC)
+    if (has_vn) n = normalize3(vn);
+    *plane = make_float4(n.x, n.y, n.z, -dot3(n, v0));
+}
+
+__global__ void k_triangle_setup(const float *__restrict__ verts, const uint8_t *__restrict__ has_vn,
+                                 const float *__restrict__ vn, int n, float4 *__restrict__ planes,
+                                 float *__restrict__ squares) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *v = verts + 9 * (size_t)i;
+    const bool hv = has_vn && vn && has_vn[i];
+    const V3 nn = hv ? mk(vn[3 * (size_t)i], vn[3 * (size_t)i + 1], vn[3 * (size_t)i + 2]) : mk(0, 0, 0);
+    float4 p;
+    float s;
+    triangle_setup(mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8]), hv, nn, &p, &s);
+    planes[i] = p;
+    squares[i] = s;
+}
+
+// ---- ordered-int encoding so that float min/max can use integer atomics -------------------------------------
+__device__ __forceinline__ int f2ord(float f) {
+    const int i = __float_as_int(f);
+    return i >= 0 ? i : i ^ 0x7fffffff;
+}
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
+
+struct BuildScratch {  // 8 ints: scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, pad
+    int lo[3], hi[3], n_large, pad;
+};
+
+__global__ void k_init_scratch(BuildScratch *s) {
+    s->lo[0] = s->lo[1] = s->lo[2] = f2ord(FLT_MAX);
+    s->hi[0] = s->hi[1] = s->hi[2] = f2ord(-FLT_MAX);
+    s->n_large = 0;
+    s->pad = 0;
+}
+
+__global__ void k_vertex_bounds(const float *__restrict__ verts, int n, BuildScratch *s) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float *v = verts + 9 * (size_t)i;
+#pragma unroll
+        for (int k = 0; k < 9; ++k) {
+            const float f = v[k];
+            if (f == f && fabsf(f) <= FLT_MAX) {
+                lo[k % 3] = fminf(lo[k % 3], f);
+                hi[k % 3] = fmaxf(hi[k % 3], f);
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        for (int o = 16; o; o >>= 1) {
+            lo[a] = fminf(lo[a], __shfl_xor_sync(0xffffffffu, lo[a], o));
+            hi[a] = fmaxf(hi[a], __shfl_xor_sync(0xffffffffu, hi[a], o));
+        }
+        if ((threadIdx.x & 31) == 0) {
+            atomicMin(&s->lo[a], f2ord(lo[a]));
+            atomicMax(&s->hi[a], f2ord(hi[a]));
+        }
+    }
+}
+
+// Conservative box of everything the reference's Intersect can accept for this triangle (see header comment).
+__device__ __forceinline__ void tri_bounds(V3 v0, V3 v1, V3 v2, float4 plane, float S, float eps, float pad, V3 *lo,
+                                           V3 *hi) {
+    const V3 v[3] = {v0, v1, v2};
+    // effective eps: the reference's sums carry fp32 rounding proportional to S
+    const float e = eps * 1.01f + 4e-6f * (S + eps);
+    V3 l = mk(fminf(v0.x, fminf(v1.x, v2.x)), fminf(v0.y, fminf(v1.y, v2.y)), fminf(v0.z, fminf(v1.z, v2.z)));
+    V3 h = mk(fmaxf(v0.x, fmaxf(v1.x, v2.x)), fmaxf(v0.y, fmaxf(v1.y, v2.y)), fmaxf(v0.z, fmaxf(v1.z, v2.z)));
+    if (!(S > 0.0f) || !(S <= FLT_MAX) || !(plane.x == plane.x)) {  // degenerate: NaN plane, never accepted here
+        *lo = l; *hi = h;
+        return;
+    }
+    const float lam = e / (2.0f * S);
+    const V3 ng = normalize3(cross3(v1 - v0, v2 - v0));
+    const V3 ns = mk(plane.x, plane.y, plane.z);
+    const float nsng = dot3(ns, ng);
+    float zmax = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 3; ++k)
+#pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            if (j == k) continue;
+            const V3 q = v[k] + (v[k] - v[j]) * lam;
+            l = mk(fminf(l.x, q.x), fminf(l.y, q.y), fminf(l.z, q.z));
+            h = mk(fmaxf(h.x, q.x), fmaxf(h.y, q.y), fmaxf(h.z, q.z));
+            // height over the geometric plane of the stored-plane point above q
+            const float z = fabsf((dot3(ns, q) + plane.w) / nsng);
+            zmax = fmaxf(zmax, z == z ? z : FLT_MAX);
+        }
+    const float per = length3(v1 - v0) + length3(v2 - v1) + length3(v0 - v2);
+    const float zlens = sqrtf(2.0f * S * e + e * e) / per;
+    const float zp = fminf(zmax * 1.001f + 1e-7f, zlens * 1.001f);
+    const V3 ex = mk(fabsf(ng.x) * zp + pad, fabsf(ng.y) * zp + pad, fabsf(ng.z) * zp + pad);
+    *lo = l - ex;
+    *hi = h + ex;
+}
+
+__device__ __forceinline__ uint64_t spread21(uint32_t v) {  // 21 bits -> every third bit of 63
+    uint64_t x = v & 0x1fffffu;
+    x = (x | x << 32) & 0x1f00000000ffffull;
+    x = (x | x << 16) & 0x1f0000ff0000ffull;
+    x = (x | x << 8) & 0x100f00f00f00f00full;
+    x = (x | x << 4) & 0x10c30c30c30c30c3ull;
+    x = (x | x << 2) & 0x1249249249249249ull;
+    return x;
+}
+
+// per triangle: dilated box, 63-bit Morton key of its centre; bit 63 marks a "large" triangle (sorted last)
+__global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *__restrict__ planes,
+                                 const float *__restrict__ squares, int n, float eps, BuildScratch *s,
+                                 float4 *__restrict__ box_lo, float4 *__restrict__ box_hi,
+                                 uint64_t *__restrict__ keys, int *__restrict__ vals, int want_large) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const V3 slo = mk(ord2f(s->lo[0]), ord2f(s->lo[1]), ord2f(s->lo[2]));
+    const V3 shi = mk(ord2f(s->hi[0]), ord2f(s->hi[1]), ord2f(s->hi[2]));
+    const float amax = fmaxf(20.0f, fmaxf(fmaxf(fmaxf(fabsf(slo.x), fabsf(shi.x)), fmaxf(fabsf(slo.y), fabsf(shi.y))),
+                                          fmaxf(fabsf(slo.z), fabsf(shi.z))));
+    const float pad = amax * (32.0f * 1.1920929e-7f);  // 32 ulp of the largest coordinate in play
+    const float *v = verts + 9 * (size_t)i;
+    V3 lo, hi;
+    tri_bounds(mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8]), planes[i], squares[i], eps, pad, &lo,
+               &hi);
+    box_lo[i] = make_float4(lo.x, lo.y, lo.z, 0.0f);
+    box_hi[i] = make_float4(hi.x, hi.y, hi.z, 0.0f);
+    const V3 ext = shi - slo;
+    const float emax = fmaxf(ext.x, fmaxf(ext.y, ext.z));
+    const V3 c = (lo + hi) * 0.5f;
+    const float sc = emax > 0.0f ? 2097151.0f / emax : 0.0f;
+    const uint32_t qx = (uint32_t)fminf(fmaxf((c.x - slo.x) * sc, 0.0f), 2097151.0f);
+    const uint32_t qy = (uint32_t)fminf(fmaxf((c.y - slo.y) * sc, 0.0f), 2097151.0f);
+    const uint32_t qz = (uint32_t)fminf(fmaxf((c.z - slo.z) * sc, 0.0f), 2097151.0f);
+    uint64_t key = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
+    const V3 be = hi - lo;
+    const bool large = want_large && fmaxf(be.x, fmaxf(be.y, be.z)) > 0.25f * emax;
+    if (large) {
+        key |= 1ull << 63;
+        atomicAdd(&s->n_large, 1);
+    }
+    keys[i] = key;
+    vals[i] = i;
+}
+
+// ---- Karras 2012: one thread per internal node over the sorted keys ------------------------------------------
+__device__ __forceinline__ int lbvh_delta(const uint64_t *__restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint64_t a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+__global__ void k_karras(const uint64_t *__restrict__ keys, int n, int2 *__restrict__ children,
+                         int *__restrict__ parent, int2 *__restrict__ range) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = lbvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (lbvh_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    const int j = i + l * d;
+    const int dnode = lbvh_delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) >> 1;; t = (t + 1) >> 1) {
+        if (lbvh_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t == 1) break;
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int first = min(i, j), last = max(i, j);
+    // children: internal node index k, or leaf encoded as ~k (k = sorted position)
+    const int c0 = (first == gamma) ? ~gamma : gamma;
+    const int c1 = (last == gamma + 1) ? ~(gamma + 1) : gamma + 1;
+    children[i] = make_int2(c0, c1);
+    range[i] = make_int2(first, last);
+    if (c0 >= 0) parent[c0] = i; else parent[n - 1 + gamma] = i;
+    if (c1 >= 0) parent[c1] = i; else parent[n - 1 + gamma + 1] = i;
+    if (i == 0) parent[0] = -1;
+}
+
+// bottom-up fit: the second thread to reach a node merges its children's boxes
+__global__ void k_fit(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
+                      const float4 *__restrict__ box_hi, int n, const int2 *__restrict__ children,
+                      const int *__restrict__ parent, int *__restrict__ flags, float4 *__restrict__ node_lo,
+                      float4 *__restrict__ node_hi) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    // leaf k's box is box_*[vals[k]]
+    int p = parent[n - 1 + k];
+    while (p >= 0) {
+        if (atomicAdd(&flags[p], 1) == 0) return;  // first arrival: the sibling is not done yet
+        __threadfence();
+        const int2 c = children[p];
+        const float4 l0 = c.x >= 0 ? __ldcg(&node_lo[c.x]) : box_lo[vals[~c.x]];
+        const float4 h0 = c.x >= 0 ? __ldcg(&node_hi[c.x]) : box_hi[vals[~c.x]];
+        const float4 l1 = c.y >= 0 ? __ldcg(&node_lo[c.y]) : box_lo[vals[~c.y]];
+        const float4 h1 = c.y >= 0 ? __ldcg(&node_hi[c.y]) : box_hi[vals[~c.y]];
+        node_lo[p] = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
+        node_hi[p] = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        __threadfence();
+        p = parent[p];
+    }
+}
+
+// final 64-byte nodes; a subtree of at most kLeafMax triangles becomes one leaf (its records are contiguous)
+__global__ void k_emit_nodes(int n, const int2 *__restrict__ children, const int2 *__restrict__ range,
+                             const int *__restrict__ vals, const float4 *__restrict__ box_lo,
+                             const float4 *__restrict__ box_hi, const float4 *__restrict__ node_lo,
+                             const float4 *__restrict__ node_hi, float4 *__restrict__ nodes) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    const int2 r = range[i];
+    if (r.y - r.x + 1 <= kLeafMax) return;  // swallowed by a leaf above
+    const int2 c = children[i];
+    float4 l[2], h[2];
+    int ref[2];
+#pragma unroll
+    for (int k = 0; k < 2; ++k) {
+        const int ck = k ? c.y : c.x;
+        if (ck >= 0) {
+            l[k] = node_lo[ck];
+            h[k] = node_hi[ck];
+            const int2 rr = range[ck];
+            const int cnt = rr.y - rr.x + 1;
+            ref[k] = cnt <= kLeafMax ? leaf_ref(rr.x, cnt) : ck;
+        } else {
+            l[k] = box_lo[vals[~ck]];
+            h[k] = box_hi[vals[~ck]];
+            ref[k] = leaf_ref(~ck, 1);
+        }
+    }
+    float4 *o = nodes + 4 * (size_t)i;
+    o[0] = make_float4(l[0].x, h[0].x, l[0].y, h[0].y);
+    o[1] = make_float4(l[1].x, h[1].x, l[1].y, h[1].y);
+    o[2] = make_float4(l[0].z, h[0].z, l[1].z, h[1].z);
+    o[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
+}
+
+// triangle records in sorted order (vals == nullptr: caller order)
+__global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__restrict__ planes,
+                            const float *__restrict__ squares, const int *__restrict__ mat_ids,
+                            const int *__restrict__ vals, int n, float4 *__restrict__ tris) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const int i = vals ? vals[k] : k;
+    const float *v = verts + 9 * (size_t)i;
+    float4 *o = tris + 4 * (size_t)k;
+    o[0] = planes[i];
+    o[1] = make_float4(v[0], v[1], v[2], squares[i]);
+    o[2] = make_float4(v[3], v[4], v[5], __int_as_float(i));
+    o[3] = make_float4(v[6], v[7], v[8], __int_as_float(mat_ids[i]));
+}
+
+// Factory (material.h:58-106) as data: which closures exist and the mirror's selection chance
+__global__ void k_pack_materials(const float *__restrict__ mats10, int m, float4 *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const float *p = mats10 + 10 * (size_t)i;
+    const bool emissive = p[0] != 0.0f || p[1] != 0.0f || p[2] != 0.0f;
+    const float Ns = p[9];
+    const bool has_mirror = (Ns != 0.0f) && (p[6] != 0.0f || p[7] != 0.0f || p[8] != 0.0f);
+    const float mirror_chance = Ns / 1000;
+    const bool has_diffuse = (1 - Ns / 1000) > 0;
+    int kind;
+    if (emissive) kind = MAT_EMISSIVE;
+    else if (has_mirror && has_diffuse) kind = MAT_BOTH;
+    else if (has_mirror) kind = MAT_MIRROR;
+    else if (has_diffuse) kind = MAT_DIFFUSE;
+    else kind = MAT_NONE;
+    out[2 * i + 0] = make_float4(p[3], p[4], p[5], __int_as_float(kind));
+    out[2 * i + 1] = make_float4(p[6], p[7], p[8], mirror_chance);
+}
+
+}  // namespace ptd

@@ -1,0 +1,279 @@
+// pt_kernels.cuh — the render loop (main.cpp:110-140) as one persistent-per-tile CUDA kernel, plus the small
+// kernels behind pt_intersect / pt_resolve / the parity probes.
+//
+// Work decomposition.  A warp owns 8 horizontally adjacent pixels; 4 consecutive lanes ("quad") own one pixel and
+// trace up to 4 of its next samples in parallel.  The reference processes a pixel's samples strictly in order
+// because (i) color_map += ... is an ordered fp32 sum and (ii) the adaptive rule (main.cpp:118-125) decides
+// whether sample s is traced from the accumulators after samples < s.  Paths are independent given the
+// counter-based RNG (keyed by pixel, sample, bounce), so the quad traces optimistically — using the skip decisions
+// implied by the accumulators at the start of the step — and then COMMITS in sample order, re-evaluating the rule
+// with the live accumulators: a sample traced but now skipped is discarded; a sample not traced but now needed
+// stops the commit and becomes the first sample of the quad's next step.  The committed result is bit-identical
+// to the sequential loop; accumulators live in registers (replicated across the quad), so there are no atomics
+// on the frame buffers and each pixel is written once.
+#pragma once
+#include "pt_trace.cuh"
+
+namespace ptd {
+
+struct RenderParams {
+    int W, H;
+    int spp;        // Config::rays_per_pixel: samples s_begin, s_begin + s_step, ... < spp
+    int s_begin, s_step;
+    int max_depth;  // Config::max_ray_reflections
+    float eps, error;
+    uint32_t seed;
+    float *sum3, *sum2_3;
+    int *count;
+    unsigned long long *stats;  // [0] committed segments, [1] traced segments, [2] nodes, [3] tris
+};
+
+constexpr float kPi = 3.141593f;  // material.h:12
+
+// the adaptive rule of main.cpp:118-125: true = skip sample s
+__device__ __forceinline__ bool adaptive_skip(int s, int n, V3 sum, V3 sum2, float error) {
+    if (!(s > 10 && n > 0)) return false;
+    if ((s % 4) == 0) return false;
+    const float fn = (float)n;
+    const float mx = sum.x / fn, my = sum.y / fn, mz = sum.z / fn;
+    const float Dx = sum2.x / fn - mx * mx, Dy = sum2.y / fn - my * my, Dz = sum2.z / fn - mz * mz;
+    return Dx < error && Dy < error && Dz < error;
+}
+
+// One path: primary ray, then `while (ray.IsValid()) scene.TraceRay(ray)` (main.cpp:126-139).
+// Returns true when the path reached an emitter from its front side (material.h:68-79); c = throughput * Kd.
+template <bool COUNT>
+__device__ __forceinline__ bool trace_path(const SceneView &sc, const float4 *s_large, const RenderParams &rp, int x,
+                                           int y, uint32_t sample, V3 *c, int *n_seg, unsigned long long &n_nodes,
+                                           unsigned long long &n_tris) {
+    const uint32_t pixel = (uint32_t)(y * rp.W + x);
+    V3 o = mk(0.0f, 0.0f, -20.0f);
+    V3 d = primary_dir(x, y, rp.W, rp.H, pixel, sample, rp.seed);
+    V3 T = mk(1.0f, 1.0f, 1.0f);
+    int depth = 0, segs = 0;
+    bool contributed = false;
+    // Ray::IsValid, ray.h:52-54
+    while (depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f)) {
+        const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
+        ++segs;
+        if (h.rec < 0) break;  // miss: Ray::MakeInvalid (scene.cpp:155); skybox handled by the caller variant
+        const float4 *r = (s_large && (sc.brute || h.rec >= sc.n_bvh))
+                              ? s_large + 4 * (sc.brute ? h.rec : h.rec - sc.n_bvh)
+                              : sc.tris + 4 * (size_t)h.rec;
+        const float4 pl = r[0];
+        const int mat = __float_as_int(r[3].w);
+        const V3 N = mk(pl.x, pl.y, pl.z);
+        const float4 m0 = __ldg(sc.mats + 2 * mat), m1 = __ldg(sc.mats + 2 * mat + 1);
+        const int kind = __float_as_int(m0.w);
+        const V3 Kd = mk(m0.x, m0.y, m0.z);
+        if (kind == MAT_EMISSIVE) {  // material.h:68-79
+            if (!(dot4w0(d, N) > 0.0f)) {
+                *c = T * Kd;
+                contributed = true;
+            }
+            break;
+        }
+        if (kind == MAT_NONE) break;  // Material::Process with no closures, material.h:37-38
+        // drop_point = begin + direction * distance (scene.cpp:122), vec4 arithmetic
+        const V3 P = mk(o.x + d.x * h.t, o.y + d.y * h.t, o.z + d.z * h.t);
+        int lobe = kind == MAT_MIRROR ? 0 : 1;
+        uint4 w = make_uint4(0, 0, 0, 0);
+        if (kind != MAT_MIRROR) w = philox4x32_10(pixel, sample, 1u + (uint32_t)depth, 0u, rp.seed, 0u);
+        uint32_t w1 = w.x, w2 = w.y;
+        if (kind == MAT_BOTH) {  // Material::Process, material.h:43-49: chances [mirror, diffuse]
+            const float smp = u01(w.x);
+            lobe = (smp > 0.0f && (smp - m1.w) > 0.0f) ? 1 : 0;
+            w1 = w.y;
+            w2 = w.z;
+        }
+        const V3 begin = mk(P.x + N.x * rp.eps, P.y + N.y * rp.eps, P.z + N.z * rp.eps);
+        V3 nd, tint;
+        if (lobe == 0) {  // mirror closure, material.h:83-85; glm::reflect = I - N * dot(N, I) * 2
+            const float dn = dot4w0(N, d);
+            nd = mk(d.x - N.x * dn * 2.0f, d.y - N.y * dn * 2.0f, d.z - N.z * dn * 2.0f);
+            tint = mk(m1.x, m1.y, m1.z);
+        } else {  // diffuse closure, material.h:90-100: cosine lobe about world +Z, flipped to N's side
+            const float xi1 = u01(w1), xi2 = u01(w2);
+            const float ang = 2 * kPi * xi2;
+            float sn, cs;
+            ref_sincosf(ang, &sn, &cs);
+            const float sq = sqrtf(xi1);
+            V3 rnd = normalize4w0(mk(sq * cs, sq * sn, sqrtf(1 - xi1)));
+            if (dot4w0(N, rnd) < 0.0f) rnd = mk(rnd.x * -1.0f, rnd.y * -1.0f, rnd.z * -1.0f);
+            const float dt = fmaxf(0.0f, dot4w0(N, rnd));
+            nd = rnd;
+            tint = mk(Kd.x * dt, Kd.y * dt, Kd.z * dt);
+        }
+        // Ray::Reflect, ray.h:45-50
+        o = begin;
+        d = normalize4w0(nd);
+        T = T * tint;
+        ++depth;
+    }
+    *n_seg = segs;
+    return contributed;
+}
+
+constexpr int kTileW = 8, kTileH = 8;       // pixels per block
+constexpr int kQuad = 4;                    // samples of one pixel traced in parallel
+constexpr int kBlockThreads = kTileW * kTileH * kQuad;  // 256
+
+template <bool COUNT>
+__global__ void __launch_bounds__(kBlockThreads)
+k_render(SceneView sc, RenderParams rp) {
+    __shared__ float4 s_large[4 * (kMaxLarge > kBruteMax ? kMaxLarge : kBruteMax)];
+    const int n_stage = sc.brute ? sc.n_tri : sc.n_large;
+    const bool staged = !sc.brute || sc.n_tri <= kBruteMax;
+    if (staged) {
+        const float4 *src = sc.tris + 4 * (size_t)(sc.brute ? 0 : sc.n_bvh);
+        for (int k = threadIdx.x; k < 4 * n_stage; k += blockDim.x) s_large[k] = src[k];
+    }
+    __syncthreads();
+    const float4 *sl = staged ? s_large : nullptr;
+
+    const int tiles_x = (rp.W + kTileW - 1) / kTileW;
+    const int tile = blockIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int q = lane & 3;                 // position in the quad
+    const int x = (tile % tiles_x) * kTileW + (lane >> 2);
+    const int y = (tile / tiles_x) * kTileH + warp;
+    const bool in_image = x < rp.W && y < rp.H;
+    const unsigned qbase = lane & ~3u;
+
+    V3 sum = mk(0, 0, 0), sum2 = mk(0, 0, 0);
+    int cnt = 0;
+    int s_next = rp.s_begin;  // next uncommitted sample of this pixel (identical across the quad)
+    unsigned long long seg_commit = 0, seg_traced = 0, n_nodes = 0, n_tris = 0;
+
+    while (__any_sync(0xffffffffu, in_image && s_next < rp.spp)) {
+        const int s = s_next + q * rp.s_step;
+        const bool live = in_image && s_next < rp.spp && s < rp.spp;
+        const bool traced = live && !adaptive_skip(s, cnt, sum, sum2, rp.error);
+        V3 c = mk(0, 0, 0);
+        int nseg = 0;
+        bool contrib = false;
+        if (traced) {
+            contrib = trace_path<COUNT>(sc, sl, rp, x, y, (uint32_t)s, &c, &nseg, n_nodes, n_tris);
+            seg_traced += nseg;
+        }
+        // ordered commit over the quad
+        bool stop = false;
+#pragma unroll
+        for (int j = 0; j < kQuad; ++j) {
+            const int src = qbase + j;
+            const int live_j = __shfl_sync(0xffffffffu, (int)live, src);
+            const int traced_j = __shfl_sync(0xffffffffu, (int)traced, src);
+            const int contrib_j = __shfl_sync(0xffffffffu, (int)contrib, src);
+            const int nseg_j = __shfl_sync(0xffffffffu, nseg, src);
+            const float cx = __shfl_sync(0xffffffffu, c.x, src);
+            const float cy = __shfl_sync(0xffffffffu, c.y, src);
+            const float cz = __shfl_sync(0xffffffffu, c.z, src);
+            if (stop || !live_j) continue;
+            const int sj = s_next;  // s_next always points at the sample being committed
+            const bool skip_now = adaptive_skip(sj, cnt, sum, sum2, rp.error);
+            if (!skip_now && !traced_j) {
+                stop = true;  // needed after all: first sample of the next step
+                continue;
+            }
+            if (!skip_now) {
+                if (contrib_j) {  // material.h:74-77
+                    sum = mk(sum.x + cx, sum.y + cy, sum.z + cz);
+                    sum2 = mk(sum2.x + cx * cx, sum2.y + cy * cy, sum2.z + cz * cz);
+                    ++cnt;
+                }
+                if (q == j) seg_commit += nseg_j;
+            }
+            s_next += rp.s_step;
+        }
+    }
+
+    if (in_image && q == 0) {
+        const size_t p = (size_t)y * rp.W + x;
+        if (rp.sum3) { rp.sum3[3 * p] = sum.x; rp.sum3[3 * p + 1] = sum.y; rp.sum3[3 * p + 2] = sum.z; }
+        if (rp.sum2_3) { rp.sum2_3[3 * p] = sum2.x; rp.sum2_3[3 * p + 1] = sum2.y; rp.sum2_3[3 * p + 2] = sum2.z; }
+        if (rp.count) rp.count[p] = cnt;
+    }
+    // statistics: one atomic per warp per counter
+    for (int o = 16; o; o >>= 1) {
+        seg_commit += __shfl_xor_sync(0xffffffffu, seg_commit, o);
+        seg_traced += __shfl_xor_sync(0xffffffffu, seg_traced, o);
+        if (COUNT) {
+            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o);
+            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o);
+        }
+    }
+    if (lane == 0 && rp.stats) {
+        atomicAdd(&rp.stats[0], seg_commit);
+        atomicAdd(&rp.stats[1], seg_traced);
+        if (COUNT) {
+            atomicAdd(&rp.stats[2], n_nodes);
+            atomicAdd(&rp.stats[3], n_tris);
+        }
+    }
+}
+
+// ---- pt_intersect: nearest hit on an explicit ray set ------------------------------------------------------
+template <bool COUNT>
+__global__ void __launch_bounds__(256)
+k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float eps, int *__restrict__ ids,
+            float *__restrict__ ts, unsigned long long *stats) {
+    __shared__ float4 s_large[4 * (kMaxLarge > kBruteMax ? kMaxLarge : kBruteMax)];
+    const int n_stage = sc.brute ? sc.n_tri : sc.n_large;
+    const bool staged = !sc.brute || sc.n_tri <= kBruteMax;
+    if (staged) {
+        const float4 *src = sc.tris + 4 * (size_t)(sc.brute ? 0 : sc.n_bvh);
+        for (int k = threadIdx.x; k < 4 * n_stage; k += blockDim.x) s_large[k] = src[k];
+    }
+    __syncthreads();
+    const float4 *sl = staged ? s_large : nullptr;
+    unsigned long long n_nodes = 0, n_tris = 0;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float *r = rays6 + 6 * i;
+        const V3 o = mk(r[0], r[1], r[2]);
+        const V3 d = normalize4w0(mk(r[3], r[4], r[5]));  // Ray's constructor, ray.h:21-25
+        const Hit h = nearest_hit<COUNT>(sc, sl, o, d, eps, n_nodes, n_tris);
+        ids[i] = h.idx;
+        ts[i] = h.t;
+    }
+    if (COUNT && stats) {
+        atomicAdd(&stats[2], n_nodes);
+        atomicAdd(&stats[3], n_tris);
+    }
+}
+
+// rgb = color_map / samples_count, 0 where the count is 0 (main.cpp:179-182 without the gamma)
+__global__ void k_resolve(const float *__restrict__ sum3, const int *__restrict__ count, long long n_pixels,
+                          float *__restrict__ rgb) {
+    const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (p >= n_pixels) return;
+    const int c = count[p];
+    const float fn = (float)c;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) rgb[3 * p + k] = c ? sum3[3 * p + k] / fn : 0.0f;
+}
+
+// ---- parity probes ----------------------------------------------------------------------------------------
+__global__ void k_philox(const uint32_t *__restrict__ ctr4, const uint32_t *__restrict__ key2, long long n,
+                         uint32_t *__restrict__ out4) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint4 w = philox4x32_10(ctr4[4 * i], ctr4[4 * i + 1], ctr4[4 * i + 2], ctr4[4 * i + 3], key2[2 * i], key2[2 * i + 1]);
+    out4[4 * i] = w.x; out4[4 * i + 1] = w.y; out4[4 * i + 2] = w.z; out4[4 * i + 3] = w.w;
+}
+__global__ void k_sincos(const float *__restrict__ x, long long n, float *__restrict__ s, float *__restrict__ c) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    ref_sincosf(x[i], &s[i], &c[i]);
+}
+__global__ void k_primary_rays(int W, int H, uint32_t seed, const int *__restrict__ xys3, long long n,
+                               float *__restrict__ rays6) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int x = xys3[3 * i], y = xys3[3 * i + 1], s = xys3[3 * i + 2];
+    const V3 d = primary_dir(x, y, W, H, (uint32_t)(y * W + x), (uint32_t)s, seed);
+    float *o = rays6 + 6 * i;
+    o[0] = 0.0f; o[1] = 0.0f; o[2] = -20.0f;
+    o[3] = d.x; o[4] = d.y; o[5] = d.z;
+}
+
+}  // namespace ptd

@@ -1,0 +1,47 @@
+// pt_scene.cuh — device-resident scene layout shared by the LBVH builder and the render kernels.
+//
+// HBM layout (all 16-byte aligned, read with LDG.128):
+//   tris   4 x float4 per triangle, in BVH (Morton) order, the "large" triangles last:
+//            [0] Triangle::plane_            (nx, ny, nz, w)            triangles.h:21,40-44
+//            [1] vertices_[0], square        (x, y, z, S)               triangles.h:23-24
+//            [2] vertices_[1], caller index  (x, y, z, bits(int))
+//            [3] vertices_[2], material id   (x, y, z, bits(int))
+//   nodes  4 x float4 per BVH2 node (both child boxes live in the parent, one 64-byte fetch per visit):
+//            [0] child0 lo.x hi.x lo.y hi.y   [1] child1 lo.x hi.x lo.y hi.y
+//            [2] child0 lo.z hi.z, child1 lo.z hi.z      [3] bits: child0 ref, child1 ref, 0, 0
+//          child ref >= 0: node index; < 0: leaf, bits 0..27 = first triangle record, bits 28..30 = count-1
+//   mats   2 x float4 per material: (Kd.xyz, bits(lobe kind)), (Ks.xyz, mirror chance Ns/1000)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace ptd {
+
+constexpr int kLeafMax = 4;          // triangles per LBVH leaf
+constexpr int kMaxLarge = 48;        // triangles kept out of the LBVH and tested from shared memory first
+constexpr int kBruteMax = 64;        // scenes up to this size skip the LBVH altogether (PT_ACCEL_AUTO)
+constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
+constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
+
+// lobe kinds built by Factory (material.h:58-106)
+enum : int { MAT_EMISSIVE = 0, MAT_NONE = 1, MAT_MIRROR = 2, MAT_DIFFUSE = 3, MAT_BOTH = 4 };
+
+__host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
+    return (int)(0x80000000u | ((uint32_t)(count - 1) << 28) | (uint32_t)first);
+}
+__host__ __device__ __forceinline__ int leaf_first(int ref) { return ref & 0x0fffffff; }
+__host__ __device__ __forceinline__ int leaf_count(int ref) { return ((ref >> 28) & 7) + 1; }
+
+struct SceneView {
+    const float4 *tris;
+    const float4 *nodes;
+    const float4 *mats;
+    int n_tri;    // all triangle records
+    int n_bvh;    // records [0, n_bvh) are in the LBVH
+    int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
+    int root;     // child ref of the LBVH root (kRefEmpty if n_bvh == 0)
+    int brute;    // 1: test records [0, n_tri) in order, no LBVH
+    unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
+};
+
+}  // namespace ptd

@@ -1,0 +1,152 @@
+// scene.cpp — OBJ/MTL loading with the reference's semantics (scene.cpp:26-109) and the GPU hand-off.
+//
+// Loader rules kept from the reference: whitespace-separated token stream; `mtllib` is resolved against
+// Config::model_path and read as newmtl blocks of Kd / Ke / Ks / Ns (everything else ignored), one material per
+// newmtl in file order; `v` x y z; `vt` skipped; `vn` x y z; `f a/b/c a/b/c a/b/c` triangles only, 1-based; when
+// the first corner carries a normal index the plane is re-derived from that `vn`; `usemtl <int>` selects a
+// material by its ordinal.  An unopenable OBJ is fatal (exit(1)), as scene.cpp:32-35.
+#include "scene.h"
+
+#include <cstdlib>
+#include <fstream>
+#include <iostream>
+
+using ptm::vec3;
+using ptm::vec4;
+
+Scene::Scene(std::vector<std::vector<vec3>> &color_map, std::vector<std::vector<vec3>> &color2_map,
+             std::vector<std::vector<int>> &samples_count)
+    : color_map_(color_map), color2_map_(color2_map), samples_count_(samples_count) {
+    if (!Config::get().skybox.empty()) skybox_.load(Config::get().skybox);
+}
+
+int Scene::AddMaterial(const MaterialCharacteristics &ch) {
+    materials_.push_back(Factory(ch));
+    return static_cast<int>(materials_.size()) - 1;
+}
+
+void Scene::AddTriangle(Triangle triangle) { triangles_.push_back(triangle); }
+
+namespace {
+// "a/b/c" -> three 0-based indices, -1 where a field is missing or empty (atoi("") - 1, scene.cpp:91-96)
+void corner(const std::string &tok, int out[3]) {
+    size_t pos = 0;
+    for (int k = 0; k < 3; ++k) {
+        if (pos == std::string::npos) { out[k] = -1; continue; }
+        const size_t slash = tok.find('/', pos);
+        const std::string field = tok.substr(pos, slash == std::string::npos ? std::string::npos : slash - pos);
+        out[k] = std::atoi(field.c_str()) - 1;
+        pos = slash == std::string::npos ? std::string::npos : slash + 1;
+    }
+}
+
+void read_mtl(const std::string &path, Scene &scene) {
+    std::ifstream in(path);
+    std::string tok = "1";
+    // the reference emits one material per pass of its outer loop, including a default-valued one when the file
+    // is missing or ends right after the last block's values (scene.cpp:45-70)
+    while (!in.eof()) {
+        MaterialCharacteristics ch;
+        while (!in.eof() && tok != "newmtl") in >> tok;
+        in >> tok;  // the material's name (unused: usemtl is an ordinal)
+        while (!in.eof() && tok != "newmtl") {
+            if (tok == "Kd") in >> ch.Kd.x >> ch.Kd.y >> ch.Kd.z;
+            else if (tok == "Ke") in >> ch.Ke.x >> ch.Ke.y >> ch.Ke.z;
+            else if (tok == "Ks") in >> ch.Ks.x >> ch.Ks.y >> ch.Ks.z;
+            else if (tok == "Ns") in >> ch.Ns;
+            in >> tok;
+        }
+        scene.AddMaterial(ch);
+    }
+}
+}  // namespace
+
+void Scene::LoadModel(std::string path) {
+    std::ifstream file(path);
+    if (!file.is_open()) {
+        std::cerr << "Impossible to open the file !" << std::endl;
+        std::exit(1);
+    }
+    std::vector<vec4> positions;
+    std::vector<vec3> normals;
+    int current_material = 0;
+    std::string tok;
+    while (file >> tok) {
+        if (tok == "mtllib") {
+            std::string name;
+            file >> name;
+            read_mtl(Config::get().model_path + name, *this);
+        } else if (tok == "v") {
+            vec4 p(1);
+            file >> p.x >> p.y >> p.z;
+            positions.push_back(p);
+        } else if (tok == "vt") {
+            float u, v;
+            file >> u >> v;
+        } else if (tok == "vn") {
+            vec3 n;
+            file >> n.x >> n.y >> n.z;
+            normals.push_back(n);
+        } else if (tok == "f") {
+            int idx[3][3];
+            for (int i = 0; i < 3; ++i) {
+                std::string c;
+                file >> c;
+                corner(c, idx[i]);
+            }
+            Triangle t({positions.at(idx[0][0]), positions.at(idx[1][0]), positions.at(idx[2][0])}, current_material);
+            if (idx[0][2] >= 0) t.SetNormal(normals.at(idx[0][2]));
+            triangles_.push_back(t);
+        } else if (tok == "usemtl") {
+            file >> current_material;
+        }
+    }
+}
+
+PtScene Scene::abi() const {
+    const size_t n = triangles_.size(), m = materials_.size();
+    vertices_.resize(9 * n); planes_.resize(4 * n); squares_.resize(n); mat_ids_.resize(n); mats_.resize(10 * m);
+    for (size_t i = 0; i < n; ++i) {
+        const Triangle &t = triangles_[i];
+        for (int k = 0; k < 3; ++k)
+            for (int a = 0; a < 3; ++a) vertices_[9 * i + 3 * k + a] = t.GetVertices()[k][a];
+        const vec4 p = t.GetPlane();
+        planes_[4 * i] = p.x; planes_[4 * i + 1] = p.y; planes_[4 * i + 2] = p.z; planes_[4 * i + 3] = p.w;
+        squares_[i] = t.GetSquare();
+        mat_ids_[i] = t.GetMaterialId();
+    }
+    for (size_t j = 0; j < m; ++j) {
+        const MaterialCharacteristics &c = materials_[j].GetCharacteristics();
+        const float row[10] = {c.Ke.x, c.Ke.y, c.Ke.z, c.Kd.x, c.Kd.y, c.Kd.z, c.Ks.x, c.Ks.y, c.Ks.z, c.Ns};
+        std::copy(row, row + 10, mats_.begin() + 10 * j);
+    }
+    PtScene s{};
+    s.n_triangles = static_cast<int32_t>(n);
+    s.vertices = vertices_.data(); s.planes = planes_.data(); s.squares = squares_.data();
+    s.material_ids = mat_ids_.data();
+    s.n_materials = static_cast<int32_t>(m);
+    s.materials = mats_.data();
+    if (skybox_.width() && skybox_.height()) {
+        s.sky_width = static_cast<int32_t>(skybox_.width());
+        s.sky_height = static_cast<int32_t>(skybox_.height());
+        s.sky_bgr = skybox_.data();
+    }
+    return s;
+}
+
+int Scene::Render(const PtConfig &cfg) {
+    const PtScene s = abi();
+    const size_t W = cfg.width, H = cfg.height;
+    std::vector<float> sum(3 * W * H), sum2(3 * W * H);
+    std::vector<int32_t> cnt(W * H);
+    const int rc = pt_render_accum(&s, &cfg, sum.data(), sum2.data(), cnt.data());
+    if (rc) return rc;
+    for (size_t y = 0; y < H; ++y)
+        for (size_t x = 0; x < W; ++x) {
+            const size_t p = y * W + x;
+            color_map_[x][y] = vec3(sum[3 * p], sum[3 * p + 1], sum[3 * p + 2]);
+            color2_map_[x][y] = vec3(sum2[3 * p], sum2[3 * p + 1], sum2[3 * p + 2]);
+            samples_count_[x][y] = cnt[p];
+        }
+    return 0;
+}

@@ -1,0 +1,38 @@
+// scene.h — Scene with the reference's surface (scene.h:7-24): constructed on the three frame accumulators,
+// LoadModel(path), AddTriangle(triangle).  TraceRay(Ray&) — one path segment on the CPU — is replaced by Render(),
+// which hands the whole sample loop of main.cpp:107-160 to the GPU through the C-ABI (pt_render_accum) and fills the
+// same three accumulators, indexed [x][y] as the reference's.
+#ifndef PT_B200_HOST_SCENE_H
+#define PT_B200_HOST_SCENE_H
+#include <string>
+#include <vector>
+
+#include "bitmap_image.h"
+#include "triangles.h"
+
+class Scene {
+    std::vector<Triangle> triangles_;
+    std::vector<std::vector<ptm::vec3>> &color_map_;
+    std::vector<std::vector<ptm::vec3>> &color2_map_;
+    std::vector<std::vector<int>> &samples_count_;
+    std::vector<Material> materials_;
+    bitmap_image skybox_;
+    // flat arrays behind abi()
+    mutable std::vector<float> vertices_, planes_, squares_, mats_;
+    mutable std::vector<int32_t> mat_ids_;
+
+public:
+    Scene(std::vector<std::vector<ptm::vec3>> &color_map, std::vector<std::vector<ptm::vec3>> &color2_map,
+          std::vector<std::vector<int>> &samples_count);
+    void LoadModel(std::string path);
+    void AddTriangle(Triangle triangle);
+    int AddMaterial(const MaterialCharacteristics &ch);
+
+    size_t TriangleCount() const { return triangles_.size(); }
+    const std::vector<Triangle> &Triangles() const { return triangles_; }
+    const std::vector<Material> &Materials() const { return materials_; }
+
+    PtScene abi() const;  // plain-data view for the C-ABI; valid until the scene is modified
+    int Render(const PtConfig &cfg);  // the loop main.cpp:107-160 on the GPU; returns a PT_* code
+};
+#endif

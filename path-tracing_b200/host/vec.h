@@ -1,0 +1,39 @@
+// vec.h — the few vector helpers the host-side types need.  The reference uses glm (un-vendored, unpinned, absent
+// from this image); the host side here needs only vec3/vec4 storage, cross, dot, normalize with the
+// evaluation order fixed in pt_math.cuh (dot sums left to right, normalize = v * (1/sqrt(dot))).
+#ifndef PT_B200_HOST_VEC_H
+#define PT_B200_HOST_VEC_H
+#include <cmath>
+
+namespace ptm {
+struct vec3 {
+    float x = 0, y = 0, z = 0;
+    vec3() = default;
+    explicit vec3(float s) : x(s), y(s), z(s) {}
+    vec3(float a, float b, float c) : x(a), y(b), z(c) {}
+    float &operator[](int i) { return i == 0 ? x : (i == 1 ? y : z); }
+    float operator[](int i) const { return i == 0 ? x : (i == 1 ? y : z); }
+};
+struct vec4 {
+    float x = 0, y = 0, z = 0, w = 0;
+    vec4() = default;
+    explicit vec4(float s) : x(s), y(s), z(s), w(s) {}
+    vec4(float a, float b, float c, float d) : x(a), y(b), z(c), w(d) {}
+    vec4(const vec3 &v, float d) : x(v.x), y(v.y), z(v.z), w(d) {}
+    vec3 xyz() const { return vec3(x, y, z); }
+};
+inline vec3 operator-(const vec3 &a, const vec3 &b) { return vec3(a.x - b.x, a.y - b.y, a.z - b.z); }
+inline vec3 operator*(const vec3 &a, float s) { return vec3(a.x * s, a.y * s, a.z * s); }
+inline bool operator==(const vec3 &a, const vec3 &b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
+inline bool operator!=(const vec3 &a, const vec3 &b) { return !(a == b); }
+inline float dot(const vec3 &a, const vec3 &b) {
+    const float px = a.x * b.x, py = a.y * b.y, pz = a.z * b.z;
+    return px + py + pz;
+}
+inline vec3 cross(const vec3 &a, const vec3 &b) {
+    return vec3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y);
+}
+inline float length(const vec3 &v) { return std::sqrt(dot(v, v)); }
+inline vec3 normalize(const vec3 &v) { return v * (1.0f / std::sqrt(dot(v, v))); }
+}  // namespace ptm
+#endif

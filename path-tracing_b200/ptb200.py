@@ -1,0 +1,274 @@
+"""ctypes binding of the B200 render library (include/pt_render.h) and of the host-side C++ loader.
+
+This module is plumbing only: it loads lib/libptrender.so (CUDA kernels + C-ABI) and lib/libpthost.so (the C++
+Scene/Config mirror of the reference's scene.cpp / config.h) and exposes their entry points on numpy arrays.  It
+contains no rendering arithmetic and no CPU fallback: if the CUDA library is missing, import fails loudly.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+RENDER_SO = os.path.join(HERE, "lib", "libptrender.so")
+HOST_SO = os.path.join(HERE, "lib", "libpthost.so")
+
+PT_ACCEL_AUTO, PT_ACCEL_BRUTE, PT_ACCEL_LBVH = 0, 1, 2
+PT_ISECT_REFERENCE, PT_ISECT_WATERTIGHT = 0, 1
+ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_ENCCL", 5: "PT_ENOMEM"}
+
+# every symbol include/pt_render.h declares (tests check that the library exports all of them)
+ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
+               "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
+               "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version"]
+
+
+class PtScene(C.Structure):
+    _fields_ = [("n_triangles", C.c_int32), ("vertices", C.c_void_p), ("planes", C.c_void_p),
+                ("squares", C.c_void_p), ("material_ids", C.c_void_p), ("n_materials", C.c_int32),
+                ("materials", C.c_void_p), ("sky_width", C.c_int32), ("sky_height", C.c_int32),
+                ("sky_bgr", C.c_void_p)]
+
+
+class PtConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("rays_per_pixel", C.c_int32),
+                ("max_ray_reflections", C.c_int32), ("eps", C.c_float), ("error", C.c_float), ("seed", C.c_uint32),
+                ("sample_begin", C.c_int32), ("sample_step", C.c_int32), ("intersector", C.c_int32),
+                ("accel", C.c_int32), ("rr_depth", C.c_int32), ("n_gpus", C.c_int32), ("device", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
+
+
+class PtStats(C.Structure):
+    _fields_ = [("segments", C.c_uint64), ("segments_traced", C.c_uint64), ("nodes_visited", C.c_uint64),
+                ("tris_tested", C.c_uint64), ("kernel_ms", C.c_float), ("build_ms", C.c_float),
+                ("upload_ms", C.c_float), ("n_nodes", C.c_int32), ("n_large", C.c_int32), ("accel", C.c_int32),
+                ("launches", C.c_int32)]
+
+
+class PtError(RuntimeError):
+    def __init__(self, code, text):
+        super().__init__(f"{ERRORS.get(code, code)}: {text}")
+        self.code = code
+
+
+def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
+           sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0):
+    """PtConfig with the reference's defaults (config.h:10,16-29)."""
+    c = PtConfig()
+    c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
+    c.eps, c.error, c.seed = eps, error, seed
+    c.sample_begin, c.sample_step = sample_begin, sample_step
+    c.intersector, c.accel, c.rr_depth, c.n_gpus, c.device = intersector, accel, rr_depth, n_gpus, device
+    return c
+
+
+def _load(path):
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: build it with `make -C path-tracing_b200` (nvcc, sm_100a). "
+                          "There is no CPU fallback.")
+    return C.CDLL(path)
+
+
+class Library:
+    """The C-ABI of include/pt_render.h on numpy arrays.  A scene is a dict of arrays:
+    verts (n,9) f32, planes (n,4) f32 | None, squares (n,) f32 | None, mat_ids (n,) i32, mats (m,10) f32."""
+
+    def __init__(self):
+        L = self.lib = _load(RENDER_SO)
+        L.pt_last_error.restype = C.c_char_p
+        L.pt_version.restype = C.c_char_p
+        L.pt_scene_create.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_int32, C.POINTER(C.c_void_p)]
+        L.pt_scene_destroy.argtypes = [C.c_void_p]
+        L.pt_scene_destroy.restype = None
+        L.pt_scene_render_device.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]
+        L.pt_resolve_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_scene_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
+        L.pt_render.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p]
+        L.pt_render_accum.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pt_intersect.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p, C.c_int64, C.c_void_p,
+                                   C.c_void_p]
+        L.pt_scene_intersect.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_int64, C.c_void_p,
+                                         C.c_void_p]
+        L.pt_triangle_setup.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
+        L.pt_sincos.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_primary_rays.argtypes = [C.POINTER(PtConfig), C.c_void_p, C.c_int64, C.c_void_p]
+
+    def check(self, rc):
+        if rc != 0:
+            raise PtError(rc, self.lib.pt_last_error().decode())
+
+    def device_count(self):
+        return int(self.lib.pt_device_count())
+
+    @staticmethod
+    def scene_struct(sc):
+        keep = {"verts": np.ascontiguousarray(sc["verts"], np.float32).reshape(-1, 9),
+                "mat_ids": np.ascontiguousarray(sc["mat_ids"], np.int32),
+                "mats": np.ascontiguousarray(sc["mats"], np.float32).reshape(-1, 10)}
+        s = PtScene()
+        s.n_triangles = keep["verts"].shape[0]
+        s.vertices = keep["verts"].ctypes.data
+        if sc.get("planes") is not None:
+            keep["planes"] = np.ascontiguousarray(sc["planes"], np.float32).reshape(-1, 4)
+            keep["squares"] = np.ascontiguousarray(sc["squares"], np.float32)
+            s.planes, s.squares = keep["planes"].ctypes.data, keep["squares"].ctypes.data
+        s.material_ids = keep["mat_ids"].ctypes.data
+        s.n_materials = keep["mats"].shape[0]
+        s.materials = keep["mats"].ctypes.data
+        s._keep = keep
+        return s
+
+    # ---- host-buffer entry points (the drop-in boundary) ----
+    def render(self, sc, cfg):
+        rgb = np.zeros((cfg.height, cfg.width, 3), np.float32)
+        s = self.scene_struct(sc)
+        self.check(self.lib.pt_render(C.byref(s), C.byref(cfg), rgb.ctypes.data))
+        return rgb
+
+    def render_accum(self, sc, cfg):
+        H, W = cfg.height, cfg.width
+        sm = np.zeros((H, W, 3), np.float32)
+        s2 = np.zeros((H, W, 3), np.float32)
+        cnt = np.zeros((H, W), np.int32)
+        s = self.scene_struct(sc)
+        self.check(self.lib.pt_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data))
+        return sm, s2, cnt
+
+    def intersect(self, sc, rays6, cfg=None):
+        cfg = cfg or config()
+        rays6 = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = rays6.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        s = self.scene_struct(sc)
+        self.check(self.lib.pt_intersect(C.byref(s), C.byref(cfg), rays6.ctypes.data, n, ids.ctypes.data, t.ctypes.data))
+        return ids, t
+
+    def triangle_setup(self, verts, vn=None, has_vn=None):
+        v = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        n = v.shape[0]
+        planes = np.zeros((n, 4), np.float32)
+        squares = np.zeros(n, np.float32)
+        hp = vp = None
+        if vn is not None:
+            vn = np.ascontiguousarray(vn, np.float32).reshape(-1, 3)
+            has_vn = np.ascontiguousarray(has_vn if has_vn is not None else np.ones(n), np.uint8)
+            hp, vp = has_vn.ctypes.data, vn.ctypes.data
+        self.check(self.lib.pt_triangle_setup(v.ctypes.data, hp, vp, n, planes.ctypes.data, squares.ctypes.data))
+        return planes, squares
+
+    def philox(self, ctr4, key2):
+        ctr4 = np.ascontiguousarray(ctr4, np.uint32).reshape(-1, 4)
+        key2 = np.ascontiguousarray(key2, np.uint32).reshape(-1, 2)
+        out = np.zeros_like(ctr4)
+        self.check(self.lib.pt_philox(ctr4.ctypes.data, key2.ctypes.data, ctr4.shape[0], out.ctypes.data))
+        return out
+
+    def sincos(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        s = np.empty_like(x)
+        c = np.empty_like(x)
+        self.check(self.lib.pt_sincos(x.ctypes.data, x.size, s.ctypes.data, c.ctypes.data))
+        return s, c
+
+    def primary_rays(self, cfg, xys3):
+        xys3 = np.ascontiguousarray(xys3, np.int32).reshape(-1, 3)
+        rays = np.zeros((xys3.shape[0], 6), np.float32)
+        self.check(self.lib.pt_primary_rays(C.byref(cfg), xys3.ctypes.data, xys3.shape[0], rays.ctypes.data))
+        return rays
+
+    # ---- device-resident API ----
+    def scene_create(self, sc, cfg, counters=False):
+        return DeviceScene(self, sc, cfg, counters)
+
+
+class DeviceScene:
+    """Handle on a device-resident scene (SoA triangles + LBVH)."""
+
+    def __init__(self, lib, sc, cfg, counters=False):
+        self.L = lib
+        self.h = C.c_void_p()
+        s = Library.scene_struct(sc)
+        lib.check(lib.lib.pt_scene_create(C.byref(s), C.byref(cfg), 1 if counters else 0, C.byref(self.h)))
+
+    def render_device(self, cfg, d_sum3=0, d_sum2=0, d_count=0, stream=0):
+        """Device pointers (ints, e.g. torch.Tensor.data_ptr()); asynchronous on `stream`."""
+        self.L.check(self.L.lib.pt_scene_render_device(self.h, C.byref(cfg), d_sum3 or None, d_sum2 or None,
+                                                       d_count or None, stream or None))
+
+    def resolve_device(self, d_sum3, d_count, n_pixels, d_rgb, stream=0):
+        self.L.check(self.L.lib.pt_resolve_device(d_sum3, d_count, n_pixels, d_rgb, stream or None))
+
+    def intersect(self, rays6, cfg=None):
+        cfg = cfg or config()
+        rays6 = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = rays6.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        self.L.check(self.L.lib.pt_scene_intersect(self.h, C.byref(cfg), rays6.ctypes.data, n, ids.ctypes.data,
+                                                   t.ctypes.data))
+        return ids, t
+
+    def stats(self):
+        st = PtStats()
+        self.L.check(self.L.lib.pt_scene_stats(self.h, C.byref(st)))
+        return {k: getattr(st, k) for k, _ in PtStats._fields_}
+
+    def close(self):
+        if self.h:
+            self.L.lib.pt_scene_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class HostLoader:
+    """The C++ host side (host/scene.cpp: Scene::LoadModel with the reference's OBJ/MTL semantics)."""
+
+    def __init__(self):
+        _load(RENDER_SO)
+        L = self.lib = _load(HOST_SO)
+        L.pth_load_obj.argtypes = [C.c_char_p, C.c_char_p]
+        L.pth_copy_scene.argtypes = [C.c_void_p] * 5
+        L.pth_triangle_setup.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pth_parse_config.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(PtConfig)]
+
+    def load_obj(self, model_path, model_name):
+        if not model_path.endswith("/"):
+            model_path += "/"
+        n = self.lib.pth_load_obj(model_path.encode(), model_name.encode())
+        if n < 0:
+            raise FileNotFoundError(model_path + model_name)
+        m = self.lib.pth_material_count()
+        sc = {"verts": np.zeros((n, 9), np.float32), "planes": np.zeros((n, 4), np.float32),
+              "squares": np.zeros(n, np.float32), "mat_ids": np.zeros(n, np.int32),
+              "mats": np.zeros((m, 10), np.float32)}
+        self.lib.pth_copy_scene(sc["verts"].ctypes.data, sc["planes"].ctypes.data, sc["squares"].ctypes.data,
+                                sc["mat_ids"].ctypes.data, sc["mats"].ctypes.data)
+        return sc
+
+    def triangle_setup(self, verts, vn=None):
+        v = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        n = v.shape[0]
+        planes = np.zeros((n, 4), np.float32)
+        squares = np.zeros(n, np.float32)
+        sq = C.c_float()
+        zero = np.zeros(3, np.float32)
+        for i in range(n):
+            has = vn is not None
+            nn = np.ascontiguousarray(vn[i], np.float32) if has else zero
+            self.lib.pth_triangle_setup(v[i].ctypes.data, int(has), nn.ctypes.data, planes[i].ctypes.data, C.byref(sq))
+            squares[i] = sq.value
+        return planes, squares
+
+    def parse_config(self, argv):
+        arr = (C.c_char_p * len(argv))(*[a.encode() for a in argv])
+        out = PtConfig()
+        self.lib.pth_parse_config(len(argv), arr, C.byref(out))
+        return out

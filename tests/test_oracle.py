@@ -1,0 +1,109 @@
+"""CPU: the oracle (oracle/pt_oracle.c, plain-C restatement) against the golden vectors produced by the unmodified
+reference (tests/golden/make_golden.py) and, where /root/reference was compiled, against the reference live."""
+import numpy as np
+import pytest
+
+import scenes
+from util import GOLDEN, MODELS, assert_bits_equal, with_planes
+
+G = np.load(GOLDEN + "/golden.npz")
+
+
+def tor_scene():
+    # geometry from the golden dump; materials from Tor.mtl (Tor.mtl:4-52) in file order
+    ns = 96.078431
+    mats = np.array([[2, 2, 2, 1, 1, 1, .5, .5, .5, ns], [0, 0, 0, 1, 1, 1, .5, .5, .5, ns],
+                     [0, 0, 0, .01, 1, .01, .5, .5, .5, ns], [0, 0, 0, 1, .01, .01, .5, .5, .5, ns],
+                     [0, 0, 0, .5, 1, .01, .5, .5, .5, ns]], np.float32)
+    ids = np.concatenate([np.full(256, 4), [2, 2, 0, 0], np.full(8, 1), [3, 3]]).astype(np.int32)
+    return {"verts": G["tor_verts"], "planes": G["tor_planes"], "squares": G["tor_squares"], "mat_ids": ids, "mats": mats}
+
+
+def test_philox_known_answers(oracle):
+    # Random123 kat_vectors, philox4x32 10 rounds
+    assert oracle.philox([0, 0, 0, 0], [0, 0]) == [0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8]
+    assert oracle.philox([0xffffffff] * 4, [0xffffffff] * 2) == [0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd]
+    assert oracle.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0]) == \
+        [0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1]
+    assert_bits_equal(G["philox_kat"][0], np.array([0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8], np.uint32))
+
+
+def test_triangle_setup_matches_reference_dump(oracle):
+    sc = scenes.cornell()
+    planes, squares = oracle.triangle_setup(sc["verts"])
+    assert_bits_equal(planes, G["cornell_planes"], "cornell planes")
+    assert_bits_equal(squares, G["cornell_squares"], "cornell squares")
+
+
+@pytest.mark.parametrize("name", ["tor_cam", "tor_rnd"])
+def test_nearest_hit_tor(oracle, name):
+    ids, t = oracle.intersect(tor_scene(), G[name + "_rays"])
+    assert_bits_equal(ids, G[name + "_ids"], name + " ids")
+    assert_bits_equal(t, G[name + "_t"], name + " t")
+    assert (ids >= 0).mean() > 0.9
+
+
+@pytest.mark.parametrize("name,make", [("cornell", scenes.cornell), ("glossy", scenes.glossy_mix),
+                                       ("torus40", lambda: scenes.torus_room(40, 20))])
+def test_nearest_hit_synthetic(oracle, name, make):
+    sc = with_planes(make(), oracle)
+    ids, t = oracle.intersect(sc, G[name + "_rays"])
+    assert_bits_equal(ids, G[name + "_ids"], name + " ids")
+    assert_bits_equal(t, G[name + "_t"], name + " t")
+
+
+def test_primary_rays(oracle):
+    cfg = oracle.config(64, 64, 256)
+    for p, want in zip(G["prim_xys"], G["prim_rays"]):
+        o, d = oracle.primary_ray(cfg, *map(int, p))
+        assert_bits_equal(np.concatenate([o, d]), want, f"primary {p}")
+
+
+def render_case(oracle, sc, name):
+    W, H, spp, depth, seed, sb, ss = map(int, G[name + "_cfg"])
+    cfg = oracle.config(W, H, spp, depth, 1e-4, float(G[name + "_error"]), seed, sb, ss)
+    sm, s2, cnt, segs, _ = oracle.render_accum(sc, cfg)
+    assert_bits_equal(cnt, G[name + "_count"], name + " count")
+    assert_bits_equal(sm, G[name + "_sum"], name + " sum")
+    assert_bits_equal(s2, G[name + "_sum2"], name + " sum2")
+    assert segs == int(G[name + "_segments"])
+    return cnt
+
+
+@pytest.mark.parametrize("name", ["tor_flat", "tor_adapt", "tor_part"])
+def test_render_tor(oracle, name):
+    cnt = render_case(oracle, tor_scene(), name)
+    assert cnt.sum() > 0
+
+
+@pytest.mark.parametrize("name,make", [("cornell", scenes.cornell), ("glossy", scenes.glossy_mix),
+                                       ("torus40", lambda: scenes.torus_room(40, 20))])
+def test_render_synthetic(oracle, name, make):
+    render_case(oracle, with_planes(make(), oracle), name)
+
+
+def test_adaptive_rule_changes_the_result():
+    # the adaptive fixture must actually exercise main.cpp:118-125 (otherwise it pins nothing)
+    assert int(G["tor_adapt_segments"]) < 32 * 32 * 24 * 8
+    flat_rate = int(G["tor_flat_segments"]) / (32 * 32 * 16)
+    assert int(G["tor_adapt_segments"]) / (32 * 32 * 24) < flat_rate
+
+
+def test_oracle_vs_live_reference(oracle, reference):
+    """Fresh seeds and sizes, not in the fixtures: restatement == reference, bit for bit."""
+    reference.set_config(24, 20, 12, 8, 1e-4, 0.001)
+    assert reference.load_obj(MODELS, "Tor.obj") == 270
+    planes, verts, squares = reference.dump()
+    sc = tor_scene()
+    assert_bits_equal(planes, sc["planes"])
+    rays = scenes.random_rays(3000, seed=77)
+    ri, rt = reference.intersect(rays)
+    oi, ot = oracle.intersect(sc, rays)
+    assert_bits_equal(oi, ri)
+    assert_bits_equal(ot, rt)
+    rs, rs2, rc, rseg, _ = reference.render_accum(seed=7)
+    os_, os2, oc, oseg, _ = oracle.render_accum(sc, oracle.config(24, 20, 12, 8, 1e-4, 0.001, 7))
+    assert_bits_equal(oc, rc)
+    assert_bits_equal(os_, rs)
+    assert_bits_equal(os2, rs2)
+    assert oseg == rseg
