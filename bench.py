@@ -194,6 +194,7 @@ def main():
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs only)")
     ap.add_argument("--accel", type=int, default=0)
+    ap.add_argument("--mode", type=int, default=0, help="0 wavefront pipeline (default), 1 megakernel variant")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference_arm(args)
@@ -218,7 +219,7 @@ def main():
     sc = make_scene(args.workload)
     lib = ptb200.Library()
     cfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
-                        accel=args.accel)
+                        accel=args.accel, mode=args.mode)
     ds = lib.scene_create(sc, cfg)
     n_px = W * H
     acc = torch.zeros(n_px * 4, device="cuda")            # [sum rgb (3*n_px) | count as f32 (n_px)] reduced together
@@ -228,6 +229,7 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
     launches_per_step = 0
+    lib_launches = [1]
 
     def step():
         nonlocal launches_per_step
@@ -241,7 +243,10 @@ def main():
         if rank == 0:
             ds.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream)
             n += 1
-        launches_per_step = n
+        launches_per_step = n - 1 + ds_launches()
+
+    def ds_launches():
+        return lib_launches[0]
 
     def barrier():
         if world > 1:
@@ -251,6 +256,7 @@ def main():
     for _ in range(args.warmup):
         step()
     barrier()
+    lib_launches[0] = ds.stats()["launches"]             # kernels one render call launches (counted by the library)
     seg_step = torch.tensor([ds.stats()["segments"]], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(seg_step)
@@ -306,7 +312,7 @@ def main():
     if rank == 0:
         cspp = max(world, min(spp, 8 * world))
         ccfg = ptb200.config(W, H, cspp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
-                             accel=args.accel)
+                             accel=args.accel, mode=args.mode)
         dsc = lib.scene_create(sc, ccfg, counters=True)
         dsc.render_device(ccfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
         torch.cuda.synchronize()

@@ -62,8 +62,8 @@ enum {
 };
 /* acceleration modes */
 enum {
-    PT_ACCEL_AUTO = 0,  /* brute force from shared memory for tiny scenes, LBVH otherwise */
-    PT_ACCEL_BRUTE = 1, /* every triangle in index order, as scene.cpp:114-120 */
+    PT_ACCEL_AUTO = 0,  /* = PT_ACCEL_LBVH: GPU LBVH, with the few scene-sized triangles (walls) in shared memory */
+    PT_ACCEL_BRUTE = 1, /* every triangle in index order, as scene.cpp:114-120 (checker mode) */
     PT_ACCEL_LBVH = 2
 };
 
@@ -85,7 +85,7 @@ typedef struct PtConfig {
     int32_t n_gpus;       /* pt_render only: 0/1 = current device; N>1 = split samples over N devices of this
                              process and sum with one NCCL reduce */
     int32_t device;       /* first CUDA device ordinal */
-    int32_t reserved[4];
+    int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant; others must be 0 */
 } PtConfig;
 
 /* Statistics of the last render on a scene handle. */
@@ -121,7 +121,9 @@ int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, floa
 int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_t flags, PtDeviceScene **out);
 void pt_scene_destroy(PtDeviceScene *ds);
 /* Render into DEVICE buffers (float sum3[H*W*3], float sum2_3[H*W*3], int32 count[H*W]; NULL allowed) on
- * `stream` (a cudaStream_t, 0 = default stream).  Asynchronous with respect to the host. */
+ * `stream` (a cudaStream_t, 0 = default stream).  All work is issued on `stream`; the call waits on the stream once
+ * per round of steps to learn whether the adaptive rule left samples to trace (one wait in a flat-spp run), so
+ * it returns with the render's last kernels still in flight. */
 int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
                            int32_t *d_count, void *stream);
 /* rgb = sum/count on the device (main.cpp:179-182 without the gamma); buffers are device pointers. */

@@ -9,6 +9,7 @@
 #include "../../include/pt_render.h"
 #include "pt_bvh.cuh"
 #include "pt_kernels.cuh"
+#include "pt_wavefront.cuh"
 
 using namespace ptd;
 
@@ -61,6 +62,7 @@ struct PtDeviceScene {
     float4 *tris = nullptr;
     float4 *nodes = nullptr;
     float4 *mats = nullptr;
+    float4 *lboxes = nullptr;
     unsigned long long *stats = nullptr;  // 4 counters
     SceneView view{};
     bool counters = false;
@@ -70,6 +72,12 @@ struct PtDeviceScene {
     int accel = PT_ACCEL_BRUTE;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     bool timed = false;
+    // wavefront workspace (path state, queues, per-pixel accumulators), sized on first use
+    WfState wf{};
+    void *wf_mem = nullptr;
+    size_t wf_slots = 0, wf_pixels = 0;
+    int *h_counters = nullptr;  // pinned, 6 ints
+    int traverse_blocks = 0;
 };
 
 static int validate_scene(const PtScene *s) {
@@ -111,6 +119,9 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     cudaFree(ds->tris);
     cudaFree(ds->nodes);
     cudaFree(ds->mats);
+    cudaFree(ds->lboxes);
+    cudaFree(ds->wf_mem);
+    if (ds->h_counters) cudaFreeHost(ds->h_counters);
     cudaFree(ds->stats);
     if (ds->ev0) cudaEventDestroy(ds->ev0);
     if (ds->ev1) cudaEventDestroy(ds->ev1);
@@ -167,7 +178,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     CK(cudaMalloc((void **)&ds->stats, 4 * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long)));
 
-    const bool brute = want == PT_ACCEL_BRUTE || (want == PT_ACCEL_AUTO && n <= kBruteMax) || n == 0;
+    const bool brute = want == PT_ACCEL_BRUTE || n == 0;
     SceneView v{};
     v.n_tri = n;
     v.counters = nullptr;
@@ -184,12 +195,15 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         DevBuf<int> vals, vals2, parent, flags;
         DevBuf<int2> children, range;
         DevBuf<unsigned char> tmp;
+        DevBuf<float4> d_root;
+        CK(d_root.alloc(2));
+        CK(cudaMalloc((void **)&ds->lboxes, 2 * (size_t)kMaxLarge * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
         CK(vals.alloc(n)); CK(vals2.alloc(n));
         k_init_scratch<<<1, 1>>>(d_scr.p);
         k_vertex_bounds<<<std::min(blocks_for(n, 256), 1184), 256>>>(d_verts.p, n, d_scr.p);
         k_tri_boxes_keys<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, n, eps, d_scr.p, box_lo.p,
-                                                      box_hi.p, keys.p, vals.p, 1);
+                                                      box_hi.p, keys.p, vals.p, n <= kAllLargeMax ? 1 : 0);
         launches += 3;
         size_t tmp_bytes = 0;
         CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys.p, keys2.p, vals.p, vals2.p, n));
@@ -203,6 +217,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         v.brute = 0; v.n_bvh = nb; v.n_large = n_large;
         k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, vals2.p, n, ds->tris);
         ++launches;
+        if (n_large) { k_large_boxes<<<1, 64>>>(vals2.p, box_lo.p, box_hi.p, nb, n_large, ds->lboxes); ++launches; }
         if (nb == 0) {
             v.root = kRefEmpty;
         } else if (nb <= kLeafMax) {
@@ -219,6 +234,14 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             v.root = 0;
             ds->n_nodes = nb - 1;
         }
+        if (nb > 0) {
+            k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, node_lo.p, node_hi.p, d_root.p);
+            ++launches;
+            float4 rb[2];
+            CK(cudaMemcpy(rb, d_root.p, sizeof rb, cudaMemcpyDeviceToHost));
+            v.root_lo = rb[0];
+            v.root_hi = rb[1];
+        }
         ds->accel = PT_ACCEL_LBVH;
         CK(cudaDeviceSynchronize());  // scratch buffers are freed on scope exit
     }
@@ -230,6 +253,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     v.tris = ds->tris;
     v.nodes = ds->nodes;
     v.mats = ds->mats;
+    v.lboxes = ds->lboxes;
     ds->view = v;
     ds->launches = launches;
     guard.p = nullptr;
@@ -252,6 +276,81 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     return rp;
 }
 
+constexpr size_t kMaxSlots = (size_t)1 << 24;  // path slots in flight (64 B of state each)
+
+static int wf_reserve(PtDeviceScene *ds, size_t npx) {
+    const size_t npc = std::min(npx, kMaxSlots / 4), slots = 4 * npc;
+    if (ds->wf_mem && ds->wf_slots >= slots && ds->wf_pixels >= npx) return PT_OK;
+    if (ds->wf_mem) { CK(cudaDeviceSynchronize()); CK(cudaFree(ds->wf_mem)); ds->wf_mem = nullptr; }
+    const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) + 256;
+    CK(cudaMalloc(&ds->wf_mem, bytes));
+    char *p = (char *)ds->wf_mem;
+    WfState &w = ds->wf;
+    w.oT = (float4 *)p; p += slots * sizeof(float4);
+    w.dR = (float4 *)p; p += slots * sizeof(float4);
+    w.Tn = (float4 *)p; p += slots * sizeof(float4);
+    w.cS = (float4 *)p; p += slots * sizeof(float4);
+    w.acc1 = (float4 *)p; p += npx * sizeof(float4);
+    w.acc2 = (float4 *)p; p += npx * sizeof(float4);
+    w.queue = (int *)p; p += 2 * slots * sizeof(int);
+    w.counters = (int *)p;
+    w.cap = (int)slots;
+    ds->wf_slots = slots;
+    ds->wf_pixels = npx;
+    if (!ds->h_counters) CK(cudaMallocHost((void **)&ds->h_counters, 8 * sizeof(int)));
+    if (!ds->traverse_blocks) {
+        int per_sm = 0, sms = 0;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false>, 128, 0));
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds->device));
+        ds->traverse_blocks = std::max(1, per_sm) * std::max(1, sms);
+    }
+    return PT_OK;
+}
+
+template <bool COUNT>
+static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStream_t st, int *launches) {
+    const size_t npx = (size_t)rp.W * rp.H;
+    int rc;
+    if ((rc = wf_reserve(ds, npx))) return rc;
+    const WfState wf = ds->wf;
+    const SceneView &sc = ds->view;
+    const int npc_max = (int)(ds->wf_slots / 4);
+    int n = 0;
+    k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp.s_begin);
+    ++n;
+    CK(cudaMemsetAsync(wf.counters, 0, 8 * sizeof(int), st));
+    const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
+    for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
+        const int npix = (int)std::min<size_t>(npc_max, npx - pix0);
+        const int slot_blocks = blocks_for(4LL * npix, 256);
+        int remaining = total;
+        while (remaining > 0) {
+            const int steps = (remaining + 3) / 4;
+            for (int i = 0; i < steps; ++i) {
+                k_wf_begin<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                for (int b = 0; b < rp.max_depth; ++b) {
+                    if (!sc.brute && sc.root != kRefEmpty)
+                        k_wf_traverse<COUNT><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                    k_wf_bounce<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    n += 2;
+                }
+                k_wf_commit<<<blocks_for(npix, 256), 256, 0, st>>>(rp, wf, (int)pix0, npix, i == steps - 1);
+                n += 2;
+            }
+            // progress check: pixels whose adaptive rule deferred samples need more steps (never in a flat-spp run)
+            CK(cudaMemcpyAsync(ds->h_counters, wf.counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+            CK(cudaMemsetAsync(wf.counters + 4, 0, 2 * sizeof(int), st));
+            CK(cudaStreamSynchronize(st));
+            remaining = ds->h_counters[4] > 0 ? ds->h_counters[5] : 0;
+        }
+    }
+    k_wf_finish<<<blocks_for((long long)npx, 256), 256, 0, st>>>(rp, wf, (int)npx);
+    ++n;
+    CK(cudaGetLastError());
+    *launches = n;
+    return PT_OK;
+}
+
 extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
                                       int32_t *d_count, void *stream) {
     if (!ds) return fail(PT_EINVAL, "scene handle is NULL");
@@ -260,14 +359,20 @@ extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, fl
     cudaStream_t st = (cudaStream_t)stream;
     CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long), st));
     const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, ds->stats);
-    const int tiles = ((rp.W + kTileW - 1) / kTileW) * ((rp.H + kTileH - 1) / kTileH);
     CK(cudaEventRecord(ds->ev0, st));
-    if (ds->counters) k_render<true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
-    else k_render<false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
-    CK(cudaGetLastError());
+    int launches = 1;
+    if (cfg->reserved[0] == 1) {  // megakernel variant
+        const int tiles = ((rp.W + kTileW - 1) / kTileW) * ((rp.H + kTileH - 1) / kTileH);
+        if (ds->counters) k_render_mega<true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+        else k_render_mega<false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+        CK(cudaGetLastError());
+    } else {
+        rc = ds->counters ? render_wavefront<true>(ds, rp, st, &launches) : render_wavefront<false>(ds, rp, st, &launches);
+        if (rc) return rc;
+    }
     CK(cudaEventRecord(ds->ev1, st));
     ds->timed = true;
-    ds->launches = 1;
+    ds->launches = launches;
     return PT_OK;
 }
 

@@ -136,7 +136,7 @@ __device__ __forceinline__ uint64_t spread21(uint32_t v) {  // 21 bits -> every 
 __global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *__restrict__ planes,
                                  const float *__restrict__ squares, int n, float eps, BuildScratch *s,
                                  float4 *__restrict__ box_lo, float4 *__restrict__ box_hi,
-                                 uint64_t *__restrict__ keys, int *__restrict__ vals, int want_large) {
+                                 uint64_t *__restrict__ keys, int *__restrict__ vals, int all_large) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const V3 slo = mk(ord2f(s->lo[0]), ord2f(s->lo[1]), ord2f(s->lo[2]));
@@ -159,7 +159,7 @@ __global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *
     const uint32_t qz = (uint32_t)fminf(fmaxf((c.z - slo.z) * sc, 0.0f), 2097151.0f);
     uint64_t key = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
     const V3 be = hi - lo;
-    const bool large = want_large && fmaxf(be.x, fmaxf(be.y, be.z)) > 0.25f * emax;
+    const bool large = all_large || fmaxf(be.x, fmaxf(be.y, be.z)) > 0.25f * emax;
     if (large) {
         key |= 1ull << 63;
         atomicAdd(&s->n_large, 1);
@@ -277,6 +277,33 @@ __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__res
     o[1] = make_float4(v[0], v[1], v[2], squares[i]);
     o[2] = make_float4(v[3], v[4], v[5], __int_as_float(i));
     o[3] = make_float4(v[6], v[7], v[8], __int_as_float(mat_ids[i]));
+}
+
+// boxes of the large triangles (sorted positions [nb, nb + n_large)) and of the LBVH root
+__global__ void k_large_boxes(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
+                              const float4 *__restrict__ box_hi, int nb, int n_large, float4 *__restrict__ lboxes) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_large) return;
+    const int i = vals[nb + k];
+    lboxes[2 * k] = box_lo[i];
+    lboxes[2 * k + 1] = box_hi[i];
+}
+__global__ void k_root_box(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
+                           const float4 *__restrict__ box_hi, int nb, const float4 *__restrict__ node_lo,
+                           const float4 *__restrict__ node_hi, float4 *__restrict__ out2) {
+    if (nb > kLeafMax) {  // internal root: node 0
+        out2[0] = node_lo[0];
+        out2[1] = node_hi[0];
+        return;
+    }
+    float4 l = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.0f), h = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.0f);
+    for (int k = 0; k < nb; ++k) {
+        const float4 a = box_lo[vals[k]], b = box_hi[vals[k]];
+        l = make_float4(fminf(l.x, a.x), fminf(l.y, a.y), fminf(l.z, a.z), 0.0f);
+        h = make_float4(fmaxf(h.x, b.x), fmaxf(h.y, b.y), fmaxf(h.z, b.z), 0.0f);
+    }
+    out2[0] = l;
+    out2[1] = h;
 }
 
 // Factory (material.h:58-106) as data: which closures exist and the mirror's selection chance

@@ -1,5 +1,5 @@
-// pt_kernels.cuh — the render loop (main.cpp:110-140) as one persistent-per-tile CUDA kernel, plus the small
-// kernels behind pt_intersect / pt_resolve / the parity probes.
+// pt_kernels.cuh — shading (the material closures), the megakernel variant of the render loop (main.cpp:110-140), and
+// the small kernels behind pt_intersect / pt_resolve / the parity probes.  The default pipeline is pt_wavefront.cuh.
 //
 // Work decomposition.  A warp owns 8 horizontally adjacent pixels; 4 consecutive lanes ("quad") own one pixel and
 // trace up to 4 of its next samples in parallel.  The reference processes a pixel's samples strictly in order
@@ -40,105 +40,90 @@ __device__ __forceinline__ bool adaptive_skip(int s, int n, V3 sum, V3 sum2, flo
     return Dx < error && Dy < error && Dz < error;
 }
 
-// One path: primary ray, then `while (ray.IsValid()) scene.TraceRay(ray)` (main.cpp:126-139).
-// Returns true when the path reached an emitter from its front side (material.h:68-79); c = throughput * Kd.
-template <bool COUNT>
-__device__ __forceinline__ bool trace_path(const SceneView &sc, const float4 *s_large, const RenderParams &rp, int x,
-                                           int y, uint32_t sample, V3 *c, int *n_seg, unsigned long long &n_nodes,
-                                           unsigned long long &n_tris) {
-    const uint32_t pixel = (uint32_t)(y * rp.W + x);
-    V3 o = mk(0.0f, 0.0f, -20.0f);
-    V3 d = primary_dir(x, y, rp.W, rp.H, pixel, sample, rp.seed);
-    V3 T = mk(1.0f, 1.0f, 1.0f);
-    int depth = 0, segs = 0;
-    bool contributed = false;
-    // Ray::IsValid, ray.h:52-54
-    while (depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f)) {
-        const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
-        ++segs;
-        if (h.rec < 0) break;  // miss: Ray::MakeInvalid (scene.cpp:155); skybox handled by the caller variant
-        const float4 *r = (s_large && (sc.brute || h.rec >= sc.n_bvh))
-                              ? s_large + 4 * (sc.brute ? h.rec : h.rec - sc.n_bvh)
-                              : sc.tris + 4 * (size_t)h.rec;
-        const float4 pl = r[0];
-        const int mat = __float_as_int(r[3].w);
-        const V3 N = mk(pl.x, pl.y, pl.z);
-        const float4 m0 = __ldg(sc.mats + 2 * mat), m1 = __ldg(sc.mats + 2 * mat + 1);
-        const int kind = __float_as_int(m0.w);
-        const V3 Kd = mk(m0.x, m0.y, m0.z);
-        if (kind == MAT_EMISSIVE) {  // material.h:68-79
-            if (!(dot4w0(d, N) > 0.0f)) {
-                *c = T * Kd;
-                contributed = true;
-            }
-            break;
+// One bounce of Scene::TraceRay after the nearest hit is known (scene.cpp:121-156): material dispatch
+// (Material::Process, material.h:36-50) and the closures Factory builds (material.h:58-106).
+// Returns false when the path ends here; *contrib is set when it ends on an emitter's front side with c = T * Kd.
+__device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large, const RenderParams &rp, const Hit &h,
+                                      uint32_t pixel, uint32_t sample, V3 &o, V3 &d, V3 &T, int &depth, V3 *c,
+                                      bool *contrib) {
+    if (h.rec < 0) return false;  // miss: Ray::MakeInvalid (scene.cpp:155)
+    const bool in_smem = !sc.brute && h.rec >= sc.n_bvh;
+    const float4 *r = in_smem ? s_large + kLargeStride * (h.rec - sc.n_bvh) : sc.tris + 4 * (size_t)h.rec;
+    const float4 pl = r[0];
+    const int mat = __float_as_int(r[3].w);
+    const V3 N = mk(pl.x, pl.y, pl.z);
+    const float4 m0 = __ldg(sc.mats + 2 * mat), m1 = __ldg(sc.mats + 2 * mat + 1);
+    const int kind = __float_as_int(m0.w);
+    const V3 Kd = mk(m0.x, m0.y, m0.z);
+    if (kind == MAT_EMISSIVE) {  // material.h:68-79
+        if (!(dot4w0(d, N) > 0.0f)) {
+            *c = T * Kd;
+            *contrib = true;
         }
-        if (kind == MAT_NONE) break;  // Material::Process with no closures, material.h:37-38
-        // drop_point = begin + direction * distance (scene.cpp:122), vec4 arithmetic
-        const V3 P = mk(o.x + d.x * h.t, o.y + d.y * h.t, o.z + d.z * h.t);
-        int lobe = kind == MAT_MIRROR ? 0 : 1;
-        uint4 w = make_uint4(0, 0, 0, 0);
-        if (kind != MAT_MIRROR) w = philox4x32_10(pixel, sample, 1u + (uint32_t)depth, 0u, rp.seed, 0u);
-        uint32_t w1 = w.x, w2 = w.y;
-        if (kind == MAT_BOTH) {  // Material::Process, material.h:43-49: chances [mirror, diffuse]
-            const float smp = u01(w.x);
-            lobe = (smp > 0.0f && (smp - m1.w) > 0.0f) ? 1 : 0;
-            w1 = w.y;
-            w2 = w.z;
-        }
-        const V3 begin = mk(P.x + N.x * rp.eps, P.y + N.y * rp.eps, P.z + N.z * rp.eps);
-        V3 nd, tint;
-        if (lobe == 0) {  // mirror closure, material.h:83-85; glm::reflect = I - N * dot(N, I) * 2
-            const float dn = dot4w0(N, d);
-            nd = mk(d.x - N.x * dn * 2.0f, d.y - N.y * dn * 2.0f, d.z - N.z * dn * 2.0f);
-            tint = mk(m1.x, m1.y, m1.z);
-        } else {  // diffuse closure, material.h:90-100: cosine lobe about world +Z, flipped to N's side
-            const float xi1 = u01(w1), xi2 = u01(w2);
-            const float ang = 2 * kPi * xi2;
-            float sn, cs;
-            ref_sincosf(ang, &sn, &cs);
-            const float sq = sqrtf(xi1);
-            V3 rnd = normalize4w0(mk(sq * cs, sq * sn, sqrtf(1 - xi1)));
-            if (dot4w0(N, rnd) < 0.0f) rnd = mk(rnd.x * -1.0f, rnd.y * -1.0f, rnd.z * -1.0f);
-            const float dt = fmaxf(0.0f, dot4w0(N, rnd));
-            nd = rnd;
-            tint = mk(Kd.x * dt, Kd.y * dt, Kd.z * dt);
-        }
-        // Ray::Reflect, ray.h:45-50
-        o = begin;
-        d = normalize4w0(nd);
-        T = T * tint;
-        ++depth;
+        return false;
     }
-    *n_seg = segs;
-    return contributed;
+    if (kind == MAT_NONE) return false;  // Material::Process with no closures, material.h:37-38
+    // drop_point = begin + direction * distance (scene.cpp:122), vec4 arithmetic
+    const V3 P = mk(o.x + d.x * h.t, o.y + d.y * h.t, o.z + d.z * h.t);
+    int lobe = kind == MAT_MIRROR ? 0 : 1;
+    uint4 w = make_uint4(0, 0, 0, 0);
+    if (kind != MAT_MIRROR) w = philox4x32_10(pixel, sample, 1u + (uint32_t)depth, 0u, rp.seed, 0u);
+    uint32_t w1 = w.x, w2 = w.y;
+    if (kind == MAT_BOTH) {  // Material::Process, material.h:43-49: chances [mirror, diffuse]
+        const float smp = u01(w.x);
+        lobe = (smp > 0.0f && (smp - m1.w) > 0.0f) ? 1 : 0;
+        w1 = w.y;
+        w2 = w.z;
+    }
+    const V3 begin = mk(P.x + N.x * rp.eps, P.y + N.y * rp.eps, P.z + N.z * rp.eps);
+    V3 nd, tint;
+    if (lobe == 0) {  // mirror closure, material.h:83-85; glm::reflect = I - N * dot(N, I) * 2
+        const float dn = dot4w0(N, d);
+        nd = mk(d.x - N.x * dn * 2.0f, d.y - N.y * dn * 2.0f, d.z - N.z * dn * 2.0f);
+        tint = mk(m1.x, m1.y, m1.z);
+    } else {  // diffuse closure, material.h:90-100: cosine lobe about world +Z, flipped to N's side
+        const float xi1 = u01(w1), xi2 = u01(w2);
+        const float ang = 2 * kPi * xi2;
+        float sn, cs;
+        ref_sincosf(ang, &sn, &cs);
+        const float sq = sqrtf(xi1);
+        V3 rnd = normalize4w0(mk(sq * cs, sq * sn, sqrtf(1 - xi1)));
+        if (dot4w0(N, rnd) < 0.0f) rnd = mk(rnd.x * -1.0f, rnd.y * -1.0f, rnd.z * -1.0f);
+        const float dt = fmaxf(0.0f, dot4w0(N, rnd));
+        nd = rnd;
+        tint = mk(Kd.x * dt, Kd.y * dt, Kd.z * dt);
+    }
+    // Ray::Reflect, ray.h:45-50
+    o = begin;
+    d = normalize4w0(nd);
+    T = T * tint;
+    ++depth;
+    return true;
 }
 
 constexpr int kTileW = 8, kTileH = 8;       // pixels per block
 constexpr int kQuad = 4;                    // samples of one pixel traced in parallel
 constexpr int kBlockThreads = kTileW * kTileH * kQuad;  // 256
 
+// ---- megakernel variant: one thread carries one path through all its bounces (PtConfig::reserved[0] == 1) -------
+// Kept as the second, independent implementation of the loop (the wavefront pipeline in pt_wavefront.cuh is the
+// default): simplest possible control flow, no global path state, best for tiny frames.
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlockThreads)
-k_render(SceneView sc, RenderParams rp) {
-    __shared__ float4 s_large[4 * (kMaxLarge > kBruteMax ? kMaxLarge : kBruteMax)];
-    const int n_stage = sc.brute ? sc.n_tri : sc.n_large;
-    const bool staged = !sc.brute || sc.n_tri <= kBruteMax;
-    if (staged) {
-        const float4 *src = sc.tris + 4 * (size_t)(sc.brute ? 0 : sc.n_bvh);
-        for (int k = threadIdx.x; k < 4 * n_stage; k += blockDim.x) s_large[k] = src[k];
-    }
+k_render_mega(SceneView sc, RenderParams rp) {
+    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    if (!sc.brute) stage_large(sc, s_large);
     __syncthreads();
-    const float4 *sl = staged ? s_large : nullptr;
 
     const int tiles_x = (rp.W + kTileW - 1) / kTileW;
     const int tile = blockIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int q = lane & 3;                 // position in the quad
+    const int qi = lane & 3;                // position in the quad
     const int x = (tile % tiles_x) * kTileW + (lane >> 2);
     const int y = (tile / tiles_x) * kTileH + warp;
     const bool in_image = x < rp.W && y < rp.H;
     const unsigned qbase = lane & ~3u;
+    const uint32_t pixel = (uint32_t)(y * rp.W + x);
 
     V3 sum = mk(0, 0, 0), sum2 = mk(0, 0, 0);
     int cnt = 0;
@@ -146,17 +131,25 @@ k_render(SceneView sc, RenderParams rp) {
     unsigned long long seg_commit = 0, seg_traced = 0, n_nodes = 0, n_tris = 0;
 
     while (__any_sync(0xffffffffu, in_image && s_next < rp.spp)) {
-        const int s = s_next + q * rp.s_step;
+        const int s = s_next + qi * rp.s_step;
         const bool live = in_image && s_next < rp.spp && s < rp.spp;
         const bool traced = live && !adaptive_skip(s, cnt, sum, sum2, rp.error);
         V3 c = mk(0, 0, 0);
         int nseg = 0;
         bool contrib = false;
-        if (traced) {
-            contrib = trace_path<COUNT>(sc, sl, rp, x, y, (uint32_t)s, &c, &nseg, n_nodes, n_tris);
+        if (traced) {  // primary ray, then `while (ray.IsValid()) scene.TraceRay(ray)` (main.cpp:126-139)
+            V3 o = mk(0.0f, 0.0f, -20.0f), T = mk(1.0f, 1.0f, 1.0f);
+            V3 d = primary_dir(x, y, rp.W, rp.H, pixel, (uint32_t)s, rp.seed);
+            int depth = 0;
+            bool alive = true;
+            while (alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f)) {  // ray.h:52-54
+                const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
+                ++nseg;
+                alive = shade(sc, s_large, rp, h, pixel, (uint32_t)s, o, d, T, depth, &c, &contrib);
+            }
             seg_traced += nseg;
         }
-        // ordered commit over the quad
+        // ---- ordered commit over the quad
         bool stop = false;
 #pragma unroll
         for (int j = 0; j < kQuad; ++j) {
@@ -169,8 +162,7 @@ k_render(SceneView sc, RenderParams rp) {
             const float cy = __shfl_sync(0xffffffffu, c.y, src);
             const float cz = __shfl_sync(0xffffffffu, c.z, src);
             if (stop || !live_j) continue;
-            const int sj = s_next;  // s_next always points at the sample being committed
-            const bool skip_now = adaptive_skip(sj, cnt, sum, sum2, rp.error);
+            const bool skip_now = adaptive_skip(s_next, cnt, sum, sum2, rp.error);  // s_next = the sample being committed
             if (!skip_now && !traced_j) {
                 stop = true;  // needed after all: first sample of the next step
                 continue;
@@ -181,25 +173,25 @@ k_render(SceneView sc, RenderParams rp) {
                     sum2 = mk(sum2.x + cx * cx, sum2.y + cy * cy, sum2.z + cz * cz);
                     ++cnt;
                 }
-                if (q == j) seg_commit += nseg_j;
+                if (qi == j) seg_commit += nseg_j;
             }
             s_next += rp.s_step;
         }
     }
 
-    if (in_image && q == 0) {
+    if (in_image && qi == 0) {
         const size_t p = (size_t)y * rp.W + x;
         if (rp.sum3) { rp.sum3[3 * p] = sum.x; rp.sum3[3 * p + 1] = sum.y; rp.sum3[3 * p + 2] = sum.z; }
         if (rp.sum2_3) { rp.sum2_3[3 * p] = sum2.x; rp.sum2_3[3 * p + 1] = sum2.y; rp.sum2_3[3 * p + 2] = sum2.z; }
         if (rp.count) rp.count[p] = cnt;
     }
     // statistics: one atomic per warp per counter
-    for (int o = 16; o; o >>= 1) {
-        seg_commit += __shfl_xor_sync(0xffffffffu, seg_commit, o);
-        seg_traced += __shfl_xor_sync(0xffffffffu, seg_traced, o);
+    for (int o2 = 16; o2; o2 >>= 1) {
+        seg_commit += __shfl_xor_sync(0xffffffffu, seg_commit, o2);
+        seg_traced += __shfl_xor_sync(0xffffffffu, seg_traced, o2);
         if (COUNT) {
-            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o);
-            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o);
+            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
+            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o2);
         }
     }
     if (lane == 0 && rp.stats) {
@@ -217,21 +209,15 @@ template <bool COUNT>
 __global__ void __launch_bounds__(256)
 k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float eps, int *__restrict__ ids,
             float *__restrict__ ts, unsigned long long *stats) {
-    __shared__ float4 s_large[4 * (kMaxLarge > kBruteMax ? kMaxLarge : kBruteMax)];
-    const int n_stage = sc.brute ? sc.n_tri : sc.n_large;
-    const bool staged = !sc.brute || sc.n_tri <= kBruteMax;
-    if (staged) {
-        const float4 *src = sc.tris + 4 * (size_t)(sc.brute ? 0 : sc.n_bvh);
-        for (int k = threadIdx.x; k < 4 * n_stage; k += blockDim.x) s_large[k] = src[k];
-    }
+    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    if (!sc.brute) stage_large(sc, s_large);
     __syncthreads();
-    const float4 *sl = staged ? s_large : nullptr;
     unsigned long long n_nodes = 0, n_tris = 0;
     for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
         const float *r = rays6 + 6 * i;
         const V3 o = mk(r[0], r[1], r[2]);
         const V3 d = normalize4w0(mk(r[3], r[4], r[5]));  // Ray's constructor, ray.h:21-25
-        const Hit h = nearest_hit<COUNT>(sc, sl, o, d, eps, n_nodes, n_tris);
+        const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, eps, n_nodes, n_tris);
         ids[i] = h.idx;
         ts[i] = h.t;
     }

@@ -1,11 +1,19 @@
-// pt_trace.cuh — nearest hit (Scene::TraceRay's loop, scene.cpp:114-120) through the LBVH, and the reference's
-// Triangle::Intersect (triangles.h:48-73) on the packed triangle records.
+// pt_trace.cuh — nearest hit (Scene::TraceRay's loop, scene.cpp:114-120) and the reference's Triangle::Intersect
+// (triangles.h:48-73) on the packed triangle records.
 //
 // Nearest-hit semantics to reproduce: the reference scans triangles in index order and accepts a triangle only when
 // its plane distance is strictly smaller than the best so far, so the answer is "minimum t over every triangle that
-// passes the inside test, ties to the lowest index".  Any traversal order gives that answer as long as (i) no box
+// passes the inside test, ties to the lowest index".  Any visiting order gives that answer as long as (i) no box
 // that can contain an accepted hit is culled — boxes are dilated for this (pt_bvh.cuh) and a box is kept while its
 // entry distance is <= the best t, not <; (ii) ties are resolved on the caller's triangle index.
+//
+// Two stages per ray:
+//   large_phase  the few "large" triangles (walls) from shared memory, all lanes in step.  The cheap part (plane
+//                distance, range test, hit point inside the triangle's dilated box) runs for every triangle; the
+//                expensive inside test (3 cross products, 3 IEEE square roots) is DEFERRED: candidates are marked in
+//                a per-lane bit mask and resolved together after the scan, so that lanes whose candidates sit at
+//                different triangle indices still run the inside test in the same instructions.
+//   traverse     stack-based BVH2 traversal over the LBVH for rays whose t-range still reaches the root box.
 #pragma once
 #include "pt_math.cuh"
 #include "pt_scene.cuh"
@@ -18,52 +26,93 @@ struct Hit {
     int rec;   // record index of the best hit in SceneView::tris
 };
 
-// Triangle::Intersect (triangles.h:48-73; PlaneIntersect :10-13, ParallelogramSquare :15-17) on record `rec`
-// (4 float4 at r).  Differences from the reference, both outside its defined behaviour: a NaN distance (0/0: ray
-// in the plane) is rejected instead of accepted, and equal distances go to the lower caller index explicitly.
-__device__ __forceinline__ void tri_intersect_ref(const float4 *__restrict__ r, int rec, V3 o, V3 d, float eps, Hit &h) {
-    const float4 p = r[0];
+__device__ __forceinline__ Hit no_hit() {
+    Hit h;
+    h.t = __int_as_float(0x7f800000);
+    h.idx = -1;
+    h.rec = -1;
+    return h;
+}
+
+// PlaneIntersect, triangles.h:10-13
+__device__ __forceinline__ float plane_distance(float4 p, V3 o, V3 d) {
     const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
-    const float nd = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w) / sd;
-    if (!(nd <= h.t) || nd < eps) return;
-    const float4 a = r[1], b = r[2], c = r[3];
-    const int idx = __float_as_int(b.w);
-    if (nd == h.t && !(idx < h.idx)) return;  // also rejects nd == +inf against the initial (inf, -1)
+    return -(o.x * p.x + o.y * p.y + o.z * p.z + p.w) / sd;
+}
+
+// the area-sum inside test of triangles.h:56-70 for the plane hit at distance nd; a = (v0, S), b = (v1, .), c = (v2, .)
+__device__ __forceinline__ bool inside_test(float4 a, float4 b, float4 c, V3 o, V3 d, float nd, float eps) {
     const float S = a.w;
     const V3 P = mk(o.x + d.x * nd, o.y + d.y * nd, o.z + d.z * nd);
     const V3 f0 = P - mk(a.x, a.y, a.z), f1 = P - mk(b.x, b.y, b.z), f2 = P - mk(c.x, c.y, c.z);
     const float s1 = length3(cross3(f0, f1));
-    if (s1 > S + eps) return;
+    if (s1 > S + eps) return false;
     const float s2 = length3(cross3(f0, f2));
-    if (s1 + s2 > S + eps) return;
+    if (s1 + s2 > S + eps) return false;
     const float s3 = length3(cross3(f2, f1));
-    if (fabsf(S - s1 - s2 - s3) > eps) return;
+    return !(fabsf(S - s1 - s2 - s3) > eps);
+}
+
+// Triangle::Intersect (triangles.h:48-73) on record `rec` (4 float4 at r).  Differences from the reference, both
+// outside its defined behaviour: a NaN distance (0/0: ray in the plane) is rejected instead of accepted, and equal
+// distances go to the lower caller index explicitly.
+__device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o, V3 d, float eps, Hit &h) {
+    const float nd = plane_distance(r[0], o, d);
+    if (!(nd <= h.t) || nd < eps) return;
+    const float4 a = r[1], b = r[2], c = r[3];
+    const int idx = __float_as_int(b.w);
+    if (nd == h.t && !(idx < h.idx)) return;  // also rejects nd == +inf against the initial (inf, -1)
+    if (!inside_test(a, b, c, o, d, nd, eps)) return;
     h.t = nd;
     h.idx = idx;
     h.rec = rec;
 }
 
-// Same test on a record staged in shared memory (the large triangles)
-__device__ __forceinline__ void tri_intersect_ref_smem(const float4 *r, int rec, V3 o, V3 d, float eps, Hit &h) {
-    const float4 p = r[0];
-    const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
-    const float nd = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w) / sd;
-    if (!(nd <= h.t) || nd < eps) return;
-    const float4 a = r[1], b = r[2], c = r[3];
-    const int idx = __float_as_int(b.w);
-    if (nd == h.t && !(idx < h.idx)) return;
-    const float S = a.w;
-    const V3 P = mk(o.x + d.x * nd, o.y + d.y * nd, o.z + d.z * nd);
-    const V3 f0 = P - mk(a.x, a.y, a.z), f1 = P - mk(b.x, b.y, b.z), f2 = P - mk(c.x, c.y, c.z);
-    const float s1 = length3(cross3(f0, f1));
-    if (s1 > S + eps) return;
-    const float s2 = length3(cross3(f0, f2));
-    if (s1 + s2 > S + eps) return;
-    const float s3 = length3(cross3(f2, f1));
-    if (fabsf(S - s1 - s2 - s3) > eps) return;
-    h.t = nd;
-    h.idx = idx;
-    h.rec = rec;
+// ---- large triangles: 6 float4 each in shared memory (the 4 record rows + dilated box lo, hi) ----------------
+constexpr int kLargeStride = 6;
+
+__device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large) {
+    for (int k = threadIdx.x; k < sc.n_large; k += blockDim.x) {
+        const float4 *r = sc.tris + 4 * (size_t)(sc.n_bvh + k);
+        float4 *o = s_large + kLargeStride * k;
+        o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+        o[4] = sc.lboxes[2 * k];
+        o[5] = sc.lboxes[2 * k + 1];
+    }
+}
+
+// Scan + resolve.  The scan is the same short instruction sequence for every lane and every triangle: exact plane
+// distance, range test, hit point against the triangle's dilated box; survivors are only MARKED (one bit per
+// triangle).  The resolve loop then runs the expensive inside test on each lane's marked triangles in index order,
+// so lanes whose candidates sit at different indices execute it together.  The scan uses the best distance known
+// when it started (conservative); the resolve re-applies the exact range / tie rule with the live best.
+__device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
+                                            Hit &h) {
+    unsigned long long mask = 0ull;
+    for (int k = 0; k < n_large; ++k) {
+        const float4 *r = s_large + kLargeStride * k;
+        const float nd = plane_distance(r[0], o, d);
+        // the hit point exactly as the inside test computes it; outside the dilated box => the test fails
+        const float Px = o.x + d.x * nd, Py = o.y + d.y * nd, Pz = o.z + d.z * nd;
+        const float4 lo = r[4], hi = r[5];
+        const bool cand = nd <= h.t && !(nd < eps) && Px >= lo.x && Px <= hi.x && Py >= lo.y && Py <= hi.y &&
+                          Pz >= lo.z && Pz <= hi.z;
+        mask |= (unsigned long long)cand << k;
+    }
+    while (mask) {
+        const int k = __ffsll((long long)mask) - 1;
+        mask &= mask - 1ull;
+        const float4 *r = s_large + kLargeStride * k;
+        const float nd = plane_distance(r[0], o, d);
+        if (!(nd <= h.t)) continue;
+        const float4 a = r[1], b = r[2], c = r[3];
+        const int idx = __float_as_int(b.w);
+        if (nd == h.t && !(idx < h.idx)) continue;
+        if (!inside_test(a, b, c, o, d, nd, eps)) continue;
+        h.t = nd;
+        h.idx = idx;
+        h.rec = rec_base + k;
+    }
 }
 
 // Slab test of one child box: entry distance, or +inf when the ray [0, tmax] misses the box.  fminf/fmaxf drop a
@@ -80,59 +129,70 @@ __device__ __forceinline__ float box_entry(float lox, float hix, float loy, floa
     return tn <= tf * 1.0000003f ? tn : __int_as_float(0x7f800000);
 }
 
+__device__ __forceinline__ bool reaches_root(const SceneView &sc, V3 o, V3 d, float tmax) {
+    if (sc.root == kRefEmpty) return false;
+    const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    return box_entry(sc.root_lo.x, sc.root_hi.x, sc.root_lo.y, sc.root_hi.y, sc.root_lo.z, sc.root_hi.z, o, inv, tmax) <
+           __int_as_float(0x7f800000);
+}
+
+// One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
+template <bool COUNT>
+__device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o, V3 d, V3 inv, float eps, Hit &h,
+                                             int *stack, int &sp, unsigned long long &n_nodes,
+                                             unsigned long long &n_tris) {
+    if (cur >= 0) {
+        const float4 *nd = sc.nodes + 4 * (size_t)cur;
+        const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3);
+        if (COUNT) ++n_nodes;
+        // box_entry clips against h.t with <=, so that an equal-distance lower index is still found; +inf = miss
+        const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
+        const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
+        const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+        const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
+        if (g0 && g1) {
+            const bool swap = t1 < t0;
+            if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
+            return swap ? c1 : c0;
+        }
+        if (g0) return c0;
+        if (g1) return c1;
+        return sp ? stack[--sp] : kRefEmpty;
+    }
+    // leaf: same scan + resolve split as large_phase (up to kLeafMax records, contiguous)
+    const int first = leaf_first(cur), cnt = leaf_count(cur);
+    unsigned mask = 0u;
+    for (int k = 0; k < cnt; ++k) {
+        const float nd = plane_distance(__ldg(sc.tris + 4 * (size_t)(first + k)), o, d);
+        mask |= (unsigned)(nd <= h.t && !(nd < eps)) << k;
+    }
+    while (mask) {
+        const int k = __ffs(mask) - 1;
+        mask &= mask - 1u;
+        tri_intersect_ref(sc.tris + 4 * (size_t)(first + k), first + k, o, d, eps, h);
+    }
+    if (COUNT) n_tris += cnt;
+    return sp ? stack[--sp] : kRefEmpty;
+}
+
+// Whole nearest-hit query in one thread (pt_intersect, and the brute-force checker mode).
 template <bool COUNT>
 __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_large, V3 o, V3 d, float eps,
                                            unsigned long long &n_nodes, unsigned long long &n_tris) {
-    Hit h;
-    h.t = __int_as_float(0x7f800000);
-    h.idx = -1;
-    h.rec = -1;
+    Hit h = no_hit();
     if (sc.brute) {  // scene.cpp:114-120 as written: every triangle, in order
-        if (s_large) {
-            for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref_smem(s_large + 4 * k, k, o, d, eps, h);
-        } else {
-            for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)k, k, o, d, eps, h);
-        }
+        for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)k, k, o, d, eps, h);
         if (COUNT) n_tris += sc.n_tri;
         return h;
     }
-    // large triangles first: they bound t before the tree is walked
-    for (int k = 0; k < sc.n_large; ++k) tri_intersect_ref_smem(s_large + 4 * k, sc.n_bvh + k, o, d, eps, h);
+    large_phase(s_large, sc.n_large, sc.n_bvh, o, d, eps, h);
     if (COUNT) n_tris += sc.n_large;
-
+    if (!reaches_root(sc, o, d, h.t)) return h;
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
     int stack[kStackDepth];
     int sp = 0;
     int cur = sc.root;
-    while (cur != kRefEmpty) {
-        if (cur >= 0) {
-            const float4 *nd = sc.nodes + 4 * (size_t)cur;
-            const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3);
-            if (COUNT) ++n_nodes;
-            const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
-            const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
-            const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-            // box_entry already clipped against h.t (<=, so that an equal-distance lower index is still found);
-            // +inf means a miss
-            const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
-            if (g0 && g1) {
-                const bool swap = t1 < t0;
-                cur = swap ? c1 : c0;
-                if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
-            } else if (g0) {
-                cur = c0;
-            } else if (g1) {
-                cur = c1;
-            } else {
-                cur = sp ? stack[--sp] : kRefEmpty;
-            }
-        } else {
-            const int first = leaf_first(cur), cnt = leaf_count(cur);
-            for (int k = 0; k < cnt; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)(first + k), first + k, o, d, eps, h);
-            if (COUNT) n_tris += cnt;
-            cur = sp ? stack[--sp] : kRefEmpty;
-        }
-    }
+    while (cur != kRefEmpty) cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
     return h;
 }
 

@@ -1,0 +1,283 @@
+// pt_wavefront.cuh — the render loop (main.cpp:110-140) as a wavefront pipeline: the default path of pt_render.
+//
+// Why not one thread per path: on the named scenes only a minority of the rays of a warp reach the mesh (the rest
+// end on a wall), and their tree walks have very different lengths; a per-thread loop then walks the LBVH with 3-6
+// of 32 lanes active (ncu, profiles/r01_v1_*).  Here the loop is cut at the two points where the set of active rays
+// changes, and path state lives in HBM between the stages (64 B per path, ~100 B of traffic per segment: a few
+// percent of the frame time at 6.5 TB/s):
+//
+//   k_wf_begin     per path slot (pixel x 4 consecutive samples): adaptive-skip decision from the pixel's
+//                  accumulators, jittered primary ray (main.cpp:118-129), then `front`:
+//     front        large triangles from shared memory (pt_trace.cuh large_phase), LBVH root test, and a
+//                  warp-ballot compaction of the rays that must walk the tree into a global queue
+//   k_wf_traverse  persistent warps drain the queue: every lane walks one ray and fetches the next one as soon as it
+//                  finishes (dynamic fetch), so the walk runs with full warps whatever fraction of rays got here
+//   k_wf_bounce    per path slot: shade the hit (Material::Process and the closures, pt_kernels.cuh shade), spawn the
+//                  next segment and run `front` on it
+//   k_wf_commit    per pixel: the ordered commit of the 4 samples (see pt_kernels.cuh header): exact replay of the
+//                  adaptive rule and of the fp32 accumulation order of material.h:74-77
+//
+// One step = begin + max_depth x (traverse, bounce) + commit over all pixels of a chunk; steps repeat until every
+// pixel has consumed its samples.
+#pragma once
+#include "pt_kernels.cuh"
+
+namespace ptd {
+
+// per-slot flag word (Tn.w): bits 0..15 depth, then:
+constexpr int WF_ALIVE = 1 << 16, WF_TRACED = 1 << 17, WF_LIVE = 1 << 18, WF_CONTRIB = 1 << 19;
+
+struct WfState {
+    float4 *oT;     // per slot: origin xyz, best hit distance t
+    float4 *dR;     // per slot: direction xyz, bits(record index of the best hit, -1 = none)
+    float4 *Tn;     // per slot: throughput rgb, bits(flags | depth)
+    float4 *cS;     // per slot: contribution rgb (T * Kd at the emitter), bits(segments traced)
+    int *queue;     // 2 x cap slot ids (ping-pong): rays that must walk the LBVH
+    int *counters;  // [0],[1] queue 0 count, head; [2],[3] queue 1 count, head; [4] pending pixels; [5] max remaining
+    float4 *acc1;   // per pixel: color_map rgb, bits(samples_count)
+    float4 *acc2;   // per pixel: color2_map rgb, bits(next uncommitted sample index)
+    int cap;        // path slots
+};
+
+__global__ void k_wf_init(WfState wf, int npx, int s_begin) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npx) return;
+    wf.acc1[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+    wf.acc2[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(s_begin));
+}
+
+// large triangles, root test, enqueue.  Must be reached by all 32 lanes of the warp (ballot); `active` lanes carry
+// a ray (o, d).  Writes oT / dR of the slot.
+template <bool COUNT>
+__device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large, const WfState &wf, int set, int slot,
+                                      bool active, V3 o, V3 d, float eps, unsigned long long &n_nodes,
+                                      unsigned long long &n_tris) {
+    bool need = false;
+    if (active) {
+        Hit h = no_hit();
+        if (sc.brute) {
+            h = nearest_hit<COUNT>(sc, s_large, o, d, eps, n_nodes, n_tris);
+        } else {
+            large_phase(s_large, sc.n_large, sc.n_bvh, o, d, eps, h);
+            if (COUNT) n_tris += sc.n_large;
+            need = reaches_root(sc, o, d, h.t);
+        }
+        wf.oT[slot] = make_float4(o.x, o.y, o.z, h.t);
+        wf.dR[slot] = make_float4(d.x, d.y, d.z, __int_as_float(h.rec));
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, need);
+    if (m) {
+        const int lane = threadIdx.x & 31, leader = __ffs(m) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&wf.counters[2 * set], __popc(m));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        if (need) wf.queue[(size_t)set * wf.cap + base + __popc(m & ((1u << lane) - 1u))] = slot;
+    }
+}
+
+template <bool COUNT>
+__global__ void __launch_bounds__(256)
+k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
+    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    if (!sc.brute) stage_large(sc, s_large);
+    if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2] = 0; wf.counters[3] = 0; }  // the other queue
+    __syncthreads();
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in_range = slot < 4 * npix;
+    unsigned long long n_nodes = 0, n_tris = 0;
+    bool traced = false;
+    V3 o = mk(0.0f, 0.0f, -20.0f), d = mk(0.0f, 0.0f, 1.0f);
+    if (in_range) {
+        const int p = pix0 + (slot >> 2), q = slot & 3;
+        const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+        const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
+        const int s = s_next + q * rp.s_step;
+        const bool live = s_next < rp.spp && s < rp.spp;
+        traced = live && !adaptive_skip(s, cnt, mk(a1.x, a1.y, a1.z), mk(a2.x, a2.y, a2.z), rp.error);
+        int flags = (live ? WF_LIVE : 0) | (traced ? WF_TRACED : 0);
+        if (traced) {
+            const int x = p % rp.W, y = p / rp.W;
+            d = primary_dir(x, y, rp.W, rp.H, (uint32_t)p, (uint32_t)s, rp.seed);
+            if (rp.max_depth > 0) flags |= WF_ALIVE;  // Ray::IsValid with depth 0, colour 1 (ray.h:52-54)
+        }
+        traced = (flags & WF_ALIVE) != 0;
+        wf.Tn[slot] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags));
+        wf.cS[slot] = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0));
+    }
+    front<COUNT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
+    if (COUNT && rp.stats) {
+        if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
+        if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+    }
+}
+
+// bounce `b` (0-based): shades segment b of every live path and starts segment b+1; writes queue (b+1)&1
+template <bool COUNT>
+__global__ void __launch_bounds__(256)
+k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
+    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    if (!sc.brute) stage_large(sc, s_large);
+    const int set = (b + 1) & 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2 * (b & 1)] = 0; wf.counters[2 * (b & 1) + 1] = 0; }
+    __syncthreads();
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long n_nodes = 0, n_tris = 0;
+    bool alive = false;
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
+    if (slot < 4 * npix) {
+        const float4 tn = wf.Tn[slot];
+        int flags = __float_as_int(tn.w);
+        if (flags & WF_ALIVE) {
+            const float4 ot = wf.oT[slot], dr = wf.dR[slot];
+            o = mk(ot.x, ot.y, ot.z);
+            d = mk(dr.x, dr.y, dr.z);
+            V3 T = mk(tn.x, tn.y, tn.z), c = mk(0, 0, 0);
+            int depth = flags & 0xffff;
+            Hit h;
+            h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
+            const int p = pix0 + (slot >> 2), q = slot & 3;
+            const int s = __float_as_int(wf.acc2[p].w) + q * rp.s_step;
+            bool contrib = false;
+            alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, &c, &contrib);
+            // Ray::IsValid before the next TraceRay (ray.h:52-54)
+            alive = alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f);
+            flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0);
+            wf.Tn[slot] = make_float4(T.x, T.y, T.z, __int_as_float(flags));
+            if (contrib) wf.cS[slot] = make_float4(c.x, c.y, c.z, __int_as_float(b + 1));
+            else if (!alive) wf.cS[slot].w = __int_as_float(b + 1);  // segments traced by this path
+        }
+    }
+    front<COUNT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
+    if (COUNT && rp.stats) {
+        if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
+        if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+    }
+}
+
+// persistent warps over queue `set`: one ray per lane, refilled as lanes finish
+template <bool COUNT>
+__global__ void __launch_bounds__(128)
+k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
+    const int count = wf.counters[2 * set];
+    if (count == 0) return;
+    int *head = &wf.counters[2 * set + 1];
+    const int *queue = wf.queue + (size_t)set * wf.cap;
+    const int lane = threadIdx.x & 31;
+    int stack[kStackDepth];
+    int sp = 0, cur = kRefEmpty, slot = -1;
+    bool done = false;
+    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 1);
+    Hit h = no_hit();
+    unsigned long long n_nodes = 0, n_tris = 0;
+    while (true) {
+        const bool need = !done && cur == kRefEmpty;
+        if (need && slot >= 0) {  // retire the finished ray
+            wf.oT[slot].w = h.t;
+            wf.dR[slot].w = __int_as_float(h.rec);
+            slot = -1;
+        }
+        const unsigned m = __ballot_sync(0xffffffffu, need);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            int base = 0;
+            if (lane == leader) base = atomicAdd(head, __popc(m));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (need) {
+                const int qi = base + __popc(m & ((1u << lane) - 1u));
+                if (qi < count) {
+                    slot = queue[qi];
+                    const float4 ot = wf.oT[slot], dr = wf.dR[slot];
+                    o = mk(ot.x, ot.y, ot.z);
+                    d = mk(dr.x, dr.y, dr.z);
+                    inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    h.t = ot.w;
+                    h.rec = __float_as_int(dr.w);
+                    h.idx = h.rec >= 0 ? __float_as_int(__ldg(sc.tris + 4 * (size_t)h.rec + 2).w) : -1;
+                    cur = sc.root;
+                    sp = 0;
+                } else {
+                    done = true;
+                }
+            }
+        }
+        if (__all_sync(0xffffffffu, done)) break;
+        // while-while (Aila & Laine 2009): walk inner nodes until this lane holds a leaf (or nothing), then do the
+        // leaves of all lanes together
+        while (cur >= 0 && cur != kRefEmpty)
+            cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
+        if (cur < 0) cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
+    }
+    if (COUNT && stats) {
+        for (int o2 = 16; o2; o2 >>= 1) {
+            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
+            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o2);
+        }
+        if (lane == 0) { atomicAdd(&stats[2], n_nodes); atomicAdd(&stats[3], n_tris); }
+    }
+}
+
+// ordered commit of the step's 4 samples of each pixel; `last` = count the pixels that still have samples left
+__global__ void __launch_bounds__(256)
+k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long seg_commit = 0, seg_traced = 0;
+    int remaining = 0;
+    if (i < npix) {
+        const int p = pix0 + i;
+        const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+        V3 sum = mk(a1.x, a1.y, a1.z), sum2 = mk(a2.x, a2.y, a2.z);
+        int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
+        bool stop = false;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int slot = 4 * i + j;
+            const int flags = __float_as_int(wf.Tn[slot].w);
+            const float4 c = wf.cS[slot];
+            const int nseg = __float_as_int(c.w);
+            if (flags & WF_TRACED) seg_traced += nseg;
+            if (stop || !(flags & WF_LIVE)) continue;
+            const bool skip_now = adaptive_skip(s_next, cnt, sum, sum2, rp.error);
+            if (!skip_now && !(flags & WF_TRACED)) { stop = true; continue; }  // needed after all: next step's first
+            if (!skip_now) {
+                if (flags & WF_CONTRIB) {  // material.h:74-77
+                    sum = mk(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+                    sum2 = mk(sum2.x + c.x * c.x, sum2.y + c.y * c.y, sum2.z + c.z * c.z);
+                    ++cnt;
+                }
+                seg_commit += nseg;
+            }
+            s_next += rp.s_step;
+        }
+        wf.acc1[p] = make_float4(sum.x, sum.y, sum.z, __int_as_float(cnt));
+        wf.acc2[p] = make_float4(sum2.x, sum2.y, sum2.z, __int_as_float(s_next));
+        if (s_next < rp.spp) remaining = (rp.spp - s_next + rp.s_step - 1) / rp.s_step;
+    }
+    for (int o2 = 16; o2; o2 >>= 1) {
+        seg_commit += __shfl_xor_sync(0xffffffffu, seg_commit, o2);
+        seg_traced += __shfl_xor_sync(0xffffffffu, seg_traced, o2);
+    }
+    if ((threadIdx.x & 31) == 0 && rp.stats) {
+        if (seg_commit) atomicAdd(&rp.stats[0], seg_commit);
+        if (seg_traced) atomicAdd(&rp.stats[1], seg_traced);
+    }
+    if (last) {
+        const unsigned m = __ballot_sync(0xffffffffu, remaining > 0);
+        int mx = remaining;
+        for (int o2 = 16; o2; o2 >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o2));
+        if ((threadIdx.x & 31) == 0 && m) {
+            atomicAdd(&wf.counters[4], __popc(m));
+            atomicMax(&wf.counters[5], mx);
+        }
+    }
+}
+
+__global__ void k_wf_finish(RenderParams rp, WfState wf, int npx) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= npx) return;
+    const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+    if (rp.sum3) { rp.sum3[3 * (size_t)p] = a1.x; rp.sum3[3 * (size_t)p + 1] = a1.y; rp.sum3[3 * (size_t)p + 2] = a1.z; }
+    if (rp.sum2_3) { rp.sum2_3[3 * (size_t)p] = a2.x; rp.sum2_3[3 * (size_t)p + 1] = a2.y; rp.sum2_3[3 * (size_t)p + 2] = a2.z; }
+    if (rp.count) rp.count[p] = __float_as_int(a1.w);
+}
+
+}  // namespace ptd

@@ -52,13 +52,15 @@ class PtError(RuntimeError):
 
 
 def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
-           sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0):
+           sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0,
+           mode=0):
     """PtConfig with the reference's defaults (config.h:10,16-29)."""
     c = PtConfig()
     c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
     c.eps, c.error, c.seed = eps, error, seed
     c.sample_begin, c.sample_step = sample_begin, sample_step
     c.intersector, c.accel, c.rr_depth, c.n_gpus, c.device = intersector, accel, rr_depth, n_gpus, device
+    c.reserved[0] = mode  # 0 = wavefront pipeline, 1 = megakernel variant
     return c
 
 

@@ -68,9 +68,9 @@ def test_nearest_hit_golden(lib, oracle, name, accel):
     assert_bits_equal(t, G[name + "_t"], name + " t")           # (tolerance allowed: T_REL_TOL)
 
 
-def run_case(lib, sc, name, accel):
+def run_case(lib, sc, name, accel, mode):
     W, H, spp, depth, seed, sb, ss = map(int, G[name + "_cfg"])
-    cfg = ptb200.config(W, H, spp, depth, 1e-4, float(G[name + "_error"]), seed, sb, ss, accel=accel)
+    cfg = ptb200.config(W, H, spp, depth, 1e-4, float(G[name + "_error"]), seed, sb, ss, accel=accel, mode=mode)
     ds = lib.scene_create(sc, cfg)
     import torch
     sm = torch.zeros(H, W, 3, device="cuda")
@@ -87,12 +87,13 @@ def run_case(lib, sc, name, accel):
     ds.close()
 
 
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
 @pytest.mark.parametrize("accel", [BRUTE, LBVH])
 @pytest.mark.parametrize("name", ["tor_flat", "tor_adapt", "tor_part", "cornell", "glossy", "torus40"])
-def test_render_golden(lib, name, accel):
+def test_render_golden(lib, name, accel, mode):
     sc = {"tor_flat": tor_scene, "tor_adapt": tor_scene, "tor_part": tor_scene, "cornell": scenes.cornell,
           "glossy": scenes.glossy_mix, "torus40": lambda: scenes.torus_room(40, 20)}[name]()
-    run_case(lib, sc, name, accel)
+    run_case(lib, sc, name, accel, mode)
 
 
 def test_render_vs_live_oracle_default_config_slice(lib, oracle, tor):
@@ -105,6 +106,9 @@ def test_render_vs_live_oracle_default_config_slice(lib, oracle, tor):
     assert_bits_equal(s2, os2)
     rgb = lib.render(tor, cfg)
     assert_bits_equal(rgb, oracle.resolve(osm, ocnt))
+    msm, ms2, mcnt = lib.render_accum(tor, ptb200.config(96, 96, 20, 8, 1e-4, 0.001, seed=1234, mode=1))
+    assert_bits_equal(mcnt, ocnt)
+    assert_bits_equal(msm, osm)
 
 
 def test_ragged_and_empty_inputs(lib, oracle):
