@@ -62,7 +62,7 @@ struct PtDeviceScene {
     float4 *tris = nullptr;
     float4 *nodes = nullptr;
     float4 *mats = nullptr;
-    float4 *lboxes = nullptr;
+    float4 *lrecs = nullptr;
     unsigned long long *stats = nullptr;  // 4 counters
     SceneView view{};
     bool counters = false;
@@ -119,7 +119,7 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     cudaFree(ds->tris);
     cudaFree(ds->nodes);
     cudaFree(ds->mats);
-    cudaFree(ds->lboxes);
+    cudaFree(ds->lrecs);
     cudaFree(ds->wf_mem);
     if (ds->h_counters) cudaFreeHost(ds->h_counters);
     cudaFree(ds->stats);
@@ -197,7 +197,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         DevBuf<unsigned char> tmp;
         DevBuf<float4> d_root;
         CK(d_root.alloc(2));
-        CK(cudaMalloc((void **)&ds->lboxes, 2 * (size_t)kMaxLarge * sizeof(float4)));
+        CK(cudaMalloc((void **)&ds->lrecs, (size_t)kLargeStride * kMaxLarge * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
         CK(vals.alloc(n)); CK(vals2.alloc(n));
         k_init_scratch<<<1, 1>>>(d_scr.p);
@@ -217,7 +217,10 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         v.brute = 0; v.n_bvh = nb; v.n_large = n_large;
         k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, vals2.p, n, ds->tris);
         ++launches;
-        if (n_large) { k_large_boxes<<<1, 64>>>(vals2.p, box_lo.p, box_hi.p, nb, n_large, ds->lboxes); ++launches; }
+        if (n_large) {
+            k_large_pack<<<1, 64>>>(vals2.p, d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb, n_large, eps, d_scr.p, ds->lrecs);
+            ++launches;
+        }
         if (nb == 0) {
             v.root = kRefEmpty;
         } else if (nb <= kLeafMax) {
@@ -253,7 +256,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     v.tris = ds->tris;
     v.nodes = ds->nodes;
     v.mats = ds->mats;
-    v.lboxes = ds->lboxes;
+    v.lrecs = ds->lrecs;
     ds->view = v;
     ds->launches = launches;
     guard.p = nullptr;

@@ -279,14 +279,44 @@ __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__res
     o[3] = make_float4(v[6], v[7], v[8], __int_as_float(mat_ids[i]));
 }
 
-// boxes of the large triangles (sorted positions [nb, nb + n_large)) and of the LBVH root
-__global__ void k_large_boxes(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
-                              const float4 *__restrict__ box_hi, int nb, int n_large, float4 *__restrict__ lboxes) {
+// Shared-memory image of the large triangles (sorted positions [nb, nb + n_large)): the 4 record rows followed by
+// three EDGE PLANES (m_i, w_i): m_i is the in-plane inward unit normal of edge i, and every point the reference's test
+// can accept satisfies m_i . P + w_i >= 0.  w_i already contains the dilation of that edge, eps'/(2 L_i) (the accepted
+// hexagon of the header comment is bounded by the three offset edge lines; a displacement along the triangle's normal
+// does not change m_i . P), plus 64 ulp of the largest coordinate for the fp32 evaluation.
+__global__ void k_large_pack(const int *__restrict__ vals, const float *__restrict__ verts,
+                             const float4 *__restrict__ planes, const float *__restrict__ squares,
+                             const int *__restrict__ mat_ids, int nb, int n_large, float eps, const BuildScratch *s,
+                             float4 *__restrict__ lrecs) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_large) return;
     const int i = vals[nb + k];
-    lboxes[2 * k] = box_lo[i];
-    lboxes[2 * k + 1] = box_hi[i];
+    const float *v = verts + 9 * (size_t)i;
+    const V3 p[3] = {mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8])};
+    const float S = squares[i];
+    float4 *o = lrecs + kLargeStride * (size_t)k;
+    o[0] = planes[i];
+    o[1] = make_float4(p[0].x, p[0].y, p[0].z, S);
+    o[2] = make_float4(p[1].x, p[1].y, p[1].z, __int_as_float(i));
+    o[3] = make_float4(p[2].x, p[2].y, p[2].z, __int_as_float(mat_ids[i]));
+    const float amax = fmaxf(20.0f, fmaxf(fmaxf(fmaxf(fabsf(ord2f(s->lo[0])), fabsf(ord2f(s->hi[0]))),
+                                                fmaxf(fabsf(ord2f(s->lo[1])), fabsf(ord2f(s->hi[1])))),
+                                          fmaxf(fabsf(ord2f(s->lo[2])), fabsf(ord2f(s->hi[2])))));
+    const float slack = amax * (64.0f * 1.1920929e-7f);
+    const float e = eps * 1.01f + 4e-6f * (S + eps);
+    const V3 ng = normalize3(cross3(p[1] - p[0], p[2] - p[0]));
+    const bool ok = S > 0.0f && S <= FLT_MAX && ng.x == ng.x;
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+        const V3 a = p[j], b = p[(j + 1) % 3], c = p[(j + 2) % 3];
+        const V3 ab = b - a;
+        const float L = length3(ab);
+        V3 m = normalize3(cross3(ng, ab));
+        if (dot3(m, c - a) < 0.0f) m = m * -1.0f;
+        const float w = -dot3(m, a) + 1.05f * e / (2.0f * L) + slack;
+        // degenerate triangle: a plane that accepts everything (the exact test decides)
+        o[4 + j] = (ok && L > 0.0f && m.x == m.x) ? make_float4(m.x, m.y, m.z, w) : make_float4(0.f, 0.f, 0.f, 1.0f);
+    }
 }
 __global__ void k_root_box(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
                            const float4 *__restrict__ box_hi, int nb, const float4 *__restrict__ node_lo,

@@ -20,6 +20,7 @@ namespace ptd {
 constexpr int kLeafMax = 4;          // triangles per LBVH leaf
 constexpr int kMaxLarge = 48;        // triangles kept out of the LBVH and tested from shared memory first
 constexpr int kAllLargeMax = 16;     // scenes up to this size keep every triangle in shared memory (no LBVH)
+constexpr int kLargeStride = 7;      // float4 per large triangle in shared memory: 4 record rows + 3 edge planes
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
 
@@ -41,7 +42,7 @@ struct SceneView {
     int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
     int root;     // child ref of the LBVH root (kRefEmpty if n_bvh == 0)
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)
-    const float4 *lboxes;    // 2 x float4 per large triangle: dilated box lo, hi (pt_bvh.cuh tri_bounds)
+    const float4 *lrecs;     // kLargeStride x float4 per large triangle: record rows + 3 edge planes (k_large_pack)
     float4 root_lo, root_hi; // box of the LBVH root
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
 };

@@ -68,43 +68,53 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     h.rec = rec;
 }
 
-// ---- large triangles: 6 float4 each in shared memory (the 4 record rows + dilated box lo, hi) ----------------
-constexpr int kLargeStride = 6;
-
-__device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large) {
-    for (int k = threadIdx.x; k < sc.n_large; k += blockDim.x) {
-        const float4 *r = sc.tris + 4 * (size_t)(sc.n_bvh + k);
-        float4 *o = s_large + kLargeStride * k;
-        o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
-        o[4] = sc.lboxes[2 * k];
-        o[5] = sc.lboxes[2 * k + 1];
-    }
+// MUFU.RCP: at most 1 ulp from 1/x (PTX ISA, rcp.approx.ftz.f32); denormal inputs flush to zero -> +-inf
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
 }
 
-// Scan + resolve.  The scan is the same short instruction sequence for every lane and every triangle: exact plane
-// distance, range test, hit point against the triangle's dilated box; survivors are only MARKED (one bit per
-// triangle).  The resolve loop then runs the expensive inside test on each lane's marked triangles in index order,
-// so lanes whose candidates sit at different indices execute it together.  The scan uses the best distance known
-// when it started (conservative); the resolve re-applies the exact range / tie rule with the live best.
+// ---- large triangles: kLargeStride float4 each in shared memory (4 record rows + 3 edge planes) -------------
+__device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large) {
+    for (int k = threadIdx.x; k < kLargeStride * sc.n_large; k += blockDim.x) s_large[k] = sc.lrecs[k];
+}
+
+// Scan + resolve.
+// The SCAN is one short, branch-free instruction sequence per triangle, the same for every lane: the plane
+// distance with an approximate reciprocal instead of the IEEE division, a range test and the three edge planes of
+// the triangle, all with tolerances that make it CONSERVATIVE — it may mark a triangle the exact test rejects, never
+// the reverse: numerator and denominator are the reference's own (bit-identical), so t' = num * rcp(sd) is within
+// 2^-21 relative of the reference's quotient; the hit point P' = o + d t' is then within |t'| 2^-20 + a few ulp of
+// the reference's, which is added to the edge planes' margin (k_large_pack).
+// The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles
+// in index order; lanes whose candidates sit at different indices execute it together.
 __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
                                             Hit &h) {
     unsigned long long mask = 0ull;
+    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
     for (int k = 0; k < n_large; ++k) {
         const float4 *r = s_large + kLargeStride * k;
-        const float nd = plane_distance(r[0], o, d);
-        // the hit point exactly as the inside test computes it; outside the dilated box => the test fails
-        const float Px = o.x + d.x * nd, Py = o.y + d.y * nd, Pz = o.z + d.z * nd;
-        const float4 lo = r[4], hi = r[5];
-        const bool cand = nd <= h.t && !(nd < eps) && Px >= lo.x && Px <= hi.x && Py >= lo.y && Py <= hi.y &&
-                          Pz >= lo.z && Pz <= hi.z;
-        mask |= (unsigned long long)cand << k;
+        const float4 p = r[0];
+        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
+        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+        const float t = num * rcp_approx(sd);
+        const float tol = fabsf(t) * 2e-6f;
+        const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
+        const float4 e0 = r[4], e1 = r[5], e2 = r[6];
+        const float g0 = __fmaf_rn(e0.x, Px, __fmaf_rn(e0.y, Py, __fmaf_rn(e0.z, Pz, e0.w)));
+        const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
+        const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
+        // written so that a NaN anywhere (sd == 0, infinities) marks the triangle: the resolve decides
+        const bool out = t > t_hi || t < t_lo || fminf(fminf(g0, g1), g2) < -tol;
+        mask |= (unsigned long long)(!out) << k;
     }
     while (mask) {
         const int k = __ffsll((long long)mask) - 1;
         mask &= mask - 1ull;
         const float4 *r = s_large + kLargeStride * k;
         const float nd = plane_distance(r[0], o, d);
-        if (!(nd <= h.t)) continue;
+        if (!(nd <= h.t) || nd < eps) continue;
         const float4 a = r[1], b = r[2], c = r[3];
         const int idx = __float_as_int(b.w);
         if (nd == h.t && !(idx < h.idx)) continue;
