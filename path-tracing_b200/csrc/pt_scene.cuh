@@ -18,7 +18,7 @@
 namespace ptd {
 
 constexpr int kLeafMax = 4;          // triangles per LBVH leaf
-constexpr int kMaxLarge = 48;        // triangles kept out of the LBVH and tested from shared memory first
+constexpr int kMaxLarge = 32;        // triangles kept out of the LBVH and tested from shared memory first
 constexpr int kAllLargeMax = 16;     // scenes up to this size keep every triangle in shared memory (no LBVH)
 constexpr int kLargeStride = 7;      // float4 per large triangle in shared memory: 4 record rows + 3 edge planes
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)

@@ -91,7 +91,7 @@ __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large
 // in index order; lanes whose candidates sit at different indices execute it together.
 __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
                                             Hit &h) {
-    unsigned long long mask = 0ull;
+    unsigned mask = 0u;  // kMaxLarge <= 32
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
     for (int k = 0; k < n_large; ++k) {
         const float4 *r = s_large + kLargeStride * k;
@@ -106,12 +106,12 @@ __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, 
         const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
         const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
         // written so that a NaN anywhere (sd == 0, infinities) marks the triangle: the resolve decides
-        const bool out = t > t_hi || t < t_lo || fminf(fminf(g0, g1), g2) < -tol;
-        mask |= (unsigned long long)(!out) << k;
+        const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
+        mask |= (out ? 0u : 1u) << k;
     }
     while (mask) {
-        const int k = __ffsll((long long)mask) - 1;
-        mask &= mask - 1ull;
+        const int k = __ffs(mask) - 1;
+        mask &= mask - 1u;
         const float4 *r = s_large + kLargeStride * k;
         const float nd = plane_distance(r[0], o, d);
         if (!(nd <= h.t) || nd < eps) continue;
