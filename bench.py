@@ -313,27 +313,66 @@ def main():
         cspp = max(world, min(spp, 8 * world))
         ccfg = ptb200.config(W, H, cspp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
                              accel=args.accel, mode=args.mode)
+        # two instrumented frames (same image, cspp samples): one with traversal counters, one with CUDA events around
+        # every launch (the counters' atomics would distort the timing)
         dsc = lib.scene_create(sc, ccfg, counters=True)
         dsc.render_device(ccfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
         torch.cuda.synchronize()
         cs = dsc.stats()
-        nodes_ray = cs["nodes_visited"] / max(1, cs["segments_traced"])
-        tris_ray = cs["tris_tested"] / max(1, cs["segments_traced"])
         dsc.close()
-        st = ds.stats()
-        k_ms = st["kernel_ms"]
-        rays_kernel = st["segments_traced"]
+        dst = lib.scene_create(sc, ccfg, timed=True)
+        for _ in range(2):  # the first frame also pays for the workspace allocation
+            dst.render_device(ccfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
+            torch.cuda.synchronize()
+        ts = dst.stats()
+        dst.close()
+        cs["class_ms"], cs["class_launches"] = ts["class_ms"], ts["class_launches"]
+        segs_c = max(1, cs["segments_traced"])
+        n_large = cs["n_large"]
+        nodes_ray = cs["nodes_visited"] / segs_c
+        tris_ray = cs["tris_tested"] / segs_c
+        leaf_tris_ray = max(0.0, tris_ray - n_large)
         bytes_ray = 64.0 * (nodes_ray + tris_ray)
         flops_ray = 54.0 * nodes_ray + 79.0 * tris_ray + 40.0
-        achieved = rays_kernel * bytes_ray / (k_ms * 1e-3) / 1e9
+        st = ds.stats()
+        k_ms, rays_kernel = st["kernel_ms"], st["segments_traced"]
         fp32_peak = 148 * 128 * 2 * sm_max * 1e6 / 1e12
-        roof = {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
-                "traffic": None, "peak_source": peak_src, "kernel": "k_render", "kernel_ms": k_ms,
+        pipeline_gbs = rays_kernel * bytes_ray / (k_ms * 1e-3) / 1e9
+        roof = {"bound": "hbm", "peak": hbm_peak, "unit": "GB/s", "peak_source": peak_src, "traffic": None,
                 "bytes_per_ray": bytes_ray, "nodes_per_ray": nodes_ray, "tris_per_ray": tris_ray,
-                "note": "algorithmic bytes are served by shared memory / L1 / L2, not HBM: frac > 1 is expected for scenes "
-                        "that fit on chip; see fp32 for the compute-side ceiling",
+                "rays_reaching_lbvh": cs["rays_queued"] / segs_c,
+                "pipeline": {"achieved": pipeline_gbs, "frac": pipeline_gbs / hbm_peak, "ms": k_ms,
+                             "what": "all kernels of one frame: rays x 64 B x (nodes visited + triangles tested)"},
+                "note": "algorithmic bytes (SURVEY 8d: 64 B per node visited / triangle tested, + path state for the "
+                        "wavefront kernels) are mostly served by shared memory and L2, so frac against the HBM peak can "
+                        "exceed 1; fp32 gives the compute-side ceiling",
                 "fp32": {"achieved_tflops": rays_kernel * flops_ray / (k_ms * 1e-3) / 1e12, "peak_tflops": fp32_peak,
                          "frac": rays_kernel * flops_ray / (k_ms * 1e-3) / 1e12 / fp32_peak, "flops_per_ray": flops_ray}}
+        if args.mode == 0 and sum(cs["class_launches"]) > 0:
+            # dominant kernel class of the wavefront pipeline, timed live with CUDA events around every launch of the
+            # instrumented frame (same image, cspp samples)
+            names = ["k_wf_begin", "k_wf_traverse", "k_wf_bounce", "k_wf_commit"]
+            paths_c = W * H * cspp // world
+            state = 96.0  # oT,dR,Tn read + written per live segment
+            per_class_bytes = [paths_c * (64.0 * n_large + 48.0),
+                               segs_c * 64.0 * (nodes_ray + leaf_tris_ray),
+                               (segs_c - paths_c) * 64.0 * n_large + segs_c * state,
+                               paths_c * 16.0 + (W * H // world) * 64.0]
+            k = max(range(4), key=lambda i: cs["class_ms"][i])
+            ach = per_class_bytes[k] / (cs["class_ms"][k] * 1e-3) / 1e9
+            roof.update({"kernel": names[k], "achieved": ach, "frac": ach / hbm_peak,
+                         "launch_ms": cs["class_ms"][k] / max(1, cs["class_launches"][k]),
+                         "launches_timed": cs["class_launches"][k],
+                         "bytes_per_launch": per_class_bytes[k] / max(1, cs["class_launches"][k]),
+                         "share_of_step": cs["class_ms"][k] / max(1e-9, sum(cs["class_ms"])),
+                         "class_ms": dict(zip(names, cs["class_ms"]))})
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+                roof["traffic"] = tr.get(args.workload, {}).get(names[k])
+            except Exception:
+                pass
+        else:
+            roof.update({"kernel": "k_render_mega", "achieved": pipeline_gbs, "frac": pipeline_gbs / hbm_peak})
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:

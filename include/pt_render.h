@@ -101,6 +101,14 @@ typedef struct PtStats {
     int32_t n_large;          /* triangles kept out of the BVH and tested from shared memory */
     int32_t accel;            /* PT_ACCEL_* actually used */
     int32_t launches;         /* kernels launched by the last call */
+    /* per kernel class of the wavefront pipeline, filled when the scene was created with flags bit 1 (timed mode:
+     * CUDA events around every launch): [0] k_wf_begin, [1] k_wf_traverse, [2] k_wf_bounce, [3] k_wf_commit */
+    float class_ms[4];
+    int32_t class_launches[4];
+    /* counters mode (flags bit 0): rays that had to walk the LBVH, and their distribution over
+     * floor(log2(1 + nodes visited)) */
+    uint64_t rays_queued;
+    uint64_t node_hist[16];
 } PtStats;
 
 typedef struct PtDeviceScene PtDeviceScene; /* opaque: device-resident SoA triangles, materials, LBVH */
@@ -117,7 +125,8 @@ int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb);
 int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count);
 
 /* ---- device-resident API (what bench.py / a multi-process host drives) ------------------------------- */
-/* Upload + SoA repack + LBVH build on the current device.  `flags` bit 0: keep traversal counters. */
+/* Upload + SoA repack + LBVH build on the current device.  `flags` bit 0: keep traversal counters; bit 1: time
+ * every kernel class with CUDA events (instrumented runs only: it serialises the launches). */
 int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_t flags, PtDeviceScene **out);
 void pt_scene_destroy(PtDeviceScene *ds);
 /* Render into DEVICE buffers (float sum3[H*W*3], float sum2_3[H*W*3], int32 count[H*W]; NULL allowed) on

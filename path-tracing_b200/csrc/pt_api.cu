@@ -63,9 +63,13 @@ struct PtDeviceScene {
     float4 *nodes = nullptr;
     float4 *mats = nullptr;
     float4 *lrecs = nullptr;
-    unsigned long long *stats = nullptr;  // 4 counters
+    unsigned long long *stats = nullptr;  // kStatWords counters
     SceneView view{};
     bool counters = false;
+    bool timed_classes = false;
+    float class_ms[4] = {0, 0, 0, 0};
+    int class_launches[4] = {0, 0, 0, 0};
+    std::vector<cudaEvent_t> class_events;  // pairs, recycled every step
     int n_nodes = 0;
     float build_ms = 0.f, upload_ms = 0.f, kernel_ms = 0.f;
     int launches = 0;
@@ -125,6 +129,7 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     cudaFree(ds->stats);
     if (ds->ev0) cudaEventDestroy(ds->ev0);
     if (ds->ev1) cudaEventDestroy(ds->ev1);
+    for (cudaEvent_t e : ds->class_events) cudaEventDestroy(e);
     delete ds;
 }
 
@@ -143,6 +148,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     ds->n_tri = n;
     ds->n_mat = m;
     ds->counters = (flags & 1) != 0;
+    ds->timed_classes = (flags & 2) != 0;
     CK(cudaEventCreate(&ds->ev0));
     CK(cudaEventCreate(&ds->ev1));
     cudaEvent_t e0, e1, e2;
@@ -175,8 +181,8 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     CK(cudaMalloc((void **)&ds->mats, (m ? 2 * (size_t)m : 1) * sizeof(float4)));
     if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, m, ds->mats); ++launches; }
     CK(cudaMalloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
-    CK(cudaMalloc((void **)&ds->stats, 4 * sizeof(unsigned long long)));
-    CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long)));
+    CK(cudaMalloc((void **)&ds->stats, kStatWords * sizeof(unsigned long long)));
+    CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
 
     const bool brute = want == PT_ACCEL_BRUTE || n == 0;
     SceneView v{};
@@ -321,6 +327,41 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     int n = 0;
     k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp.s_begin);
     ++n;
+    // timed mode: an event pair around every launch of a step, read back after the step
+    const bool timed = ds->timed_classes;
+    std::vector<int> ev_class;
+    size_t ev_used = 0;
+    for (int c = 0; c < 4; ++c) { ds->class_ms[c] = 0.f; ds->class_launches[c] = 0; }
+    auto tick = [&](int cls) -> int {
+        if (!timed) return PT_OK;
+        if (ev_used + 2 > ds->class_events.size()) {
+            cudaEvent_t a, b;
+            CK(cudaEventCreate(&a)); CK(cudaEventCreate(&b));
+            ds->class_events.push_back(a); ds->class_events.push_back(b);
+        }
+        CK(cudaEventRecord(ds->class_events[ev_used], st));
+        ev_class.push_back(cls);
+        return PT_OK;
+    };
+    auto tock = [&]() -> int {
+        if (!timed) return PT_OK;
+        CK(cudaEventRecord(ds->class_events[ev_used + 1], st));
+        ev_used += 2;
+        return PT_OK;
+    };
+    auto collect = [&]() -> int {
+        if (!timed) return PT_OK;
+        CK(cudaStreamSynchronize(st));
+        for (size_t i = 0; i < ev_class.size(); ++i) {
+            float ms = 0.f;
+            CK(cudaEventElapsedTime(&ms, ds->class_events[2 * i], ds->class_events[2 * i + 1]));
+            ds->class_ms[ev_class[i]] += ms;
+            ds->class_launches[ev_class[i]] += 1;
+        }
+        ev_class.clear();
+        ev_used = 0;
+        return PT_OK;
+    };
     CK(cudaMemsetAsync(wf.counters, 0, 8 * sizeof(int), st));
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
     for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
@@ -330,15 +371,26 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
         while (remaining > 0) {
             const int steps = (remaining + 3) / 4;
             for (int i = 0; i < steps; ++i) {
+                if ((rc = tick(0))) return rc;
                 k_wf_begin<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                if ((rc = tock())) return rc;
                 for (int b = 0; b < rp.max_depth; ++b) {
-                    if (!sc.brute && sc.root != kRefEmpty)
+                    if (!sc.brute && sc.root != kRefEmpty) {
+                        if ((rc = tick(1))) return rc;
                         k_wf_traverse<COUNT><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                        if ((rc = tock())) return rc;
+                        ++n;
+                    }
+                    if ((rc = tick(2))) return rc;
                     k_wf_bounce<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
-                    n += 2;
+                    if ((rc = tock())) return rc;
+                    ++n;
                 }
+                if ((rc = tick(3))) return rc;
                 k_wf_commit<<<blocks_for(npix, 256), 256, 0, st>>>(rp, wf, (int)pix0, npix, i == steps - 1);
+                if ((rc = tock())) return rc;
                 n += 2;
+                if ((rc = collect())) return rc;
             }
             // progress check: pixels whose adaptive rule deferred samples need more steps (never in a flat-spp run)
             CK(cudaMemcpyAsync(ds->h_counters, wf.counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -360,7 +412,7 @@ extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, fl
     int rc;
     if ((rc = validate_config(cfg))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
-    CK(cudaMemsetAsync(ds->stats, 0, 4 * sizeof(unsigned long long), st));
+    CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
     const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, ds->stats);
     CK(cudaEventRecord(ds->ev0, st));
     int launches = 1;
@@ -391,7 +443,7 @@ extern "C" int pt_resolve_device(const float *d_sum3, const int32_t *d_count, in
 extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
     if (!ds || !out) return fail(PT_EINVAL, "NULL argument");
     memset(out, 0, sizeof *out);
-    unsigned long long st[4] = {0, 0, 0, 0};
+    unsigned long long st[kStatWords] = {0};
     if (ds->timed) {
         CK(cudaEventSynchronize(ds->ev1));
         CK(cudaEventElapsedTime(&ds->kernel_ms, ds->ev0, ds->ev1));
@@ -401,6 +453,9 @@ extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
     out->kernel_ms = ds->kernel_ms; out->build_ms = ds->build_ms; out->upload_ms = ds->upload_ms;
     out->n_nodes = ds->n_nodes; out->n_large = ds->view.n_large; out->accel = ds->accel;
     out->launches = ds->launches;
+    out->rays_queued = st[4];
+    for (int c = 0; c < 16; ++c) out->node_hist[c] = st[5 + c];
+    for (int c = 0; c < 4; ++c) { out->class_ms[c] = ds->class_ms[c]; out->class_launches[c] = ds->class_launches[c]; }
     return PT_OK;
 }
 
@@ -413,7 +468,7 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
     DevBuf<int> d_ids;
     CK(d_rays.alloc(6 * (size_t)n)); CK(d_t.alloc(n)); CK(d_ids.alloc(n));
     CK(cudaMemcpy(d_rays.p, rays6, 6 * (size_t)n * sizeof(float), cudaMemcpyHostToDevice));
-    CK(cudaMemset(ds->stats, 0, 4 * sizeof(unsigned long long)));
+    CK(cudaMemset(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
     const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 32);
     CK(cudaEventRecord(ds->ev0));
     if (ds->counters) k_intersect<true><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);

@@ -22,6 +22,7 @@ constexpr int kMaxLarge = 32;        // triangles kept out of the LBVH and teste
 constexpr int kAllLargeMax = 16;     // scenes up to this size keep every triangle in shared memory (no LBVH)
 constexpr int kLargeStride = 7;      // float4 per large triangle in shared memory: 4 record rows + 3 edge planes
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
+constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
 
 // lobe kinds built by Factory (material.h:58-106)

@@ -17,6 +17,9 @@
 //   k_wf_commit    per pixel: the ordered commit of the 4 samples (see pt_kernels.cuh header): exact replay of the
 //                  adaptive rule and of the fp32 accumulation order of material.h:74-77
 //
+// Path state, queues and accumulators are streamed with evict-first loads/stores (ld.global.cs / st.global.cs) so
+// that they do not push the LBVH out of L2 between two traverse launches.
+//
 // One step = begin + max_depth x (traverse, bounce) + commit over all pixels of a chunk; steps repeat until every
 // pixel has consumed its samples.
 #pragma once
@@ -62,8 +65,8 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
             if (COUNT) n_tris += sc.n_large;
             need = reaches_root(sc, o, d, h.t);
         }
-        wf.oT[slot] = make_float4(o.x, o.y, o.z, h.t);
-        wf.dR[slot] = make_float4(d.x, d.y, d.z, __int_as_float(h.rec));
+        __stcs(&wf.oT[slot], make_float4(o.x, o.y, o.z, h.t));
+        __stcs(&wf.dR[slot], make_float4(d.x, d.y, d.z, __int_as_float(h.rec)));
     }
     const unsigned m = __ballot_sync(0xffffffffu, need);
     if (m) {
@@ -71,7 +74,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
         int base = 0;
         if (lane == leader) base = atomicAdd(&wf.counters[2 * set], __popc(m));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (need) wf.queue[(size_t)set * wf.cap + base + __popc(m & ((1u << lane) - 1u))] = slot;
+        if (need) __stcs(&wf.queue[(size_t)set * wf.cap + base + __popc(m & ((1u << lane) - 1u))], slot);
     }
 }
 
@@ -89,7 +92,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     V3 o = mk(0.0f, 0.0f, -20.0f), d = mk(0.0f, 0.0f, 1.0f);
     if (in_range) {
         const int p = pix0 + (slot >> 2), q = slot & 3;
-        const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+        const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
         const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
         const int s = s_next + q * rp.s_step;
         const bool live = s_next < rp.spp && s < rp.spp;
@@ -101,13 +104,19 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
             if (rp.max_depth > 0) flags |= WF_ALIVE;  // Ray::IsValid with depth 0, colour 1 (ray.h:52-54)
         }
         traced = (flags & WF_ALIVE) != 0;
-        wf.Tn[slot] = make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags));
-        wf.cS[slot] = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0));
+        __stcs(&wf.Tn[slot], make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags)));
+        __stcs(&wf.cS[slot], make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0)));
     }
     front<COUNT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
-    if (COUNT && rp.stats) {
-        if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
-        if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+    if (COUNT && rp.stats) {  // one atomic per warp per counter
+        for (int o2 = 16; o2; o2 >>= 1) {
+            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
+            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o2);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
+            if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+        }
     }
 }
 
@@ -125,10 +134,10 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
     bool alive = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
     if (slot < 4 * npix) {
-        const float4 tn = wf.Tn[slot];
+        const float4 tn = __ldcs(&wf.Tn[slot]);
         int flags = __float_as_int(tn.w);
         if (flags & WF_ALIVE) {
-            const float4 ot = wf.oT[slot], dr = wf.dR[slot];
+            const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
             o = mk(ot.x, ot.y, ot.z);
             d = mk(dr.x, dr.y, dr.z);
             V3 T = mk(tn.x, tn.y, tn.z), c = mk(0, 0, 0);
@@ -136,23 +145,31 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
             Hit h;
             h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
             const int p = pix0 + (slot >> 2), q = slot & 3;
-            const int s = __float_as_int(wf.acc2[p].w) + q * rp.s_step;
+            const int s = __float_as_int(__ldcs(&wf.acc2[p].w)) + q * rp.s_step;
             bool contrib = false;
             alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, &c, &contrib);
             // Ray::IsValid before the next TraceRay (ray.h:52-54)
             alive = alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f);
             flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0);
-            wf.Tn[slot] = make_float4(T.x, T.y, T.z, __int_as_float(flags));
-            if (contrib) wf.cS[slot] = make_float4(c.x, c.y, c.z, __int_as_float(b + 1));
-            else if (!alive) wf.cS[slot].w = __int_as_float(b + 1);  // segments traced by this path
+            __stcs(&wf.Tn[slot], make_float4(T.x, T.y, T.z, __int_as_float(flags)));
+            if (contrib) __stcs(&wf.cS[slot], make_float4(c.x, c.y, c.z, __int_as_float(b + 1)));
+            else if (!alive) __stcs(&wf.cS[slot].w, __int_as_float(b + 1));  // segments traced by this path
         }
     }
     front<COUNT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
-    if (COUNT && rp.stats) {
-        if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
-        if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+    if (COUNT && rp.stats) {  // one atomic per warp per counter
+        for (int o2 = 16; o2; o2 >>= 1) {
+            n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
+            n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o2);
+        }
+        if ((threadIdx.x & 31) == 0) {
+            if (n_nodes) atomicAdd(&rp.stats[2], n_nodes);
+            if (n_tris) atomicAdd(&rp.stats[3], n_tris);
+        }
     }
 }
+
+constexpr int kNodeBurst = 4;  // inner-node steps between two refill checks
 
 // persistent warps over queue `set`: one ray per lane, refilled as lanes finish
 template <bool COUNT>
@@ -168,12 +185,16 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     bool done = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 1);
     Hit h = no_hit();
-    unsigned long long n_nodes = 0, n_tris = 0;
+    unsigned long long n_nodes = 0, n_tris = 0, ray_nodes0 = 0;
     while (true) {
         const bool need = !done && cur == kRefEmpty;
         if (need && slot >= 0) {  // retire the finished ray
-            wf.oT[slot].w = h.t;
-            wf.dR[slot].w = __int_as_float(h.rec);
+            if (COUNT && stats) {
+                atomicAdd(&stats[4], 1ull);
+                atomicAdd(&stats[5 + min(15, 31 - __clz((int)(n_nodes - ray_nodes0) + 1))], 1ull);
+            }
+            __stcs(&wf.oT[slot].w, h.t);
+            __stcs(&wf.dR[slot].w, __int_as_float(h.rec));
             slot = -1;
         }
         const unsigned m = __ballot_sync(0xffffffffu, need);
@@ -185,8 +206,8 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             if (need) {
                 const int qi = base + __popc(m & ((1u << lane) - 1u));
                 if (qi < count) {
-                    slot = queue[qi];
-                    const float4 ot = wf.oT[slot], dr = wf.dR[slot];
+                    slot = __ldcs(&queue[qi]);
+                    const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
                     o = mk(ot.x, ot.y, ot.z);
                     d = mk(dr.x, dr.y, dr.z);
                     inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
@@ -195,6 +216,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
                     h.idx = h.rec >= 0 ? __float_as_int(__ldg(sc.tris + 4 * (size_t)h.rec + 2).w) : -1;
                     cur = sc.root;
                     sp = 0;
+                    ray_nodes0 = n_nodes;
                 } else {
                     done = true;
                 }
@@ -203,7 +225,9 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         if (__all_sync(0xffffffffu, done)) break;
         // while-while (Aila & Laine 2009): walk inner nodes until this lane holds a leaf (or nothing), then do the
         // leaves of all lanes together
-        while (cur >= 0 && cur != kRefEmpty)
+        // (bounded, so that a lane that ran out of work is refilled after a few node steps of its neighbours)
+#pragma unroll 1
+        for (int it = 0; it < kNodeBurst && cur >= 0 && cur != kRefEmpty; ++it)
             cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
         if (cur < 0) cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
     }
@@ -224,15 +248,15 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
     int remaining = 0;
     if (i < npix) {
         const int p = pix0 + i;
-        const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+        const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
         V3 sum = mk(a1.x, a1.y, a1.z), sum2 = mk(a2.x, a2.y, a2.z);
         int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
         bool stop = false;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int slot = 4 * i + j;
-            const int flags = __float_as_int(wf.Tn[slot].w);
-            const float4 c = wf.cS[slot];
+            const int flags = __float_as_int(__ldcs(&wf.Tn[slot].w));
+            const float4 c = __ldcs(&wf.cS[slot]);
             const int nseg = __float_as_int(c.w);
             if (flags & WF_TRACED) seg_traced += nseg;
             if (stop || !(flags & WF_LIVE)) continue;
@@ -248,8 +272,8 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
             }
             s_next += rp.s_step;
         }
-        wf.acc1[p] = make_float4(sum.x, sum.y, sum.z, __int_as_float(cnt));
-        wf.acc2[p] = make_float4(sum2.x, sum2.y, sum2.z, __int_as_float(s_next));
+        __stcs(&wf.acc1[p], make_float4(sum.x, sum.y, sum.z, __int_as_float(cnt)));
+        __stcs(&wf.acc2[p], make_float4(sum2.x, sum2.y, sum2.z, __int_as_float(s_next)));
         if (s_next < rp.spp) remaining = (rp.spp - s_next + rp.s_step - 1) / rp.s_step;
     }
     for (int o2 = 16; o2; o2 >>= 1) {
@@ -274,7 +298,7 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
 __global__ void k_wf_finish(RenderParams rp, WfState wf, int npx) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npx) return;
-    const float4 a1 = wf.acc1[p], a2 = wf.acc2[p];
+    const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
     if (rp.sum3) { rp.sum3[3 * (size_t)p] = a1.x; rp.sum3[3 * (size_t)p + 1] = a1.y; rp.sum3[3 * (size_t)p + 2] = a1.z; }
     if (rp.sum2_3) { rp.sum2_3[3 * (size_t)p] = a2.x; rp.sum2_3[3 * (size_t)p + 1] = a2.y; rp.sum2_3[3 * (size_t)p + 2] = a2.z; }
     if (rp.count) rp.count[p] = __float_as_int(a1.w);

@@ -42,7 +42,8 @@ class PtStats(C.Structure):
     _fields_ = [("segments", C.c_uint64), ("segments_traced", C.c_uint64), ("nodes_visited", C.c_uint64),
                 ("tris_tested", C.c_uint64), ("kernel_ms", C.c_float), ("build_ms", C.c_float),
                 ("upload_ms", C.c_float), ("n_nodes", C.c_int32), ("n_large", C.c_int32), ("accel", C.c_int32),
-                ("launches", C.c_int32)]
+                ("launches", C.c_int32), ("class_ms", C.c_float * 4), ("class_launches", C.c_int32 * 4),
+                ("rays_queued", C.c_uint64), ("node_hist", C.c_uint64 * 16)]
 
 
 class PtError(RuntimeError):
@@ -182,18 +183,19 @@ class Library:
         return rays
 
     # ---- device-resident API ----
-    def scene_create(self, sc, cfg, counters=False):
-        return DeviceScene(self, sc, cfg, counters)
+    def scene_create(self, sc, cfg, counters=False, timed=False):
+        return DeviceScene(self, sc, cfg, counters, timed)
 
 
 class DeviceScene:
     """Handle on a device-resident scene (SoA triangles + LBVH)."""
 
-    def __init__(self, lib, sc, cfg, counters=False):
+    def __init__(self, lib, sc, cfg, counters=False, timed=False):
         self.L = lib
         self.h = C.c_void_p()
         s = Library.scene_struct(sc)
-        lib.check(lib.lib.pt_scene_create(C.byref(s), C.byref(cfg), 1 if counters else 0, C.byref(self.h)))
+        lib.check(lib.lib.pt_scene_create(C.byref(s), C.byref(cfg), (1 if counters else 0) | (2 if timed else 0),
+                                          C.byref(self.h)))
 
     def render_device(self, cfg, d_sum3=0, d_sum2=0, d_count=0, stream=0):
         """Device pointers (ints, e.g. torch.Tensor.data_ptr()); asynchronous on `stream`."""
@@ -216,7 +218,11 @@ class DeviceScene:
     def stats(self):
         st = PtStats()
         self.L.check(self.L.lib.pt_scene_stats(self.h, C.byref(st)))
-        return {k: getattr(st, k) for k, _ in PtStats._fields_}
+        out = {k: getattr(st, k) for k, _ in PtStats._fields_}
+        out["class_ms"] = list(st.class_ms)
+        out["class_launches"] = list(st.class_launches)
+        out["node_hist"] = list(st.node_hist)
+        return out
 
     def close(self):
         if self.h:
