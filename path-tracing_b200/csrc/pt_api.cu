@@ -250,6 +250,11 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             CK(cudaMemcpy(rb, d_root.p, sizeof rb, cudaMemcpyDeviceToHost));
             v.root_lo = rb[0];
             v.root_hi = rb[1];
+            if (v.root == 0) {
+                float4 rn[3];
+                CK(cudaMemcpy(rn, ds->nodes, sizeof rn, cudaMemcpyDeviceToHost));
+                v.root_n0 = rn[0]; v.root_n1 = rn[1]; v.root_n2 = rn[2];
+            }
         }
         ds->accel = PT_ACCEL_LBVH;
         CK(cudaDeviceSynchronize());  // scratch buffers are freed on scope exit

@@ -18,8 +18,8 @@
 namespace ptd {
 
 constexpr int kLeafMax = 4;          // triangles per LBVH leaf
-constexpr int kMaxLarge = 32;        // triangles kept out of the LBVH and tested from shared memory first
-constexpr int kAllLargeMax = 16;     // scenes up to this size keep every triangle in shared memory (no LBVH)
+constexpr int kMaxLarge = 64;        // triangles kept out of the LBVH and tested from shared memory first
+constexpr int kAllLargeMax = 48;     // scenes up to this size keep every triangle in shared memory (no LBVH)
 constexpr int kLargeStride = 7;      // float4 per large triangle in shared memory: 4 record rows + 3 edge planes
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
 constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray
@@ -45,6 +45,7 @@ struct SceneView {
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)
     const float4 *lrecs;     // kLargeStride x float4 per large triangle: record rows + 3 edge planes (k_large_pack)
     float4 root_lo, root_hi; // box of the LBVH root
+    float4 root_n0, root_n1, root_n2;  // the root node's two child boxes (node layout rows 0..2) when root == 0
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
 };
 

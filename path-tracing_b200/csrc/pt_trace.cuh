@@ -89,12 +89,12 @@ __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large
 // the reference's, which is added to the edge planes' margin (k_large_pack).
 // The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles
 // in index order; lanes whose candidates sit at different indices execute it together.
-__device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
-                                            Hit &h) {
-    unsigned mask = 0u;  // kMaxLarge <= 32
-    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
-    for (int k = 0; k < n_large; ++k) {
-        const float4 *r = s_large + kLargeStride * k;
+// one 32-triangle chunk of the scan: returns the candidate mask of triangles [k0, k0 + n)
+__device__ __forceinline__ unsigned large_scan32(const float4 *s_large, int k0, int n, V3 o, V3 d, float t_lo,
+                                                 float t_hi) {
+    unsigned mask = 0u;
+    for (int k = 0; k < n; ++k) {
+        const float4 *r = s_large + kLargeStride * (k0 + k);
         const float4 p = r[0];
         const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
         const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
@@ -109,8 +109,13 @@ __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, 
         const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
         mask |= (out ? 0u : 1u) << k;
     }
+    return mask;
+}
+
+__device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, unsigned mask, int rec_base, V3 o, V3 d,
+                                                float eps, Hit &h) {
     while (mask) {
-        const int k = __ffs(mask) - 1;
+        const int k = k0 + __ffs(mask) - 1;
         mask &= mask - 1u;
         const float4 *r = s_large + kLargeStride * k;
         const float nd = plane_distance(r[0], o, d);
@@ -123,6 +128,15 @@ __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, 
         h.idx = idx;
         h.rec = rec_base + k;
     }
+}
+
+__device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
+                                            Hit &h) {
+    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
+    const unsigned m0 = large_scan32(s_large, 0, min(n_large, 32), o, d, t_lo, t_hi);
+    const unsigned m1 = n_large > 32 ? large_scan32(s_large, 32, n_large - 32, o, d, t_lo, t_hi) : 0u;
+    large_resolve32(s_large, 0, m0, rec_base, o, d, eps, h);
+    if (m1) large_resolve32(s_large, 32, m1, rec_base, o, d, eps, h);
 }
 
 // Slab test of one child box: entry distance, or +inf when the ray [0, tmax] misses the box.  fminf/fmaxf drop a
@@ -139,11 +153,17 @@ __device__ __forceinline__ float box_entry(float lox, float hix, float loy, floa
     return tn <= tf * 1.0000003f ? tn : __int_as_float(0x7f800000);
 }
 
+// Does the ray [0, tmax] have to walk the tree?  Tested against the root's two child boxes (tighter than the root
+// box: on the 1M-triangle scene half of the rays that enter the root box leave it without entering a child).
 __device__ __forceinline__ bool reaches_root(const SceneView &sc, V3 o, V3 d, float tmax) {
     if (sc.root == kRefEmpty) return false;
+    const float inf = __int_as_float(0x7f800000);
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    return box_entry(sc.root_lo.x, sc.root_hi.x, sc.root_lo.y, sc.root_hi.y, sc.root_lo.z, sc.root_hi.z, o, inv, tmax) <
-           __int_as_float(0x7f800000);
+    if (sc.root < 0)  // the whole tree is one leaf
+        return box_entry(sc.root_lo.x, sc.root_hi.x, sc.root_lo.y, sc.root_hi.y, sc.root_lo.z, sc.root_hi.z, o, inv, tmax) < inf;
+    const float4 n0 = sc.root_n0, n1 = sc.root_n1, n2 = sc.root_n2;
+    return box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, tmax) < inf ||
+           box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, tmax) < inf;
 }
 
 // One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
