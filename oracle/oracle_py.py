@@ -16,7 +16,8 @@ _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 
 class OrScene(C.Structure):
     _fields_ = [("n_tri", C.c_int), ("verts9", C.c_void_p), ("planes4", C.c_void_p), ("squares", C.c_void_p),
-                ("mat_ids", C.c_void_p), ("n_mat", C.c_int), ("mats10", C.c_void_p)]
+                ("mat_ids", C.c_void_p), ("n_mat", C.c_int), ("mats10", C.c_void_p),
+                ("sky_w", C.c_int), ("sky_h", C.c_int), ("sky_bgr", C.c_void_p)]
 
 
 class OrConfig(C.Structure):
@@ -56,6 +57,10 @@ class Oracle:
         s = OrScene(int(keep["verts"].shape[0]), keep["verts"].ctypes.data, keep["planes"].ctypes.data,
                     keep["squares"].ctypes.data, keep["mat_ids"].ctypes.data, int(keep["mats"].shape[0]),
                     keep["mats"].ctypes.data)
+        if sc.get("sky") is not None:  # (H, W, 3) uint8, blue green red, rows top-down
+            keep["sky"] = np.ascontiguousarray(sc["sky"], np.uint8)
+            s.sky_h, s.sky_w = keep["sky"].shape[:2]
+            s.sky_bgr = keep["sky"].ctypes.data
         s._keep = keep
         return s
 

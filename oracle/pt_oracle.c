@@ -33,6 +33,8 @@ typedef struct {
     const int *mat_ids;
     int n_mat;
     const float *mats10; /* Ke[3] Kd[3] Ks[3] Ns  (MaterialCharacteristics, material.h:22-28) */
+    int sky_w, sky_h;             /* Scene::skybox_ (scene.cpp:20-22): 0 x 0 = Config::skybox empty */
+    const unsigned char *sky_bgr; /* rows top-down, blue green red, as bitmap_image holds them */
 } or_scene;
 
 typedef struct {
@@ -204,7 +206,33 @@ typedef struct {
 static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r, or_rng *g, or_pixel *px) {
     float dist;
     const int hit = nearest_hit(sc, r->o, r->d, cfg->eps, &dist);
-    if (hit < 0) { r->depth = cfg->max_depth; return; }
+    if (hit < 0) { /* scene.cpp:125-156 */
+        if (sc->sky_bgr && sc->sky_w > 0 && sc->sky_h > 0) {
+            const float theta = acosf(r->d[1]) / PT_PI;
+            const float phi = atan2f(r->d[2], -r->d[0]) / PT_PI / 2 + 0.5f;
+            const float x = phi * sc->sky_w, y = theta * sc->sky_h;
+            unsigned x1 = (unsigned)x, y1 = (unsigned)y;
+            if (x1 > (unsigned)sc->sky_w - 1u) x1 = (unsigned)sc->sky_w - 1u; /* the reference reads out of bounds here */
+            if (y1 > (unsigned)sc->sky_h - 1u) y1 = (unsigned)sc->sky_h - 1u;
+            const unsigned x2 = (x1 + 1u) % (unsigned)sc->sky_w, y2 = (y1 + 1u) % (unsigned)sc->sky_h;
+            const unsigned char *t11 = sc->sky_bgr + ((size_t)y1 * sc->sky_w + x1) * 3;
+            const unsigned char *t21 = sc->sky_bgr + ((size_t)y1 * sc->sky_w + x2) * 3;
+            const unsigned char *t12 = sc->sky_bgr + ((size_t)y2 * sc->sky_w + x1) * 3;
+            const unsigned char *t22 = sc->sky_bgr + ((size_t)y2 * sc->sky_w + x2) * 3;
+            const float wx = 1 - x + x1, wy = 1 - y + y1;
+            for (int k = 0; k < 3; ++k) { /* k = r,g,b; stored b,g,r */
+                const float c1 = t11[2 - k], c2 = t21[2 - k], c3 = t12[2 - k], c4 = t22[2 - k];
+                const float c12 = c1 * (1.0f - wx) + c2 * wx;
+                const float c34 = c3 * (1.0f - wx) + c4 * wx;
+                const float c = (c12 * (1.0f - wy) + c34 * wy) / 256.f;
+                px->sum[k] += c; /* not multiplied by the throughput, scene.cpp:151 */
+                px->sum2[k] += c * c;
+            }
+            px->count++;
+        }
+        r->depth = cfg->max_depth;
+        return;
+    }
     const float P[3] = {r->o[0] + r->d[0] * dist, r->o[1] + r->d[1] * dist, r->o[2] + r->d[2] * dist};
     const float *N = sc->planes4 + 4 * (size_t)hit;
     const float *m = sc->mats10 + 10 * (size_t)sc->mat_ids[hit];

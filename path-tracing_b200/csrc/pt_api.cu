@@ -63,6 +63,7 @@ struct PtDeviceScene {
     float4 *nodes = nullptr;
     float4 *mats = nullptr;
     float4 *lrecs = nullptr;
+    unsigned char *sky = nullptr;
     unsigned long long *stats = nullptr;  // kStatWords counters
     SceneView view{};
     bool counters = false;
@@ -124,6 +125,7 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     cudaFree(ds->nodes);
     cudaFree(ds->mats);
     cudaFree(ds->lrecs);
+    cudaFree(ds->sky);
     cudaFree(ds->wf_mem);
     if (ds->h_counters) cudaFreeHost(ds->h_counters);
     cudaFree(ds->stats);
@@ -268,6 +270,12 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     v.nodes = ds->nodes;
     v.mats = ds->mats;
     v.lrecs = ds->lrecs;
+    if (scene->sky_bgr && scene->sky_width > 0 && scene->sky_height > 0) {
+        const size_t sb = (size_t)scene->sky_width * scene->sky_height * 3;
+        CK(cudaMalloc((void **)&ds->sky, sb));
+        CK(cudaMemcpy(ds->sky, scene->sky_bgr, sb, cudaMemcpyHostToDevice));
+        v.sky = ds->sky; v.sky_w = scene->sky_width; v.sky_h = scene->sky_height;
+    }
     ds->view = v;
     ds->launches = launches;
     guard.p = nullptr;

@@ -40,13 +40,46 @@ __device__ __forceinline__ bool adaptive_skip(int s, int n, V3 sum, V3 sum2, flo
     return Dx < error && Dy < error && Dz < error;
 }
 
+// Equirectangular skybox lookup of scene.cpp:126-149, quirks included: `pi` is the float 3.141593, the lerp weights
+// are (1 - frac) on the SECOND texel (i.e. inverted), the result is divided by 256.  Deviations: y1 == height (only
+// for direction.y == -1, where the reference reads past the image) is clamped; acosf / atan2f are CUDA's, which can
+// differ from glibc's in the last ulp (tests allow 1e-5 relative on skybox radiance).
+__device__ __forceinline__ V3 sky_color(const SceneView &sc, V3 d) {
+    const float theta = acosf(d.y) / kPi;
+    const float phi = atan2f(d.z, -d.x) / kPi / 2 + 0.5f;
+    const float x = phi * (float)sc.sky_w, y = theta * (float)sc.sky_h;
+    unsigned x1 = (unsigned)x, y1 = (unsigned)y;
+    x1 = min(x1, (unsigned)sc.sky_w - 1u);
+    y1 = min(y1, (unsigned)sc.sky_h - 1u);
+    const unsigned x2 = (x1 + 1u) % (unsigned)sc.sky_w, y2 = (y1 + 1u) % (unsigned)sc.sky_h;
+    auto texel = [&](unsigned px, unsigned py) {
+        const unsigned char *t = sc.sky + ((size_t)py * sc.sky_w + px) * 3;
+        return mk((float)t[2], (float)t[1], (float)t[0]);  // stored blue, green, red
+    };
+    auto mix = [](V3 a, V3 b, float w) {  // glm::mix = x * (1 - a) + y * a
+        const float u = 1.0f - w;
+        return mk(a.x * u + b.x * w, a.y * u + b.y * w, a.z * u + b.z * w);
+    };
+    const float wx = 1 - x + (float)x1, wy = 1 - y + (float)y1;
+    const V3 c12 = mix(texel(x1, y1), texel(x2, y1), wx);
+    const V3 c34 = mix(texel(x1, y2), texel(x2, y2), wx);
+    const V3 c = mix(c12, c34, wy);
+    return mk(c.x / 256.f, c.y / 256.f, c.z / 256.f);
+}
+
 // One bounce of Scene::TraceRay after the nearest hit is known (scene.cpp:121-156): material dispatch
 // (Material::Process, material.h:36-50) and the closures Factory builds (material.h:58-106).
 // Returns false when the path ends here; *contrib is set when it ends on an emitter's front side with c = T * Kd.
 __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large, const RenderParams &rp, const Hit &h,
                                       uint32_t pixel, uint32_t sample, V3 &o, V3 &d, V3 &T, int &depth, V3 *c,
                                       bool *contrib) {
-    if (h.rec < 0) return false;  // miss: Ray::MakeInvalid (scene.cpp:155)
+    if (h.rec < 0) {  // miss: optional skybox, then Ray::MakeInvalid (scene.cpp:125-156)
+        if (sc.sky) {
+            *c = sky_color(sc, d);  // accumulated as is: the reference does not multiply by the throughput (scene.cpp:151)
+            *contrib = true;
+        }
+        return false;
+    }
     const bool in_smem = !sc.brute && h.rec >= sc.n_bvh;
     const float4 *r = in_smem ? s_large + kLargeStride * (h.rec - sc.n_bvh) : sc.tris + 4 * (size_t)h.rec;
     const float4 pl = r[0];

@@ -46,6 +46,8 @@ struct SceneView {
     const float4 *lrecs;     // kLargeStride x float4 per large triangle: record rows + 3 edge planes (k_large_pack)
     float4 root_lo, root_hi; // box of the LBVH root
     float4 root_n0, root_n1, root_n2;  // the root node's two child boxes (node layout rows 0..2) when root == 0
+    const unsigned char *sky;  // equirect skybox, 24-bit BGR rows top-down (bitmap_image's layout); nullptr = none
+    int sky_w, sky_h;
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
 };
 

@@ -120,6 +120,10 @@ class Library:
         s.material_ids = keep["mat_ids"].ctypes.data
         s.n_materials = keep["mats"].shape[0]
         s.materials = keep["mats"].ctypes.data
+        if sc.get("sky") is not None:  # (H, W, 3) uint8, blue green red, rows top-down (bitmap_image's layout)
+            keep["sky"] = np.ascontiguousarray(sc["sky"], np.uint8)
+            s.sky_height, s.sky_width = keep["sky"].shape[:2]
+            s.sky_bgr = keep["sky"].ctypes.data
         s._keep = keep
         return s
 

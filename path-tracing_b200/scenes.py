@@ -136,6 +136,41 @@ def glossy_mix():
     return _scene(tris, ids, mats)
 
 
+def open_scene():
+    """Skybox test scene (scene.cpp:125-156): the Cornell room without ceiling, back wall and light, so that most
+    paths leave it; plus the two boxes.  No emitter: all radiance comes from the sky lookup."""
+    c = cornell()
+    keep = [i for i in range(34) if i not in (6, 7, 10, 11, 12, 13)]  # drop +y wall, +z wall, light
+    return {"verts": c["verts"][keep], "planes": None, "squares": None, "mat_ids": c["mat_ids"][keep], "mats": c["mats"]}
+
+
+def sky_image(width=64, height=32, seed=7):
+    """Synthetic equirect skybox: smooth gradients plus noise, uint8 (H, W, 3) in blue-green-red order."""
+    rng = np.random.default_rng(seed)
+    y, x = np.meshgrid(np.linspace(0, 1, height), np.linspace(0, 1, width), indexing="ij")
+    img = np.stack([200 * (1 - y) + 30, 120 + 100 * np.sin(6.283 * x), 80 + 150 * y], -1)
+    return np.clip(img + rng.integers(-20, 20, img.shape), 0, 255).astype(np.uint8)
+
+
+def write_bmp(path, bgr):
+    """24-bit bottom-up BMP of a (H, W, 3) blue-green-red image (for the reference's bitmap_image loader)."""
+    h, w = bgr.shape[:2]
+    stride = (w * 3 + 3) & ~3
+    rows = np.zeros((h, stride), np.uint8)
+    rows[:, :w * 3] = bgr[::-1].reshape(h, w * 3)
+    hdr = bytearray(54)
+    hdr[0:2] = b"BM"
+    hdr[2:6] = (54 + stride * h).to_bytes(4, "little")
+    hdr[10:14] = (54).to_bytes(4, "little")
+    hdr[14:18] = (40).to_bytes(4, "little")
+    hdr[18:22] = w.to_bytes(4, "little")
+    hdr[22:26] = h.to_bytes(4, "little")
+    hdr[26:28] = (1).to_bytes(2, "little")
+    hdr[28:30] = (24).to_bytes(2, "little")
+    hdr[34:38] = (stride * h).to_bytes(4, "little")
+    open(path, "wb").write(bytes(hdr) + rows.tobytes())
+
+
 def random_rays(n, seed=0, inside=True):
     """Seeded ray set: origins in the room, uniform directions (unnormalised: Ray's constructor normalises)."""
     rng = np.random.default_rng(seed)

@@ -24,6 +24,12 @@ def render_case(ref, name, W, H, spp, depth, error, seed=42, s_begin=0, s_step=1
             f"{name}_cfg": np.array([W, H, spp, depth, seed, s_begin, s_step], np.int64), f"{name}_error": np.float32(error)}
 
 
+def render_case_sky(ref, name, W, H, spp, depth, bmp):
+    sm, s2, cnt, segs, _ = ref.render_accum(seed=42)
+    return {f"{name}_sum": sm, f"{name}_sum2": s2, f"{name}_count": cnt, f"{name}_segments": np.int64(segs),
+            f"{name}_cfg": np.array([W, H, spp, depth, 42, 0, 1], np.int64), f"{name}_error": np.float32(-1.0)}
+
+
 def main():
     ref, orc = Reference(), Oracle()
     out = {}
@@ -62,6 +68,16 @@ def main():
     ids, t = ref.intersect(rays)
     out["torus40_rays"], out["torus40_ids"], out["torus40_t"] = rays, ids, t
     out.update(render_case(ref, "torus40", 32, 32, 4, 8, -1.0))
+    # skybox (scene.cpp:125-156): open room, synthetic equirect image written as BMP for the reference's own loader
+    sky = scenes.sky_image()
+    bmp = os.path.join(OUT, "_sky_tmp.bmp")
+    scenes.write_bmp(bmp, sky)
+    sc = scenes.open_scene()
+    ref.set_config(32, 32, 8, 8, 1e-4, -1.0, bmp)
+    ref.from_arrays(sc["verts"], sc["mat_ids"], sc["mats"])
+    out["sky_bgr"] = sky
+    out.update(render_case_sky(ref, "sky", 32, 32, 8, 8, bmp))
+    os.unlink(bmp)
     # Philox4x32-10 known answers (Random123 kat_vectors) through the oracle's implementation
     out["philox_kat"] = np.array([orc.philox([0, 0, 0, 0], [0, 0]), orc.philox([0xffffffff] * 4, [0xffffffff] * 2),
                                   orc.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0])],

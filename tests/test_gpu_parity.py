@@ -96,6 +96,20 @@ def test_render_golden(lib, name, accel, mode):
     run_case(lib, sc, name, accel, mode)
 
 
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
+def test_render_skybox(lib, mode):
+    """scene.cpp:125-156.  acosf / atan2f are CUDA's here and glibc's in the reference: counts and segment counts
+    must be exact, radiance within 1e-5 relative (RADIANCE_REL_TOL is 1e-4)."""
+    from test_oracle import sky_scene
+    from oracle_py import Oracle
+    sc = sky_scene(Oracle())
+    W, H, spp, depth, seed, sb, ss = map(int, G["sky_cfg"])
+    sm, s2, cnt = lib.render_accum(sc, ptb200.config(W, H, spp, depth, 1e-4, -1.0, seed, mode=mode))
+    assert_bits_equal(cnt, G["sky_count"])
+    np.testing.assert_allclose(sm, G["sky_sum"], rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(s2, G["sky_sum2"], rtol=2e-5, atol=1e-6)
+
+
 def test_render_vs_live_oracle_default_config_slice(lib, oracle, tor):
     """C1's scene and parameters (Tor.obj, depth 8, adaptive error 0.001, 20 spp) at 96x96, fresh seed."""
     cfg = ptb200.config(96, 96, 20, 8, 1e-4, 0.001, seed=1234)

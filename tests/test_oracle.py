@@ -82,6 +82,18 @@ def test_render_synthetic(oracle, name, make):
     render_case(oracle, with_planes(make(), oracle), name)
 
 
+def sky_scene(oracle):
+    sc = with_planes(scenes.open_scene(), oracle)
+    sc["sky"] = G["sky_bgr"]
+    return sc
+
+
+def test_render_skybox(oracle):
+    """miss -> equirect lookup with the reference's inverted lerp weights, accumulated without the throughput"""
+    cnt = render_case(oracle, sky_scene(oracle), "sky")
+    assert cnt.sum() > 32 * 32 * 4  # most paths leave the open room
+
+
 def test_adaptive_rule_changes_the_result():
     # the adaptive fixture must actually exercise main.cpp:118-125 (otherwise it pins nothing)
     assert int(G["tor_adapt_segments"]) < 32 * 32 * 24 * 8
