@@ -53,6 +53,11 @@ typedef struct PtScene {
     const float *materials;
     int32_t sky_width, sky_height;
     const uint8_t *sky_bgr;
+    /* EXTENSION (BASELINE configs[4], "refractive materials from .mtl"; the reference never parses Ni and its
+     * Refract(), main.cpp:35-47, is dead code): m×2 floats (Ni, Tr) per material, NULL = none.  A non-emissive
+     * material with Tr > 0 and Ni > 0 gets a third lobe after Factory's two (material.h:81-103) with chance Tr
+     * (the other chances are scaled by 1 - Tr): Refract about the normal facing the ray, tint Ks. */
+    const float *materials_ext;
 } PtScene;
 
 /* intersector modes */
@@ -81,7 +86,10 @@ typedef struct PtConfig {
     int32_t sample_step;  /* stride between sample indices; 0 is read as 1 */
     int32_t intersector;  /* PT_ISECT_* */
     int32_t accel;        /* PT_ACCEL_* */
-    int32_t rr_depth;     /* Russian roulette from this bounce on; 0 = off (the reference has none) */
+    int32_t rr_depth;     /* Russian roulette once Ray::depth >= rr_depth; 0 = off (the reference has none).
+                             After each Reflect: p = clamp(max(T), 0.05, 1), survive when u < p (u = word 3 of the
+                             bounce's Philox block), then T /= p and the path weight w /= p.  The estimator's divisor
+                             (samples_count, main.cpp:180) becomes the sum of the contributing paths' weights. */
     int32_t n_gpus;       /* pt_render only: 0/1 = current device; N>1 = split samples over N devices of this
                              process and sum with one NCCL reduce */
     int32_t device;       /* first CUDA device ordinal */
@@ -124,6 +132,9 @@ int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb);
  * Any of the three may be NULL. */
 int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count);
 
+int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count,
+                      float *weight); /* + weight sum per pixel (float[H*W], see rr_depth) */
+
 /* ---- device-resident API (what bench.py / a multi-process host drives) ------------------------------- */
 /* Upload + SoA repack + LBVH build on the current device.  `flags` bit 0: keep traversal counters; bit 1: time
  * every kernel class with CUDA events (instrumented runs only: it serialises the launches). */
@@ -137,6 +148,12 @@ int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3
                            int32_t *d_count, void *stream);
 /* rgb = sum/count on the device (main.cpp:179-182 without the gamma); buffers are device pointers. */
 int pt_resolve_device(const float *d_sum3, const int32_t *d_count, int64_t n_pixels, float *d_rgb, void *stream);
+/* Same with the per-pixel weight sum (float[H*W], may be NULL): equal to (float)count unless cfg->rr_depth > 0, where
+ * it is the divisor of the estimator and the `n` of the adaptive rule. */
+int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                             int32_t *d_count, float *d_weight, void *stream);
+int pt_resolve_device_w(const float *d_sum3, const int32_t *d_count, const float *d_weight, int64_t n_pixels,
+                        float *d_rgb, void *stream);
 /* Statistics of the last render on this handle (synchronises the device). */
 int pt_scene_stats(PtDeviceScene *ds, PtStats *out);
 

@@ -17,13 +17,13 @@ _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 class OrScene(C.Structure):
     _fields_ = [("n_tri", C.c_int), ("verts9", C.c_void_p), ("planes4", C.c_void_p), ("squares", C.c_void_p),
                 ("mat_ids", C.c_void_p), ("n_mat", C.c_int), ("mats10", C.c_void_p),
-                ("sky_w", C.c_int), ("sky_h", C.c_int), ("sky_bgr", C.c_void_p)]
+                ("sky_w", C.c_int), ("sky_h", C.c_int), ("sky_bgr", C.c_void_p), ("mats_ext2", C.c_void_p)]
 
 
 class OrConfig(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("spp", C.c_int), ("max_depth", C.c_int),
                 ("eps", C.c_float), ("error", C.c_float), ("seed", C.c_uint32),
-                ("s_begin", C.c_int), ("s_step", C.c_int)]
+                ("s_begin", C.c_int), ("s_step", C.c_int), ("rr_depth", C.c_int)]
 
 
 def _load(path):
@@ -40,13 +40,13 @@ class Oracle:
         L = self.lib = _load(ORACLE_SO)
         L.or_render_accum.restype = C.c_ulonglong
         L.or_render_accum.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_void_p, C.c_void_p, C.c_void_p,
-                                      C.c_int, C.POINTER(C.c_double)]
+                                      C.c_void_p, C.c_int, C.POINTER(C.c_double)]
         L.or_intersect.argtypes = [C.POINTER(OrScene), C.c_float, _f32p, C.c_long, _i32p, _f32p, C.c_int]
         L.or_triangle_setup.argtypes = [_f32p, C.c_int, _f32p, _f32p, C.POINTER(C.c_float)]
         L.or_primary_ray.argtypes = [C.POINTER(OrConfig), C.c_int, C.c_int, C.c_int, _f32p, _f32p]
         L.or_trace_path.restype = C.c_int
         L.or_trace_path.argtypes = [C.POINTER(OrScene), C.POINTER(OrConfig), C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
-        L.or_resolve.argtypes = [_f32p, _i32p, C.c_long, _f32p]
+        L.or_resolve.argtypes = [_f32p, _i32p, C.c_void_p, C.c_long, _f32p]
         L.or_libm_sincos.argtypes = [_f32p, C.c_long, _f32p, _f32p]
         L.or_max_threads.restype = C.c_int
 
@@ -61,12 +61,15 @@ class Oracle:
             keep["sky"] = np.ascontiguousarray(sc["sky"], np.uint8)
             s.sky_h, s.sky_w = keep["sky"].shape[:2]
             s.sky_bgr = keep["sky"].ctypes.data
+        if sc.get("mats_ext") is not None:  # extension: (m, 2) = Ni, Tr
+            keep["mats_ext"] = np.ascontiguousarray(sc["mats_ext"], np.float32)
+            s.mats_ext2 = keep["mats_ext"].ctypes.data
         s._keep = keep
         return s
 
     @staticmethod
-    def config(width, height, spp, max_depth=8, eps=1e-4, error=-1.0, seed=42, s_begin=0, s_step=1):
-        return OrConfig(width, height, spp, max_depth, eps, error, seed, s_begin, s_step)
+    def config(width, height, spp, max_depth=8, eps=1e-4, error=-1.0, seed=42, s_begin=0, s_step=1, rr_depth=0):
+        return OrConfig(width, height, spp, max_depth, eps, error, seed, s_begin, s_step, rr_depth)
 
     def max_threads(self):
         return int(self.lib.or_max_threads())
@@ -109,8 +112,21 @@ class Oracle:
         sec = C.c_double()
         s = self.scene_struct(sc)
         segs = self.lib.or_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data,
-                                        threads or self.max_threads(), C.byref(sec))
+                                        None, threads or self.max_threads(), C.byref(sec))
         return sm, s2, cnt, int(segs), sec.value
+
+    def render_accum_w(self, sc, cfg, threads=0):
+        """Extension outputs too: -> (sum, sum2, count, weight[H,W] f32, segments)"""
+        H, W = cfg.height, cfg.width
+        sm = np.zeros((H, W, 3), np.float32)
+        s2 = np.zeros((H, W, 3), np.float32)
+        cnt = np.zeros((H, W), np.int32)
+        wt = np.zeros((H, W), np.float32)
+        sec = C.c_double()
+        s = self.scene_struct(sc)
+        segs = self.lib.or_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data,
+                                        wt.ctypes.data, threads or self.max_threads(), C.byref(sec))
+        return sm, s2, cnt, wt, int(segs)
 
     def trace_path(self, sc, cfg, x, y, s, max_seg=64):
         rec = np.zeros((max_seg, 9), np.float32)
@@ -118,9 +134,11 @@ class Oracle:
         n = self.lib.or_trace_path(C.byref(st), C.byref(cfg), x, y, s, max_seg, rec)
         return rec[:min(n, max_seg)], n
 
-    def resolve(self, sm, cnt):
+    def resolve(self, sm, cnt, weight=None):
         rgb = np.zeros_like(sm)
-        self.lib.or_resolve(np.ascontiguousarray(sm), np.ascontiguousarray(cnt), cnt.size, rgb)
+        w = None if weight is None else np.ascontiguousarray(weight, np.float32)
+        self.lib.or_resolve(np.ascontiguousarray(sm), np.ascontiguousarray(cnt), None if w is None else w.ctypes.data,
+                            cnt.size, rgb)
         return rgb
 
     def libm_sincos(self, x):

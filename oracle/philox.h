@@ -36,6 +36,13 @@ static inline void pt_philox4x32_10(const uint32_t ctr[4], const uint32_t key[2]
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
 }
 
-static inline float pt_u01(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }
+/* u in (0,1): the top 24 bits times 2^-24, with the all-zero pattern mapped to 2^-25.  Zero is excluded because the
+ * reference's Material::Process indexes functions_[-1] on a zero draw (material.h:43-48: `while (sample > 0)` never
+ * runs) — undefined behaviour that the reference's own engine reaches once in 2^31 draws and a 24-bit stream once
+ * in 2^24, i.e. in every full-size render. */
+static inline float pt_u01(uint32_t w) {
+    const float u = (float)(w >> 8) * (1.0f / 16777216.0f);
+    return u > 0.0f ? u : (1.0f / 33554432.0f);
+}
 
 #endif

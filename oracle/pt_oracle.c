@@ -35,6 +35,8 @@ typedef struct {
     const float *mats10; /* Ke[3] Kd[3] Ks[3] Ns  (MaterialCharacteristics, material.h:22-28) */
     int sky_w, sky_h;             /* Scene::skybox_ (scene.cpp:20-22): 0 x 0 = Config::skybox empty */
     const unsigned char *sky_bgr; /* rows top-down, blue green red, as bitmap_image holds them */
+    const float *mats_ext2; /* EXTENSION (C5), may be NULL: per material (Ni, Tr); Tr > 0 && Ni > 0 adds a refractive
+                               lobe built on Refract (main.cpp:35-47, dead code upstream) */
 } or_scene;
 
 typedef struct {
@@ -45,6 +47,7 @@ typedef struct {
     float error;     /* config.h:23; adaptive rule of main.cpp:118-125 */
     uint32_t seed;   /* config.h:10 */
     int s_begin, s_step; /* sample partition: samples s_begin, s_begin+s_step, ... < spp */
+    int rr_depth;        /* EXTENSION (C5): Russian roulette once Ray::depth >= rr_depth; 0 = off (the reference) */
 } or_config;
 
 #define PT_PI 3.141593f /* material.h:12 */
@@ -142,6 +145,7 @@ void or_intersect(const or_scene *sc, float eps, const float *rays6, long n, int
 typedef struct {
     float o[3], d[3], T[3];
     int depth;
+    float w; /* EXTENSION: 1 / (product of the Russian-roulette survival probabilities); 1 without RR */
 } or_ray;
 
 typedef struct {
@@ -157,6 +161,10 @@ static inline void rng_slot(or_rng *g, uint32_t seed, uint32_t pixel, uint32_t s
 static inline float rng_next(or_rng *g) { /* Random(), material.h:16-20, under the Philox contract */
     if (!g->filled) { pt_philox4x32_10(g->ctr, g->key, g->w); g->filled = 1; }
     return pt_u01(g->w[(g->dim++) & 3]);
+}
+static inline float rng_word3(or_rng *g) { /* word 3 of the bounce's block: the Russian-roulette draw */
+    if (!g->filled) { pt_philox4x32_10(g->ctr, g->key, g->w); g->filled = 1; }
+    return pt_u01(g->w[3]);
 }
 
 /* primary ray, main.cpp:126-129 + ray.h:21-25; the x/y expressions are evaluated in double */
@@ -174,6 +182,7 @@ static inline void primary_ray(const or_config *cfg, int x, int y, int s, or_ray
     r->o[0] = 0.0f; r->o[1] = 0.0f; r->o[2] = -20.0f;
     r->T[0] = r->T[1] = r->T[2] = 1.0f;
     r->depth = 0;
+    r->w = 1.0f;
 }
 
 void or_primary_ray(const or_config *cfg, int x, int y, int s, float *o3, float *d3) {
@@ -199,7 +208,23 @@ static inline void ray_reflect(or_ray *r, const float begin[3], float dir[3], co
 typedef struct {
     float sum[3], sum2[3];
     int count;
+    float wsum; /* EXTENSION: sum of the contributing paths' RR weights (== count without RR) */
 } or_pixel;
+
+/* EXTENSION (C5, no reference semantics): Russian roulette after Ray::Reflect once depth >= rr_depth.
+ * p = clamp(max(T), 0.05, 1); the path survives when u < p (u = word 3 of the bounce's Philox block) and then
+ * carries T / p and w / p.  A killed path is dropped like a depth-limited one (uncounted).  The reference's
+ * estimator divides by the NUMBER of contributing paths (main.cpp:180); under RR that number becomes the sum of
+ * the weights w, which keeps the ratio estimator consistent. */
+static inline void russian_roulette(const or_config *cfg, or_ray *r, or_rng *g) {
+    if (cfg->rr_depth <= 0 || r->depth < cfg->rr_depth) return;
+    float p = fmaxf(fmaxf(r->T[0], r->T[1]), r->T[2]);
+    p = fminf(fmaxf(p, 0.05f), 1.0f);
+    const float u = rng_word3(g);
+    if (!(u < p)) { r->depth = cfg->max_depth; return; }
+    r->T[0] = r->T[0] / p; r->T[1] = r->T[1] / p; r->T[2] = r->T[2] / p;
+    r->w = r->w / p;
+}
 
 /* Scene::TraceRay (scene.cpp:113-157) with Material::Process (material.h:36-50) and the closures that
  * Factory builds (material.h:58-106).  Skybox (scene.cpp:126-154) is off: a miss just kills the path. */
@@ -224,11 +249,12 @@ static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r
                 const float c1 = t11[2 - k], c2 = t21[2 - k], c3 = t12[2 - k], c4 = t22[2 - k];
                 const float c12 = c1 * (1.0f - wx) + c2 * wx;
                 const float c34 = c3 * (1.0f - wx) + c4 * wx;
-                const float c = (c12 * (1.0f - wy) + c34 * wy) / 256.f;
+                const float c = (c12 * (1.0f - wy) + c34 * wy) / 256.f * r->w; /* w == 1 without RR */
                 px->sum[k] += c; /* not multiplied by the throughput, scene.cpp:151 */
                 px->sum2[k] += c * c;
             }
             px->count++;
+            px->wsum += r->w;
         }
         r->depth = cfg->max_depth;
         return;
@@ -246,25 +272,33 @@ static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r
             px->sum2[k] += c * c;
         }
         px->count++;
+        px->wsum += r->w;
         r->depth = cfg->max_depth;
         return;
     }
     const int has_mirror = (Ns != 0.0f) && (Ks[0] != 0.0f || Ks[1] != 0.0f || Ks[2] != 0.0f);
-    const float mirror_chance = Ns / 1000.0f;
-    const float diffuse_chance = 1.0f - Ns / 1000.0f;
-    const int has_diffuse = diffuse_chance > 0.0f;
-    int lobe; /* 0 mirror, 1 diffuse */
-    if (!has_mirror && !has_diffuse) { r->depth = cfg->max_depth; return; }
-    if (has_mirror && has_diffuse) {
+    const float Ni = sc->mats_ext2 ? sc->mats_ext2[2 * (size_t)sc->mat_ids[hit]] : 0.0f;
+    const float Tr = sc->mats_ext2 ? sc->mats_ext2[2 * (size_t)sc->mat_ids[hit] + 1] : 0.0f;
+    const int has_refract = Tr > 0.0f && Ni > 0.0f; /* EXTENSION: third lobe, appended after Factory's two */
+    const int has_diffuse = (1.0f - Ns / 1000.0f) > 0.0f;
+    /* chance_ as Factory fills it (material.h:86,101); a refractive material scales both by (1 - Tr) */
+    float chance[3];
+    int lobes[3], n_lobes = 0;
+    if (has_mirror) { chance[n_lobes] = has_refract ? Ns / 1000.0f * (1.0f - Tr) : Ns / 1000.0f; lobes[n_lobes++] = 0; }
+    if (has_diffuse) { chance[n_lobes] = has_refract ? (1.0f - Ns / 1000.0f) * (1.0f - Tr) : 1.0f - Ns / 1000.0f; lobes[n_lobes++] = 1; }
+    if (has_refract) { chance[n_lobes] = Tr; lobes[n_lobes++] = 2; }
+    int lobe; /* 0 mirror, 1 diffuse, 2 refract */
+    if (n_lobes == 0) { r->depth = cfg->max_depth; return; }
+    if (n_lobes > 1) {
         float sample = rng_next(g);
         int i = -1;
-        while (sample > 0.0f && i < 1) { /* material.h:43-48; i clamps to the last lobe */
+        while (sample > 0.0f && i < n_lobes - 1) { /* material.h:43-48; i clamps to the last lobe */
             ++i;
-            sample -= (i == 0) ? mirror_chance : diffuse_chance;
+            sample -= chance[i];
         }
-        lobe = i < 0 ? 0 : i; /* sample == 0 indexes [-1] in the reference (UB); lobe 0 here */
+        lobe = lobes[i < 0 ? 0 : i]; /* sample == 0 indexes [-1] in the reference (UB); first lobe here */
     } else {
-        lobe = has_mirror ? 0 : 1;
+        lobe = lobes[0];
     }
     const float eps = cfg->eps;
     const float begin[3] = {P[0] + N[0] * eps, P[1] + N[1] * eps, P[2] + N[2] * eps};
@@ -273,7 +307,7 @@ static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r
         float dir[3];
         for (int k = 0; k < 3; ++k) dir[k] = r->d[k] - N[k] * dn * 2.0f;
         ray_reflect(r, begin, dir, Ks);
-    } else { /* diffuse, material.h:90-100: cosine lobe about world +Z, flipped to N's side */
+    } else if (lobe == 1) { /* diffuse, material.h:90-100: cosine lobe about world +Z, flipped to N's side */
         const float xi1 = rng_next(g), xi2 = rng_next(g);
         const float ang = 2 * PT_PI * xi2;
         float rnd[3] = {sqrtf(xi1) * cosf(ang), sqrtf(xi1) * sinf(ang), sqrtf(1 - xi1)};
@@ -282,13 +316,33 @@ static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r
         const float dt = fmaxf(0.0f, dot4w0(N, rnd));
         const float tint[3] = {Kd[0] * dt, Kd[1] * dt, Kd[2] * dt};
         ray_reflect(r, begin, rnd, tint);
+    } else { /* EXTENSION: Refract (main.cpp:35-47) about the normal facing the incoming ray; tint Ks */
+        const float side = dot4w0(N, r->d);
+        const float sgn = side < 0.0f ? 1.0f : -1.0f;
+        const float n[3] = {N[0] * sgn, N[1] * sgn, N[2] * sgn};
+        const float eta = side < 0.0f ? 1.0f / Ni : Ni;
+        const float cos_inc = -dot4w0(n, r->d);
+        const float sin_refr = eta * sqrtf(fmaxf(0.0f, 1.0f - cos_inc * cos_inc)); /* fmaxf: guards |cos| > 1 by an ulp */
+        float dir[3], org[3];
+        if (sin_refr > 1.0f) { /* total internal reflection: reflect(d, n), stay on the incoming side */
+            const float dn = dot4w0(n, r->d);
+            for (int k = 0; k < 3; ++k) { dir[k] = r->d[k] - n[k] * dn * 2.0f; org[k] = P[k] + n[k] * eps; }
+        } else {
+            const float cos_refr = sqrtf(1.0f - sin_refr * sin_refr);
+            const float f = eta * cos_inc - cos_refr;
+            for (int k = 0; k < 3; ++k) { dir[k] = r->d[k] * eta + n[k] * f; org[k] = P[k] - n[k] * eps; }
+        }
+        ray_reflect(r, org, dir, Ks);
     }
+    russian_roulette(cfg, r, g);
 }
 
 /* The sample loop, main.cpp:110-140, per pixel (pixels are independent under the counter-based RNG).
  * Outputs row-major [y][x].  Returns the number of TraceRay calls (ray segments). */
+/* `weight` (may be NULL) receives the per-pixel weight sum: == (float)count unless rr_depth > 0, in which case it
+ * replaces the count in the adaptive rule and in the resolve. */
 unsigned long long or_render_accum(const or_scene *sc, const or_config *cfg, float *sum3, float *sum2_3, int *count,
-                                   int threads, double *seconds) {
+                                   float *weight, int threads, double *seconds) {
     const int W = cfg->width, H = cfg->height;
     unsigned long long segments = 0;
     struct timespec t0, t1;
@@ -299,7 +353,7 @@ unsigned long long or_render_accum(const or_scene *sc, const or_config *cfg, flo
             or_pixel px;
             memset(&px, 0, sizeof px);
             for (int s = cfg->s_begin; s < cfg->spp; s += cfg->s_step) {
-                const float n = (float)px.count;
+                const float n = cfg->rr_depth > 0 ? px.wsum : (float)px.count;
                 if (s > 10 && n > 0) { /* adaptive skip, main.cpp:118-125 */
                     float D[3];
                     for (int k = 0; k < 3; ++k) {
@@ -321,6 +375,7 @@ unsigned long long or_render_accum(const or_scene *sc, const or_config *cfg, flo
             if (sum3) memcpy(sum3 + 3 * p, px.sum, 12);
             if (sum2_3) memcpy(sum2_3 + 3 * p, px.sum2, 12);
             if (count) count[p] = px.count;
+            if (weight) weight[p] = px.wsum;
         }
     }
     clock_gettime(CLOCK_MONOTONIC, &t1);
@@ -350,9 +405,9 @@ int or_trace_path(const or_scene *sc, const or_config *cfg, int x, int y, int s,
 }
 
 /* resolve, main.cpp:179-182 without the gamma: rgb = sum / count, 0 where count == 0 */
-void or_resolve(const float *sum3, const int *count, long n_pixels, float *rgb) {
+void or_resolve(const float *sum3, const int *count, const float *weight, long n_pixels, float *rgb) {
     for (long p = 0; p < n_pixels; ++p) {
-        const float n = (float)count[p];
+        const float n = weight ? weight[p] : (float)count[p];
         for (int k = 0; k < 3; ++k) rgb[3 * p + k] = count[p] ? sum3[3 * p + k] / n : 0.0f;
     }
 }

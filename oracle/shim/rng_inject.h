@@ -19,7 +19,7 @@ struct PathCtx {
     bool filled;
 };
 PathCtx &ctx();                 // thread-local
-float next_uniform();           // word `dim++` of block (pixel,sample,slot,0) -> [0,1)
+float next_uniform();           // word `dim++` of block (pixel,sample,slot,0) -> (0,1), see oracle/philox.h
 }  // namespace ptshim
 
 namespace std {

@@ -107,7 +107,7 @@ static int validate_config(const PtConfig *c) {
     if (c->rays_per_pixel < 0 || c->max_ray_reflections < 0) return fail(PT_EINVAL, "negative spp / depth");
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
     if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
-    if (c->rr_depth != 0) return fail(PT_EINVAL, "Russian roulette not available in this build");
+    if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
     return PT_OK;
 }
 
@@ -158,7 +158,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     struct EvGuard { cudaEvent_t a, b, c; ~EvGuard() { cudaEventDestroy(a); cudaEventDestroy(b); cudaEventDestroy(c); } } evg{e0, e1, e2};
 
     // ---- upload the caller's arrays (AoS as the loader produced them) ----
-    DevBuf<float> d_verts, d_squares, d_mats10;
+    DevBuf<float> d_verts, d_squares, d_mats10, d_ext2;
     DevBuf<float4> d_planes;
     DevBuf<int> d_matid;
     CK(cudaEventRecord(e0));
@@ -173,6 +173,10 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         }
     }
     if (m) CK(cudaMemcpyAsync(d_mats10.p, scene->materials, 10 * (size_t)m * sizeof(float), cudaMemcpyHostToDevice));
+    if (m && scene->materials_ext) {
+        CK(d_ext2.alloc(2 * (size_t)m));
+        CK(cudaMemcpyAsync(d_ext2.p, scene->materials_ext, 2 * (size_t)m * sizeof(float), cudaMemcpyHostToDevice));
+    }
     CK(cudaEventRecord(e1));
 
     int launches = 0;
@@ -180,8 +184,8 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         k_triangle_setup<<<blocks_for(n, 256), 256>>>(d_verts.p, nullptr, nullptr, n, d_planes.p, d_squares.p);
         ++launches;
     }
-    CK(cudaMalloc((void **)&ds->mats, (m ? 2 * (size_t)m : 1) * sizeof(float4)));
-    if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, m, ds->mats); ++launches; }
+    CK(cudaMalloc((void **)&ds->mats, (m ? 3 * (size_t)m : 1) * sizeof(float4)));
+    if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, d_ext2.p, m, ds->mats); ++launches; }
     CK(cudaMalloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
     CK(cudaMalloc((void **)&ds->stats, kStatWords * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
@@ -283,7 +287,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     return PT_OK;
 }
 
-static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum2, int *d_count,
+static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum2, int *d_count, float *d_weight,
                                 unsigned long long *stats) {
     RenderParams rp{};
     rp.W = cfg->width; rp.H = cfg->height;
@@ -295,6 +299,8 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     rp.seed = cfg->seed;
     rp.sum3 = d_sum3; rp.sum2_3 = d_sum2; rp.count = d_count;
     rp.stats = stats;
+    rp.rr_depth = cfg->rr_depth;
+    rp.weight = d_weight;
     return rp;
 }
 
@@ -304,7 +310,9 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx) {
     const size_t npc = std::min(npx, kMaxSlots / 4), slots = 4 * npc;
     if (ds->wf_mem && ds->wf_slots >= slots && ds->wf_pixels >= npx) return PT_OK;
     if (ds->wf_mem) { CK(cudaDeviceSynchronize()); CK(cudaFree(ds->wf_mem)); ds->wf_mem = nullptr; }
-    const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) + 256;
+    const size_t npx4 = (npx + 3) & ~(size_t)3;  // keeps the queue 16-byte aligned behind the per-pixel weights
+    const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) +
+                         npx4 * sizeof(float) + 256;
     CK(cudaMalloc(&ds->wf_mem, bytes));
     char *p = (char *)ds->wf_mem;
     WfState &w = ds->wf;
@@ -314,6 +322,7 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx) {
     w.cS = (float4 *)p; p += slots * sizeof(float4);
     w.acc1 = (float4 *)p; p += npx * sizeof(float4);
     w.acc2 = (float4 *)p; p += npx * sizeof(float4);
+    w.accw = (float *)p; p += npx4 * sizeof(float);
     w.queue = (int *)p; p += 2 * slots * sizeof(int);
     w.counters = (int *)p;
     w.cap = (int)slots;
@@ -421,12 +430,17 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
 
 extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
                                       int32_t *d_count, void *stream) {
+    return pt_scene_render_device_w(ds, cfg, d_sum3, d_sum2_3, d_count, nullptr, stream);
+}
+
+extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                                        int32_t *d_count, float *d_weight, void *stream) {
     if (!ds) return fail(PT_EINVAL, "scene handle is NULL");
     int rc;
     if ((rc = validate_config(cfg))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
-    const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, ds->stats);
+    const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
     CK(cudaEventRecord(ds->ev0, st));
     int launches = 1;
     if (cfg->reserved[0] == 1) {  // megakernel variant
@@ -446,9 +460,14 @@ extern "C" int pt_scene_render_device(PtDeviceScene *ds, const PtConfig *cfg, fl
 
 extern "C" int pt_resolve_device(const float *d_sum3, const int32_t *d_count, int64_t n_pixels, float *d_rgb,
                                  void *stream) {
+    return pt_resolve_device_w(d_sum3, d_count, nullptr, n_pixels, d_rgb, stream);
+}
+
+extern "C" int pt_resolve_device_w(const float *d_sum3, const int32_t *d_count, const float *d_weight, int64_t n_pixels,
+                                   float *d_rgb, void *stream) {
     if (!d_sum3 || !d_count || !d_rgb || n_pixels < 0) return fail(PT_EINVAL, "bad resolve arguments");
     if (n_pixels == 0) return PT_OK;
-    k_resolve<<<blocks_for(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(d_sum3, d_count, n_pixels, d_rgb);
+    k_resolve<<<blocks_for(n_pixels, 256), 256, 0, (cudaStream_t)stream>>>(d_sum3, d_count, d_weight, n_pixels, d_rgb);
     CK(cudaGetLastError());
     return PT_OK;
 }
@@ -506,6 +525,11 @@ extern "C" int pt_intersect(const PtScene *scene, const PtConfig *cfg, const flo
 }
 
 extern "C" int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count) {
+    return pt_render_accum_w(scene, cfg, sum3, sum2_3, count, nullptr);
+}
+
+extern "C" int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count,
+                                 float *weight) {
     int rc;
     if ((rc = validate_config(cfg))) return rc;
     if ((rc = validate_scene(scene))) return rc;
@@ -516,11 +540,13 @@ extern "C" int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float 
     if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
     struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
     const size_t px = (size_t)cfg->width * cfg->height;
-    DevBuf<float> d_sum, d_sum2;
+    DevBuf<float> d_sum, d_sum2, d_wt;
     DevBuf<int> d_cnt;
     CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px));
-    if ((rc = pt_scene_render_device(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, nullptr))) return rc;
+    if (weight) CK(d_wt.alloc(px));
+    if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, weight ? d_wt.p : nullptr, nullptr))) return rc;
     CK(cudaDeviceSynchronize());
+    if (weight) CK(cudaMemcpy(weight, d_wt.p, px * sizeof(float), cudaMemcpyDeviceToHost));
     if (sum3) CK(cudaMemcpy(sum3, d_sum.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
     if (sum2_3) CK(cudaMemcpy(sum2_3, d_sum2.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
     if (count) CK(cudaMemcpy(count, d_cnt.p, px * sizeof(int), cudaMemcpyDeviceToHost));
@@ -539,11 +565,13 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
     struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
     const size_t px = (size_t)cfg->width * cfg->height;
-    DevBuf<float> d_sum, d_rgb;
+    DevBuf<float> d_sum, d_rgb, d_wt;
     DevBuf<int> d_cnt;
     CK(d_sum.alloc(3 * px)); CK(d_rgb.alloc(3 * px)); CK(d_cnt.alloc(px));
-    if ((rc = pt_scene_render_device(ds, cfg, d_sum.p, nullptr, d_cnt.p, nullptr))) return rc;
-    if ((rc = pt_resolve_device(d_sum.p, d_cnt.p, (int64_t)px, d_rgb.p, nullptr))) return rc;
+    const bool rr = cfg->rr_depth > 0;  // the divisor is then the weight sum
+    if (rr) CK(d_wt.alloc(px));
+    if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, nullptr, d_cnt.p, rr ? d_wt.p : nullptr, nullptr))) return rc;
+    if ((rc = pt_resolve_device_w(d_sum.p, d_cnt.p, rr ? d_wt.p : nullptr, (int64_t)px, d_rgb.p, nullptr))) return rc;
     CK(cudaMemcpy(rgb, d_rgb.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
     return PT_OK;
 }

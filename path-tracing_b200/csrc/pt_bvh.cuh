@@ -337,23 +337,34 @@ __global__ void k_root_box(const int *__restrict__ vals, const float4 *__restric
 }
 
 // Factory (material.h:58-106) as data: which closures exist and the mirror's selection chance
-__global__ void k_pack_materials(const float *__restrict__ mats10, int m, float4 *__restrict__ out) {
+__global__ void k_pack_materials(const float *__restrict__ mats10, const float *__restrict__ ext2, int m,
+                                 float4 *__restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= m) return;
     const float *p = mats10 + 10 * (size_t)i;
     const bool emissive = p[0] != 0.0f || p[1] != 0.0f || p[2] != 0.0f;
     const float Ns = p[9];
     const bool has_mirror = (Ns != 0.0f) && (p[6] != 0.0f || p[7] != 0.0f || p[8] != 0.0f);
-    const float mirror_chance = Ns / 1000;
-    const bool has_diffuse = (1 - Ns / 1000) > 0;
+    float mirror_chance = Ns / 1000;
+    float diffuse_chance = 1 - Ns / 1000;
+    const bool has_diffuse = diffuse_chance > 0;
+    const float Ni = ext2 ? ext2[2 * (size_t)i] : 0.0f, Tr = ext2 ? ext2[2 * (size_t)i + 1] : 0.0f;
+    const bool has_refract = Tr > 0.0f && Ni > 0.0f;  // extension (oracle/pt_oracle.c trace_ray)
     int kind;
     if (emissive) kind = MAT_EMISSIVE;
+    else if (has_refract) kind = MAT_MULTI;
     else if (has_mirror && has_diffuse) kind = MAT_BOTH;
     else if (has_mirror) kind = MAT_MIRROR;
     else if (has_diffuse) kind = MAT_DIFFUSE;
     else kind = MAT_NONE;
-    out[2 * i + 0] = make_float4(p[3], p[4], p[5], __int_as_float(kind));
-    out[2 * i + 1] = make_float4(p[6], p[7], p[8], mirror_chance);
+    if (has_refract) {
+        mirror_chance = Ns / 1000 * (1.0f - Tr);
+        diffuse_chance = (1 - Ns / 1000) * (1.0f - Tr);
+    }
+    const int mask = (has_mirror ? 1 : 0) | (has_diffuse ? 2 : 0) | (has_refract ? 4 : 0);
+    out[3 * i + 0] = make_float4(p[3], p[4], p[5], __int_as_float(kind));
+    out[3 * i + 1] = make_float4(p[6], p[7], p[8], mirror_chance);
+    out[3 * i + 2] = make_float4(Ni, Tr, __int_as_float(mask), diffuse_chance);
 }
 
 }  // namespace ptd

@@ -26,15 +26,17 @@ struct RenderParams {
     float *sum3, *sum2_3;
     int *count;
     unsigned long long *stats;  // [0] committed segments, [1] traced segments, [2] nodes, [3] tris
+    int rr_depth;   // extension: Russian roulette once Ray::depth >= rr_depth (0 = off, the reference)
+    float *weight;  // extension: per-pixel sum of the contributing paths' RR weights (== count without RR)
 };
 
 constexpr float kPi = 3.141593f;  // material.h:12
 
 // the adaptive rule of main.cpp:118-125: true = skip sample s
-__device__ __forceinline__ bool adaptive_skip(int s, int n, V3 sum, V3 sum2, float error) {
-    if (!(s > 10 && n > 0)) return false;
+// fn = (float)samples_count (under Russian roulette: the weight sum that replaces it)
+__device__ __forceinline__ bool adaptive_skip(int s, float fn, V3 sum, V3 sum2, float error) {
+    if (!(s > 10 && fn > 0)) return false;
     if ((s % 4) == 0) return false;
-    const float fn = (float)n;
     const float mx = sum.x / fn, my = sum.y / fn, mz = sum.z / fn;
     const float Dx = sum2.x / fn - mx * mx, Dy = sum2.y / fn - my * my, Dz = sum2.z / fn - mz * mz;
     return Dx < error && Dy < error && Dz < error;
@@ -70,12 +72,17 @@ __device__ __forceinline__ V3 sky_color(const SceneView &sc, V3 d) {
 // One bounce of Scene::TraceRay after the nearest hit is known (scene.cpp:121-156): material dispatch
 // (Material::Process, material.h:36-50) and the closures Factory builds (material.h:58-106).
 // Returns false when the path ends here; *contrib is set when it ends on an emitter's front side with c = T * Kd.
+// `depth` is incremented only by Ray::Reflect, so "returned false with depth unchanged" = the path ended inside
+// Material::Process, "returned false with depth + 1" = Russian roulette killed it after the reflection.
+// Extensions (no reference semantics, restated in oracle/pt_oracle.c): the refractive lobe of MAT_MULTI materials
+// and Russian roulette with the path weight `wgt` (1 / product of the survival probabilities).
 __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large, const RenderParams &rp, const Hit &h,
-                                      uint32_t pixel, uint32_t sample, V3 &o, V3 &d, V3 &T, int &depth, V3 *c,
-                                      bool *contrib) {
+                                      uint32_t pixel, uint32_t sample, V3 &o, V3 &d, V3 &T, int &depth, float &wgt,
+                                      V3 *c, bool *contrib) {
     if (h.rec < 0) {  // miss: optional skybox, then Ray::MakeInvalid (scene.cpp:125-156)
         if (sc.sky) {
-            *c = sky_color(sc, d);  // accumulated as is: the reference does not multiply by the throughput (scene.cpp:151)
+            const V3 k = sky_color(sc, d);  // accumulated as is: the reference does not multiply by the throughput (scene.cpp:151)
+            *c = mk(k.x * wgt, k.y * wgt, k.z * wgt);
             *contrib = true;
         }
         return false;
@@ -85,7 +92,7 @@ __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large
     const float4 pl = r[0];
     const int mat = __float_as_int(r[3].w);
     const V3 N = mk(pl.x, pl.y, pl.z);
-    const float4 m0 = __ldg(sc.mats + 2 * mat), m1 = __ldg(sc.mats + 2 * mat + 1);
+    const float4 m0 = __ldg(sc.mats + 3 * mat), m1 = __ldg(sc.mats + 3 * mat + 1);
     const int kind = __float_as_int(m0.w);
     const V3 Kd = mk(m0.x, m0.y, m0.z);
     if (kind == MAT_EMISSIVE) {  // material.h:68-79
@@ -98,23 +105,38 @@ __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large
     if (kind == MAT_NONE) return false;  // Material::Process with no closures, material.h:37-38
     // drop_point = begin + direction * distance (scene.cpp:122), vec4 arithmetic
     const V3 P = mk(o.x + d.x * h.t, o.y + d.y * h.t, o.z + d.z * h.t);
+    const bool rr = rp.rr_depth > 0 && depth + 1 >= rp.rr_depth;
     int lobe = kind == MAT_MIRROR ? 0 : 1;
     uint4 w = make_uint4(0, 0, 0, 0);
-    if (kind != MAT_MIRROR) w = philox4x32_10(pixel, sample, 1u + (uint32_t)depth, 0u, rp.seed, 0u);
+    if (kind != MAT_MIRROR || rr) w = philox4x32_10(pixel, sample, 1u + (uint32_t)depth, 0u, rp.seed, 0u);
     uint32_t w1 = w.x, w2 = w.y;
+    float Ni = 0.0f;
     if (kind == MAT_BOTH) {  // Material::Process, material.h:43-49: chances [mirror, diffuse]
         const float smp = u01(w.x);
         lobe = (smp > 0.0f && (smp - m1.w) > 0.0f) ? 1 : 0;
         w1 = w.y;
         w2 = w.z;
+    } else if (kind == MAT_MULTI) {  // extension: lobes [mirror, diffuse, refract] as present, same selection loop
+        const float4 m2 = __ldg(sc.mats + 3 * mat + 2);  // Ni, Tr, bits(lobe mask), diffuse chance
+        const int mask = __float_as_int(m2.z);
+        Ni = m2.x;
+        lobe = (mask & 1) ? 0 : (mask & 2) ? 1 : 2;
+        if (__popc(mask) > 1) {
+            float smp = u01(w.x);
+            if ((mask & 1) && smp > 0.0f) { lobe = 0; smp -= m1.w; }
+            if ((mask & 2) && smp > 0.0f) { lobe = 1; smp -= m2.w; }
+            if ((mask & 4) && smp > 0.0f) { lobe = 2; }
+            w1 = w.y;
+            w2 = w.z;
+        }
     }
-    const V3 begin = mk(P.x + N.x * rp.eps, P.y + N.y * rp.eps, P.z + N.z * rp.eps);
+    V3 begin = mk(P.x + N.x * rp.eps, P.y + N.y * rp.eps, P.z + N.z * rp.eps);
     V3 nd, tint;
     if (lobe == 0) {  // mirror closure, material.h:83-85; glm::reflect = I - N * dot(N, I) * 2
         const float dn = dot4w0(N, d);
         nd = mk(d.x - N.x * dn * 2.0f, d.y - N.y * dn * 2.0f, d.z - N.z * dn * 2.0f);
         tint = mk(m1.x, m1.y, m1.z);
-    } else {  // diffuse closure, material.h:90-100: cosine lobe about world +Z, flipped to N's side
+    } else if (lobe == 1) {  // diffuse closure, material.h:90-100: cosine lobe about world +Z, flipped to N's side
         const float xi1 = u01(w1), xi2 = u01(w2);
         const float ang = 2 * kPi * xi2;
         float sn, cs;
@@ -125,12 +147,36 @@ __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large
         const float dt = fmaxf(0.0f, dot4w0(N, rnd));
         nd = rnd;
         tint = mk(Kd.x * dt, Kd.y * dt, Kd.z * dt);
+    } else {  // extension: Refract (main.cpp:35-47) about the normal that faces the incoming ray; tint Ks
+        const float side = dot4w0(N, d);
+        const float sgn = side < 0.0f ? 1.0f : -1.0f;
+        const V3 n = mk(N.x * sgn, N.y * sgn, N.z * sgn);
+        const float eta = side < 0.0f ? 1.0f / Ni : Ni;
+        const float cos_inc = -dot4w0(n, d);
+        const float sin_refr = eta * sqrtf(fmaxf(0.0f, 1.0f - cos_inc * cos_inc));
+        if (sin_refr > 1.0f) {  // total internal reflection
+            const float dn = dot4w0(n, d);
+            nd = mk(d.x - n.x * dn * 2.0f, d.y - n.y * dn * 2.0f, d.z - n.z * dn * 2.0f);
+            begin = mk(P.x + n.x * rp.eps, P.y + n.y * rp.eps, P.z + n.z * rp.eps);
+        } else {
+            const float cos_refr = sqrtf(1.0f - sin_refr * sin_refr);
+            const float f = eta * cos_inc - cos_refr;
+            nd = mk(d.x * eta + n.x * f, d.y * eta + n.y * f, d.z * eta + n.z * f);
+            begin = mk(P.x - n.x * rp.eps, P.y - n.y * rp.eps, P.z - n.z * rp.eps);
+        }
+        tint = mk(m1.x, m1.y, m1.z);
     }
     // Ray::Reflect, ray.h:45-50
     o = begin;
     d = normalize4w0(nd);
     T = T * tint;
     ++depth;
+    if (rr) {  // extension: p = clamp(max(T), 0.05, 1), survive when u < p, then T / p and w / p
+        const float p = fminf(fmaxf(fmaxf(fmaxf(T.x, T.y), T.z), 0.05f), 1.0f);
+        if (!(u01(w.w) < p)) return false;
+        T = mk(T.x / p, T.y / p, T.z / p);
+        wgt = wgt / p;
+    }
     return true;
 }
 
@@ -160,16 +206,19 @@ k_render_mega(SceneView sc, RenderParams rp) {
 
     V3 sum = mk(0, 0, 0), sum2 = mk(0, 0, 0);
     int cnt = 0;
+    float wsum = 0.0f;        // weight sum of the contributing paths (Russian roulette only)
+    const bool rr_on = rp.rr_depth > 0;
     int s_next = rp.s_begin;  // next uncommitted sample of this pixel (identical across the quad)
     unsigned long long seg_commit = 0, seg_traced = 0, n_nodes = 0, n_tris = 0;
 
     while (__any_sync(0xffffffffu, in_image && s_next < rp.spp)) {
         const int s = s_next + qi * rp.s_step;
         const bool live = in_image && s_next < rp.spp && s < rp.spp;
-        const bool traced = live && !adaptive_skip(s, cnt, sum, sum2, rp.error);
+        const bool traced = live && !adaptive_skip(s, rr_on ? wsum : (float)cnt, sum, sum2, rp.error);
         V3 c = mk(0, 0, 0);
         int nseg = 0;
         bool contrib = false;
+        float wgt = 1.0f;
         if (traced) {  // primary ray, then `while (ray.IsValid()) scene.TraceRay(ray)` (main.cpp:126-139)
             V3 o = mk(0.0f, 0.0f, -20.0f), T = mk(1.0f, 1.0f, 1.0f);
             V3 d = primary_dir(x, y, rp.W, rp.H, pixel, (uint32_t)s, rp.seed);
@@ -178,7 +227,7 @@ k_render_mega(SceneView sc, RenderParams rp) {
             while (alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f)) {  // ray.h:52-54
                 const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
                 ++nseg;
-                alive = shade(sc, s_large, rp, h, pixel, (uint32_t)s, o, d, T, depth, &c, &contrib);
+                alive = shade(sc, s_large, rp, h, pixel, (uint32_t)s, o, d, T, depth, wgt, &c, &contrib);
             }
             seg_traced += nseg;
         }
@@ -194,8 +243,10 @@ k_render_mega(SceneView sc, RenderParams rp) {
             const float cx = __shfl_sync(0xffffffffu, c.x, src);
             const float cy = __shfl_sync(0xffffffffu, c.y, src);
             const float cz = __shfl_sync(0xffffffffu, c.z, src);
+            const float wj = __shfl_sync(0xffffffffu, wgt, src);
             if (stop || !live_j) continue;
-            const bool skip_now = adaptive_skip(s_next, cnt, sum, sum2, rp.error);  // s_next = the sample being committed
+            // s_next = the sample being committed
+            const bool skip_now = adaptive_skip(s_next, rr_on ? wsum : (float)cnt, sum, sum2, rp.error);
             if (!skip_now && !traced_j) {
                 stop = true;  // needed after all: first sample of the next step
                 continue;
@@ -205,6 +256,7 @@ k_render_mega(SceneView sc, RenderParams rp) {
                     sum = mk(sum.x + cx, sum.y + cy, sum.z + cz);
                     sum2 = mk(sum2.x + cx * cx, sum2.y + cy * cy, sum2.z + cz * cz);
                     ++cnt;
+                    wsum += wj;
                 }
                 if (qi == j) seg_commit += nseg_j;
             }
@@ -217,6 +269,7 @@ k_render_mega(SceneView sc, RenderParams rp) {
         if (rp.sum3) { rp.sum3[3 * p] = sum.x; rp.sum3[3 * p + 1] = sum.y; rp.sum3[3 * p + 2] = sum.z; }
         if (rp.sum2_3) { rp.sum2_3[3 * p] = sum2.x; rp.sum2_3[3 * p + 1] = sum2.y; rp.sum2_3[3 * p + 2] = sum2.z; }
         if (rp.count) rp.count[p] = cnt;
+        if (rp.weight) rp.weight[p] = rr_on ? wsum : (float)cnt;
     }
     // statistics: one atomic per warp per counter
     for (int o2 = 16; o2; o2 >>= 1) {
@@ -260,13 +313,14 @@ k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float ep
     }
 }
 
-// rgb = color_map / samples_count, 0 where the count is 0 (main.cpp:179-182 without the gamma)
-__global__ void k_resolve(const float *__restrict__ sum3, const int *__restrict__ count, long long n_pixels,
-                          float *__restrict__ rgb) {
+// rgb = color_map / samples_count, 0 where the count is 0 (main.cpp:179-182 without the gamma); `weight` (may be null)
+// replaces (float)count as the divisor (Russian-roulette renders)
+__global__ void k_resolve(const float *__restrict__ sum3, const int *__restrict__ count, const float *__restrict__ weight,
+                          long long n_pixels, float *__restrict__ rgb) {
     const long long p = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     if (p >= n_pixels) return;
     const int c = count[p];
-    const float fn = (float)c;
+    const float fn = weight ? weight[p] : (float)c;
 #pragma unroll
     for (int k = 0; k < 3; ++k) rgb[3 * p + k] = c ? sum3[3 * p + k] / fn : 0.0f;
 }

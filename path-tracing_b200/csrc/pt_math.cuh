@@ -57,7 +57,11 @@ __device__ __forceinline__ uint4 philox4x32_10(uint32_t c0, uint32_t c1, uint32_
     }
     return make_uint4(c0, c1, c2, c3);
 }
-__device__ __forceinline__ float u01(uint32_t w) { return (float)(w >> 8) * (1.0f / 16777216.0f); }
+// u in (0,1): top 24 bits * 2^-24, the zero pattern mapped to 2^-25 (a zero draw is undefined behaviour in the
+// reference's Material::Process, material.h:43-48; see oracle/philox.h)
+__device__ __forceinline__ float u01(uint32_t w) {
+    return fmaxf((float)(w >> 8) * (1.0f / 16777216.0f), 1.0f / 33554432.0f);
+}
 
 // ---- sinf / cosf as the reference's libm computes them.
 // material.h:93-94 calls std::cos/std::sin(float); the reference links glibc, whose sinf/cosf (since 2.28) is the

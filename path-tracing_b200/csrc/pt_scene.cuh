@@ -10,7 +10,8 @@
 //            [0] child0 lo.x hi.x lo.y hi.y   [1] child1 lo.x hi.x lo.y hi.y
 //            [2] child0 lo.z hi.z, child1 lo.z hi.z      [3] bits: child0 ref, child1 ref, 0, 0
 //          child ref >= 0: node index; < 0: leaf, bits 0..27 = first triangle record, bits 28..30 = count-1
-//   mats   2 x float4 per material: (Kd.xyz, bits(lobe kind)), (Ks.xyz, mirror chance Ns/1000)
+//   mats   3 x float4 per material: (Kd.xyz, bits(lobe kind)), (Ks.xyz, mirror chance), (Ni, Tr, bits(lobe mask),
+//          diffuse chance) — the third row is read for MAT_MULTI (refractive extension) only
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -26,7 +27,8 @@ constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
 
 // lobe kinds built by Factory (material.h:58-106)
-enum : int { MAT_EMISSIVE = 0, MAT_NONE = 1, MAT_MIRROR = 2, MAT_DIFFUSE = 3, MAT_BOTH = 4 };
+// MAT_MULTI (extension): a material with the refractive lobe; its lobe set is the mask in row 2 (1 mirror, 2 diffuse, 4 refract)
+enum : int { MAT_EMISSIVE = 0, MAT_NONE = 1, MAT_MIRROR = 2, MAT_DIFFUSE = 3, MAT_BOTH = 4, MAT_MULTI = 5 };
 
 __host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
     return (int)(0x80000000u | ((uint32_t)(count - 1) << 28) | (uint32_t)first);

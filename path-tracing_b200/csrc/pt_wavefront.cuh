@@ -28,17 +28,20 @@
 namespace ptd {
 
 // per-slot flag word (Tn.w): bits 0..15 depth, then:
-constexpr int WF_ALIVE = 1 << 16, WF_TRACED = 1 << 17, WF_LIVE = 1 << 18, WF_CONTRIB = 1 << 19;
+// WF_SHADE_END: the path ended inside Material::Process (emitter, miss, no closure) rather than after a Reflect, so it
+// traced depth + 1 segments; otherwise (depth limit, zero throughput, Russian roulette) it traced `depth` segments.
+constexpr int WF_ALIVE = 1 << 16, WF_TRACED = 1 << 17, WF_LIVE = 1 << 18, WF_CONTRIB = 1 << 19, WF_SHADE_END = 1 << 20;
 
 struct WfState {
     float4 *oT;     // per slot: origin xyz, best hit distance t
     float4 *dR;     // per slot: direction xyz, bits(record index of the best hit, -1 = none)
     float4 *Tn;     // per slot: throughput rgb, bits(flags | depth)
-    float4 *cS;     // per slot: contribution rgb (T * Kd at the emitter), bits(segments traced)
+    float4 *cS;     // per slot: contribution rgb (T * Kd at the emitter), path weight (Russian roulette; 1 otherwise)
     int *queue;     // 2 x cap slot ids (ping-pong): rays that must walk the LBVH
     int *counters;  // [0],[1] queue 0 count, head; [2],[3] queue 1 count, head; [4] pending pixels; [5] max remaining
     float4 *acc1;   // per pixel: color_map rgb, bits(samples_count)
     float4 *acc2;   // per pixel: color2_map rgb, bits(next uncommitted sample index)
+    float *accw;    // per pixel: weight sum of the contributing paths (touched by Russian-roulette renders only)
     int cap;        // path slots
 };
 
@@ -47,6 +50,7 @@ __global__ void k_wf_init(WfState wf, int npx, int s_begin) {
     if (p >= npx) return;
     wf.acc1[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
     wf.acc2[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(s_begin));
+    wf.accw[p] = 0.f;
 }
 
 // large triangles, root test, enqueue.  Must be reached by all 32 lanes of the warp (ballot); `active` lanes carry
@@ -96,7 +100,8 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
         const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
         const int s = s_next + q * rp.s_step;
         const bool live = s_next < rp.spp && s < rp.spp;
-        traced = live && !adaptive_skip(s, cnt, mk(a1.x, a1.y, a1.z), mk(a2.x, a2.y, a2.z), rp.error);
+        const float fn = rp.rr_depth > 0 ? __ldcs(&wf.accw[p]) : (float)cnt;
+        traced = live && !adaptive_skip(s, fn, mk(a1.x, a1.y, a1.z), mk(a2.x, a2.y, a2.z), rp.error);
         int flags = (live ? WF_LIVE : 0) | (traced ? WF_TRACED : 0);
         if (traced) {
             const int x = p % rp.W, y = p / rp.W;
@@ -105,7 +110,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
         }
         traced = (flags & WF_ALIVE) != 0;
         __stcs(&wf.Tn[slot], make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags)));
-        __stcs(&wf.cS[slot], make_float4(0.0f, 0.0f, 0.0f, __int_as_float(0)));
+        __stcs(&wf.cS[slot], make_float4(0.0f, 0.0f, 0.0f, 1.0f));
     }
     front<COUNT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
     if (COUNT && rp.stats) {  // one atomic per warp per counter
@@ -147,13 +152,19 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
             const int p = pix0 + (slot >> 2), q = slot & 3;
             const int s = __float_as_int(__ldcs(&wf.acc2[p].w)) + q * rp.s_step;
             bool contrib = false;
-            alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, &c, &contrib);
+            const bool rr_on = rp.rr_depth > 0;  // the path weight lives in cS.w; it is 1 unless roulette has been played
+            float wgt = rr_on && depth + 1 > rp.rr_depth ? __ldcs(&wf.cS[slot].w) : 1.0f;
+            const float wgt0 = wgt;
+            const int depth0 = depth;
+            alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, wgt, &c, &contrib);
+            const bool shade_end = !alive && depth == depth0;
             // Ray::IsValid before the next TraceRay (ray.h:52-54)
             alive = alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f);
-            flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0);
+            flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0) |
+                    (shade_end ? WF_SHADE_END : 0);
             __stcs(&wf.Tn[slot], make_float4(T.x, T.y, T.z, __int_as_float(flags)));
-            if (contrib) __stcs(&wf.cS[slot], make_float4(c.x, c.y, c.z, __int_as_float(b + 1)));
-            else if (!alive) __stcs(&wf.cS[slot].w, __int_as_float(b + 1));  // segments traced by this path
+            if (contrib) __stcs(&wf.cS[slot], make_float4(c.x, c.y, c.z, wgt));
+            else if (wgt != wgt0) __stcs(&wf.cS[slot].w, wgt);
         }
     }
     front<COUNT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
@@ -251,22 +262,25 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
         const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
         V3 sum = mk(a1.x, a1.y, a1.z), sum2 = mk(a2.x, a2.y, a2.z);
         int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
+        const bool rr_on = rp.rr_depth > 0;
+        float wsum = rr_on ? __ldcs(&wf.accw[p]) : 0.0f;
         bool stop = false;
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
             const int slot = 4 * i + j;
             const int flags = __float_as_int(__ldcs(&wf.Tn[slot].w));
             const float4 c = __ldcs(&wf.cS[slot]);
-            const int nseg = __float_as_int(c.w);
+            const int nseg = (flags & 0xffff) + ((flags & WF_SHADE_END) ? 1 : 0);
             if (flags & WF_TRACED) seg_traced += nseg;
             if (stop || !(flags & WF_LIVE)) continue;
-            const bool skip_now = adaptive_skip(s_next, cnt, sum, sum2, rp.error);
+            const bool skip_now = adaptive_skip(s_next, rr_on ? wsum : (float)cnt, sum, sum2, rp.error);
             if (!skip_now && !(flags & WF_TRACED)) { stop = true; continue; }  // needed after all: next step's first
             if (!skip_now) {
                 if (flags & WF_CONTRIB) {  // material.h:74-77
                     sum = mk(sum.x + c.x, sum.y + c.y, sum.z + c.z);
                     sum2 = mk(sum2.x + c.x * c.x, sum2.y + c.y * c.y, sum2.z + c.z * c.z);
                     ++cnt;
+                    wsum += c.w;
                 }
                 seg_commit += nseg;
             }
@@ -274,6 +288,7 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
         }
         __stcs(&wf.acc1[p], make_float4(sum.x, sum.y, sum.z, __int_as_float(cnt)));
         __stcs(&wf.acc2[p], make_float4(sum2.x, sum2.y, sum2.z, __int_as_float(s_next)));
+        if (rr_on) __stcs(&wf.accw[p], wsum);
         if (s_next < rp.spp) remaining = (rp.spp - s_next + rp.s_step - 1) / rp.s_step;
     }
     for (int o2 = 16; o2; o2 >>= 1) {
@@ -302,6 +317,7 @@ __global__ void k_wf_finish(RenderParams rp, WfState wf, int npx) {
     if (rp.sum3) { rp.sum3[3 * (size_t)p] = a1.x; rp.sum3[3 * (size_t)p + 1] = a1.y; rp.sum3[3 * (size_t)p + 2] = a1.z; }
     if (rp.sum2_3) { rp.sum2_3[3 * (size_t)p] = a2.x; rp.sum2_3[3 * (size_t)p + 1] = a2.y; rp.sum2_3[3 * (size_t)p + 2] = a2.z; }
     if (rp.count) rp.count[p] = __float_as_int(a1.w);
+    if (rp.weight) rp.weight[p] = rp.rr_depth > 0 ? wf.accw[p] : (float)__float_as_int(a1.w);
 }
 
 }  // namespace ptd

@@ -34,6 +34,7 @@ public:
     // extensions of the B200 build (defaults = reference behaviour)
     int gpus = 1;
     int accel = PT_ACCEL_AUTO;
+    int rr = 0;  // -RR <depth>: Russian roulette once a path's depth reaches <depth> (0 = off)
 
     static Config &get() {
         static Config instance;
@@ -63,6 +64,7 @@ public:
             else if (is("-TL")) time_limit = std::atoi(val);
             else if (is("-GPUS")) gpus = std::atoi(val);
             else if (is("-ACCEL")) accel = std::atoi(val);
+            else if (is("-RR")) rr = std::atoi(val);
         }
     }
 
@@ -83,6 +85,7 @@ public:
         c.intersector = PT_ISECT_REFERENCE;
         c.accel = accel;
         c.n_gpus = gpus;
+        c.rr_depth = rr;
         return c;
     }
 };

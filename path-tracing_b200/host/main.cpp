@@ -33,7 +33,8 @@ int main(int argc, char *argv[]) {
     }
     std::cerr << cfg.rays_per_pixel << " rays per pixel were sent" << std::endl;
 
-    const DispersionStats st = ResolveAndStats(color_map, color2_map, samples_count, cfg.width, cfg.height, cfg.gamma_correction);
+    const DispersionStats st = ResolveAndStats(color_map, color2_map, samples_count, cfg.width, cfg.height,
+                                               cfg.gamma_correction, cfg.rr > 0 ? &scene.Weights() : nullptr);
     if (cfg.gauss) color_map = GaussBlur(color_map, cfg.gauss, cfg.width, cfg.height);
     if (cfg.median) color_map = MedianFilter(color_map, cfg.median, cfg.width, cfg.height);
     for (int y = 0; y < cfg.height; ++y)

@@ -12,6 +12,9 @@ const float pi = 3.141593f;  // material.h:12
 struct MaterialCharacteristics {
     ptm::vec3 Ke, Kd, Ks;
     float Ns = 0;
+    // extension (not parsed by the reference): index of refraction `Ni` and transmission `Tr` (= 1 - `d`) of the MTL
+    // block; Tr > 0 && Ni > 0 adds the refractive lobe built on the reference's unused Refract (main.cpp:35-47)
+    float Ni = 0, Tr = 0;
 };
 
 class Material {
@@ -26,6 +29,7 @@ public:
     bool HasMirror() const { return !IsEmissive() && ch_.Ns != 0 && ch_.Ks != ptm::vec3(0); }
     bool HasDiffuse() const { return !IsEmissive() && (1 - ch_.Ns / 1000 > 0); }
     float MirrorChance() const { return ch_.Ns / 1000; }
+    bool HasRefract() const { return !IsEmissive() && ch_.Tr > 0 && ch_.Ni > 0; }  // extension
 };
 
 inline Material Factory(const MaterialCharacteristics &characteristics) { return Material(characteristics); }

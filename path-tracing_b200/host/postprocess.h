@@ -20,12 +20,13 @@ struct DispersionStats {
 // color_map becomes pow(sum / n, gamma) * 255 in place.
 inline DispersionStats ResolveAndStats(Image &color_map, const Image &color2_map,
                                        const std::vector<std::vector<int>> &samples_count, int width, int height,
-                                       float gamma) {
+                                       float gamma, const std::vector<float> *divisor = nullptr) {
     DispersionStats st;
     for (int y = 0; y < height; ++y)
         for (int x = 0; x < width; ++x) {
             if (!samples_count[x][y]) { st.average_dispersion += 1; continue; }
-            const float n = static_cast<float>(samples_count[x][y]);
+            // Russian-roulette renders divide by the weight sum (row-major [y][x]) instead of the count
+            const float n = divisor ? (*divisor)[static_cast<size_t>(y) * width + x] : static_cast<float>(samples_count[x][y]);
             const ptm::vec3 s = color_map[x][y], s2 = color2_map[x][y];
             const float mx = s.x / n, my = s.y / n, mz = s.z / n;
             const float disp = (s2.x / n - mx * mx) + (s2.y / n - my * my) + (s2.z / n - mz * mz);

@@ -54,6 +54,9 @@ void read_mtl(const std::string &path, Scene &scene) {
             else if (tok == "Ke") in >> ch.Ke.x >> ch.Ke.y >> ch.Ke.z;
             else if (tok == "Ks") in >> ch.Ks.x >> ch.Ks.y >> ch.Ks.z;
             else if (tok == "Ns") in >> ch.Ns;
+            else if (tok == "Ni") in >> ch.Ni;                                  // extension (the reference skips these)
+            else if (tok == "Tr") in >> ch.Tr;
+            else if (tok == "d") { float d = 1; in >> d; ch.Tr = 1 - d; }
             in >> tok;
         }
         scene.AddMaterial(ch);
@@ -106,6 +109,8 @@ void Scene::LoadModel(std::string path) {
 PtScene Scene::abi() const {
     const size_t n = triangles_.size(), m = materials_.size();
     vertices_.resize(9 * n); planes_.resize(4 * n); squares_.resize(n); mat_ids_.resize(n); mats_.resize(10 * m);
+    mats_ext_.resize(2 * m);
+    bool any_refract = false;
     for (size_t i = 0; i < n; ++i) {
         const Triangle &t = triangles_[i];
         for (int k = 0; k < 3; ++k)
@@ -119,6 +124,8 @@ PtScene Scene::abi() const {
         const MaterialCharacteristics &c = materials_[j].GetCharacteristics();
         const float row[10] = {c.Ke.x, c.Ke.y, c.Ke.z, c.Kd.x, c.Kd.y, c.Kd.z, c.Ks.x, c.Ks.y, c.Ks.z, c.Ns};
         std::copy(row, row + 10, mats_.begin() + 10 * j);
+        mats_ext_[2 * j] = c.Ni; mats_ext_[2 * j + 1] = c.Tr;
+        any_refract = any_refract || materials_[j].HasRefract();
     }
     PtScene s{};
     s.n_triangles = static_cast<int32_t>(n);
@@ -126,6 +133,7 @@ PtScene Scene::abi() const {
     s.material_ids = mat_ids_.data();
     s.n_materials = static_cast<int32_t>(m);
     s.materials = mats_.data();
+    if (any_refract) s.materials_ext = mats_ext_.data();
     if (skybox_.width() && skybox_.height()) {
         s.sky_width = static_cast<int32_t>(skybox_.width());
         s.sky_height = static_cast<int32_t>(skybox_.height());
@@ -139,7 +147,8 @@ int Scene::Render(const PtConfig &cfg) {
     const size_t W = cfg.width, H = cfg.height;
     std::vector<float> sum(3 * W * H), sum2(3 * W * H);
     std::vector<int32_t> cnt(W * H);
-    const int rc = pt_render_accum(&s, &cfg, sum.data(), sum2.data(), cnt.data());
+    weight_.assign(W * H, 0.0f);
+    const int rc = pt_render_accum_w(&s, &cfg, sum.data(), sum2.data(), cnt.data(), weight_.data());
     if (rc) return rc;
     for (size_t y = 0; y < H; ++y)
         for (size_t x = 0; x < W; ++x) {

@@ -18,7 +18,8 @@ class Scene {
     std::vector<Material> materials_;
     bitmap_image skybox_;
     // flat arrays behind abi()
-    mutable std::vector<float> vertices_, planes_, squares_, mats_;
+    mutable std::vector<float> vertices_, planes_, squares_, mats_, mats_ext_;
+    std::vector<float> weight_;  // per-pixel divisor of the last Render, row-major [y][x] (== samples_count without -RR)
     mutable std::vector<int32_t> mat_ids_;
 
 public:
@@ -34,5 +35,7 @@ public:
 
     PtScene abi() const;  // plain-data view for the C-ABI; valid until the scene is modified
     int Render(const PtConfig &cfg);  // the loop main.cpp:107-160 on the GPU; returns a PT_* code
+    // per-pixel divisor for the resolve, row-major [y][x]: samples_count, or the weight sum of a Russian-roulette render
+    const std::vector<float> &Weights() const { return weight_; }
 };
 #endif

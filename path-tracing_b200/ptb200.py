@@ -20,14 +20,15 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 # every symbol include/pt_render.h declares (tests check that the library exports all of them)
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
-               "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version"]
+               "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w"]
 
 
 class PtScene(C.Structure):
     _fields_ = [("n_triangles", C.c_int32), ("vertices", C.c_void_p), ("planes", C.c_void_p),
                 ("squares", C.c_void_p), ("material_ids", C.c_void_p), ("n_materials", C.c_int32),
                 ("materials", C.c_void_p), ("sky_width", C.c_int32), ("sky_height", C.c_int32),
-                ("sky_bgr", C.c_void_p)]
+                ("sky_bgr", C.c_void_p), ("materials_ext", C.c_void_p)]
 
 
 class PtConfig(C.Structure):
@@ -86,6 +87,11 @@ class Library:
         L.pt_scene_render_device.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p]
         L.pt_resolve_device.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_scene_render_device_w.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
+                                               C.c_void_p, C.c_void_p]
+        L.pt_resolve_device_w.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_render_accum_w.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]
         L.pt_scene_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
         L.pt_render.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p]
         L.pt_render_accum.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p]
@@ -124,6 +130,10 @@ class Library:
             keep["sky"] = np.ascontiguousarray(sc["sky"], np.uint8)
             s.sky_height, s.sky_width = keep["sky"].shape[:2]
             s.sky_bgr = keep["sky"].ctypes.data
+        if sc.get("mats_ext") is not None:  # extension: (m, 2) f32 = Ni, Tr per material
+            keep["mats_ext"] = np.ascontiguousarray(sc["mats_ext"], np.float32).reshape(-1, 2)
+            assert keep["mats_ext"].shape[0] == keep["mats"].shape[0]
+            s.materials_ext = keep["mats_ext"].ctypes.data
         s._keep = keep
         return s
 
@@ -142,6 +152,18 @@ class Library:
         s = self.scene_struct(sc)
         self.check(self.lib.pt_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data))
         return sm, s2, cnt
+
+    def render_accum_w(self, sc, cfg):
+        """-> sum, sum2, count, weight (the divisor under Russian roulette; == count otherwise)"""
+        H, W = cfg.height, cfg.width
+        sm = np.zeros((H, W, 3), np.float32)
+        s2 = np.zeros((H, W, 3), np.float32)
+        cnt = np.zeros((H, W), np.int32)
+        wt = np.zeros((H, W), np.float32)
+        s = self.scene_struct(sc)
+        self.check(self.lib.pt_render_accum_w(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data,
+                                              wt.ctypes.data))
+        return sm, s2, cnt, wt
 
     def intersect(self, sc, rays6, cfg=None):
         cfg = cfg or config()
@@ -201,13 +223,13 @@ class DeviceScene:
         lib.check(lib.lib.pt_scene_create(C.byref(s), C.byref(cfg), (1 if counters else 0) | (2 if timed else 0),
                                           C.byref(self.h)))
 
-    def render_device(self, cfg, d_sum3=0, d_sum2=0, d_count=0, stream=0):
+    def render_device(self, cfg, d_sum3=0, d_sum2=0, d_count=0, stream=0, d_weight=0):
         """Device pointers (ints, e.g. torch.Tensor.data_ptr()); asynchronous on `stream`."""
-        self.L.check(self.L.lib.pt_scene_render_device(self.h, C.byref(cfg), d_sum3 or None, d_sum2 or None,
-                                                       d_count or None, stream or None))
+        self.L.check(self.L.lib.pt_scene_render_device_w(self.h, C.byref(cfg), d_sum3 or None, d_sum2 or None,
+                                                         d_count or None, d_weight or None, stream or None))
 
-    def resolve_device(self, d_sum3, d_count, n_pixels, d_rgb, stream=0):
-        self.L.check(self.L.lib.pt_resolve_device(d_sum3, d_count, n_pixels, d_rgb, stream or None))
+    def resolve_device(self, d_sum3, d_count, n_pixels, d_rgb, stream=0, d_weight=0):
+        self.L.check(self.L.lib.pt_resolve_device_w(d_sum3, d_count, d_weight or None, n_pixels, d_rgb, stream or None))
 
     def intersect(self, rays6, cfg=None):
         cfg = cfg or config()

@@ -136,6 +136,21 @@ def glossy_mix():
     return _scene(tris, ids, mats)
 
 
+def glass_mix():
+    """C5 with the refractive extension: glossy_mix() where the short box is glass (Ni 1.5, Tr 0.8, tint Ks) and the
+    tall box a mirror/diffuse/refractive mix, so that all three lobes and every lobe-count case are exercised.
+    `mats_ext` rows are (Ni, Tr) per material (PtScene.materials_ext)."""
+    sc = glossy_mix()
+    sc["mats"][4] = mat((0.9, 0.9, 0.9), Ks=(0.95, 0.97, 0.95), Ns=200.0)   # mirror + diffuse + refract
+    sc["mats"][5] = mat((0.8, 0.8, 1), Ks=(0.9, 0.9, 1.0), Ns=1000.0)       # mirror + refract (no diffuse lobe)
+    ext = np.zeros((sc["mats"].shape[0], 2), np.float32)
+    ext[4] = (1.5, 0.8)
+    ext[5] = (1.33, 0.5)
+    ext[6] = (1.5, 1.0)                                                     # Ns 1000, Tr 1: chances (0, -, 1)
+    sc["mats_ext"] = ext
+    return sc
+
+
 def open_scene():
     """Skybox test scene (scene.cpp:125-156): the Cornell room without ceiling, back wall and light, so that most
     paths leave it; plus the two boxes.  No emitter: all radiance comes from the sky lookup."""

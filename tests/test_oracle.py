@@ -119,3 +119,37 @@ def test_oracle_vs_live_reference(oracle, reference):
     assert_bits_equal(os_, rs)
     assert_bits_equal(os2, rs2)
     assert oseg == rseg
+
+
+def test_extensions_default_to_the_reference(oracle):
+    """rr_depth = 0 and an all-zero materials_ext must not change a single bit (C5's extensions are opt-in)."""
+    sc = with_planes(scenes.glossy_mix(), oracle)
+    base = oracle.render_accum(sc, oracle.config(24, 16, 8, 12, 1e-4, 0.001, 7))
+    sc2 = dict(sc, mats_ext=np.zeros((sc["mats"].shape[0], 2), np.float32))
+    got = oracle.render_accum_w(sc2, oracle.config(24, 16, 8, 12, 1e-4, 0.001, 7, rr_depth=0))
+    for a, b in zip(base[:3], got[:3]):
+        assert_bits_equal(a, b)
+    assert np.array_equal(got[3], got[2].astype(np.float32))    # weight == count without roulette
+    assert base[3] == got[4]
+
+
+def test_russian_roulette_keeps_the_expectation(oracle):
+    """Extension (no reference semantics): the compensated throughput keeps E[sum of contributions per path]; the
+    weight sum is an unbiased (if heavy-tailed) estimate of the no-roulette contributing-path count."""
+    sc = with_planes(scenes.cornell(), oracle)
+    n_paths = 32 * 18 * 256
+    sm0, _, cnt0, wt0, segs0 = oracle.render_accum_w(sc, oracle.config(32, 18, 256, 16, 1e-4, -1.0, 42))
+    sm1, _, cnt1, wt1, segs1 = oracle.render_accum_w(sc, oracle.config(32, 18, 256, 16, 1e-4, -1.0, 42, rr_depth=6))
+    assert segs1 < 0.5 * segs0                                   # what roulette is for
+    assert abs(sm1.sum() / sm0.sum() - 1) < 0.02, (sm1.sum() / n_paths, sm0.sum() / n_paths)
+    # weights reach 20^k (p >= 0.05 per bounce): the sum converges slowly and sits below its mean at this sample count
+    assert 0.5 < wt1.sum() / wt0.sum() < 1.5
+    assert cnt1.sum() < cnt0.sum() and np.all(wt1 >= cnt1 - 1e-3)
+
+
+def test_refraction_lobe_runs_and_is_selected(oracle):
+    sc = with_planes(scenes.glass_mix(), oracle)
+    a = oracle.render_accum_w(sc, oracle.config(32, 18, 16, 16, 1e-4, -1.0, 42))
+    b = oracle.render_accum_w(dict(sc, mats_ext=None), oracle.config(32, 18, 16, 16, 1e-4, -1.0, 42))
+    assert np.isfinite(a[0]).all() and a[2].sum() > 0
+    assert not np.array_equal(a[0], b[0])                       # the glass boxes changed the image
