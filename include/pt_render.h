@@ -93,7 +93,9 @@ typedef struct PtConfig {
     int32_t n_gpus;       /* pt_render only: 0/1 = current device; N>1 = split samples over N devices of this
                              process and sum with one NCCL reduce */
     int32_t device;       /* first CUDA device ordinal */
-    int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant; others must be 0 */
+    int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant;
+                             [1]: 0 = automatic, 1..6 = log2 of the samples per pixel one wavefront step carries;
+                             [2], [3] must be 0 */
 } PtConfig;
 
 /* Statistics of the last render on a scene handle. */
@@ -173,6 +175,10 @@ int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float 
 int pt_philox(const uint32_t *ctr4, const uint32_t *key2, int64_t n, uint32_t *out4);
 int pt_sincos(const float *x, int64_t n, float *s, float *c);
 int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
+
+/* pt_render / pt_scene_destroy keep the last path-state workspace (up to 9.7 GB of HBM) for the next call on the same
+ * device; this frees it. */
+void pt_release_workspace(void);
 
 const char *pt_last_error(void);
 int pt_device_count(void);

@@ -49,6 +49,8 @@ class Oracle:
         L.or_resolve.argtypes = [_f32p, _i32p, C.c_void_p, C.c_long, _f32p]
         L.or_libm_sincos.argtypes = [_f32p, C.c_long, _f32p, _f32p]
         L.or_max_threads.restype = C.c_int
+        L.or_refract.restype = C.c_int
+        L.or_refract.argtypes = [_f32p, _f32p, C.c_float, _f32p]
 
     @staticmethod
     def scene_struct(sc):
@@ -141,6 +143,11 @@ class Oracle:
                             cnt.size, rgb)
         return rgb
 
+    def refract(self, d, n, eta):
+        out = np.zeros(3, np.float32)
+        tir = self.lib.or_refract(np.ascontiguousarray(d, np.float32), np.ascontiguousarray(n, np.float32), eta, out)
+        return out, bool(tir)
+
     def libm_sincos(self, x):
         x = np.ascontiguousarray(x, np.float32)
         s = np.empty_like(x)
@@ -174,6 +181,9 @@ class Reference:
         L.ref_trace_path.restype = C.c_int
         L.ref_trace_path.argtypes = [C.c_uint, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
         L.ref_max_threads.restype = C.c_int
+        L.ref_gauss_blur.argtypes = [C.c_int, C.c_int, _f32p, C.c_float, _f32p]
+        L.ref_median_filter.argtypes = [C.c_int, C.c_int, _f32p, C.c_int, _f32p]
+        L.ref_refract.argtypes = [_f32p, _f32p, C.c_float, _f32p]
         self.cfg = None
 
     @staticmethod
@@ -224,6 +234,24 @@ class Reference:
         d = np.zeros(3, np.float32)
         self.lib.ref_primary_ray(seed, x, y, s, o, d)
         return o, d
+
+    # main.cpp's free functions; images are (H, W, 3) float32
+    def gauss_blur(self, img, r):
+        img = np.ascontiguousarray(img, np.float32)
+        out = np.zeros_like(img)
+        self.lib.ref_gauss_blur(img.shape[1], img.shape[0], img, float(r), out)
+        return out
+
+    def median_filter(self, img, window):
+        img = np.ascontiguousarray(img, np.float32)
+        out = np.zeros_like(img)
+        self.lib.ref_median_filter(img.shape[1], img.shape[0], img, int(window), out)
+        return out
+
+    def refract(self, d, n, refractive):
+        out = np.zeros(3, np.float32)
+        self.lib.ref_refract(np.ascontiguousarray(d, np.float32), np.ascontiguousarray(n, np.float32), refractive, out)
+        return out
 
     def render_accum(self, seed=42, s_begin=0, s_end=None, s_step=1, threads=0, accumulate=False):
         W, H, spp, _ = self.cfg

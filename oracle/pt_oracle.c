@@ -205,6 +205,24 @@ static inline void ray_reflect(or_ray *r, const float begin[3], float dir[3], co
     r->depth++;
 }
 
+/* Refract, main.cpp:35-47 (dead code upstream; vec4 arithmetic with w = 0), for unit d and n with dot(n, d) <= 0.
+ * Returns 1 when it took the total-internal-reflection branch (glm::reflect).  One deviation: the radicand
+ * 1 - cos^2 is clamped at 0 (the reference would produce NaN when |cos| exceeds 1 by an ulp). */
+static inline int refract_dir(const float d[3], const float n[3], float eta, float dir[3]) {
+    const float cos_inc = -dot4w0(n, d);
+    const float sin_refr = eta * sqrtf(fmaxf(0.0f, 1.0f - cos_inc * cos_inc));
+    if (sin_refr > 1.0f) {
+        const float dn = dot4w0(n, d);
+        for (int k = 0; k < 3; ++k) dir[k] = d[k] - n[k] * dn * 2.0f;
+        return 1;
+    }
+    const float cos_refr = sqrtf(1.0f - sin_refr * sin_refr);
+    const float f = eta * cos_inc - cos_refr;
+    for (int k = 0; k < 3; ++k) dir[k] = d[k] * eta + n[k] * f;
+    return 0;
+}
+int or_refract(const float d[3], const float n[3], float eta, float dir[3]) { return refract_dir(d, n, eta, dir); }
+
 typedef struct {
     float sum[3], sum2[3];
     int count;
@@ -321,17 +339,10 @@ static inline void trace_ray(const or_scene *sc, const or_config *cfg, or_ray *r
         const float sgn = side < 0.0f ? 1.0f : -1.0f;
         const float n[3] = {N[0] * sgn, N[1] * sgn, N[2] * sgn};
         const float eta = side < 0.0f ? 1.0f / Ni : Ni;
-        const float cos_inc = -dot4w0(n, r->d);
-        const float sin_refr = eta * sqrtf(fmaxf(0.0f, 1.0f - cos_inc * cos_inc)); /* fmaxf: guards |cos| > 1 by an ulp */
         float dir[3], org[3];
-        if (sin_refr > 1.0f) { /* total internal reflection: reflect(d, n), stay on the incoming side */
-            const float dn = dot4w0(n, r->d);
-            for (int k = 0; k < 3; ++k) { dir[k] = r->d[k] - n[k] * dn * 2.0f; org[k] = P[k] + n[k] * eps; }
-        } else {
-            const float cos_refr = sqrtf(1.0f - sin_refr * sin_refr);
-            const float f = eta * cos_inc - cos_refr;
-            for (int k = 0; k < 3; ++k) { dir[k] = r->d[k] * eta + n[k] * f; org[k] = P[k] - n[k] * eps; }
-        }
+        const int tir = refract_dir(r->d, n, eta, dir);
+        /* total internal reflection stays on the incoming side, a refracted ray starts behind the surface */
+        for (int k = 0; k < 3; ++k) org[k] = tir ? P[k] + n[k] * eps : P[k] - n[k] * eps;
         ray_reflect(r, org, dir, Ks);
     }
     russian_roulette(cfg, r, g);

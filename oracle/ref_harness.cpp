@@ -253,4 +253,36 @@ int ref_trace_path(unsigned seed, int x, int y, int s, int max_seg, float *rec9)
 
 int ref_max_threads() { return omp_get_max_threads(); }
 
+// ---- main.cpp's free functions (compiled from the reference's own main.cpp, main() renamed) ----
+// images cross as row-major [y][x] float rgb; the reference indexes its maps [x][y]
+static std::vector<std::vector<vec3>> to_map(const float *rgb, int W, int H) {
+    std::vector<std::vector<vec3>> m(W, std::vector<vec3>(H));
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) m[x][y] = vec3(rgb[3 * (y * W + x)], rgb[3 * (y * W + x) + 1], rgb[3 * (y * W + x) + 2]);
+    return m;
+}
+static void from_map(const std::vector<std::vector<vec3>> &m, int W, int H, float *rgb) {
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            rgb[3 * (y * W + x)] = m[x][y].x; rgb[3 * (y * W + x) + 1] = m[x][y].y; rgb[3 * (y * W + x) + 2] = m[x][y].z;
+        }
+}
+}  // extern "C"
+std::vector<std::vector<vec3>> GaussBlur(std::vector<std::vector<vec3>> color_map, float r);          // main.cpp:11-33
+std::vector<std::vector<vec3>> MedianFilter(std::vector<std::vector<vec3>> color_map, int window_size);  // main.cpp:49-80
+vec4 Refract(vec4 incidence_direction, vec4 normal, float refractive);                                 // main.cpp:35-47
+extern "C" {
+void ref_gauss_blur(int W, int H, const float *rgb_in, float r, float *rgb_out) {
+    Config::get().width = W; Config::get().height = H;
+    from_map(GaussBlur(to_map(rgb_in, W, H), r), W, H, rgb_out);
+}
+void ref_median_filter(int W, int H, const float *rgb_in, int window, float *rgb_out) {
+    Config::get().width = W; Config::get().height = H;
+    from_map(MedianFilter(to_map(rgb_in, W, H), window), W, H, rgb_out);
+}
+void ref_refract(const float *d3, const float *n3, float refractive, float *out3) {
+    const vec4 r = Refract(vec4(d3[0], d3[1], d3[2], 0.0f), vec4(n3[0], n3[1], n3[2], 0.0f), refractive);
+    out3[0] = r.x; out3[1] = r.y; out3[2] = r.z;
+}
+
 }  // extern "C"

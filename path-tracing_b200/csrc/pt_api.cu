@@ -4,6 +4,9 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <chrono>
+#include <mutex>
+#include <stdlib.h>
 #include <vector>
 
 #include "../../include/pt_render.h"
@@ -52,6 +55,7 @@ struct DevBuf {  // RAII device allocation
     ~DevBuf() { if (p) cudaFree(p); }
     cudaError_t alloc(size_t n) { return cudaMalloc((void **)&p, (n ? n : 1) * sizeof(T)); }
     T *release() { T *q = p; p = nullptr; return q; }
+    void free() { if (p) cudaFree(p); p = nullptr; }
 };
 
 }  // namespace
@@ -80,7 +84,7 @@ struct PtDeviceScene {
     // wavefront workspace (path state, queues, per-pixel accumulators), sized on first use
     WfState wf{};
     void *wf_mem = nullptr;
-    size_t wf_slots = 0, wf_pixels = 0;
+    size_t wf_slots = 0, wf_pixels = 0, wf_bytes = 0;
     int *h_counters = nullptr;  // pinned, 6 ints
     int traverse_blocks = 0;
 };
@@ -108,6 +112,8 @@ static int validate_config(const PtConfig *c) {
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
     if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
     if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
+    if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] || c->reserved[3])
+        return fail(PT_EINVAL, "reserved[1] must be 0..6 (log2 samples per wavefront step), reserved[2..3] zero");
     return PT_OK;
 }
 
@@ -119,15 +125,46 @@ extern "C" int pt_device_count(void) {
     return n;
 }
 
+// One released workspace per process is kept for the next scene handle on the same device (pt_render creates and
+// destroys a handle per call; re-allocating gigabytes of path state every call costs more than a small frame).
+struct WorkspaceCache { void *mem = nullptr; size_t bytes = 0; int device = -1; };
+static WorkspaceCache g_ws;
+static std::mutex g_ws_mutex;
+
+static void ws_release(void *mem, size_t bytes, int device) {
+    if (!mem) return;
+    std::lock_guard<std::mutex> lock(g_ws_mutex);
+    if (g_ws.mem && g_ws.bytes >= bytes) { cudaFree(mem); return; }
+    if (g_ws.mem) cudaFree(g_ws.mem);
+    g_ws.mem = mem; g_ws.bytes = bytes; g_ws.device = device;
+}
+
+extern "C" void pt_release_workspace(void) {
+    std::lock_guard<std::mutex> lock(g_ws_mutex);
+    if (g_ws.mem) cudaFree(g_ws.mem);
+    g_ws = WorkspaceCache();
+}
+
 extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     if (!ds) return;
+    const bool prof = getenv("PT_PROFILE") != nullptr;
+    auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (!prof) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[pt_scene_destroy] %-12s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    };
     cudaFree(ds->tris);
     cudaFree(ds->nodes);
     cudaFree(ds->mats);
     cudaFree(ds->lrecs);
     cudaFree(ds->sky);
-    cudaFree(ds->wf_mem);
+    lap("scene arrays");
+    ws_release(ds->wf_mem, ds->wf_bytes, ds->device);
+    lap("workspace");
     if (ds->h_counters) cudaFreeHost(ds->h_counters);
+    lap("pinned");
     cudaFree(ds->stats);
     if (ds->ev0) cudaEventDestroy(ds->ev0);
     if (ds->ev1) cudaEventDestroy(ds->ev1);
@@ -299,21 +336,36 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     rp.seed = cfg->seed;
     rp.sum3 = d_sum3; rp.sum2_3 = d_sum2; rp.count = d_count;
     rp.stats = stats;
+    // samples per wavefront step: reserved[1] = log2 (1..6) overrides; otherwise up to 64 for a flat-spp render (the
+    // largest power of two <= the samples this rank traces), 4 when the adaptive rule can discard samples traced
+    // ahead of it
+    const int per_rank = cfg->rays_per_pixel / (cfg->sample_step > 0 ? cfg->sample_step : 1);
+    int q_auto = 2;
+    if (cfg->error < 0.0f) while (q_auto < 6 && (2 << q_auto) <= per_rank) ++q_auto;
+    rp.q_shift = cfg->reserved[1] ? cfg->reserved[1] : q_auto;
     rp.rr_depth = cfg->rr_depth;
     rp.weight = d_weight;
     return rp;
 }
 
-constexpr size_t kMaxSlots = (size_t)1 << 24;  // path slots in flight (64 B of state each)
+constexpr size_t kMaxSlots = (size_t)1 << 27;  // path slots in flight (64 B of state + 8 B of queue each: <= 9.7 GB)
 
-static int wf_reserve(PtDeviceScene *ds, size_t npx) {
-    const size_t npc = std::min(npx, kMaxSlots / 4), slots = 4 * npc;
-    if (ds->wf_mem && ds->wf_slots >= slots && ds->wf_pixels >= npx) return PT_OK;
-    if (ds->wf_mem) { CK(cudaDeviceSynchronize()); CK(cudaFree(ds->wf_mem)); ds->wf_mem = nullptr; }
+static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
+    const size_t npc = std::min(npx, kMaxSlots >> q_shift), slots = npc << q_shift;
     const size_t npx4 = (npx + 3) & ~(size_t)3;  // keeps the queue 16-byte aligned behind the per-pixel weights
     const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) +
                          npx4 * sizeof(float) + 256;
-    CK(cudaMalloc(&ds->wf_mem, bytes));
+    if (!ds->wf_mem || ds->wf_bytes < bytes) {
+        if (ds->wf_mem) { CK(cudaDeviceSynchronize()); CK(cudaFree(ds->wf_mem)); ds->wf_mem = nullptr; ds->wf_bytes = 0; }
+        {
+            std::lock_guard<std::mutex> lock(g_ws_mutex);
+            if (g_ws.mem && g_ws.device == ds->device && g_ws.bytes >= bytes) {
+                ds->wf_mem = g_ws.mem; ds->wf_bytes = g_ws.bytes;
+                g_ws = WorkspaceCache();
+            }
+        }
+        if (!ds->wf_mem) { CK(cudaMalloc(&ds->wf_mem, bytes)); ds->wf_bytes = bytes; }
+    }
     char *p = (char *)ds->wf_mem;
     WfState &w = ds->wf;
     w.oT = (float4 *)p; p += slots * sizeof(float4);
@@ -342,10 +394,11 @@ template <bool COUNT>
 static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStream_t st, int *launches) {
     const size_t npx = (size_t)rp.W * rp.H;
     int rc;
-    if ((rc = wf_reserve(ds, npx))) return rc;
+    if ((rc = wf_reserve(ds, npx, rp.q_shift))) return rc;
+    const int Q = 1 << rp.q_shift;
     const WfState wf = ds->wf;
     const SceneView &sc = ds->view;
-    const int npc_max = (int)(ds->wf_slots / 4);
+    const int npc_max = (int)(ds->wf_slots >> rp.q_shift);
     int n = 0;
     k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp.s_begin);
     ++n;
@@ -388,10 +441,10 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
     for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
         const int npix = (int)std::min<size_t>(npc_max, npx - pix0);
-        const int slot_blocks = blocks_for(4LL * npix, 256);
+        const int slot_blocks = blocks_for((long long)npix << rp.q_shift, 256);
         int remaining = total;
         while (remaining > 0) {
-            const int steps = (remaining + 3) / 4;
+            const int steps = (remaining + Q - 1) / Q;
             for (int i = 0; i < steps; ++i) {
                 if ((rc = tick(0))) return rc;
                 k_wf_begin<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix);
@@ -561,18 +614,36 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
+    const bool prof = getenv("PT_PROFILE") != nullptr;  // wall-clock phase times on stderr
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    auto lap = [&](const char *what) {
+        if (!prof) return;
+        cudaDeviceSynchronize();
+        const auto t1 = clk::now();
+        fprintf(stderr, "[pt_render] %-14s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    };
     PtDeviceScene *ds = nullptr;
     if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
     struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    lap("scene_create");
     const size_t px = (size_t)cfg->width * cfg->height;
     DevBuf<float> d_sum, d_rgb, d_wt;
     DevBuf<int> d_cnt;
     CK(d_sum.alloc(3 * px)); CK(d_rgb.alloc(3 * px)); CK(d_cnt.alloc(px));
     const bool rr = cfg->rr_depth > 0;  // the divisor is then the weight sum
     if (rr) CK(d_wt.alloc(px));
+    lap("frame buffers");
     if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, nullptr, d_cnt.p, rr ? d_wt.p : nullptr, nullptr))) return rc;
+    lap("render");
     if ((rc = pt_resolve_device_w(d_sum.p, d_cnt.p, rr ? d_wt.p : nullptr, (int64_t)px, d_rgb.p, nullptr))) return rc;
     CK(cudaMemcpy(rgb, d_rgb.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
+    lap("resolve + d2h");
+    pt_scene_destroy(ds);
+    guard.p = nullptr;
+    d_sum.free(); d_rgb.free(); d_wt.free(); d_cnt.free();
+    lap("release");
     return PT_OK;
 }
 

@@ -26,6 +26,7 @@ struct RenderParams {
     float *sum3, *sum2_3;
     int *count;
     unsigned long long *stats;  // [0] committed segments, [1] traced segments, [2] nodes, [3] tris
+    int q_shift;    // wavefront pipeline: 2^q_shift consecutive samples of a pixel per step
     int rr_depth;   // extension: Russian roulette once Ray::depth >= rr_depth (0 = off, the reference)
     float *weight;  // extension: per-pixel sum of the contributing paths' RR weights (== count without RR)
 };

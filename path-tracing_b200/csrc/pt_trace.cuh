@@ -166,12 +166,36 @@ __device__ __forceinline__ bool reaches_root(const SceneView &sc, V3 o, V3 d, fl
            box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, tmax) < inf;
 }
 
-// One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
+// The triangles of one leaf: plane distances of all of them first (cheap, same instructions for every lane), then
+// the reference's exact test on those whose distance can still win (up to kLeafMax records, contiguous).
 template <bool COUNT>
-__device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o, V3 d, V3 inv, float eps, Hit &h,
-                                             int *stack, int &sp, unsigned long long &n_nodes,
-                                             unsigned long long &n_tris) {
-    if (cur >= 0) {
+__device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3 d, float eps, Hit &h,
+                                          unsigned long long &n_tris) {
+    const int first = leaf_first(ref), cnt = leaf_count(ref);
+    unsigned mask = 0u;
+    // all plane rows first (independent loads in flight together), then the arithmetic
+    float4 pl[kLeafMax];
+#pragma unroll
+    for (int k = 0; k < kLeafMax; ++k)
+        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int k = 0; k < kLeafMax; ++k) {
+        const float nd = plane_distance(pl[k], o, d);
+        mask |= (unsigned)(k < cnt && nd <= h.t && !(nd < eps)) << k;
+    }
+    while (mask) {
+        const int k = __ffs(mask) - 1;
+        mask &= mask - 1u;
+        tri_intersect_ref(sc.tris + 4 * (size_t)(first + k), first + k, o, d, eps, h);
+    }
+    if (COUNT) n_tris += cnt;
+}
+
+// One step on the inner node `cur` (>= 0); returns the next ref: a node, a leaf (< 0) or kRefEmpty when the stack ran out.
+template <bool COUNT>
+__device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 inv, const Hit &h, int *stack, int &sp,
+                                         unsigned long long &n_nodes) {
+    {
         const float4 *nd = sc.nodes + 4 * (size_t)cur;
         const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3);
         if (COUNT) ++n_nodes;
@@ -189,19 +213,15 @@ __device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o,
         if (g1) return c1;
         return sp ? stack[--sp] : kRefEmpty;
     }
-    // leaf: same scan + resolve split as large_phase (up to kLeafMax records, contiguous)
-    const int first = leaf_first(cur), cnt = leaf_count(cur);
-    unsigned mask = 0u;
-    for (int k = 0; k < cnt; ++k) {
-        const float nd = plane_distance(__ldg(sc.tris + 4 * (size_t)(first + k)), o, d);
-        mask |= (unsigned)(nd <= h.t && !(nd < eps)) << k;
-    }
-    while (mask) {
-        const int k = __ffs(mask) - 1;
-        mask &= mask - 1u;
-        tri_intersect_ref(sc.tris + 4 * (size_t)(first + k), first + k, o, d, eps, h);
-    }
-    if (COUNT) n_tris += cnt;
+}
+
+// One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
+template <bool COUNT>
+__device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o, V3 d, V3 inv, float eps, Hit &h,
+                                             int *stack, int &sp, unsigned long long &n_nodes,
+                                             unsigned long long &n_tris) {
+    if (cur >= 0) return node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
+    leaf_step<COUNT>(sc, cur, o, d, eps, h, n_tris);
     return sp ? stack[--sp] : kRefEmpty;
 }
 

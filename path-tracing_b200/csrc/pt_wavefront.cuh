@@ -6,7 +6,7 @@
 // changes, and path state lives in HBM between the stages (64 B per path, ~100 B of traffic per segment: a few
 // percent of the frame time at 6.5 TB/s):
 //
-//   k_wf_begin     per path slot (pixel x 4 consecutive samples): adaptive-skip decision from the pixel's
+//   k_wf_begin     per path slot (pixel x Q consecutive samples): adaptive-skip decision from the pixel's
 //                  accumulators, jittered primary ray (main.cpp:118-129), then `front`:
 //     front        large triangles from shared memory (pt_trace.cuh large_phase), LBVH root test, and a
 //                  warp-ballot compaction of the rays that must walk the tree into a global queue
@@ -14,14 +14,16 @@
 //                  finishes (dynamic fetch), so the walk runs with full warps whatever fraction of rays got here
 //   k_wf_bounce    per path slot: shade the hit (Material::Process and the closures, pt_kernels.cuh shade), spawn the
 //                  next segment and run `front` on it
-//   k_wf_commit    per pixel: the ordered commit of the 4 samples (see pt_kernels.cuh header): exact replay of the
+//   k_wf_commit    per pixel: the ordered commit of the Q samples (see pt_kernels.cuh header): exact replay of the
 //                  adaptive rule and of the fp32 accumulation order of material.h:74-77
 //
 // Path state, queues and accumulators are streamed with evict-first loads/stores (ld.global.cs / st.global.cs) so
 // that they do not push the LBVH out of L2 between two traverse launches.
 //
 // One step = begin + max_depth x (traverse, bounce) + commit over all pixels of a chunk; steps repeat until every
-// pixel has consumed its samples.
+// pixel has consumed its samples.  A step carries Q = 2^q_shift consecutive samples of every pixel: 4 when the
+// adaptive rule is on (samples traced ahead of the rule may be discarded), more in a flat-spp render (bigger
+// traversal batches: fewer, fuller launches — up to 64, 9.5 GB of path state at 1080p).
 #pragma once
 #include "pt_kernels.cuh"
 
@@ -90,12 +92,12 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2] = 0; wf.counters[3] = 0; }  // the other queue
     __syncthreads();
     const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool in_range = slot < 4 * npix;
+    const bool in_range = slot < (npix << rp.q_shift);
     unsigned long long n_nodes = 0, n_tris = 0;
     bool traced = false;
     V3 o = mk(0.0f, 0.0f, -20.0f), d = mk(0.0f, 0.0f, 1.0f);
     if (in_range) {
-        const int p = pix0 + (slot >> 2), q = slot & 3;
+        const int p = pix0 + (slot >> rp.q_shift), q = slot & ((1 << rp.q_shift) - 1);
         const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
         const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
         const int s = s_next + q * rp.s_step;
@@ -138,7 +140,7 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
     unsigned long long n_nodes = 0, n_tris = 0;
     bool alive = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
-    if (slot < 4 * npix) {
+    if (slot < (npix << rp.q_shift)) {
         const float4 tn = __ldcs(&wf.Tn[slot]);
         int flags = __float_as_int(tn.w);
         if (flags & WF_ALIVE) {
@@ -149,7 +151,7 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
             int depth = flags & 0xffff;
             Hit h;
             h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
-            const int p = pix0 + (slot >> 2), q = slot & 3;
+            const int p = pix0 + (slot >> rp.q_shift), q = slot & ((1 << rp.q_shift) - 1);
             const int s = __float_as_int(__ldcs(&wf.acc2[p].w)) + q * rp.s_step;
             bool contrib = false;
             const bool rr_on = rp.rr_depth > 0;  // the path weight lives in cS.w; it is 1 unless roulette has been played
@@ -180,9 +182,20 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
     }
 }
 
-constexpr int kNodeBurst = 4;  // inner-node steps between two refill checks
+#ifndef PT_NODE_BURST
+#define PT_NODE_BURST 8      // upper bound of inner-node steps between two refill checks
+#endif
+#ifndef PT_MIN_NODE_LANES
+#define PT_MIN_NODE_LANES 8   // the node phase ends when fewer lanes than this can still take a node step
+#endif
+constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
 
-// persistent warps over queue `set`: one ray per lane, refilled as lanes finish
+// persistent warps over queue `set`: one ray per lane, refilled as lanes finish.
+// while-while with a postponed leaf (Aila & Laine 2009, "speculative traversal"): a lane that reaches a leaf parks
+// it and keeps walking inner nodes until it reaches a second one; the warp switches to the leaf phase only when few
+// lanes can still take a node step, so that the expensive exact triangle tests run with most lanes active (the
+// first version of this kernel ran them with 3 of 32, profiles/r01_wf_sass_traverse_torus1m.txt).  Walking on
+// with a not-yet-shortened t only visits extra nodes: the nearest-hit rule is order independent (pt_trace.cuh).
 template <bool COUNT>
 __global__ void __launch_bounds__(128)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
@@ -192,13 +205,13 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
     int stack[kStackDepth];
-    int sp = 0, cur = kRefEmpty, slot = -1;
+    int sp = 0, cur = kRefEmpty, leaf = 0, slot = -1;  // leaf refs are negative: 0 = no parked leaf
     bool done = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 1);
     Hit h = no_hit();
     unsigned long long n_nodes = 0, n_tris = 0, ray_nodes0 = 0;
     while (true) {
-        const bool need = !done && cur == kRefEmpty;
+        const bool need = !done && cur == kRefEmpty && leaf == 0;
         if (need && slot >= 0) {  // retire the finished ray
             if (COUNT && stats) {
                 atomicAdd(&stats[4], 1ull);
@@ -234,13 +247,29 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             }
         }
         if (__all_sync(0xffffffffu, done)) break;
-        // while-while (Aila & Laine 2009): walk inner nodes until this lane holds a leaf (or nothing), then do the
-        // leaves of all lanes together
-        // (bounded, so that a lane that ran out of work is refilled after a few node steps of its neighbours)
+        // ---- node phase
 #pragma unroll 1
-        for (int it = 0; it < kNodeBurst && cur >= 0 && cur != kRefEmpty; ++it)
-            cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
-        if (cur < 0) cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
+        for (int it = 0; it < kNodeBurst; ++it) {
+            if (cur < 0 && leaf == 0) {  // park the leaf, go on with the next subtree
+                leaf = cur;
+                cur = sp ? stack[--sp] : kRefEmpty;
+            }
+            const bool can = cur >= 0 && cur != kRefEmpty;
+            const unsigned cm = __ballot_sync(0xffffffffu, can);
+            if (cm == 0u || (it > 0 && __popc(cm) < kMinNodeLanes)) break;
+            if (can) cur = node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
+        }
+        if (cur < 0 && leaf == 0) {
+            leaf = cur;
+            cur = sp ? stack[--sp] : kRefEmpty;
+        }
+        // ---- leaf phase: every parked leaf
+        if (__any_sync(0xffffffffu, leaf != 0)) {
+            if (leaf != 0) {
+                leaf_step<COUNT>(sc, leaf, o, d, eps, h, n_tris);
+                leaf = 0;
+            }
+        }
     }
     if (COUNT && stats) {
         for (int o2 = 16; o2; o2 >>= 1) {
@@ -265,9 +294,10 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
         const bool rr_on = rp.rr_depth > 0;
         float wsum = rr_on ? __ldcs(&wf.accw[p]) : 0.0f;
         bool stop = false;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const int slot = 4 * i + j;
+        const int Q = 1 << rp.q_shift;
+#pragma unroll 4
+        for (int j = 0; j < Q; ++j) {
+            const int slot = (i << rp.q_shift) + j;
             const int flags = __float_as_int(__ldcs(&wf.Tn[slot].w));
             const float4 c = __ldcs(&wf.cS[slot]);
             const int nseg = (flags & 0xffff) + ((flags & WF_SHADE_END) ? 1 : 0);

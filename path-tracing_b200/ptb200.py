@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-RENDER_SO = os.path.join(HERE, "lib", "libptrender.so")
+RENDER_SO = os.environ.get("PTB200_RENDER_SO") or os.path.join(HERE, "lib", "libptrender.so")
 HOST_SO = os.path.join(HERE, "lib", "libpthost.so")
 
 PT_ACCEL_AUTO, PT_ACCEL_BRUTE, PT_ACCEL_LBVH = 0, 1, 2
@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace"]
 
 
 class PtScene(C.Structure):
@@ -55,7 +55,7 @@ class PtError(RuntimeError):
 
 def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
            sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0,
-           mode=0):
+           mode=0, q_shift=0):
     """PtConfig with the reference's defaults (config.h:10,16-29)."""
     c = PtConfig()
     c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
@@ -63,6 +63,7 @@ def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, se
     c.sample_begin, c.sample_step = sample_begin, sample_step
     c.intersector, c.accel, c.rr_depth, c.n_gpus, c.device = intersector, accel, rr_depth, n_gpus, device
     c.reserved[0] = mode  # 0 = wavefront pipeline, 1 = megakernel variant
+    c.reserved[1] = q_shift  # 0 = automatic, else log2(samples per pixel per wavefront step)
     return c
 
 

@@ -161,6 +161,25 @@ def test_extensions_vs_oracle(lib, oracle, case, accel, mode):
     ds.close()
 
 
+@pytest.mark.parametrize("q_shift", [1, 3, 4, 5])
+@pytest.mark.parametrize("error", [-1.0, 0.001])
+def test_samples_per_step_do_not_change_the_result(lib, oracle, q_shift, error):
+    """The wavefront pipeline carries 2^q_shift samples of every pixel per step; the ordered commit must make that
+    invisible, with and without the adaptive rule, also when spp is not a multiple of the step."""
+    sc = scenes.torus_room(24, 12)
+    osc = with_planes(sc, oracle)
+    osm, os2, ocnt, segs, _ = oracle.render_accum(osc, oracle.config(40, 24, 37, 8, 1e-4, error, 9))
+    cfg = ptb200.config(40, 24, 37, 8, 1e-4, error, seed=9, q_shift=q_shift)
+    sm, s2, cnt = lib.render_accum(sc, cfg)
+    assert_bits_equal(cnt, ocnt)
+    assert_bits_equal(sm, osm)
+    assert_bits_equal(s2, os2)
+    ds = lib.scene_create(sc, cfg)
+    ds.render_device(cfg)
+    assert ds.stats()["segments"] == segs
+    ds.close()
+
+
 def test_ragged_and_empty_inputs(lib, oracle):
     sc = scenes.cornell()
     # image sizes that are not multiples of the 8x8 tile, 1 sample, depth 1

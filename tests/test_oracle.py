@@ -153,3 +153,21 @@ def test_refraction_lobe_runs_and_is_selected(oracle):
     b = oracle.render_accum_w(dict(sc, mats_ext=None), oracle.config(32, 18, 16, 16, 1e-4, -1.0, 42))
     assert np.isfinite(a[0]).all() and a[2].sum() > 0
     assert not np.array_equal(a[0], b[0])                       # the glass boxes changed the image
+
+
+def test_refract_matches_the_references_dead_code(oracle, reference):
+    """The refractive lobe's direction arithmetic against Refract() of the reference's own main.cpp (:35-47, never
+    called upstream), both branches, bit for bit."""
+    rng = np.random.default_rng(5)
+    n_tir = 0
+    for _ in range(4000):
+        n = rng.normal(size=3); n /= np.linalg.norm(n)
+        d = rng.normal(size=3); d /= np.linalg.norm(d)
+        if np.dot(n, d) > 0:
+            n = -n
+        n, d = n.astype(np.float32), d.astype(np.float32)
+        eta = float(np.float32(rng.choice([1 / 1.5, 1.5, 1.33, 1 / 1.33, 2.4])))
+        got, tir = oracle.refract(d, n, eta)
+        n_tir += tir
+        assert_bits_equal(got, reference.refract(d, n, eta))
+    assert 0 < n_tir < 4000
