@@ -390,7 +390,7 @@ def main():
                "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                "config": {"workload": desc, "width": W, "height": H, "spp": spp, "max_depth": depth, "triangles": int(sc["verts"].shape[0]),
                           "accel": {1: "brute-force (shared memory)", 2: "GPU LBVH"}[st["accel"]], "bvh_nodes": st["n_nodes"],
-                          "large_tris_in_smem": st["n_large"], "intersector": "reference-exact (triangles.h:48-73)",
+                          "large_tris_in_smem": st["n_large"], "quad_scan_units": st["n_quads"], "intersector": "reference-exact (triangles.h:48-73)",
                           "l2": "flushed between iterations (256 MiB fill inside the timed region)",
                           "parallelism": f"spp split over {world} GPU(s), one NCCL reduce" if world > 1 else "1 GPU",
                           "segments_per_frame": segments_per_step},

@@ -119,6 +119,8 @@ typedef struct PtStats {
      * floor(log2(1 + nodes visited)) */
     uint64_t rays_queued;
     uint64_t node_hist[16];
+    int32_t n_quads;          /* of the n_large shared-memory triangles, 2 n_quads are scanned as quad units */
+    int32_t reserved0;
 } PtStats;
 
 typedef struct PtDeviceScene PtDeviceScene; /* opaque: device-resident SoA triangles, materials, LBVH */

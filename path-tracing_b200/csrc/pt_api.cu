@@ -246,7 +246,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         DevBuf<unsigned char> tmp;
         DevBuf<float4> d_root;
         CK(d_root.alloc(2));
-        CK(cudaMalloc((void **)&ds->lrecs, (size_t)kLargeStride * kMaxLarge * sizeof(float4)));
+        CK(cudaMalloc((void **)&ds->lrecs, (size_t)kLargeRowsMax * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
         CK(vals.alloc(n)); CK(vals2.alloc(n));
         k_init_scratch<<<1, 1>>>(d_scr.p);
@@ -264,12 +264,14 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         const int n_large = std::min(scr.n_large, kMaxLarge);
         const int nb = n - n_large;
         v.brute = 0; v.n_bvh = nb; v.n_large = n_large;
+        if (n_large) {  // pairs the large triangles into quad scan units and reorders the tail of vals2 accordingly
+            k_large_pack<<<1, kMaxLarge>>>(vals2.p, d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb, n_large, eps, d_scr.p, ds->lrecs);
+            ++launches;
+            CK(cudaMemcpy(&scr, d_scr.p, sizeof scr, cudaMemcpyDeviceToHost));
+            v.n_quads = scr.n_quads;
+        }
         k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, vals2.p, n, ds->tris);
         ++launches;
-        if (n_large) {
-            k_large_pack<<<1, 64>>>(vals2.p, d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb, n_large, eps, d_scr.p, ds->lrecs);
-            ++launches;
-        }
         if (nb == 0) {
             v.root = kRefEmpty;
         } else if (nb <= kLeafMax) {
@@ -539,6 +541,7 @@ extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
     out->n_nodes = ds->n_nodes; out->n_large = ds->view.n_large; out->accel = ds->accel;
     out->launches = ds->launches;
     out->rays_queued = st[4];
+    out->n_quads = ds->view.n_quads;
     for (int c = 0; c < 16; ++c) out->node_hist[c] = st[5 + c];
     for (int c = 0; c < 4; ++c) { out->class_ms[c] = ds->class_ms[c]; out->class_launches[c] = ds->class_launches[c]; }
     return PT_OK;

@@ -48,15 +48,15 @@ __device__ __forceinline__ int f2ord(float f) {
 }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
-struct BuildScratch {  // 8 ints: scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, pad
-    int lo[3], hi[3], n_large, pad;
+struct BuildScratch {  // 8 ints: scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, quad units
+    int lo[3], hi[3], n_large, n_quads;
 };
 
 __global__ void k_init_scratch(BuildScratch *s) {
     s->lo[0] = s->lo[1] = s->lo[2] = f2ord(FLT_MAX);
     s->hi[0] = s->hi[1] = s->hi[2] = f2ord(-FLT_MAX);
     s->n_large = 0;
-    s->pad = 0;
+    s->n_quads = 0;
 }
 
 __global__ void k_vertex_bounds(const float *__restrict__ verts, int n, BuildScratch *s) {
@@ -279,43 +279,159 @@ __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__res
     o[3] = make_float4(v[6], v[7], v[8], __int_as_float(mat_ids[i]));
 }
 
-// Shared-memory image of the large triangles (sorted positions [nb, nb + n_large)): the 4 record rows followed by
-// three EDGE PLANES (m_i, w_i): m_i is the in-plane inward unit normal of edge i, and every point the reference's test
-// can accept satisfies m_i . P + w_i >= 0.  w_i already contains the dilation of that edge, eps'/(2 L_i) (the accepted
-// hexagon of the header comment is bounded by the three offset edge lines; a displacement along the triangle's normal
-// does not change m_i . P), plus 64 ulp of the largest coordinate for the fp32 evaluation.
-__global__ void k_large_pack(const int *__restrict__ vals, const float *__restrict__ verts,
-                             const float4 *__restrict__ planes, const float *__restrict__ squares,
-                             const int *__restrict__ mat_ids, int nb, int n_large, float eps, const BuildScratch *s,
-                             float4 *__restrict__ lrecs) {
-    const int k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n_large) return;
-    const int i = vals[nb + k];
-    const float *v = verts + 9 * (size_t)i;
-    const V3 p[3] = {mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8])};
-    const float S = squares[i];
-    float4 *o = lrecs + kLargeStride * (size_t)k;
-    o[0] = planes[i];
-    o[1] = make_float4(p[0].x, p[0].y, p[0].z, S);
-    o[2] = make_float4(p[1].x, p[1].y, p[1].z, __int_as_float(i));
-    o[3] = make_float4(p[2].x, p[2].y, p[2].z, __int_as_float(mat_ids[i]));
+// ---- shared-memory image of the large triangles (layout: pt_scene.cuh) -----------------------------------------
+// EDGE PLANES (m, w): m is the in-plane inward unit normal of an edge, and every point the reference's test can accept
+// satisfies m . P + w >= 0.  w already contains the dilation of that edge, eps'/(2 L) (the accepted hexagon of the
+// header comment is bounded by the three offset edge lines; a displacement along the triangle's normal does not
+// change m . P), plus 64 ulp of the largest coordinate for the fp32 evaluation.
+struct LargeTri {
+    V3 p[3];
+    float4 plane;
+    float S;
+    int idx, mat;
+};
+
+__device__ __forceinline__ float4 edge_plane(const LargeTri &t, int j, V3 ng, bool ok, float e, float slack) {
+    const V3 a = t.p[j], b = t.p[(j + 1) % 3], c = t.p[(j + 2) % 3];
+    const V3 ab = b - a;
+    const float L = length3(ab);
+    V3 m = normalize3(cross3(ng, ab));
+    if (dot3(m, c - a) < 0.0f) m = m * -1.0f;
+    const float w = -dot3(m, a) + 1.05f * e / (2.0f * L) + slack;
+    // degenerate triangle: a plane that accepts everything (the exact test decides)
+    return (ok && L > 0.0f && m.x == m.x) ? make_float4(m.x, m.y, m.z, w) : make_float4(0.f, 0.f, 0.f, 1.0f);
+}
+__device__ __forceinline__ bool same_point(V3 a, V3 b) { return a.x == b.x && a.y == b.y && a.z == b.z; }
+// index of the edge (p[j], p[j+1]) of `t` whose two end points are both vertices of `u`; -1 unless exactly two are shared
+__device__ __forceinline__ int shared_edge(const LargeTri &t, const LargeTri &u) {
+    bool in[3];
+    int n = 0;
+    for (int k = 0; k < 3; ++k) {
+        in[k] = same_point(t.p[k], u.p[0]) || same_point(t.p[k], u.p[1]) || same_point(t.p[k], u.p[2]);
+        n += in[k];
+    }
+    if (n != 2) return -1;
+    return in[0] && in[1] ? 0 : in[1] && in[2] ? 1 : 2;
+}
+__device__ __forceinline__ float tri_e(const LargeTri &t, float eps) { return eps * 1.01f + 4e-6f * (t.S + eps); }
+// largest value of the plane function f over the region of t's plane the reference can accept (the dilated hexagon
+// v_k + (v_k - v_j) e / (2 S)); with `absolute`, of |f|
+__device__ __forceinline__ float max_over_hexagon(const LargeTri &t, float eps, float4 f, bool absolute) {
+    const float lam = 1.05f * tri_e(t, eps) / (2.0f * t.S);
+    float best = -FLT_MAX;
+    for (int k = 0; k < 3; ++k)
+        for (int j = 0; j < 3; ++j) {
+            if (j == k) continue;
+            const V3 q = t.p[k] + (t.p[k] - t.p[j]) * lam;
+            float v = f.x * q.x + f.y * q.y + f.z * q.z + f.w;
+            if (absolute) v = fabsf(v);
+            best = fmaxf(best, v == v ? v : FLT_MAX);
+        }
+    return best;
+}
+
+// Can a and b be scanned as one unit?  They must share an edge, carry stored planes that are (nearly) their geometric
+// planes and (nearly) each other's, and form a convex quadrilateral.
+__device__ bool quad_eligible(const LargeTri &a, const LargeTri &b, float eps, float amax) {
+    if (!(a.S > 0.0f && a.S <= FLT_MAX && b.S > 0.0f && b.S <= FLT_MAX)) return false;
+    const int ja = shared_edge(a, b), jb = shared_edge(b, a);
+    if (ja < 0 || jb < 0) return false;
+    const V3 nga = normalize3(cross3(a.p[1] - a.p[0], a.p[2] - a.p[0])), ngb = normalize3(cross3(b.p[1] - b.p[0], b.p[2] - b.p[0]));
+    const V3 nsa = mk(a.plane.x, a.plane.y, a.plane.z), nsb = mk(b.plane.x, b.plane.y, b.plane.z);
+    if (!(fabsf(dot3(nsa, nga)) >= 0.999999f && fabsf(dot3(nsb, ngb)) >= 0.999999f && dot3(nsa, nsb) >= 0.999999f)) return false;
+    if (!(max_over_hexagon(b, eps, a.plane, true) <= 1e-4f && max_over_hexagon(a, eps, b.plane, true) <= 1e-4f)) return false;
+    // convex: the far vertex of each lies strictly inside the two outer edges of the other
+    const V3 fa = a.p[(ja + 2) % 3], fb = b.p[(jb + 2) % 3];
+    const float margin = 1e-5f * amax;
+    for (int j = 0; j < 3; ++j) {
+        if (j != ja) {
+            const float4 pl = edge_plane(a, j, nga, true, 0.0f, 0.0f);
+            if (!(pl.x * fb.x + pl.y * fb.y + pl.z * fb.z + pl.w > margin)) return false;
+        }
+        if (j != jb) {
+            const float4 pl = edge_plane(b, j, ngb, true, 0.0f, 0.0f);
+            if (!(pl.x * fa.x + pl.y * fa.y + pl.z * fa.z + pl.w > margin)) return false;
+        }
+    }
+    return true;
+}
+
+// One block of kMaxLarge threads: pairs the large triangles (sorted positions [nb, nb + n_large) of `vals`) into quad
+// scan units, REORDERS that tail of `vals` (quads first, partners adjacent: k_pack_tris runs afterwards and must see
+// the same order), writes the shared-memory image and the number of quads (s->n_quads).
+__global__ void __launch_bounds__(kMaxLarge)
+k_large_pack(int *__restrict__ vals, const float *__restrict__ verts, const float4 *__restrict__ planes,
+             const float *__restrict__ squares, const int *__restrict__ mat_ids, int nb, int n_large, float eps,
+             BuildScratch *s, float4 *__restrict__ lrecs) {
+    __shared__ LargeTri tri[kMaxLarge];
+    __shared__ int order[kMaxLarge], partner[kMaxLarge], n_quads_s;
+    const int k = threadIdx.x;
     const float amax = fmaxf(20.0f, fmaxf(fmaxf(fmaxf(fabsf(ord2f(s->lo[0])), fabsf(ord2f(s->hi[0]))),
                                                 fmaxf(fabsf(ord2f(s->lo[1])), fabsf(ord2f(s->hi[1])))),
                                           fmaxf(fabsf(ord2f(s->lo[2])), fabsf(ord2f(s->hi[2])))));
+    if (k < n_large) {
+        const int i = vals[nb + k];
+        const float *v = verts + 9 * (size_t)i;
+        tri[k].p[0] = mk(v[0], v[1], v[2]); tri[k].p[1] = mk(v[3], v[4], v[5]); tri[k].p[2] = mk(v[6], v[7], v[8]);
+        tri[k].plane = planes[i];
+        tri[k].S = squares[i];
+        tri[k].idx = i;
+        tri[k].mat = mat_ids[i];
+        partner[k] = -1;
+    }
+    __syncthreads();
+    if (k == 0) {  // greedy matching, at most 64 x 64 / 2 cheap tests
+        int nq = 0, pos = 0;
+        for (int a = 0; a < n_large; ++a) {
+            if (partner[a] >= 0) continue;
+            for (int b = a + 1; b < n_large; ++b)
+                if (partner[b] < 0 && quad_eligible(tri[a], tri[b], eps, amax)) { partner[a] = b; partner[b] = a; break; }
+        }
+        for (int a = 0; a < n_large; ++a)
+            if (partner[a] > a) { order[pos++] = a; order[pos++] = partner[a]; ++nq; }
+        for (int a = 0; a < n_large; ++a)
+            if (partner[a] < 0) order[pos++] = a;
+        n_quads_s = nq;
+        s->n_quads = nq;
+    }
+    __syncthreads();
+    const int nq = n_quads_s, n_single = n_large - 2 * nq;
     const float slack = amax * (64.0f * 1.1920929e-7f);
-    const float e = eps * 1.01f + 4e-6f * (S + eps);
-    const V3 ng = normalize3(cross3(p[1] - p[0], p[2] - p[0]));
-    const bool ok = S > 0.0f && S <= FLT_MAX && ng.x == ng.x;
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-        const V3 a = p[j], b = p[(j + 1) % 3], c = p[(j + 2) % 3];
-        const V3 ab = b - a;
-        const float L = length3(ab);
-        V3 m = normalize3(cross3(ng, ab));
-        if (dot3(m, c - a) < 0.0f) m = m * -1.0f;
-        const float w = -dot3(m, a) + 1.05f * e / (2.0f * L) + slack;
-        // degenerate triangle: a plane that accepts everything (the exact test decides)
-        o[4 + j] = (ok && L > 0.0f && m.x == m.x) ? make_float4(m.x, m.y, m.z, w) : make_float4(0.f, 0.f, 0.f, 1.0f);
+    if (k < n_large) {  // record rows in the new order
+        const LargeTri &t = tri[order[k]];
+        float4 *o = lrecs + 4 * (size_t)k;
+        o[0] = t.plane;
+        o[1] = make_float4(t.p[0].x, t.p[0].y, t.p[0].z, t.S);
+        o[2] = make_float4(t.p[1].x, t.p[1].y, t.p[1].z, __int_as_float(t.idx));
+        o[3] = make_float4(t.p[2].x, t.p[2].y, t.p[2].z, __int_as_float(t.mat));
+        vals[nb + k] = t.idx;
+    }
+    if (k < nq) {  // quad unit k: records 2k (A) and 2k + 1 (B)
+        const LargeTri &a = tri[order[2 * k]], &b = tri[order[2 * k + 1]];
+        const int ja = shared_edge(a, b), jb = shared_edge(b, a);
+        const V3 nga = normalize3(cross3(a.p[1] - a.p[0], a.p[2] - a.p[0])), ngb = normalize3(cross3(b.p[1] - b.p[0], b.p[2] - b.p[0]));
+        const float ea = tri_e(a, eps), eb = tri_e(b, eps);
+        float4 *o = lrecs + 4 * (size_t)n_large + kQuadRows * (size_t)k;
+        o[0] = a.plane;
+        o[1] = edge_plane(a, (ja + 1) % 3, nga, true, ea, slack);
+        o[2] = edge_plane(a, (ja + 2) % 3, nga, true, ea, slack);
+        o[3] = edge_plane(b, (jb + 1) % 3, ngb, true, eb, slack);
+        o[4] = edge_plane(b, (jb + 2) % 3, ngb, true, eb, slack);
+        const float4 diag = edge_plane(a, ja, nga, true, ea, slack);
+        o[5] = diag;
+        // B is scanned with A's plane: its own hit distance differs by at most (distance of B's hit point from A's
+        // plane + the rounding of both numerators) / |d . n| and by |t| times the rounding of the denominators
+        const float dev = max_over_hexagon(b, eps, a.plane, true);
+        o[6] = make_float4(1.5f * dev + amax * 1e-6f, 1e-6f, max_over_hexagon(b, eps, diag, false) + slack, 0.0f);
+    }
+    if (k < n_single) {
+        const LargeTri &t = tri[order[2 * nq + k]];
+        const V3 ng = normalize3(cross3(t.p[1] - t.p[0], t.p[2] - t.p[0]));
+        const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x;
+        const float e = tri_e(t, eps);
+        float4 *o = lrecs + 4 * (size_t)n_large + kQuadRows * (size_t)nq + kSingleRows * (size_t)k;
+        o[0] = t.plane;
+        for (int j = 0; j < 3; ++j) o[1 + j] = edge_plane(t, j, ng, ok, e, slack);
     }
 }
 __global__ void k_root_box(const int *__restrict__ vals, const float4 *__restrict__ box_lo,

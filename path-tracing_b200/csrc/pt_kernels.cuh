@@ -89,7 +89,7 @@ __device__ __forceinline__ bool shade(const SceneView &sc, const float4 *s_large
         return false;
     }
     const bool in_smem = !sc.brute && h.rec >= sc.n_bvh;
-    const float4 *r = in_smem ? s_large + kLargeStride * (h.rec - sc.n_bvh) : sc.tris + 4 * (size_t)h.rec;
+    const float4 *r = in_smem ? s_large + 4 * (h.rec - sc.n_bvh) : sc.tris + 4 * (size_t)h.rec;
     const float4 pl = r[0];
     const int mat = __float_as_int(r[3].w);
     const V3 N = mk(pl.x, pl.y, pl.z);
@@ -191,7 +191,7 @@ constexpr int kBlockThreads = kTileW * kTileH * kQuad;  // 256
 template <bool COUNT>
 __global__ void __launch_bounds__(kBlockThreads)
 k_render_mega(SceneView sc, RenderParams rp) {
-    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
     __syncthreads();
 
@@ -296,7 +296,7 @@ template <bool COUNT>
 __global__ void __launch_bounds__(256)
 k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float eps, int *__restrict__ ids,
             float *__restrict__ ts, unsigned long long *stats) {
-    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
     __syncthreads();
     unsigned long long n_nodes = 0, n_tris = 0;

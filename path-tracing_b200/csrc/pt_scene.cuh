@@ -21,7 +21,13 @@ namespace ptd {
 constexpr int kLeafMax = 4;          // triangles per LBVH leaf
 constexpr int kMaxLarge = 64;        // triangles kept out of the LBVH and tested from shared memory first
 constexpr int kAllLargeMax = 48;     // scenes up to this size keep every triangle in shared memory (no LBVH)
-constexpr int kLargeStride = 7;      // float4 per large triangle in shared memory: 4 record rows + 3 edge planes
+// Shared-memory image of the large triangles (k_large_pack), rows of float4:
+//   [0, 4 n_large)            the 4 record rows of every large triangle (same layout as `tris`)
+//   then n_quads x kQuadRows  scan units of two near-coplanar triangles sharing an edge (records 2u, 2u + 1):
+//                             plane of the first, 4 outer edge planes, the shared edge's plane, (tolerances, threshold)
+//   then n_single x kSingleRows  scan units of the remaining triangles (records 2 n_quads + s): plane, 3 edge planes
+constexpr int kQuadRows = 7, kSingleRows = 4;
+constexpr int kLargeRowsMax = 4 * kMaxLarge + kSingleRows * kMaxLarge;  // worst case: no pairs
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
 constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
@@ -36,6 +42,11 @@ __host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
 __host__ __device__ __forceinline__ int leaf_first(int ref) { return ref & 0x0fffffff; }
 __host__ __device__ __forceinline__ int leaf_count(int ref) { return ((ref >> 28) & 7) + 1; }
 
+struct SceneView;
+__host__ __device__ __forceinline__ int large_rows(int n_large, int n_quads) {
+    return 4 * n_large + kQuadRows * n_quads + kSingleRows * (n_large - 2 * n_quads);
+}
+
 struct SceneView {
     const float4 *tris;
     const float4 *nodes;
@@ -43,9 +54,10 @@ struct SceneView {
     int n_tri;    // all triangle records
     int n_bvh;    // records [0, n_bvh) are in the LBVH
     int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
+    int n_quads;  // of which the first 2 n_quads form quad scan units
     int root;     // child ref of the LBVH root (kRefEmpty if n_bvh == 0)
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)
-    const float4 *lrecs;     // kLargeStride x float4 per large triangle: record rows + 3 edge planes (k_large_pack)
+    const float4 *lrecs;     // shared-memory image of the large triangles (layout above), large_rows() float4
     float4 root_lo, root_hi; // box of the LBVH root
     float4 root_n0, root_n1, root_n2;  // the root node's two child boxes (node layout rows 0..2) when root == 0
     const unsigned char *sky;  // equirect skybox, 24-bit BGR rows top-down (bitmap_image's layout); nullptr = none

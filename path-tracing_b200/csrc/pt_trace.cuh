@@ -75,33 +75,63 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
-// ---- large triangles: kLargeStride float4 each in shared memory (4 record rows + 3 edge planes) -------------
+// ---- large triangles from shared memory (image layout: pt_scene.cuh, built by k_large_pack) ------------------
 __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large) {
-    for (int k = threadIdx.x; k < kLargeStride * sc.n_large; k += blockDim.x) s_large[k] = sc.lrecs[k];
+    const int rows = large_rows(sc.n_large, sc.n_quads);
+    for (int k = threadIdx.x; k < rows; k += blockDim.x) s_large[k] = sc.lrecs[k];
 }
 
 // Scan + resolve.
-// The SCAN is one short, branch-free instruction sequence per triangle, the same for every lane: the plane
-// distance with an approximate reciprocal instead of the IEEE division, a range test and the three edge planes of
-// the triangle, all with tolerances that make it CONSERVATIVE — it may mark a triangle the exact test rejects, never
-// the reverse: numerator and denominator are the reference's own (bit-identical), so t' = num * rcp(sd) is within
-// 2^-21 relative of the reference's quotient; the hit point P' = o + d t' is then within |t'| 2^-20 + a few ulp of
-// the reference's, which is added to the edge planes' margin (k_large_pack).
-// The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles
-// in index order; lanes whose candidates sit at different indices execute it together.
-// one 32-triangle chunk of the scan: returns the candidate mask of triangles [k0, k0 + n)
-__device__ __forceinline__ unsigned large_scan32(const float4 *s_large, int k0, int n, V3 o, V3 d, float t_lo,
-                                                 float t_hi) {
+// The SCAN is one short, branch-free instruction sequence per unit, the same for every lane: the plane distance with
+// an approximate reciprocal instead of the IEEE division, a range test and the edge planes of the unit, all with
+// tolerances that make it CONSERVATIVE — it may mark a triangle the exact test rejects, never the reverse: numerator
+// and denominator are the reference's own (bit-identical), so t' = num * rcp(sd) is within 2^-21 relative of the
+// reference's quotient; the hit point P' = o + d t' is then within |t'| 2^-20 + a few ulp of the reference's, which
+// is added to the edge planes' margin (k_large_pack).
+// A QUAD unit covers two near-coplanar triangles A, B that share an edge with one plane evaluation: the plane is
+// A's; B's own distance differs from it by at most tau = (c_abs + |t| c_rel) / |d . n| (k_large_pack), which widens
+// the range test and every edge margin; the four outer edges bound the union, the shared edge's plane splits the
+// marks between A and B (both near the diagonal).
+// The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles;
+// lanes whose candidates sit at different indices execute it together.
+__device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int n, V3 o, V3 d, float t_lo, float t_hi) {
+    unsigned mask = 0u;  // bit 2 (u - u0) = A of unit u, bit 2 (u - u0) + 1 = B
+    for (int u = 0; u < n; ++u) {
+        const float4 *r = units + kQuadRows * (u0 + u);
+        const float4 p = r[0], meta = r[6];
+        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
+        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+        const float rc = rcp_approx(sd);
+        const float t = num * rc;
+        const float tau = __fmaf_rn(fabsf(t), meta.y, meta.x) * fabsf(rc);
+        const float tol = __fmaf_rn(fabsf(t), 2e-6f, tau);
+        const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
+        const float4 e0 = r[1], e1 = r[2], e2 = r[3], e3 = r[4], e4 = r[5];
+        const float g0 = __fmaf_rn(e0.x, Px, __fmaf_rn(e0.y, Py, __fmaf_rn(e0.z, Pz, e0.w)));
+        const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
+        const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
+        const float g3 = __fmaf_rn(e3.x, Px, __fmaf_rn(e3.y, Py, __fmaf_rn(e3.z, Pz, e3.w)));
+        const float gd = __fmaf_rn(e4.x, Px, __fmaf_rn(e4.y, Py, __fmaf_rn(e4.z, Pz, e4.w)));
+        // written so that a NaN anywhere (sd == 0, infinities) marks both triangles: the resolve decides
+        const bool out = (t - tau > t_hi) | (t + tau < t_lo) | (fminf(fminf(g0, g1), fminf(g2, g3)) < -tol);
+        const unsigned a = (out | (gd < -tol)) ? 0u : 1u, b = (out | (gd > meta.z + tol)) ? 0u : 2u;
+        mask |= (a | b) << (2 * u);
+    }
+    return mask;
+}
+
+// one 32-triangle chunk of single units [s0, s0 + n): returns their candidate mask
+__device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, int n, V3 o, V3 d, float t_lo, float t_hi) {
     unsigned mask = 0u;
     for (int k = 0; k < n; ++k) {
-        const float4 *r = s_large + kLargeStride * (k0 + k);
+        const float4 *r = units + kSingleRows * (s0 + k);
         const float4 p = r[0];
         const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
         const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
         const float t = num * rcp_approx(sd);
         const float tol = fabsf(t) * 2e-6f;
         const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
-        const float4 e0 = r[4], e1 = r[5], e2 = r[6];
+        const float4 e0 = r[1], e1 = r[2], e2 = r[3];
         const float g0 = __fmaf_rn(e0.x, Px, __fmaf_rn(e0.y, Py, __fmaf_rn(e0.z, Pz, e0.w)));
         const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
         const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
@@ -112,12 +142,13 @@ __device__ __forceinline__ unsigned large_scan32(const float4 *s_large, int k0, 
     return mask;
 }
 
+// exact test on the marked records k0 + bit of the shared-memory record rows
 __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, unsigned mask, int rec_base, V3 o, V3 d,
                                                 float eps, Hit &h) {
     while (mask) {
         const int k = k0 + __ffs(mask) - 1;
         mask &= mask - 1u;
-        const float4 *r = s_large + kLargeStride * k;
+        const float4 *r = s_large + 4 * k;
         const float nd = plane_distance(r[0], o, d);
         if (!(nd <= h.t) || nd < eps) continue;
         const float4 a = r[1], b = r[2], c = r[3];
@@ -130,13 +161,20 @@ __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, u
     }
 }
 
-__device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int rec_base, V3 o, V3 d, float eps,
-                                            Hit &h) {
+__device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int n_quads, int rec_base, V3 o, V3 d,
+                                            float eps, Hit &h) {
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
-    const unsigned m0 = large_scan32(s_large, 0, min(n_large, 32), o, d, t_lo, t_hi);
-    const unsigned m1 = n_large > 32 ? large_scan32(s_large, 32, n_large - 32, o, d, t_lo, t_hi) : 0u;
-    large_resolve32(s_large, 0, m0, rec_base, o, d, eps, h);
-    if (m1) large_resolve32(s_large, 32, m1, rec_base, o, d, eps, h);
+    const float4 *quads = s_large + 4 * n_large, *singles = quads + kQuadRows * n_quads;
+    const int n_single = n_large - 2 * n_quads;
+    // records 2u, 2u + 1 belong to quad u; record 2 n_quads + s to single s
+    const unsigned q0 = scan_quads(quads, 0, min(n_quads, 16), o, d, t_lo, t_hi);
+    const unsigned q1 = n_quads > 16 ? scan_quads(quads, 16, n_quads - 16, o, d, t_lo, t_hi) : 0u;
+    const unsigned s0 = scan_singles(singles, 0, min(n_single, 32), o, d, t_lo, t_hi);
+    const unsigned s1 = n_single > 32 ? scan_singles(singles, 32, n_single - 32, o, d, t_lo, t_hi) : 0u;
+    large_resolve32(s_large, 0, q0, rec_base, o, d, eps, h);
+    if (q1) large_resolve32(s_large, 32, q1, rec_base, o, d, eps, h);
+    large_resolve32(s_large, 2 * n_quads, s0, rec_base, o, d, eps, h);
+    if (s1) large_resolve32(s_large, 2 * n_quads + 32, s1, rec_base, o, d, eps, h);
 }
 
 // Slab test of one child box: entry distance, or +inf when the ray [0, tmax] misses the box.  fminf/fmaxf drop a
@@ -235,7 +273,7 @@ __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_
         if (COUNT) n_tris += sc.n_tri;
         return h;
     }
-    large_phase(s_large, sc.n_large, sc.n_bvh, o, d, eps, h);
+    large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
     if (COUNT) n_tris += sc.n_large;
     if (!reaches_root(sc, o, d, h.t)) return h;
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);

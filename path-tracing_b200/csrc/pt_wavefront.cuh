@@ -67,7 +67,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
         if (sc.brute) {
             h = nearest_hit<COUNT>(sc, s_large, o, d, eps, n_nodes, n_tris);
         } else {
-            large_phase(s_large, sc.n_large, sc.n_bvh, o, d, eps, h);
+            large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
             if (COUNT) n_tris += sc.n_large;
             need = reaches_root(sc, o, d, h.t);
         }
@@ -87,7 +87,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
 template <bool COUNT>
 __global__ void __launch_bounds__(256)
 k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
-    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
     if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2] = 0; wf.counters[3] = 0; }  // the other queue
     __syncthreads();
@@ -131,7 +131,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
 template <bool COUNT>
 __global__ void __launch_bounds__(256)
 k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
-    __shared__ float4 s_large[kLargeStride * kMaxLarge];
+    __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
     const int set = (b + 1) & 1;
     if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2 * (b & 1)] = 0; wf.counters[2 * (b & 1) + 1] = 0; }

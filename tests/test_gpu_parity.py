@@ -180,6 +180,54 @@ def test_samples_per_step_do_not_change_the_result(lib, oracle, q_shift, error):
     ds.close()
 
 
+def _stress_rays(sc, n, seed):
+    """Rays that stress the conservative scan of the shared-memory triangles: aimed at points on / next to edges and
+    vertices (inside the reference's eps dilation and just outside it), and grazing rays nearly in a triangle's plane."""
+    rng = np.random.default_rng(seed)
+    v = sc["verts"].reshape(-1, 3, 3).astype(np.float64)
+    tri = rng.integers(0, v.shape[0], n)
+    a, b, c = v[tri, 0], v[tri, 1], v[tri, 2]
+    u = rng.random((n, 1))
+    on_edge = a + (b - a) * u                                   # a point of edge ab
+    inward = c - on_edge
+    inward /= np.linalg.norm(inward, axis=1, keepdims=True) + 1e-30
+    off = rng.choice([0.0, 1e-6, -1e-6, 3e-5, -3e-5, 1e-4, -1e-4, 3e-4, -3e-4, 1e-2, -1e-2], (n, 1))
+    target = on_edge + inward * off
+    kind = rng.integers(0, 3, n)
+    target[kind == 1] = a[kind == 1] + rng.normal(size=(int((kind == 1).sum()), 3)) * 1e-4      # next to a vertex
+    org = rng.uniform([-9.5, -9.5, -20.5], [9.5, 9.5, 9.5], (n, 3))
+    nrm = np.cross(b - a, c - a)
+    nrm /= np.linalg.norm(nrm, axis=1, keepdims=True) + 1e-30
+    g = kind == 2                                                                           # grazing
+    org[g] = target[g] + (rng.normal(size=(int(g.sum()), 3)) * 5.0)
+    org[g] -= nrm[g] * (np.sum((org[g] - target[g]) * nrm[g], 1, keepdims=True) - rng.choice([1e-5, 1e-3, -1e-3, 1e-2], (int(g.sum()), 1)))
+    d = target - org
+    return np.concatenate([org, d], 1).astype(np.float32)
+
+
+@pytest.mark.parametrize("name", ["cornell", "glossy", "tor", "torus40", "composite"])
+def test_shared_memory_scan_never_misses(lib, tor, name):
+    """The scan of the shared-memory triangles (single and quad units, pt_trace.cuh) is conservative by construction;
+    here it is checked against the brute-force mode (scene.cpp:114-120 as written) on 600k rays per scene, most of
+    them aimed at edges, vertices and grazing directions."""
+    sc = {"cornell": scenes.cornell, "glossy": scenes.glossy_mix, "tor": lambda: tor,
+          "torus40": lambda: scenes.torus_room(40, 20), "composite": lambda: scenes.composite(tor)}[name]()
+    rays = np.concatenate([_stress_rays(sc, 400000, 11), scenes.random_rays(200000, seed=3)])
+    cfg_b, cfg_l = ptb200.config(accel=BRUTE), ptb200.config(accel=LBVH)
+    db, dl = lib.scene_create(sc, cfg_b), lib.scene_create(sc, cfg_l)
+    ib, tb = db.intersect(rays, cfg_b)
+    il, tl = dl.intersect(rays, cfg_l)
+    st = dl.stats()
+    db.close(); dl.close()
+    assert (ib >= 0).mean() > 0.5
+    assert_bits_equal(il, ib, name + " ids")
+    assert_bits_equal(tl, tb, name + " t")
+    if name in ("cornell", "glossy"):
+        assert st["n_quads"] == 17, st["n_quads"]       # every wall, light and box face is scanned as one unit
+    if name == "torus40":
+        assert st["n_quads"] == 6 and st["n_large"] == 12       # the 12 walls; the small light lives in the LBVH
+
+
 def test_ragged_and_empty_inputs(lib, oracle):
     sc = scenes.cornell()
     # image sizes that are not multiples of the 8x8 tile, 1 sample, depth 1
