@@ -161,6 +161,31 @@ int pt_resolve_device_w(const float *d_sum3, const int32_t *d_count, const float
 /* Statistics of the last render on this handle (synchronises the device). */
 int pt_scene_stats(PtDeviceScene *ds, PtStats *out);
 
+/* ---- after the loop: main.cpp:162-201 on the device ---------------------------------------------------------
+ * Dispersion statistics + gamma resolve (main.cpp:162-185), optional GaussBlur (main.cpp:11-33) or MedianFilter
+ * (main.cpp:49-80), and the 8-bit conversion of bitmap_image::set_pixel (main.cpp:193-201).  Bit-identical to the
+ * reference built with g++/glibc on x86-64: pow() is glibc's powf restated on the device, sums keep the reference's
+ * order.  rgb8 = H*W*3 bytes, row-major [y][x], red green blue; pixels without samples stay 0 (image.clear()). */
+typedef struct PtPostConfig {
+    int32_t width, height;
+    float gamma_correction; /* config.h:25 */
+    int32_t gauss, median;  /* config.h:20-21: Gauss radius / median half-window, 0 = off */
+    int32_t reserved[3];
+} PtPostConfig;
+typedef struct PtDispersion { /* the three numbers of the output file name, main.cpp:162,185,203-209 */
+    float max_dispersion, min_dispersion, average_dispersion;
+} PtDispersion;
+/* HOST accumulators (as pt_render_accum returns them; weight may be NULL) -> HOST rgb8 */
+int pt_postprocess(const float *sum3, const float *sum2_3, const int32_t *count, const float *weight,
+                   const PtPostConfig *post, uint8_t *rgb8, PtDispersion *stats);
+/* DEVICE accumulators -> DEVICE rgb8; `stats` is a host pointer (may be NULL); waits for the stream */
+int pt_postprocess_device(const float *d_sum3, const float *d_sum2_3, const int32_t *d_count, const float *d_weight,
+                          const PtPostConfig *post, uint8_t *d_rgb8, PtDispersion *stats, void *stream);
+/* The whole of main() between LoadModel and save_image: pt_render_accum + pt_postprocess without the round trip;
+ * 3 bytes per pixel leave the device. */
+int pt_render_image(const PtScene *scene, const PtConfig *cfg, const PtPostConfig *post, uint8_t *rgb8,
+                    PtDispersion *stats);
+
 /* Nearest hit on an explicit ray set, exactly the loop scene.cpp:114-120: rays6 = n×(ox,oy,oz,dx,dy,dz) HOST
  * floats; the direction is normalised as Ray's constructor does (ray.h:21-25).  tri_id[i] = index in the
  * caller's triangle order, -1 on a miss; t[i] = hit distance, +inf on a miss. */
@@ -176,6 +201,7 @@ int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float 
 /* Device building blocks exposed for the parity tests (HOST pointers). */
 int pt_philox(const uint32_t *ctr4, const uint32_t *key2, int64_t n, uint32_t *out4);
 int pt_sincos(const float *x, int64_t n, float *s, float *c);
+int pt_powf(const float *x, int64_t n, float y, float *out); /* the device's restatement of glibc powf */
 int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
 
 /* pt_render / pt_scene_destroy keep the last path-state workspace (up to 9.7 GB of HBM) for the next call on the same

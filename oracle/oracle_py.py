@@ -49,6 +49,11 @@ class Oracle:
         L.or_resolve.argtypes = [_f32p, _i32p, C.c_void_p, C.c_long, _f32p]
         L.or_libm_sincos.argtypes = [_f32p, C.c_long, _f32p, _f32p]
         L.or_max_threads.restype = C.c_int
+        L.or_resolve_display.argtypes = [_f32p, _f32p, _i32p, C.c_void_p, C.c_int, C.c_int, C.c_float, _f32p, _u8p, _f32p]
+        L.or_to_rgb8.argtypes = [_f32p, _i32p, C.c_long, _u8p]
+        L.or_powf_check.restype = C.c_long
+        L.or_powf_check.argtypes = [_f32p, C.c_long, C.c_float, C.POINTER(C.c_float)]
+        L.or_libm_powf.argtypes = [_f32p, C.c_long, C.c_float, _f32p]
         L.or_refract.restype = C.c_int
         L.or_refract.argtypes = [_f32p, _f32p, C.c_float, _f32p]
 
@@ -142,6 +147,35 @@ class Oracle:
         self.lib.or_resolve(np.ascontiguousarray(sm), np.ascontiguousarray(cnt), None if w is None else w.ctypes.data,
                             cnt.size, rgb)
         return rgb
+
+    def resolve_display(self, sm, s2, cnt, gamma=1 / 2.2, weight=None):
+        """main.cpp:162-185,193-201 -> (float image (H,W,3), rgb8 (H,W,3), (max, min, average) dispersion)"""
+        H, W = cnt.shape
+        color = np.zeros((H, W, 3), np.float32)
+        img = np.zeros((H, W, 3), np.uint8)
+        st = np.zeros(3, np.float32)
+        w = None if weight is None else np.ascontiguousarray(weight, np.float32)
+        self.lib.or_resolve_display(np.ascontiguousarray(sm, np.float32), np.ascontiguousarray(s2, np.float32),
+                                    np.ascontiguousarray(cnt, np.int32), None if w is None else w.ctypes.data, W, H, gamma,
+                                    color, img, st)
+        return color, img, tuple(float(v) for v in st)
+
+    def to_rgb8(self, color, cnt):
+        img = np.zeros(color.shape, np.uint8)
+        self.lib.or_to_rgb8(np.ascontiguousarray(color, np.float32), np.ascontiguousarray(cnt, np.int32), cnt.size, img)
+        return img
+
+    def powf_check(self, x, y):
+        """number of inputs where the oracle's restatement of glibc powf differs from the host libm"""
+        x = np.ascontiguousarray(x, np.float32)
+        fb = C.c_float()
+        return int(self.lib.or_powf_check(x, x.size, y, C.byref(fb))), fb.value
+
+    def libm_powf(self, x, y):
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.empty_like(x)
+        self.lib.or_libm_powf(x, x.size, y, out)
+        return out
 
     def refract(self, d, n, eta):
         out = np.zeros(3, np.float32)

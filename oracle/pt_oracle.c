@@ -423,12 +423,122 @@ void or_resolve(const float *sum3, const int *count, const float *weight, long n
     }
 }
 
+/* main.cpp:162-185 + 193-201: dispersion statistics, gamma resolve, float -> unsigned char of set_pixel (the x86-64
+ * conversion: cvttss2si, low byte).  color3 (may be NULL) receives the float image the filters work on;
+ * stats3 = max, min, average dispersion.  weight (may be NULL) replaces the count as divisor (RR extension). */
+static inline unsigned char or_u8(float v) {
+    if (!(fabsf(v) < 2147483648.0f)) return 0;
+    return (unsigned char)((int)v & 0xff);
+}
+void or_resolve_display(const float *sum3, const float *sum2_3, const int *count, const float *weight, int W, int H,
+                        float gamma, float *color3, unsigned char *rgb8, float *stats3) {
+    float max_d = 0, min_d = INFINITY, avg = 0;
+    for (int y = 0; y < H; ++y)
+        for (int x = 0; x < W; ++x) {
+            const size_t p = (size_t)y * W + x;
+            float c[3] = {sum3[3 * p], sum3[3 * p + 1], sum3[3 * p + 2]};
+            if (!count[p]) {
+                avg += 1;
+            } else {
+                const float n = weight ? weight[p] : (float)count[p];
+                float disp = 0;
+                float D[3];
+                for (int k = 0; k < 3; ++k) {
+                    const float m = c[k] / n;
+                    D[k] = sum2_3[3 * p + k] / n - m * m;
+                    c[k] = powf(m, gamma) * 255.0f;
+                }
+                disp = D[0] + D[1] + D[2];
+                if (disp > max_d) max_d = disp;
+                if (disp < min_d) min_d = disp;
+                avg += disp;
+            }
+            for (int k = 0; k < 3; ++k) {
+                if (color3) color3[3 * p + k] = c[k];
+                if (rgb8) rgb8[3 * p + k] = count[p] ? or_u8(c[k]) : 0;
+            }
+        }
+    avg /= W * H;
+    if (stats3) { stats3[0] = max_d; stats3[1] = min_d; stats3[2] = avg; }
+}
+void or_to_rgb8(const float *color3, const int *count, long npx, unsigned char *rgb8) {
+    for (long p = 0; p < npx; ++p)
+        for (int k = 0; k < 3; ++k) rgb8[3 * p + k] = count[p] ? or_u8(color3[3 * p + k]) : 0;
+}
+
 void or_philox(const uint32_t ctr[4], const uint32_t key[2], uint32_t out[4]) { pt_philox4x32_10(ctr, key, out); }
 
 /* libm the reference resolves std::cos/std::sin(float) to (material.h:93-94) — exposed so that the
  * GPU test can compare the device sincos against it over the renderer's whole input domain. */
 void or_libm_sincos(const float *x, long n, float *s, float *c) {
     for (long i = 0; i < n; ++i) { s[i] = sinf(x[i]); c[i] = cosf(x[i]); }
+}
+
+/* ---- glibc powf restated (sysdeps/ieee754/flt-32/e_powf.c, the FMA build x86-64 selects on current CPUs), for
+ * x >= 0 and finite y > 0: what the device's gamma resolve implements.  Checked against the host's powf in
+ * tests/test_host.py; the tables come from the image's libm (tools/extract_libm_tables.py). ---- */
+#include "libm_tables.h"
+static inline uint32_t f2u(float f) { uint32_t u; memcpy(&u, &f, 4); return u; }
+static inline float u2f(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+static inline uint64_t d2u(double f) { uint64_t u; memcpy(&u, &f, 8); return u; }
+static inline double u2d(uint64_t u) { double f; memcpy(&f, &u, 8); return f; }
+float or_powf_restated(float x, float y) {
+    uint32_t ix = f2u(x);
+    if (x != x || y != y) return x + y;
+    if (ix & 0x80000000u) return ix == 0x80000000u ? 0.0f : NAN; /* -0 -> 0 for y > 0; negative base: NaN */
+    if (ix == 0) return 0.0f;
+    if (ix == 0x7f800000u) return INFINITY;
+    if (ix < 0x00800000u) { /* subnormal: normalise */
+        ix = f2u(x * 0x1p23f);
+        ix -= 23u << 23;
+    }
+    const uint32_t tmp = ix - 0x3f330000u;
+    const int i = (tmp >> 19) % 16;
+    const uint32_t top = tmp & 0xff800000u;
+    const uint32_t iz = ix - top;
+    const int k = (int32_t)top >> 23;
+    const double invc = kPowLog2Tab[2 * i], logc = kPowLog2Tab[2 * i + 1];
+    const double z = (double)u2f(iz);
+    const double r = __builtin_fma(z, invc, -1.0);
+    const double y0 = logc + (double)k;
+    const double r2 = r * r;
+    double yy = __builtin_fma(kPowLog2Poly[0], r, kPowLog2Poly[1]);
+    const double p = __builtin_fma(kPowLog2Poly[2], r, kPowLog2Poly[3]);
+    const double r4 = r2 * r2;
+    double q = __builtin_fma(kPowLog2Poly[4], r, y0);
+    q = __builtin_fma(p, r2, q);
+    yy = __builtin_fma(yy, r4, q);
+    const double ylogx = (double)y * yy;
+    if (((d2u(ylogx) >> 47) & 0xffff) >= (d2u(126.0) >> 47)) { /* |y log2 x| >= 126 */
+        if (ylogx > 0x1.fffffffd1d571p+6) return INFINITY;
+        if (ylogx <= -150.0) return 0.0f;
+    }
+    const double shift = 0x1.8p+47;
+    double kd = ylogx + shift;
+    const uint64_t ki = d2u(kd);
+    kd -= shift;
+    const double rr = ylogx - kd;
+    uint64_t t = kExp2fTab[ki % 32];
+    t += ki << 47;
+    const double sc = u2d(t);
+    const double zz = __builtin_fma(0x1.c6af84b912394p-5, rr, 0x1.ebfce50fac4f3p-3);
+    const double rr2 = rr * rr;
+    double e = __builtin_fma(0x1.62e42ff0c52d6p-1, rr, 1.0);
+    e = __builtin_fma(zz, rr2, e);
+    e = e * sc;
+    return (float)e;
+}
+/* bulk compare against the host libm: returns the number of inputs where the restatement differs */
+long or_powf_check(const float *x, long n, float y, float *first_bad) {
+    long bad = 0;
+    for (long i = 0; i < n; ++i) {
+        const float a = powf(x[i], y), b = or_powf_restated(x[i], y);
+        if (f2u(a) != f2u(b) && !(a != a && b != b)) { if (!bad && first_bad) *first_bad = x[i]; ++bad; }
+    }
+    return bad;
+}
+void or_libm_powf(const float *x, long n, float y, float *out) {
+    for (long i = 0; i < n; ++i) out[i] = powf(x[i], y);
 }
 
 int or_max_threads(void) {

@@ -13,6 +13,7 @@
 #include "pt_bvh.cuh"
 #include "pt_kernels.cuh"
 #include "pt_wavefront.cuh"
+#include "pt_post.cuh"
 
 using namespace ptd;
 
@@ -647,6 +648,130 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     guard.p = nullptr;
     d_sum.free(); d_rgb.free(); d_wt.free(); d_cnt.free();
     lap("release");
+    return PT_OK;
+}
+
+// ---- after the loop: main.cpp:162-201 on the device ------------------------------------------------------------
+static int validate_post(const PtPostConfig *post) {
+    if (!post) return fail(PT_EINVAL, "post config is NULL");
+    if (post->width <= 0 || post->height <= 0 || (long long)post->width * post->height > 0x7fffffffLL)
+        return fail(PT_EINVAL, "bad image size");
+    if (post->gauss < 0 || post->median < 0) return fail(PT_EINVAL, "negative filter size");
+    if (post->median > kMedianMaxW) return fail(PT_EINVAL, "median window %d too large (max %d)", post->median, kMedianMaxW);
+    if (post->gauss > 64) return fail(PT_EINVAL, "gauss radius %d too large (max 64)", post->gauss);
+    return PT_OK;
+}
+
+extern "C" int pt_postprocess_device(const float *d_sum3, const float *d_sum2_3, const int32_t *d_count,
+                                     const float *d_weight, const PtPostConfig *post, uint8_t *d_rgb8,
+                                     PtDispersion *stats, void *stream) {
+    int rc;
+    if ((rc = validate_post(post))) return rc;
+    if (!d_sum3 || !d_sum2_3 || !d_count || !d_rgb8) return fail(PT_EINVAL, "NULL buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const int W = post->width, H = post->height;
+    const long long npx = (long long)W * H;
+    DevBuf<float> color, tmp, disp, d_avg, d_wtab;
+    DevBuf<int> d_minmax;
+    CK(color.alloc(3 * npx)); CK(disp.alloc(npx)); CK(d_avg.alloc(1)); CK(d_minmax.alloc(2));
+    const int init[2] = {0, 0x7f800000};  // max_dispersion = 0, min_dispersion = INFINITY (main.cpp:162)
+    CK(cudaMemcpyAsync(d_minmax.p, init, sizeof init, cudaMemcpyHostToDevice, st));
+    k_tonemap<<<blocks_for(npx, 256), 256, 0, st>>>(d_sum3, d_sum2_3, d_count, d_weight, npx, post->gamma_correction,
+                                                   color.p, disp.p, d_minmax.p);
+    k_dispersion_sum<<<1, 1024, 0, st>>>(disp.p, npx, d_avg.p);
+    float *img = color.p;
+    if (post->gauss) {  // main.cpp:187-189
+        const float r = (float)post->gauss;
+        const int rs = (int)ceil(r * 2.57);
+        std::vector<float> wtab(2 * (size_t)rs * rs + 1);
+        const float pi = 3.141593f;  // material.h:12
+        for (int dsq = 0; dsq < (int)wtab.size(); ++dsq) wtab[dsq] = expf((float)(-dsq) / (2 * r * r)) / (pi * 2 * r * r);
+        CK(d_wtab.alloc(wtab.size())); CK(tmp.alloc(3 * npx));
+        CK(cudaMemcpyAsync(d_wtab.p, wtab.data(), wtab.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));  // wtab goes out of scope
+        k_gauss<<<dim3(blocks_for(W, 256), H), 256, 0, st>>>(img, W, H, rs, d_wtab.p, tmp.p);
+        img = tmp.p;
+    }
+    DevBuf<float> tmp2;
+    if (post->median) {  // main.cpp:190-192
+        CK(tmp2.alloc(3 * npx));
+        k_median<<<dim3(blocks_for(W, 128), H, 3), 128, 0, st>>>(img, W, H, post->median, tmp2.p);
+        img = tmp2.p;
+    }
+    k_to_rgb8<<<blocks_for(npx, 256), 256, 0, st>>>(img, d_count, npx, d_rgb8);
+    CK(cudaGetLastError());
+    int mm[2];
+    float avg = 0.f;
+    CK(cudaMemcpyAsync(mm, d_minmax.p, sizeof mm, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&avg, d_avg.p, sizeof avg, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));  // the temporaries are freed on return
+    if (stats) {
+        memcpy(&stats->max_dispersion, &mm[0], 4);
+        const int b = mm[1] >= 0 ? mm[1] : mm[1] ^ 0x7fffffff;
+        memcpy(&stats->min_dispersion, &b, 4);
+        stats->average_dispersion = avg / (float)(W * H);  // main.cpp:185: float /= int
+    }
+    return PT_OK;
+}
+
+extern "C" int pt_postprocess(const float *sum3, const float *sum2_3, const int32_t *count, const float *weight,
+                              const PtPostConfig *post, uint8_t *rgb8, PtDispersion *stats) {
+    int rc;
+    if ((rc = validate_post(post)) || (rc = check_device())) return rc;
+    if (!sum3 || !sum2_3 || !count || !rgb8) return fail(PT_EINVAL, "NULL buffer");
+    const size_t px = (size_t)post->width * post->height;
+    DevBuf<float> d_sum, d_sum2, d_wt;
+    DevBuf<int> d_cnt;
+    DevBuf<uint8_t> d_img;
+    CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px)); CK(d_img.alloc(3 * px));
+    CK(cudaMemcpy(d_sum.p, sum3, 3 * px * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_sum2.p, sum2_3, 3 * px * sizeof(float), cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_cnt.p, count, px * sizeof(int), cudaMemcpyHostToDevice));
+    if (weight) {
+        CK(d_wt.alloc(px));
+        CK(cudaMemcpy(d_wt.p, weight, px * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, weight ? d_wt.p : nullptr, post, d_img.p, stats, nullptr))) return rc;
+    CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_render_image(const PtScene *scene, const PtConfig *cfg, const PtPostConfig *post, uint8_t *rgb8,
+                               PtDispersion *stats) {
+    int rc;
+    if (!rgb8) return fail(PT_EINVAL, "rgb8 is NULL");
+    if ((rc = validate_config(cfg)) || (rc = validate_scene(scene)) || (rc = validate_post(post))) return rc;
+    if (post->width != cfg->width || post->height != cfg->height) return fail(PT_EINVAL, "post and render sizes differ");
+    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
+    if ((rc = check_device())) return rc;
+    CK(cudaSetDevice(cfg->device));
+    PtDeviceScene *ds = nullptr;
+    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
+    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    const size_t px = (size_t)cfg->width * cfg->height;
+    DevBuf<float> d_sum, d_sum2, d_wt;
+    DevBuf<int> d_cnt;
+    DevBuf<uint8_t> d_img;
+    CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px)); CK(d_img.alloc(3 * px));
+    const bool rr = cfg->rr_depth > 0;
+    if (rr) CK(d_wt.alloc(px));
+    if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, nullptr))) return rc;
+    if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, post, d_img.p, stats, nullptr))) return rc;
+    CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+extern "C" int pt_powf(const float *x, int64_t n, float y, float *out) {
+    if (!x || !out || n < 0) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    if (n == 0) return PT_OK;
+    DevBuf<float> dx, dy;
+    CK(dx.alloc(n)); CK(dy.alloc(n));
+    CK(cudaMemcpy(dx.p, x, 4 * (size_t)n, cudaMemcpyHostToDevice));
+    k_powf<<<blocks_for(n, 256), 256>>>(dx.p, n, y, dy.p);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, dy.p, 4 * (size_t)n, cudaMemcpyDeviceToHost));
     return PT_OK;
 }
 

@@ -2,7 +2,6 @@
 // loader through ctypes: load an OBJ with Scene::LoadModel and copy out the arrays behind Scene::abi().
 #include <cstring>
 
-#include "postprocess.h"
 #include "scene.h"
 
 namespace {

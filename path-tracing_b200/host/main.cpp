@@ -1,12 +1,13 @@
-// main.cpp — the reference's driver (main.cpp:87-216) with its sample loop (lines 107-160) replaced by ONE call
-// into the B200 library: Scene::Render -> pt_render_accum.  Everything around the loop keeps the reference's
-// behaviour: Config flags, Scene::LoadModel, dispersion statistics, gamma resolve, optional Gauss / median filter,
-// BMP output under the same two names.  The progressive "../result.bmp" refresh every `update` samples
-// (main.cpp:141-158) and the time limit (main.cpp:111-114) have no equivalent: the whole loop is one kernel launch.
+// main.cpp — the reference's driver (main.cpp:87-216) with everything between LoadModel and save_image handed to the
+// B200 library in ONE call: Scene::RenderImage -> pt_render_image = the sample loop (main.cpp:107-160), the
+// dispersion statistics and gamma resolve (:162-185), the optional Gauss / median filter (:187-192) and the 8-bit
+// conversion of set_pixel (:193-201).  What stays here is the reference's surface: Config flags, Scene::LoadModel,
+// the BMP written under the same two names with the same statistics in the file name.  The progressive
+// "../result.bmp" refresh every `update` samples (main.cpp:141-158) and the time limit (main.cpp:111-114) have no
+// equivalent: the whole loop is a few kernel launches.
 #include <chrono>
 #include <iostream>
 
-#include "postprocess.h"
 #include "scene.h"
 
 int main(int argc, char *argv[]) {
@@ -26,20 +27,23 @@ int main(int argc, char *argv[]) {
     image.clear();
 
     const PtConfig abi = cfg.to_abi();
-    const int rc = scene.Render(abi);
+    PtPostConfig post{};
+    post.width = cfg.width; post.height = cfg.height;
+    post.gamma_correction = cfg.gamma_correction;
+    post.gauss = cfg.gauss; post.median = cfg.median;
+    std::vector<uint8_t> rgb8;
+    PtDispersion st{};
+    const int rc = scene.RenderImage(abi, post, rgb8, st);
     if (rc) {
-        std::cerr << "pt_render failed (" << rc << "): " << pt_last_error() << std::endl;
+        std::cerr << "pt_render_image failed (" << rc << "): " << pt_last_error() << std::endl;
         return 2;
     }
     std::cerr << cfg.rays_per_pixel << " rays per pixel were sent" << std::endl;
-
-    const DispersionStats st = ResolveAndStats(color_map, color2_map, samples_count, cfg.width, cfg.height,
-                                               cfg.gamma_correction, cfg.rr > 0 ? &scene.Weights() : nullptr);
-    if (cfg.gauss) color_map = GaussBlur(color_map, cfg.gauss, cfg.width, cfg.height);
-    if (cfg.median) color_map = MedianFilter(color_map, cfg.median, cfg.width, cfg.height);
     for (int y = 0; y < cfg.height; ++y)
-        for (int x = 0; x < cfg.width; ++x)
-            if (samples_count[x][y]) image.set_pixel(x, y, color_map[x][y].x, color_map[x][y].y, color_map[x][y].z);
+        for (int x = 0; x < cfg.width; ++x) {
+            const uint8_t *c = &rgb8[3 * (static_cast<size_t>(y) * cfg.width + x)];
+            image.set_pixel(x, y, c[0], c[1], c[2]);  // unsampled pixels are 0 = image.clear()
+        }
 
     const long long ms = std::chrono::duration_cast<std::chrono::milliseconds>(clock::now() - start).count();
     const time_t t = time(nullptr);

@@ -145,17 +145,29 @@ PtScene Scene::abi() const {
 int Scene::Render(const PtConfig &cfg) {
     const PtScene s = abi();
     const size_t W = cfg.width, H = cfg.height;
-    std::vector<float> sum(3 * W * H), sum2(3 * W * H);
-    std::vector<int32_t> cnt(W * H);
+    sum_.assign(3 * W * H, 0.0f); sum2_.assign(3 * W * H, 0.0f);
+    count_.assign(W * H, 0);
     weight_.assign(W * H, 0.0f);
-    const int rc = pt_render_accum_w(&s, &cfg, sum.data(), sum2.data(), cnt.data(), weight_.data());
+    const int rc = pt_render_accum_w(&s, &cfg, sum_.data(), sum2_.data(), count_.data(), weight_.data());
     if (rc) return rc;
     for (size_t y = 0; y < H; ++y)
         for (size_t x = 0; x < W; ++x) {
             const size_t p = y * W + x;
-            color_map_[x][y] = vec3(sum[3 * p], sum[3 * p + 1], sum[3 * p + 2]);
-            color2_map_[x][y] = vec3(sum2[3 * p], sum2[3 * p + 1], sum2[3 * p + 2]);
-            samples_count_[x][y] = cnt[p];
+            color_map_[x][y] = vec3(sum_[3 * p], sum_[3 * p + 1], sum_[3 * p + 2]);
+            color2_map_[x][y] = vec3(sum2_[3 * p], sum2_[3 * p + 1], sum2_[3 * p + 2]);
+            samples_count_[x][y] = count_[p];
         }
+    rr_ = cfg.rr_depth > 0;
     return 0;
+}
+
+int Scene::Resolve(const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats) const {
+    rgb8.assign(3 * static_cast<size_t>(post.width) * post.height, 0);
+    return pt_postprocess(sum_.data(), sum2_.data(), count_.data(), rr_ ? weight_.data() : nullptr, &post, rgb8.data(), &stats);
+}
+
+int Scene::RenderImage(const PtConfig &cfg, const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats) {
+    const PtScene s = abi();
+    rgb8.assign(3 * static_cast<size_t>(post.width) * post.height, 0);
+    return pt_render_image(&s, &cfg, &post, rgb8.data(), &stats);
 }

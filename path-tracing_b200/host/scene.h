@@ -10,6 +10,8 @@
 #include "bitmap_image.h"
 #include "triangles.h"
 
+using Image = std::vector<std::vector<ptm::vec3>>;  // indexed [x][y] like the reference's color_map
+
 class Scene {
     std::vector<Triangle> triangles_;
     std::vector<std::vector<ptm::vec3>> &color_map_;
@@ -19,6 +21,9 @@ class Scene {
     bitmap_image skybox_;
     // flat arrays behind abi()
     mutable std::vector<float> vertices_, planes_, squares_, mats_, mats_ext_;
+    std::vector<float> sum_, sum2_;    // flat copies of the last Render's accumulators, row-major [y][x]
+    std::vector<int32_t> count_;
+    bool rr_ = false;                  // the last Render used Russian roulette: the divisor is weight_
     std::vector<float> weight_;  // per-pixel divisor of the last Render, row-major [y][x] (== samples_count without -RR)
     mutable std::vector<int32_t> mat_ids_;
 
@@ -37,5 +42,10 @@ public:
     int Render(const PtConfig &cfg);  // the loop main.cpp:107-160 on the GPU; returns a PT_* code
     // per-pixel divisor for the resolve, row-major [y][x]: samples_count, or the weight sum of a Russian-roulette render
     const std::vector<float> &Weights() const { return weight_; }
+    // main.cpp:162-201 on the GPU (pt_postprocess) from the accumulators of the last Render: dispersion statistics,
+    // gamma resolve, Gauss / median filter, 8-bit conversion.  rgb8 = H*W*3, row-major [y][x]
+    int Resolve(const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats) const;
+    // Render + Resolve without the round trip through host accumulators (pt_render_image)
+    int RenderImage(const PtConfig &cfg, const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats);
 };
 #endif

@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf"]
 
 
 class PtScene(C.Structure):
@@ -45,6 +45,15 @@ class PtStats(C.Structure):
                 ("upload_ms", C.c_float), ("n_nodes", C.c_int32), ("n_large", C.c_int32), ("accel", C.c_int32),
                 ("launches", C.c_int32), ("class_ms", C.c_float * 4), ("class_launches", C.c_int32 * 4),
                 ("rays_queued", C.c_uint64), ("node_hist", C.c_uint64 * 16), ("n_quads", C.c_int32), ("reserved0", C.c_int32)]
+
+
+class PtPostConfig(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("gamma_correction", C.c_float), ("gauss", C.c_int32),
+                ("median", C.c_int32), ("reserved", C.c_int32 * 3)]
+
+
+class PtDispersion(C.Structure):
+    _fields_ = [("max_dispersion", C.c_float), ("min_dispersion", C.c_float), ("average_dispersion", C.c_float)]
 
 
 class PtError(RuntimeError):
@@ -104,6 +113,14 @@ class Library:
         L.pt_philox.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]
         L.pt_sincos.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
         L.pt_primary_rays.argtypes = [C.POINTER(PtConfig), C.c_void_p, C.c_int64, C.c_void_p]
+        L.pt_postprocess.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(PtPostConfig), C.c_void_p,
+                                     C.POINTER(PtDispersion)]
+        L.pt_postprocess_device.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(PtPostConfig),
+                                            C.c_void_p, C.POINTER(PtDispersion), C.c_void_p]
+        L.pt_render_image.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.POINTER(PtPostConfig), C.c_void_p,
+                                      C.POINTER(PtDispersion)]
+        L.pt_powf.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_void_p]
+        L.pt_release_workspace.restype = None
 
     def check(self, rc):
         if rc != 0:
@@ -202,6 +219,35 @@ class Library:
         c = np.empty_like(x)
         self.check(self.lib.pt_sincos(x.ctypes.data, x.size, s.ctypes.data, c.ctypes.data))
         return s, c
+
+    def powf(self, x, y):
+        x = np.ascontiguousarray(x, np.float32)
+        out = np.empty_like(x)
+        self.check(self.lib.pt_powf(x.ctypes.data, x.size, y, out.ctypes.data))
+        return out
+
+    # ---- after the loop (main.cpp:162-201) ----
+    @staticmethod
+    def post_config(width, height, gamma=1 / 2.2, gauss=0, median=0):
+        return PtPostConfig(width, height, gamma, gauss, median)
+
+    def postprocess(self, sm, s2, cnt, post, weight=None):
+        """HOST accumulators -> (rgb8 (H, W, 3) uint8, (max, min, average) dispersion)"""
+        sm, s2 = np.ascontiguousarray(sm, np.float32), np.ascontiguousarray(s2, np.float32)
+        cnt = np.ascontiguousarray(cnt, np.int32)
+        w = None if weight is None else np.ascontiguousarray(weight, np.float32)
+        img = np.zeros((post.height, post.width, 3), np.uint8)
+        st = PtDispersion()
+        self.check(self.lib.pt_postprocess(sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data, None if w is None else w.ctypes.data,
+                                           C.byref(post), img.ctypes.data, C.byref(st)))
+        return img, (st.max_dispersion, st.min_dispersion, st.average_dispersion)
+
+    def render_image(self, sc, cfg, post):
+        img = np.zeros((post.height, post.width, 3), np.uint8)
+        st = PtDispersion()
+        s = self.scene_struct(sc)
+        self.check(self.lib.pt_render_image(C.byref(s), C.byref(cfg), C.byref(post), img.ctypes.data, C.byref(st)))
+        return img, (st.max_dispersion, st.min_dispersion, st.average_dispersion)
 
     def primary_rays(self, cfg, xys3):
         xys3 = np.ascontiguousarray(xys3, np.int32).reshape(-1, 3)

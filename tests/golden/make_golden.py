@@ -78,6 +78,21 @@ def main():
     out["sky_bgr"] = sky
     out.update(render_case_sky(ref, "sky", 32, 32, 8, 8, bmp))
     os.unlink(bmp)
+    # after the loop (main.cpp:162-201): the accumulators of two render cases above -> float image (the oracle's
+    # restatement of the inline resolve, host libm powf) -> the REFERENCE's own GaussBlur / MedianFilter (main.cpp
+    # compiled into oracle/_ref) -> 8 bits.  Also a synthetic image with values over the whole 0..255 range.
+    for nm in ("tor_adapt", "cornell"):
+        color, img, st = orc.resolve_display(out[f"{nm}_sum"], out[f"{nm}_sum2"], out[f"{nm}_count"], 1 / 2.2)
+        out[f"post_{nm}_rgb8"], out[f"post_{nm}_stats"] = img, np.array(st, np.float32)
+        for r in (1, 2):
+            out[f"post_{nm}_gauss{r}"] = orc.to_rgb8(ref.gauss_blur(color, r), out[f"{nm}_count"])
+        for w in (1, 2, 3):
+            out[f"post_{nm}_median{w}"] = orc.to_rgb8(ref.median_filter(color, w), out[f"{nm}_count"])
+    rng = np.random.default_rng(12)
+    img = (rng.random((20, 28, 3)) * 255).astype(np.float32)
+    out["post_img"] = img
+    out["post_img_gauss2"], out["post_img_gauss3"] = ref.gauss_blur(img, 2), ref.gauss_blur(img, 3)
+    out["post_img_median1"], out["post_img_median2"] = ref.median_filter(img, 1), ref.median_filter(img, 2)
     # Philox4x32-10 known answers (Random123 kat_vectors) through the oracle's implementation
     out["philox_kat"] = np.array([orc.philox([0, 0, 0, 0], [0, 0]), orc.philox([0xffffffff] * 4, [0xffffffff] * 2),
                                   orc.philox([0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344], [0xa4093822, 0x299f31d0])],

@@ -228,6 +228,50 @@ def test_shared_memory_scan_never_misses(lib, tor, name):
         assert st["n_quads"] == 6 and st["n_large"] == 12       # the 12 walls; the small light lives in the LBVH
 
 
+def test_powf_device_matches_host_libm(lib, oracle):
+    """The gamma resolve's pow (main.cpp:180: glm::pow -> glibc powf) restated on the device, bit for bit: every
+    k * 2^-24 in [0, 1) and random bit patterns over the whole positive range."""
+    rng = np.random.default_rng(4)
+    unit = np.arange(1 << 24, dtype=np.float32) * np.float32(2.0 ** -24)
+    wide = rng.integers(0, 0x7f800000, 4_000_000, dtype=np.uint32).view(np.float32)
+    edge = np.array([0.0, 1.0, np.inf, 1e-45, 1.17e-38, 3.4e38, 255.0], np.float32)
+    for gamma in (1 / 2.2, 1.0, 2.2):
+        for x in (unit, wide, edge):
+            assert_bits_equal(lib.powf(x, gamma), oracle.libm_powf(x, gamma), f"powf(x, {gamma})")
+
+
+@pytest.mark.parametrize("name", ["tor_adapt", "cornell"])
+def test_postprocess_golden(lib, oracle, name):
+    """main.cpp:162-201 on the device against the oracle's restatement (statistics, 8-bit image) and against the
+    reference's own GaussBlur / MedianFilter applied to the same accumulators (golden)."""
+    sm, s2, cnt = G[name + "_sum"], G[name + "_sum2"], G[name + "_count"]
+    H, W = cnt.shape
+    img, st = lib.postprocess(sm, s2, cnt, lib.post_config(W, H))
+    _, oimg, ost = oracle.resolve_display(sm, s2, cnt, 1 / 2.2)
+    assert np.array_equal(img, G[f"post_{name}_rgb8"]) and np.array_equal(img, oimg)
+    assert_bits_equal(np.array(st, np.float32), G[f"post_{name}_stats"], "max/min/average dispersion")
+    for r in (1, 2):
+        img, _ = lib.postprocess(sm, s2, cnt, lib.post_config(W, H, gauss=r))
+        assert np.array_equal(img, G[f"post_{name}_gauss{r}"]), f"gauss {r}"
+    for w in (1, 2, 3):
+        img, _ = lib.postprocess(sm, s2, cnt, lib.post_config(W, H, median=w))
+        assert np.array_equal(img, G[f"post_{name}_median{w}"]), f"median {w}"
+
+
+def test_render_image_is_render_plus_postprocess(lib, oracle, tor):
+    """pt_render_image (what the host main() calls) = pt_render_accum + pt_postprocess, at a ragged size with an
+    odd gamma, with and without roulette; and the sequential dispersion sum at a size that spans many chunks."""
+    for rr in (0, 3):
+        cfg = ptb200.config(301, 203, 6, 8, 1e-4, 0.001, seed=5, rr_depth=rr)
+        post = lib.post_config(301, 203, gamma=0.6, gauss=1)
+        img, st = lib.render_image(tor, cfg, post)
+        sm, s2, cnt, wt = lib.render_accum_w(tor, cfg)
+        img2, st2 = lib.postprocess(sm, s2, cnt, post, weight=wt if rr else None)
+        assert np.array_equal(img, img2) and st == st2
+        _, _, ost = oracle.resolve_display(sm, s2, cnt, 0.6, weight=wt if rr else None)
+        assert_bits_equal(np.array(st, np.float32), np.array(ost, np.float32), "dispersion statistics")
+
+
 def test_ragged_and_empty_inputs(lib, oracle):
     sc = scenes.cornell()
     # image sizes that are not multiples of the 8x8 tile, 1 sample, depth 1

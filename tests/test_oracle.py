@@ -171,3 +171,27 @@ def test_refract_matches_the_references_dead_code(oracle, reference):
         n_tir += tir
         assert_bits_equal(got, reference.refract(d, n, eta))
     assert 0 < n_tir < 4000
+
+
+def test_powf_restatement_matches_host_libm(oracle):
+    """glibc powf restated (oracle/pt_oracle.c or_powf_restated = what csrc/pt_post.cuh ref_powf implements) against
+    the host's powf: every k * 2^-24 in [0, 1) plus random bit patterns over the whole positive range."""
+    rng = np.random.default_rng(3)
+    unit = np.arange(1 << 24, dtype=np.float32) * np.float32(2.0 ** -24)
+    wide = rng.integers(0, 0x7f800000, 4_000_000, dtype=np.uint32).view(np.float32)
+    edge = np.array([0.0, 1.0, np.inf, 1e-45, 1.17e-38, 3.4e38, 255.0, 1.0000001, 0.99999994], np.float32)
+    for gamma in (1 / 2.2, 0.5, 1.0, 2.2):
+        for x in (unit, wide, edge):
+            bad, first = oracle.powf_check(x, gamma)
+            assert bad == 0, (gamma, first)
+
+
+def test_post_goldens_are_the_references(oracle, reference):
+    """The filter goldens come from the reference's own GaussBlur / MedianFilter (main.cpp:11-33, 49-80)."""
+    img = G["post_img"]
+    assert_bits_equal(reference.gauss_blur(img, 2), G["post_img_gauss2"])
+    assert_bits_equal(reference.median_filter(img, 1), G["post_img_median1"])
+    color, rgb8, st = oracle.resolve_display(G["cornell_sum"], G["cornell_sum2"], G["cornell_count"], 1 / 2.2)
+    assert np.array_equal(rgb8, G["post_cornell_rgb8"])
+    assert np.array_equal(oracle.to_rgb8(reference.gauss_blur(color, 2), G["cornell_count"]), G["post_cornell_gauss2"])
+    assert np.array_equal(oracle.to_rgb8(reference.median_filter(color, 3), G["cornell_count"]), G["post_cornell_median3"])
