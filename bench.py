@@ -314,7 +314,7 @@ def main():
     hbm_peak, peak_src, sm_max = peaks()
     roof = None
     if rank == 0:
-        cspp = max(world, min(spp, 8 * world))
+        cspp = max(world, min(spp, 64 * world))  # one full wavefront step of the production size per rank
         ccfg = ptb200.config(W, H, cspp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
                              accel=args.accel, mode=args.mode, q_shift=args.q_shift)
         # two instrumented frames (same image, cspp samples): one with traversal counters, one with CUDA events around
@@ -370,9 +370,12 @@ def main():
                          "bytes_per_launch": per_class_bytes[k] / max(1, cs["class_launches"][k]),
                          "share_of_step": cs["class_ms"][k] / max(1e-9, sum(cs["class_ms"])),
                          "class_ms": dict(zip(names, cs["class_ms"]))})
-            try:
+            try:  # measured DRAM traffic of that kernel (one ncu --set full capture), scaled to the timed launch
                 tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-                roof["traffic"] = tr.get(args.workload, {}).get(names[k])
+                per_slot = tr.get(args.workload, {}).get(names[k], {}).get("dram_bytes_per_slot")
+                if per_slot:
+                    roof["traffic"] = per_slot * paths_c / max(1, cs["class_launches"][0])
+                    roof["traffic_source"] = tr[args.workload][names[k]]["source"]
             except Exception:
                 pass
         else:
