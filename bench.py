@@ -30,6 +30,7 @@ WORKLOADS = {
     "cornell": ("configs[1]: synthetic Cornell box, 34 tris, 1080p 256 spp depth 8", 1920, 1080, 256, 8, -1.0),
     "torus1m": ("configs[2]: subdivided torus 1,000,014 tris, 1080p 256 spp depth 8, GPU LBVH", 1920, 1080, 256, 8, -1.0),
     "tor": ("configs[0]: models/Tor.obj 512x512 20 spp depth 8, adaptive error 0.001", 512, 512, 20, 8, 0.001),
+    "composite4k": ("configs[3]: Tor.obj + the two Cornell boxes, 290 tris, 4K 1024 spp depth 8 (spp split across the ranks)", 3840, 2160, 1024, 8, -1.0),
     "glossy": ("configs[4]: mixed glossy materials, 1080p 64 spp depth 32 (no Russian roulette)", 1920, 1080, 64, 32, -1.0),
 }
 
@@ -43,6 +44,8 @@ def make_scene(name):
         return scenes.torus_room(1000, 500)
     if name == "glossy":
         return scenes.glossy_mix()
+    if name == "composite4k":
+        return scenes.composite(ptb200.HostLoader().load_obj(os.path.join(ROOT, "assets", "models"), "Tor.obj"))
     if name == "tor":
         return ptb200.HostLoader().load_obj(os.path.join(ROOT, "assets", "models"), "Tor.obj")
     raise SystemExit(f"unknown workload {name}")
@@ -284,7 +287,7 @@ def main():
     # ---- end to end through the drop-in entry point: HOST scene -> pt_render -> HOST rgb (upload, LBVH build, render,
     # resolve, download all inside the timed region).  One call per step; with N ranks every rank renders its sample
     # partition through pt_render_accum and the accumulators are reduced from pinned host memory.
-    e2e_steps = max(1, min(args.steps, 2))
+    e2e_steps = max(1, min(args.steps, 3))
     h2d = int(sc["verts"].nbytes + sc["mat_ids"].nbytes + sc["mats"].nbytes +
               (sc["planes"].nbytes + sc["squares"].nbytes if sc.get("planes") is not None else 0))
     d2h = n_px * 3 * 4
@@ -300,8 +303,11 @@ def main():
         e2e_call()  # one untimed call: the library keeps its path-state workspace (GBs of HBM) between calls
     barrier()
     t0 = time.perf_counter()
+    e2e_calls = []
     for _ in range(e2e_steps):
+        tc = time.perf_counter()
         rgb = e2e_call()
+        e2e_calls.append({"ms": round((time.perf_counter() - tc) * 1e3, 1), "phases_ms": lib.last_phases() if world == 1 else None})
     barrier()
     e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device="cuda")
     if world > 1:
@@ -399,7 +405,8 @@ def main():
                           "segments_per_frame": segments_per_step},
                "frame_ms": ms_per_step, "frame_ms_e2e": float(e2e_s.item()) * 1e3,
                "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                       "api": "pt_render(const PtScene*, const PtConfig*, float* rgb)" if world == 1 else "pt_render_accum + NCCL reduce"},
+                       "api": "pt_render(const PtScene*, const PtConfig*, float* rgb)" if world == 1 else "pt_render_accum + NCCL reduce",
+                       "calls": e2e_calls},
                "gpu_launches": launches_per_step * args.steps, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         print(json.dumps(out))
     ds.close()

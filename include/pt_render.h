@@ -208,6 +208,9 @@ int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *
  * device; this frees it. */
 void pt_release_workspace(void);
 
+/* Host wall-clock milliseconds of the last pt_render call's phases: scene upload + LBVH build, frame buffers, render
+ * (returns when the last kernels are issued), resolve + download (waits for them), release. */
+void pt_last_phases(float *ms5);
 const char *pt_last_error(void);
 int pt_device_count(void);
 const char *pt_version(void);

@@ -20,6 +20,7 @@ using namespace ptd;
 namespace {
 
 thread_local char g_err[512] = "";
+float g_phase_ms[5] = {0, 0, 0, 0, 0};  // last pt_render: scene_create, frame buffers, render (issue), resolve + d2h, release
 
 int fail(int code, const char *fmt, ...) {
     va_list ap;
@@ -119,6 +120,7 @@ static int validate_config(const PtConfig *c) {
 }
 
 extern "C" const char *pt_last_error(void) { return g_err; }
+extern "C" void pt_last_phases(float *ms5) { for (int i = 0; i < 5; ++i) ms5[i] = g_phase_ms[i]; }
 extern "C" const char *pt_version(void) { return "path-tracing_b200 0.1 (sm_100a)"; }
 extern "C" int pt_device_count(void) {
     int n = 0;
@@ -621,11 +623,14 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     const bool prof = getenv("PT_PROFILE") != nullptr;  // wall-clock phase times on stderr
     using clk = std::chrono::steady_clock;
     auto t0 = clk::now();
-    auto lap = [&](const char *what) {
-        if (!prof) return;
-        cudaDeviceSynchronize();
+    int phase = 0;
+    for (float &v : g_phase_ms) v = 0.f;
+    auto lap = [&](const char *what) {  // host wall clock per phase (pt_last_phases); every phase ends in a blocking call
+        if (prof) cudaDeviceSynchronize();
         const auto t1 = clk::now();
-        fprintf(stderr, "[pt_render] %-14s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        const float ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
+        if (phase < 5) g_phase_ms[phase++] = ms;
+        if (prof) fprintf(stderr, "[pt_render] %-14s %8.2f ms\n", what, ms);
         t0 = t1;
     };
     PtDeviceScene *ds = nullptr;

@@ -94,13 +94,17 @@ __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large
 // marks between A and B (both near the diagonal).
 // The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles;
 // lanes whose candidates sit at different indices execute it together.
-__device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int n, V3 o, V3 d, float t_lo, float t_hi) {
+// (tnear, rnear): smallest scanned distance among the marked units so far and the first record of that unit
+__device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int n, V3 o, V3 d, float t_lo, float t_hi,
+                                               float &tnear, int &rnear) {
     unsigned mask = 0u;  // bit 2 (u - u0) = A of unit u, bit 2 (u - u0) + 1 = B
     for (int u = 0; u < n; ++u) {
         const float4 *r = units + kQuadRows * (u0 + u);
         const float4 p = r[0], meta = r[6];
-        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
-        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+        // contracted (FMA) dot products: they differ from the reference's by a few roundings of terms <= 2 amax, which
+        // tau already covers for both triangles of the unit (k_large_pack: c_abs >= 1e-6 amax, c_rel = 1e-6)
+        const float sd = __fmaf_rn(d.x, p.x, __fmaf_rn(d.y, p.y, d.z * p.z));
+        const float num = -__fmaf_rn(o.x, p.x, __fmaf_rn(o.y, p.y, __fmaf_rn(o.z, p.z, p.w)));
         const float rc = rcp_approx(sd);
         const float t = num * rc;
         const float tau = __fmaf_rn(fabsf(t), meta.y, meta.x) * fabsf(rc);
@@ -116,12 +120,16 @@ __device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int 
         const bool out = (t - tau > t_hi) | (t + tau < t_lo) | (fminf(fminf(g0, g1), fminf(g2, g3)) < -tol);
         const unsigned a = (out | (gd < -tol)) ? 0u : 1u, b = (out | (gd > meta.z + tol)) ? 0u : 2u;
         mask |= (a | b) << (2 * u);
+        const bool nearer = (a | b) != 0u && t < tnear;
+        tnear = nearer ? t : tnear;
+        rnear = nearer ? 2 * (u0 + u) : rnear;
     }
     return mask;
 }
 
 // one 32-triangle chunk of single units [s0, s0 + n): returns their candidate mask
-__device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, int n, V3 o, V3 d, float t_lo, float t_hi) {
+__device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, int n, int rec0, V3 o, V3 d, float t_lo,
+                                                 float t_hi, float &tnear, int &rnear) {
     unsigned mask = 0u;
     for (int k = 0; k < n; ++k) {
         const float4 *r = units + kSingleRows * (s0 + k);
@@ -138,6 +146,9 @@ __device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, in
         // written so that a NaN anywhere (sd == 0, infinities) marks the triangle: the resolve decides
         const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
         mask |= (out ? 0u : 1u) << k;
+        const bool nearer = !out && t < tnear;
+        tnear = nearer ? t : tnear;
+        rnear = nearer ? rec0 + s0 + k : rnear;
     }
     return mask;
 }
@@ -167,10 +178,30 @@ __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, 
     const float4 *quads = s_large + 4 * n_large, *singles = quads + kQuadRows * n_quads;
     const int n_single = n_large - 2 * n_quads;
     // records 2u, 2u + 1 belong to quad u; record 2 n_quads + s to single s
-    const unsigned q0 = scan_quads(quads, 0, min(n_quads, 16), o, d, t_lo, t_hi);
-    const unsigned q1 = n_quads > 16 ? scan_quads(quads, 16, n_quads - 16, o, d, t_lo, t_hi) : 0u;
-    const unsigned s0 = scan_singles(singles, 0, min(n_single, 32), o, d, t_lo, t_hi);
-    const unsigned s1 = n_single > 32 ? scan_singles(singles, 32, n_single - 32, o, d, t_lo, t_hi) : 0u;
+    float tnear = __int_as_float(0x7f800000);
+    int rnear = -1;
+    unsigned q0 = scan_quads(quads, 0, min(n_quads, 16), o, d, t_lo, t_hi, tnear, rnear);
+    unsigned q1 = n_quads > 16 ? scan_quads(quads, 16, n_quads - 16, o, d, t_lo, t_hi, tnear, rnear) : 0u;
+    unsigned s0 = scan_singles(singles, 0, min(n_single, 32), 2 * n_quads, o, d, t_lo, t_hi, tnear, rnear);
+    unsigned s1 = n_single > 32 ? scan_singles(singles, 32, n_single - 32, 2 * n_quads, o, d, t_lo, t_hi, tnear, rnear) : 0u;
+    // The unit with the smallest scanned distance first, all lanes together: it is the hit for most rays, and once
+    // h.t is set the other candidates leave the exact test at its range check.  Any order gives the same answer
+    // (header comment).
+    if (rnear >= 0) {
+        unsigned bits;
+        if (rnear < 2 * n_quads) {
+            unsigned &q = rnear < 32 ? q0 : q1;
+            const int sh = rnear & 31;
+            bits = (q >> sh) & 3u;
+            q &= ~(3u << sh);
+        } else {
+            const int k = rnear - 2 * n_quads;
+            unsigned &m = k < 32 ? s0 : s1;
+            bits = 1u;
+            m &= ~(1u << (k & 31));
+        }
+        large_resolve32(s_large, rnear, bits, rec_base, o, d, eps, h);
+    }
     large_resolve32(s_large, 0, q0, rec_base, o, d, eps, h);
     if (q1) large_resolve32(s_large, 32, q1, rec_base, o, d, eps, h);
     large_resolve32(s_large, 2 * n_quads, s0, rec_base, o, d, eps, h);

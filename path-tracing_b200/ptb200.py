@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases"]
 
 
 class PtScene(C.Structure):
@@ -121,6 +121,11 @@ class Library:
                                       C.POINTER(PtDispersion)]
         L.pt_powf.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_void_p]
         L.pt_release_workspace.restype = None
+
+    def last_phases(self):
+        ms = (C.c_float * 5)()
+        self.lib.pt_last_phases(ms)
+        return dict(zip(("scene_create", "frame_buffers", "render_issue", "resolve_d2h", "release"), [round(float(v), 2) for v in ms]))
 
     def check(self, rc):
         if rc != 0:
