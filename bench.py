@@ -292,12 +292,23 @@ def main():
               (sc["planes"].nbytes + sc["squares"].nbytes if sc.get("planes") is not None else 0))
     d2h = n_px * 3 * 4
     def e2e_call():
+        """HOST scene arrays -> HOST rgb through the C-ABI.  One GPU: pt_render.  N ranks: what a multi-process host does
+        with the device-resident entry points — pt_scene_create (upload + LBVH build), pt_scene_render_device on this
+        rank's sample partition, one NCCL reduce of (sum, count), pt_resolve_device, download on rank 0."""
         if world == 1:
             return lib.render(sc, cfg)
-        sm, _, cn = lib.render_accum(sc, cfg)
-        buf = torch.from_numpy(np.concatenate([sm.ravel(), cn.ravel().astype(np.float32)])).pin_memory().cuda(non_blocking=True)
-        dist.reduce(buf, 0, op=dist.ReduceOp.SUM)
-        return buf.cpu() if rank == 0 else None
+        h = lib.scene_create(sc, cfg)
+        h.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
+        acc[3 * n_px:].copy_(d_cnt_i)
+        dist.reduce(acc, 0, op=dist.ReduceOp.SUM)
+        out = None
+        if rank == 0:
+            d_cnt_i.copy_(acc[3 * n_px:])
+            h.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream)
+            out = d_rgb.cpu()
+        torch.cuda.synchronize()
+        h.close()
+        return out
 
     if args.warmup > 0:
         e2e_call()  # one untimed call: the library keeps its path-state workspace (GBs of HBM) between calls
@@ -312,7 +323,6 @@ def main():
     e2e_s = torch.tensor([(time.perf_counter() - t0) / e2e_steps], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-        d2h = n_px * 4 * 4
     e2e_mrays = segments_per_step / float(e2e_s.item()) / 1e6
 
     # ---- roofline of the dominant kernel (k_render): algorithmic bytes per ray = 64 B per BVH node visited + 64 B per
@@ -405,7 +415,7 @@ def main():
                           "segments_per_frame": segments_per_step},
                "frame_ms": ms_per_step, "frame_ms_e2e": float(e2e_s.item()) * 1e3,
                "e2e": {"value": e2e_mrays, "unit": "Mrays/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                       "api": "pt_render(const PtScene*, const PtConfig*, float* rgb)" if world == 1 else "pt_render_accum + NCCL reduce",
+                       "api": "pt_render(const PtScene*, const PtConfig*, float* rgb)" if world == 1 else "pt_scene_create + pt_scene_render_device + NCCL reduce + pt_resolve_device",
                        "calls": e2e_calls},
                "gpu_launches": launches_per_step * args.steps, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         print(json.dumps(out))

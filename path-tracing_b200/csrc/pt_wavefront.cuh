@@ -188,6 +188,9 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
 #ifndef PT_MIN_NODE_LANES
 #define PT_MIN_NODE_LANES 8   // the node phase ends when fewer lanes than this can still take a node step
 #endif
+#ifndef PT_TRAV_MIN_BLOCKS
+#define PT_TRAV_MIN_BLOCKS 10  // resident blocks of 128 threads per SM the traversal kernel is compiled for
+#endif
 constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
 
 // persistent warps over queue `set`: one ray per lane, refilled as lanes finish.
@@ -197,7 +200,7 @@ constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
 // first version of this kernel ran them with 3 of 32, profiles/r01_wf_sass_traverse_torus1m.txt).  Walking on
 // with a not-yet-shortened t only visits extra nodes: the nearest-hit rule is order independent (pt_trace.cuh).
 template <bool COUNT>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
     const int count = wf.counters[2 * set];
     if (count == 0) return;
