@@ -4,7 +4,9 @@
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
+#include <algorithm>
 #include <chrono>
+#include <map>
 #include <mutex>
 #include <stdlib.h>
 #include <vector>
@@ -51,13 +53,76 @@ int check_device() {
 
 inline int blocks_for(long long n, int bs) { return (int)((n + bs - 1) / bs); }
 
+// ---- device memory pool ---------------------------------------------------------------------------------------------
+// cudaMalloc / cudaFree take driver-wide locks and were measured to stall for 10-250 ms now and then on a shared box
+// (bench.py e2e, phases "frame buffers" / "release").  pt_render allocates the same sizes on every call, so freed
+// blocks are kept per device and handed out again: in the steady state a call makes no allocator calls at all.
+// Blocks are reused only after the work that used them has been waited for (every entry point synchronises before it
+// releases; pt_scene_destroy synchronises the device first).  pt_release_workspace() returns everything to the driver.
+struct DevPool {
+    std::mutex m;
+    std::multimap<std::pair<int, size_t>, void *> free_blocks;  // (device, bytes) -> block
+    std::map<void *, std::pair<int, size_t>> live;              // block -> (device, bytes)
+    std::vector<void *> pinned_free;                            // 64-byte pinned host blocks
+};
+DevPool g_pool;
+
+cudaError_t pool_alloc(void **out, size_t bytes) {
+    bytes = (std::max<size_t>(bytes, 1) + 255) & ~(size_t)255;
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    {
+        std::lock_guard<std::mutex> lock(g_pool.m);
+        auto it = g_pool.free_blocks.lower_bound({dev, bytes});
+        // the smallest cached block that fits, if it wastes less than half of itself (+1 MB for the small ones)
+        if (it != g_pool.free_blocks.end() && it->first.first == dev && it->first.second <= 2 * bytes + (1u << 20)) {
+            *out = it->second;
+            g_pool.live[*out] = it->first;
+            g_pool.free_blocks.erase(it);
+            return cudaSuccess;
+        }
+    }
+    e = cudaMalloc(out, bytes);
+    if (e == cudaErrorMemoryAllocation) {  // give the cache back and retry once
+        cudaGetLastError();
+        pt_release_workspace();
+        e = cudaMalloc(out, bytes);
+    }
+    if (e == cudaSuccess) {
+        std::lock_guard<std::mutex> lock(g_pool.m);
+        g_pool.live[*out] = {dev, bytes};
+    }
+    return e;
+}
+void pool_free(void *p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lock(g_pool.m);
+    auto it = g_pool.live.find(p);
+    if (it == g_pool.live.end()) { cudaFree(p); return; }
+    g_pool.free_blocks.insert({it->second, p});
+    g_pool.live.erase(it);
+}
+cudaError_t pool_alloc_pinned(void **out) {
+    {
+        std::lock_guard<std::mutex> lock(g_pool.m);
+        if (!g_pool.pinned_free.empty()) { *out = g_pool.pinned_free.back(); g_pool.pinned_free.pop_back(); return cudaSuccess; }
+    }
+    return cudaMallocHost(out, 64);
+}
+void pool_free_pinned(void *p) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lock(g_pool.m);
+    g_pool.pinned_free.push_back(p);
+}
+
 template <class T>
-struct DevBuf {  // RAII device allocation
+struct DevBuf {  // RAII device allocation (from the pool)
     T *p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t n) { return cudaMalloc((void **)&p, (n ? n : 1) * sizeof(T)); }
+    ~DevBuf() { pool_free(p); }
+    cudaError_t alloc(size_t n) { return pool_alloc((void **)&p, (n ? n : 1) * sizeof(T)); }
     T *release() { T *q = p; p = nullptr; return q; }
-    void free() { if (p) cudaFree(p); p = nullptr; }
+    void free() { pool_free(p); p = nullptr; }
 };
 
 }  // namespace
@@ -128,24 +193,12 @@ extern "C" int pt_device_count(void) {
     return n;
 }
 
-// One released workspace per process is kept for the next scene handle on the same device (pt_render creates and
-// destroys a handle per call; re-allocating gigabytes of path state every call costs more than a small frame).
-struct WorkspaceCache { void *mem = nullptr; size_t bytes = 0; int device = -1; };
-static WorkspaceCache g_ws;
-static std::mutex g_ws_mutex;
-
-static void ws_release(void *mem, size_t bytes, int device) {
-    if (!mem) return;
-    std::lock_guard<std::mutex> lock(g_ws_mutex);
-    if (g_ws.mem && g_ws.bytes >= bytes) { cudaFree(mem); return; }
-    if (g_ws.mem) cudaFree(g_ws.mem);
-    g_ws.mem = mem; g_ws.bytes = bytes; g_ws.device = device;
-}
-
 extern "C" void pt_release_workspace(void) {
-    std::lock_guard<std::mutex> lock(g_ws_mutex);
-    if (g_ws.mem) cudaFree(g_ws.mem);
-    g_ws = WorkspaceCache();
+    std::lock_guard<std::mutex> lock(g_pool.m);
+    for (auto &kv : g_pool.free_blocks) cudaFree(kv.second);
+    g_pool.free_blocks.clear();
+    for (void *p : g_pool.pinned_free) cudaFreeHost(p);
+    g_pool.pinned_free.clear();
 }
 
 extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
@@ -158,17 +211,18 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
         fprintf(stderr, "[pt_scene_destroy] %-12s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
     };
-    cudaFree(ds->tris);
-    cudaFree(ds->nodes);
-    cudaFree(ds->mats);
-    cudaFree(ds->lrecs);
-    cudaFree(ds->sky);
+    cudaDeviceSynchronize();  // blocks go back to the pool: nothing may still be using them (cudaFree used to wait)
+    pool_free(ds->tris);
+    pool_free(ds->nodes);
+    pool_free(ds->mats);
+    pool_free(ds->lrecs);
+    pool_free(ds->sky);
     lap("scene arrays");
-    ws_release(ds->wf_mem, ds->wf_bytes, ds->device);
+    pool_free(ds->wf_mem);
     lap("workspace");
-    if (ds->h_counters) cudaFreeHost(ds->h_counters);
+    pool_free_pinned(ds->h_counters);
     lap("pinned");
-    cudaFree(ds->stats);
+    pool_free(ds->stats);
     if (ds->ev0) cudaEventDestroy(ds->ev0);
     if (ds->ev1) cudaEventDestroy(ds->ev1);
     for (cudaEvent_t e : ds->class_events) cudaEventDestroy(e);
@@ -224,10 +278,10 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         k_triangle_setup<<<blocks_for(n, 256), 256>>>(d_verts.p, nullptr, nullptr, n, d_planes.p, d_squares.p);
         ++launches;
     }
-    CK(cudaMalloc((void **)&ds->mats, (m ? 3 * (size_t)m : 1) * sizeof(float4)));
+    CK(pool_alloc((void **)&ds->mats, (m ? 3 * (size_t)m : 1) * sizeof(float4)));
     if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, d_ext2.p, m, ds->mats); ++launches; }
-    CK(cudaMalloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
-    CK(cudaMalloc((void **)&ds->stats, kStatWords * sizeof(unsigned long long)));
+    CK(pool_alloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
+    CK(pool_alloc((void **)&ds->stats, kStatWords * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
 
     const bool brute = want == PT_ACCEL_BRUTE || n == 0;
@@ -249,7 +303,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         DevBuf<unsigned char> tmp;
         DevBuf<float4> d_root;
         CK(d_root.alloc(2));
-        CK(cudaMalloc((void **)&ds->lrecs, (size_t)kLargeRowsMax * sizeof(float4)));
+        CK(pool_alloc((void **)&ds->lrecs, (size_t)kLargeRowsMax * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
         CK(vals.alloc(n)); CK(vals2.alloc(n));
         k_init_scratch<<<1, 1>>>(d_scr.p);
@@ -282,7 +336,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         } else {
             CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb)); CK(children.alloc(nb)); CK(range.alloc(nb));
             CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
-            CK(cudaMalloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
+            CK(pool_alloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
             CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
             k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
             k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
@@ -318,7 +372,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     v.lrecs = ds->lrecs;
     if (scene->sky_bgr && scene->sky_width > 0 && scene->sky_height > 0) {
         const size_t sb = (size_t)scene->sky_width * scene->sky_height * 3;
-        CK(cudaMalloc((void **)&ds->sky, sb));
+        CK(pool_alloc((void **)&ds->sky, sb));
         CK(cudaMemcpy(ds->sky, scene->sky_bgr, sb, cudaMemcpyHostToDevice));
         v.sky = ds->sky; v.sky_w = scene->sky_width; v.sky_h = scene->sky_height;
     }
@@ -361,15 +415,9 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
     const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) +
                          npx4 * sizeof(float) + 256;
     if (!ds->wf_mem || ds->wf_bytes < bytes) {
-        if (ds->wf_mem) { CK(cudaDeviceSynchronize()); CK(cudaFree(ds->wf_mem)); ds->wf_mem = nullptr; ds->wf_bytes = 0; }
-        {
-            std::lock_guard<std::mutex> lock(g_ws_mutex);
-            if (g_ws.mem && g_ws.device == ds->device && g_ws.bytes >= bytes) {
-                ds->wf_mem = g_ws.mem; ds->wf_bytes = g_ws.bytes;
-                g_ws = WorkspaceCache();
-            }
-        }
-        if (!ds->wf_mem) { CK(cudaMalloc(&ds->wf_mem, bytes)); ds->wf_bytes = bytes; }
+        if (ds->wf_mem) { CK(cudaDeviceSynchronize()); pool_free(ds->wf_mem); ds->wf_mem = nullptr; ds->wf_bytes = 0; }
+        CK(pool_alloc(&ds->wf_mem, bytes));
+        ds->wf_bytes = bytes;
     }
     char *p = (char *)ds->wf_mem;
     WfState &w = ds->wf;
@@ -385,7 +433,7 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
     w.cap = (int)slots;
     ds->wf_slots = slots;
     ds->wf_pixels = npx;
-    if (!ds->h_counters) CK(cudaMallocHost((void **)&ds->h_counters, 8 * sizeof(int)));
+    if (!ds->h_counters) CK(pool_alloc_pinned((void **)&ds->h_counters));
     if (!ds->traverse_blocks) {
         int per_sm = 0, sms = 0;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false>, 128, 0));

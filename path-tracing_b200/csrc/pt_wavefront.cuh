@@ -132,19 +132,27 @@ template <bool COUNT>
 __global__ void __launch_bounds__(256)
 k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
     __shared__ float4 s_large[kLargeRowsMax];
+    // this thread's path state first: the loads are in flight while the block stages the shared-memory image
+    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in_range = slot < (npix << rp.q_shift);
+    float4 tn = make_float4(0.f, 0.f, 0.f, 0.f), ot = tn, dr = tn;
+    int s_base = 0;
+    if (in_range) {
+        tn = __ldcs(&wf.Tn[slot]);
+        ot = __ldcs(&wf.oT[slot]);
+        dr = __ldcs(&wf.dR[slot]);
+        s_base = __float_as_int(__ldcs(&wf.acc2[pix0 + (slot >> rp.q_shift)].w));
+    }
     if (!sc.brute) stage_large(sc, s_large);
     const int set = (b + 1) & 1;
     if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2 * (b & 1)] = 0; wf.counters[2 * (b & 1) + 1] = 0; }
     __syncthreads();
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long n_nodes = 0, n_tris = 0;
     bool alive = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
-    if (slot < (npix << rp.q_shift)) {
-        const float4 tn = __ldcs(&wf.Tn[slot]);
+    if (in_range) {
         int flags = __float_as_int(tn.w);
         if (flags & WF_ALIVE) {
-            const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
             o = mk(ot.x, ot.y, ot.z);
             d = mk(dr.x, dr.y, dr.z);
             V3 T = mk(tn.x, tn.y, tn.z), c = mk(0, 0, 0);
@@ -152,7 +160,7 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
             Hit h;
             h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
             const int p = pix0 + (slot >> rp.q_shift), q = slot & ((1 << rp.q_shift) - 1);
-            const int s = __float_as_int(__ldcs(&wf.acc2[p].w)) + q * rp.s_step;
+            const int s = s_base + q * rp.s_step;
             bool contrib = false;
             const bool rr_on = rp.rr_depth > 0;  // the path weight lives in cS.w; it is 1 unless roulette has been played
             float wgt = rr_on && depth + 1 > rp.rr_depth ? __ldcs(&wf.cS[slot].w) : 1.0f;

@@ -272,6 +272,21 @@ def test_render_image_is_render_plus_postprocess(lib, oracle, tor):
         assert_bits_equal(np.array(st, np.float32), np.array(ost, np.float32), "dispersion statistics")
 
 
+def test_memory_pool_reuse_is_invisible(lib, tor):
+    """The library recycles its device allocations between calls (pt_api.cu DevPool): alternating scenes, sizes and
+    entry points, with and without releasing the pool, must give the bits of a fresh call."""
+    cfg_a, cfg_b = ptb200.config(64, 64, 8, 8, 1e-4, 0.001, seed=3), ptb200.config(80, 48, 16, 8, 1e-4, -1.0, seed=4)
+    big = scenes.torus_room(60, 30)
+    first_a, first_b = lib.render_accum(tor, cfg_a), lib.render_accum(big, cfg_b)
+    for round_ in range(3):
+        for got, want in ((lib.render_accum(tor, cfg_a), first_a), (lib.render_accum(big, cfg_b), first_b)):
+            for g, w in zip(got, want):
+                assert_bits_equal(g, w)
+        lib.intersect(big, scenes.random_rays(5000, seed=round_))
+        if round_ == 1:
+            lib.lib.pt_release_workspace()
+
+
 def test_ragged_and_empty_inputs(lib, oracle):
     sc = scenes.cornell()
     # image sizes that are not multiples of the 8x8 tile, 1 sample, depth 1
