@@ -36,6 +36,15 @@ PTH_API void pth_copy_scene(float *vertices9, float *planes4, float *squares, in
     std::memcpy(mat_ids, g_view.material_ids, n * sizeof(int32_t));
     std::memcpy(mats10, g_view.materials, 10 * m * sizeof(float));
 }
+// extension: (Ni, Tr) per material as parsed; pth_has_refraction = some material would get the refractive lobe
+PTH_API void pth_copy_materials_ext(float *ext2) {
+    const auto &m = g_scene->Materials();
+    for (size_t j = 0; j < m.size(); ++j) {
+        ext2[2 * j] = m[j].GetCharacteristics().Ni;
+        ext2[2 * j + 1] = m[j].GetCharacteristics().Tr;
+    }
+}
+PTH_API int pth_has_refraction(void) { return g_scene && g_view.materials_ext != nullptr; }
 // Triangle's constructor (+ optional SetNormal) on raw arrays, for the loader parity test
 PTH_API void pth_triangle_setup(const float *v9, int has_vn, const float *vn3, float *plane4, float *square) {
     Triangle t({ptm::vec4(v9[0], v9[1], v9[2], 1), ptm::vec4(v9[3], v9[4], v9[5], 1), ptm::vec4(v9[6], v9[7], v9[8], 1)}, 0);

@@ -8,6 +8,7 @@
 #include "scene.h"
 
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <iostream>
 
@@ -29,14 +30,18 @@ void Scene::AddTriangle(Triangle triangle) { triangles_.push_back(triangle); }
 
 namespace {
 // "a/b/c" -> three 0-based indices, -1 where a field is missing or empty (atoi("") - 1, scene.cpp:91-96)
-void corner(const std::string &tok, int out[3]) {
-    size_t pos = 0;
+void corner(const char *b, const char *e, int out[3]) {
     for (int k = 0; k < 3; ++k) {
-        if (pos == std::string::npos) { out[k] = -1; continue; }
-        const size_t slash = tok.find('/', pos);
-        const std::string field = tok.substr(pos, slash == std::string::npos ? std::string::npos : slash - pos);
-        out[k] = std::atoi(field.c_str()) - 1;
-        pos = slash == std::string::npos ? std::string::npos : slash + 1;
+        if (b > e) { out[k] = -1; continue; }  // no more fields
+        // atoi: optional sign, digits; anything else ends the number (the token's '/' or its end)
+        const char *q = b;
+        bool neg = false;
+        if (q < e && (*q == '-' || *q == '+')) neg = *q++ == '-';
+        long v = 0;
+        while (q < e && *q >= '0' && *q <= '9') v = v * 10 + (*q++ - '0');
+        out[k] = static_cast<int>(neg ? -v : v) - 1;
+        while (q < e && *q != '/') ++q;  // rest of the field
+        b = q + 1;                        // past the '/', or past the end: later fields are missing
     }
 }
 
@@ -64,44 +69,99 @@ void read_mtl(const std::string &path, Scene &scene) {
 }
 }  // namespace
 
+namespace {
+// The OBJ as one buffer, read token by token.  Same token stream as the reference's `file >> input` (whitespace
+// separated; scene.cpp:37-38), same numeric conversion (strtof / strtol are what libstdc++'s operator>> ends in), but
+// no locale, sentry and stream-state work per token: a 1 M-triangle OBJ (40 MB) loads in a fraction of a second
+// instead of the seconds the stream extraction takes.
+class TokenStream {
+    std::string buf_;
+    const char *p_, *end_;
+
+public:
+    explicit TokenStream(std::ifstream &in) {
+        in.seekg(0, std::ios::end);
+        const std::streamoff n = in.tellg();
+        in.seekg(0, std::ios::beg);
+        buf_.resize(n > 0 ? static_cast<size_t>(n) : 0);
+        if (n > 0) in.read(&buf_[0], n);
+        buf_.push_back(' ');  // strtof / strtol stop here
+        p_ = buf_.data();
+        end_ = p_ + buf_.size() - 1;
+    }
+    static bool space(char c) { return c == ' ' || c == '\n' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
+    // next token as [b, e); false at end of file
+    bool next(const char *&b, const char *&e) {
+        while (p_ < end_ && space(*p_)) ++p_;
+        if (p_ >= end_) return false;
+        b = p_;
+        while (p_ < end_ && !space(*p_)) ++p_;
+        e = p_;
+        return true;
+    }
+    float next_float() {  // like `file >> f`: skips whitespace, converts the longest numeric prefix
+        while (p_ < end_ && space(*p_)) ++p_;
+        char *q = nullptr;
+        const float f = std::strtof(p_, &q);
+        if (q == p_) {  // not a number: the stream would fail here; consume the token, value 0
+            const char *b, *e;
+            next(b, e);
+            return 0.0f;
+        }
+        p_ = q;
+        return f;
+    }
+    int next_int() {
+        while (p_ < end_ && space(*p_)) ++p_;
+        char *q = nullptr;
+        const long v = std::strtol(p_, &q, 10);
+        if (q == p_) { const char *b, *e; next(b, e); return 0; }
+        p_ = q;
+        return static_cast<int>(v);
+    }
+};
+inline bool is_tok(const char *b, const char *e, const char *lit) {
+    const size_t n = std::strlen(lit);
+    return static_cast<size_t>(e - b) == n && std::memcmp(b, lit, n) == 0;
+}
+}  // namespace
+
 void Scene::LoadModel(std::string path) {
-    std::ifstream file(path);
+    std::ifstream file(path, std::ios::binary);
     if (!file.is_open()) {
         std::cerr << "Impossible to open the file !" << std::endl;
         std::exit(1);
     }
+    TokenStream ts(file);
     std::vector<vec4> positions;
     std::vector<vec3> normals;
     int current_material = 0;
-    std::string tok;
-    while (file >> tok) {
-        if (tok == "mtllib") {
-            std::string name;
-            file >> name;
-            read_mtl(Config::get().model_path + name, *this);
-        } else if (tok == "v") {
+    const char *b, *e;
+    while (ts.next(b, e)) {
+        if (is_tok(b, e, "mtllib")) {
+            if (!ts.next(b, e)) break;
+            read_mtl(Config::get().model_path + std::string(b, e), *this);
+        } else if (is_tok(b, e, "v")) {
             vec4 p(1);
-            file >> p.x >> p.y >> p.z;
+            p.x = ts.next_float(); p.y = ts.next_float(); p.z = ts.next_float();
             positions.push_back(p);
-        } else if (tok == "vt") {
-            float u, v;
-            file >> u >> v;
-        } else if (tok == "vn") {
+        } else if (is_tok(b, e, "vt")) {
+            ts.next_float(); ts.next_float();
+        } else if (is_tok(b, e, "vn")) {
             vec3 n;
-            file >> n.x >> n.y >> n.z;
+            n.x = ts.next_float(); n.y = ts.next_float(); n.z = ts.next_float();
             normals.push_back(n);
-        } else if (tok == "f") {
+        } else if (is_tok(b, e, "f")) {
             int idx[3][3];
             for (int i = 0; i < 3; ++i) {
-                std::string c;
-                file >> c;
-                corner(c, idx[i]);
+                if (!ts.next(b, e)) { b = e = ""; }
+                corner(b, e, idx[i]);
             }
             Triangle t({positions.at(idx[0][0]), positions.at(idx[1][0]), positions.at(idx[2][0])}, current_material);
             if (idx[0][2] >= 0) t.SetNormal(normals.at(idx[0][2]));
             triangles_.push_back(t);
-        } else if (tok == "usemtl") {
-            file >> current_material;
+        } else if (is_tok(b, e, "usemtl")) {
+            current_material = ts.next_int();
         }
     }
 }

@@ -322,6 +322,7 @@ class HostLoader:
         L = self.lib = _load(HOST_SO)
         L.pth_load_obj.argtypes = [C.c_char_p, C.c_char_p]
         L.pth_copy_scene.argtypes = [C.c_void_p] * 5
+        L.pth_copy_materials_ext.argtypes = [C.c_void_p]
         L.pth_triangle_setup.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pth_parse_config.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(PtConfig)]
 
@@ -337,6 +338,10 @@ class HostLoader:
               "mats": np.zeros((m, 10), np.float32)}
         self.lib.pth_copy_scene(sc["verts"].ctypes.data, sc["planes"].ctypes.data, sc["squares"].ctypes.data,
                                 sc["mat_ids"].ctypes.data, sc["mats"].ctypes.data)
+        ext = np.zeros((m, 2), np.float32)  # Ni, Tr as read from the MTL (extension; d -> Tr = 1 - d)
+        self.lib.pth_copy_materials_ext(ext.ctypes.data)
+        sc["mats_ext"] = ext if self.lib.pth_has_refraction() else None
+        sc["mats_ext_raw"] = ext
         return sc
 
     def triangle_setup(self, verts, vn=None):

@@ -63,6 +63,63 @@ def test_loader_matches_reference_loader(tor):
     np.testing.assert_allclose(tor["mats"][3][3:6], [1, .01, .01], rtol=1e-7)
 
 
+def _write_awkward_obj(d, n_quads=4000, seed=2):
+    """An OBJ that exercises the tokeniser: CRLF and tabs, scientific notation, explicit signs, vt / vn records, the
+    f forms a, a/b, a//c and a/b/c, several usemtl switches, comments-as-unknown-tokens; plus an MTL with the lines
+    the reference parses, the extension lines (Ni, d) and lines it ignores."""
+    rng = np.random.default_rng(seed)
+    with open(os.path.join(d, "awk.mtl"), "w") as f:
+        for k in range(3):
+            f.write(f"newmtl m{k}\nNs {96.078431 * k}\nKa 1 1 1\nKd {0.25 * (k + 1)} 0.5 1e-2\nKs .5 .5 .5\n"
+                    f"Ke {2 if k == 0 else 0} 0 0\nNi {1.0 + 0.25 * k}\nd {1.0 - 0.4 * k}\nillum 2\n\n")
+    verts = rng.uniform(-9, 9, (n_quads * 4, 3)).astype(np.float32)
+    fmt = ["{:.9g}", "{:+.8e}", "{:.7f}", "{:E}"]
+    lines = ["mtllib awk.mtl", "o thing"]
+    for i, v in enumerate(verts):
+        txt = [fmt[(i + k) % 4].format(float(c)) for k, c in enumerate(v)]
+        lines.append("v\t" + "  ".join(txt))
+        verts[i] = [np.float32(float(t)) for t in txt]  # what the text says (the short formats drop digits)
+    lines += ["vt 0.5 0.25", "vn 0 1 0", "vn 0.6 0 0.8", "s off"]
+    tris, mats, has_vn = [], [], []
+    forms = ["{a}", "{a}/1", "{a}//2", "{a}/1/1"]
+    for q in range(n_quads):
+        if q % 1000 == 0:
+            lines.append(f"usemtl {(q // 1000) % 3}")
+        a, b, c, e = 4 * q + 1, 4 * q + 2, 4 * q + 3, 4 * q + 4
+        for t in ((a, b, c), (a, c, e)):
+            form = forms[(q + t[1]) % 4]
+            lines.append("f " + " ".join(form.format(a=i) for i in t))
+            tris.append([verts[i - 1] for i in t])
+            mats.append((q // 1000) % 3)
+            has_vn.append({"{a}": 0, "{a}/1": 0, "{a}//2": 2, "{a}/1/1": 1}[form])
+    with open(os.path.join(d, "awk.obj"), "w", newline="") as f:
+        f.write("\r\n".join(lines) + "\r\n")
+    return np.asarray(tris, np.float32).reshape(-1, 9), np.asarray(mats, np.int32), np.asarray(has_vn)
+
+
+def test_fast_tokeniser_keeps_the_references_loader_semantics(loader, tmp_path):
+    """host/scene.cpp reads the OBJ from one buffer instead of `file >> token`; it must build what
+    the reference's Scene::LoadModel builds from the same file — compared live where oracle/_ref exists."""
+    verts, mats, has_vn = _write_awkward_obj(str(tmp_path))
+    sc = loader.load_obj(str(tmp_path), "awk.obj")
+    assert_bits_equal(sc["verts"], verts, "vertices")
+    assert np.array_equal(sc["mat_ids"], mats)
+    assert sc["mats"].shape[0] == 3 and sc["mats"][2][9] == np.float32(96.078431 * 2)
+    np.testing.assert_allclose(sc["mats_ext_raw"], [[1.0, 0.0], [1.25, 0.4], [1.5, 0.8]], rtol=1e-6)
+    vn = {1: (0, 1, 0), 2: (0.6, 0, 0.8)}
+    for i in np.flatnonzero(has_vn)[:50]:
+        np.testing.assert_allclose(sc["planes"][i][:3], vn[has_vn[i]], rtol=1e-6)
+    from oracle_py import Reference
+    if Reference.available():
+        ref = Reference()
+        ref.set_config(8, 8, 1, 1)
+        assert ref.load_obj(str(tmp_path), "awk.obj") == verts.shape[0]
+        planes, rverts, squares = ref.dump()
+        assert_bits_equal(sc["verts"], rverts, "vertices vs reference loader")
+        assert_bits_equal(sc["planes"], planes, "planes vs reference loader")
+        assert_bits_equal(sc["squares"], squares, "squares vs reference loader")
+
+
 def test_loader_missing_file(loader):
     with pytest.raises(FileNotFoundError):
         loader.load_obj("/nonexistent", "x.obj")
