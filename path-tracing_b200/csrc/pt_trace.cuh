@@ -53,13 +53,25 @@ __device__ __forceinline__ bool inside_test(float4 a, float4 b, float4 c, V3 o, 
     return !(fabsf(S - s1 - s2 - s3) > eps);
 }
 
+// 256-bit read-only load (LDG.E.256, sm_100): two float4 rows with one request.  A divergent warp pays one L1 tag
+// lookup per lane and instruction, and the traversal kernel is bound by exactly that (ncu: l1tex throughput 77 %,
+// issue 56 %), so a 64-byte node or triangle record is fetched with two of these instead of four LDG.128.
+// p must be 32-byte aligned (nodes and records are 64-byte aligned).
+__device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+}
+
 // Triangle::Intersect (triangles.h:48-73) on record `rec` (4 float4 at r).  Differences from the reference, both
 // outside its defined behaviour: a NaN distance (0/0: ray in the plane) is rejected instead of accepted, and equal
 // distances go to the lower caller index explicitly.
 __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o, V3 d, float eps, Hit &h) {
-    const float nd = plane_distance(r[0], o, d);
+    float4 pl, a, b, c;
+    ldg256(r, pl, a);
+    ldg256(r + 2, b, c);
+    const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
-    const float4 a = r[1], b = r[2], c = r[3];
     const int idx = __float_as_int(b.w);
     if (nd == h.t && !(idx < h.idx)) return;  // also rejects nd == +inf against the initial (inf, -1)
     if (!inside_test(a, b, c, o, d, nd, eps)) return;
@@ -266,7 +278,9 @@ __device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 
                                          unsigned long long &n_nodes) {
     {
         const float4 *nd = sc.nodes + 4 * (size_t)cur;
-        const float4 n0 = __ldg(nd), n1 = __ldg(nd + 1), n2 = __ldg(nd + 2), n3 = __ldg(nd + 3);
+        float4 n0, n1, n2, n3;
+        ldg256(nd, n0, n1);
+        ldg256(nd + 2, n2, n3);
         if (COUNT) ++n_nodes;
         // box_entry clips against h.t with <=, so that an equal-distance lower index is still found; +inf = miss
         const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
