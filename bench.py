@@ -230,6 +230,7 @@ def main():
     d_sum = acc[:3 * n_px]
     d_cnt_i = torch.zeros(n_px, dtype=torch.int32, device="cuda")
     d_rgb = torch.zeros(n_px * 3, device="cuda")
+    h_rgb = torch.empty(n_px * 3, pin_memory=True) if world > 1 and rank == 0 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
     launches_per_step = 0
@@ -305,7 +306,8 @@ def main():
         if rank == 0:
             d_cnt_i.copy_(acc[3 * n_px:])
             h.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream)
-            out = d_rgb.cpu()
+            h_rgb.copy_(d_rgb, non_blocking=True)  # pinned host buffer
+            out = h_rgb
         torch.cuda.synchronize()
         h.close()
         return out
