@@ -18,7 +18,10 @@
 
 namespace ptd {
 
-constexpr int kLeafMax = 4;          // triangles per LBVH leaf
+#ifndef PT_LEAF_MAX
+#define PT_LEAF_MAX 4
+#endif
+constexpr int kLeafMax = PT_LEAF_MAX;  // triangles per LBVH leaf (<= 8: leaf_count)
 constexpr int kMaxLarge = 64;        // triangles kept out of the LBVH and tested from shared memory first
 constexpr int kAllLargeMax = 48;     // scenes up to this size keep every triangle in shared memory (no LBVH)
 // Shared-memory image of the large triangles (k_large_pack), rows of float4:
