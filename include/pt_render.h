@@ -14,6 +14,7 @@
 #ifndef PT_RENDER_H
 #define PT_RENDER_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -202,6 +203,11 @@ int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float 
 int pt_philox(const uint32_t *ctr4, const uint32_t *key2, int64_t n, uint32_t *out4);
 int pt_sincos(const float *x, int64_t n, float *s, float *c);
 int pt_powf(const float *x, int64_t n, float y, float *out); /* the device's restatement of glibc powf */
+
+/* Measurement aid: read bandwidth in GB/s of a `footprint_bytes` buffer streamed `passes` times with
+ * 256-bit loads after one warm-up sweep — L2 bandwidth for a footprint below the L2 capacity (bench.py: 64 MB), HBM
+ * read bandwidth far above it.  No reference counterpart. */
+int pt_probe_read_bandwidth(size_t footprint_bytes, int passes, double *gb_per_s);
 int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
 
 /* pt_render / pt_scene_destroy keep the last path-state workspace (up to 9.7 GB of HBM) for the next call on the same

@@ -828,6 +828,52 @@ extern "C" int pt_powf(const float *x, int64_t n, float y, float *out) {
     return PT_OK;
 }
 
+// ---- read-bandwidth probe (the L2 peak is not in MEASURED_PEAKS.json; measured once per bench run) ------
+// Every thread streams 32-byte pieces of a `footprint`-byte buffer, `passes` times; a footprint below the L2 capacity
+// (126 MB) measures L2 read bandwidth, one far above it HBM read bandwidth.  The XOR of everything read goes to a
+// sink so that the loads stay.
+__global__ void __launch_bounds__(256) k_probe_read(const float4 *__restrict__ buf, size_t n_pairs, int passes,
+                                                    unsigned *sink) {
+    unsigned acc = 0;
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (int p = 0; p < passes; ++p)
+        for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n_pairs; i += stride) {
+            float4 a, b;
+            ldg256(buf + 2 * i, a, b);
+            acc ^= __float_as_uint(a.x) ^ __float_as_uint(a.w) ^ __float_as_uint(b.y) ^ __float_as_uint(b.z);
+        }
+    if (acc == 0x9e3779b9u) *sink = acc;
+}
+
+extern "C" int pt_probe_read_bandwidth(size_t footprint_bytes, int passes, double *gb_per_s) {
+    if (!gb_per_s || footprint_bytes < 4096 || passes < 1) return fail(PT_EINVAL, "bad arguments");
+    int rc;
+    if ((rc = check_device())) return rc;
+    const size_t n_pairs = footprint_bytes / 32;
+    DevBuf<float4> buf;
+    DevBuf<unsigned> sink;
+    CK(buf.alloc(2 * n_pairs)); CK(sink.alloc(1));
+    CK(cudaMemset(buf.p, 0, 32 * n_pairs));
+    cudaDeviceProp prop;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaGetDeviceProperties(&prop, dev));
+    const int blocks = prop.multiProcessorCount * 8;
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    k_probe_read<<<blocks, 256>>>(buf.p, n_pairs, 2, sink.p);  // warm-up: the footprint becomes L2 resident if it fits
+    CK(cudaEventRecord(e0));
+    k_probe_read<<<blocks, 256>>>(buf.p, n_pairs, passes, sink.p);
+    CK(cudaEventRecord(e1));
+    CK(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    CK(cudaGetLastError());
+    *gb_per_s = 32.0 * (double)n_pairs * passes / (ms * 1e-3) / 1e9;
+    return PT_OK;
+}
+
 // ---- building blocks exposed for parity tests ---------------------------------------------------------------
 extern "C" int pt_triangle_setup(const float *vertices, const uint8_t *has_vn, const float *vn, int64_t n,
                                  float *planes, float *squares) {

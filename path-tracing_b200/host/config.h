@@ -35,6 +35,7 @@ public:
     int gpus = 1;
     int accel = PT_ACCEL_AUTO;
     int rr = 0;  // -RR <depth>: Russian roulette once a path's depth reaches <depth> (0 = off)
+    std::string cache = "";  // -CACHE <dir>: keep a binary image of the parsed model there (scene.cpp, LoadModel)
 
     static Config &get() {
         static Config instance;
@@ -65,6 +66,7 @@ public:
             else if (is("-GPUS")) gpus = std::atoi(val);
             else if (is("-ACCEL")) accel = std::atoi(val);
             else if (is("-RR")) rr = std::atoi(val);
+            else if (is("-CACHE")) cache = val;
         }
     }
 

@@ -7,6 +7,9 @@
 // material by its ordinal.  An unopenable OBJ is fatal (exit(1)), as scene.cpp:32-35.
 #include "scene.h"
 
+#include <sys/stat.h>
+
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
@@ -126,12 +129,119 @@ inline bool is_tok(const char *b, const char *e, const char *lit) {
 }
 }  // namespace
 
+// ---- binary scene cache (extension; -CACHE <dir>) ------------------------------------------------------------
+// What LoadModel produces — triangles as constructed (vertices, plane, area, material ordinal) and the material
+// table — written as flat arrays next to a validity record: size and modification time of the OBJ and of every MTL
+// it pulled in.  A stale, truncated or foreign file is ignored and rewritten; a cache that cannot be written is not
+// an error.  The 1 000 014-triangle model: 60 MB of cache read in tens of milliseconds instead of parsing 70 MB of
+// text.
+namespace {
+struct FileStamp {
+    int64_t size = -1, mtime_ns = 0;
+    bool operator==(const FileStamp &o) const { return size == o.size && mtime_ns == o.mtime_ns; }
+};
+FileStamp stamp_of(const std::string &path) {
+    struct stat st;
+    FileStamp s;
+    if (::stat(path.c_str(), &st) == 0) {
+        s.size = static_cast<int64_t>(st.st_size);
+        s.mtime_ns = static_cast<int64_t>(st.st_mtim.tv_sec) * 1000000000ll + st.st_mtim.tv_nsec;
+    }
+    return s;
+}
+const char kCacheMagic[8] = {'P', 'T', 'B', '2', 'S', 'C', '0', '1'};
+struct CacheHeader {
+    char magic[8];
+    int64_t n_triangles, n_materials, n_mtl_files;
+    FileStamp obj;
+};
+template <class T> bool put(std::FILE *f, const T *p, size_t n) { return std::fwrite(p, sizeof(T), n, f) == n; }
+template <class T> bool get(std::FILE *f, T *p, size_t n) { return std::fread(p, sizeof(T), n, f) == n; }
+std::string cache_name(const std::string &dir, const std::string &obj_path) {
+    const size_t slash = obj_path.find_last_of('/');
+    std::string d = dir;
+    if (!d.empty() && d.back() != '/') d += '/';
+    return d + (slash == std::string::npos ? obj_path : obj_path.substr(slash + 1)) + ".ptscene";
+}
+}  // namespace
+
+void Scene::SaveCache(const std::string &cache_file, const std::string &obj_path) const {
+    const std::string tmp = cache_file + ".tmp";
+    std::FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return;
+    CacheHeader h;
+    std::memcpy(h.magic, kCacheMagic, 8);
+    h.n_triangles = static_cast<int64_t>(triangles_.size());
+    h.n_materials = static_cast<int64_t>(materials_.size());
+    h.n_mtl_files = static_cast<int64_t>(mtl_files_.size());
+    h.obj = stamp_of(obj_path);
+    bool ok = put(f, &h, 1);
+    for (const std::string &m : mtl_files_) {
+        const int64_t len = static_cast<int64_t>(m.size());
+        const FileStamp st = stamp_of(m);
+        ok = ok && put(f, &len, 1) && put(f, m.data(), m.size()) && put(f, &st, 1);
+    }
+    const PtScene s = abi();  // the flat arrays
+    const size_t n = triangles_.size(), m = materials_.size();
+    ok = ok && put(f, s.vertices, 9 * n) && put(f, s.planes, 4 * n) && put(f, s.squares, n) && put(f, s.material_ids, n) &&
+         put(f, s.materials, 10 * m) && put(f, mats_ext_.data(), 2 * m);
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok || std::rename(tmp.c_str(), cache_file.c_str()) != 0) std::remove(tmp.c_str());
+}
+
+bool Scene::LoadCache(const std::string &cache_file, const std::string &obj_path) {
+    std::FILE *f = std::fopen(cache_file.c_str(), "rb");
+    if (!f) return false;
+    CacheHeader h;
+    bool ok = get(f, &h, 1) && std::memcmp(h.magic, kCacheMagic, 8) == 0 && h.obj == stamp_of(obj_path) &&
+              h.n_triangles >= 0 && h.n_triangles <= 0x7fffffff && h.n_materials >= 0 && h.n_materials < (1 << 24) &&
+              h.n_mtl_files >= 0 && h.n_mtl_files < 4096;
+    std::vector<std::string> mtls;
+    for (int64_t k = 0; ok && k < h.n_mtl_files; ++k) {
+        int64_t len = 0;
+        FileStamp st;
+        ok = get(f, &len, 1) && len >= 0 && len < 65536;
+        std::string name(ok ? static_cast<size_t>(len) : 0, '\0');
+        ok = ok && get(f, &name[0], name.size()) && get(f, &st, 1) && st == stamp_of(name);
+        mtls.push_back(name);
+    }
+    if (!ok) { std::fclose(f); return false; }
+    const size_t n = static_cast<size_t>(h.n_triangles), m = static_cast<size_t>(h.n_materials);
+    std::vector<float> v(9 * n), p(4 * n), sq(n), mt(10 * m), ext(2 * m);
+    std::vector<int32_t> ids(n);
+    ok = get(f, v.data(), v.size()) && get(f, p.data(), p.size()) && get(f, sq.data(), n) && get(f, ids.data(), n) &&
+         get(f, mt.data(), mt.size()) && get(f, ext.data(), ext.size());
+    char extra;
+    ok = ok && std::fread(&extra, 1, 1, f) == 0;  // nothing may follow
+    std::fclose(f);
+    if (!ok) return false;
+    for (size_t j = 0; j < m; ++j) {
+        MaterialCharacteristics ch;
+        const float *r = &mt[10 * j];
+        ch.Ke = vec3(r[0], r[1], r[2]); ch.Kd = vec3(r[3], r[4], r[5]); ch.Ks = vec3(r[6], r[7], r[8]);
+        ch.Ns = r[9]; ch.Ni = ext[2 * j]; ch.Tr = ext[2 * j + 1];
+        AddMaterial(ch);
+    }
+    triangles_.reserve(triangles_.size() + n);
+    for (size_t i = 0; i < n; ++i) triangles_.emplace_back(&v[9 * i], &p[4 * i], sq[i], ids[i]);
+    mtl_files_ = mtls;
+    return true;
+}
+
 void Scene::LoadModel(std::string path) {
     std::ifstream file(path, std::ios::binary);
     if (!file.is_open()) {
         std::cerr << "Impossible to open the file !" << std::endl;
         std::exit(1);
     }
+    loaded_from_cache = false;
+    const std::string &cache_dir = Config::get().cache;
+    const bool fresh = triangles_.empty() && materials_.empty();  // the image describes a whole scene, not an increment
+    if (!cache_dir.empty() && fresh && LoadCache(cache_name(cache_dir, path), path)) {
+        loaded_from_cache = true;
+        return;
+    }
+    mtl_files_.clear();
     TokenStream ts(file);
     std::vector<vec4> positions;
     std::vector<vec3> normals;
@@ -140,7 +250,8 @@ void Scene::LoadModel(std::string path) {
     while (ts.next(b, e)) {
         if (is_tok(b, e, "mtllib")) {
             if (!ts.next(b, e)) break;
-            read_mtl(Config::get().model_path + std::string(b, e), *this);
+            mtl_files_.push_back(Config::get().model_path + std::string(b, e));
+            read_mtl(mtl_files_.back(), *this);
         } else if (is_tok(b, e, "v")) {
             vec4 p(1);
             p.x = ts.next_float(); p.y = ts.next_float(); p.z = ts.next_float();
@@ -164,6 +275,7 @@ void Scene::LoadModel(std::string path) {
             current_material = ts.next_int();
         }
     }
+    if (!cache_dir.empty() && fresh) SaveCache(cache_name(cache_dir, path), path);
 }
 
 PtScene Scene::abi() const {

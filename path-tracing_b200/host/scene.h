@@ -27,7 +27,13 @@ class Scene {
     std::vector<float> weight_;  // per-pixel divisor of the last Render, row-major [y][x] (== samples_count without -RR)
     mutable std::vector<int32_t> mat_ids_;
 
+    // binary image of a parsed model (extension): see scene.cpp
+    bool LoadCache(const std::string &cache_file, const std::string &obj_path);
+    void SaveCache(const std::string &cache_file, const std::string &obj_path) const;
+    std::vector<std::string> mtl_files_;  // the MTL files LoadModel read, for the cache's validity record
+
 public:
+    bool loaded_from_cache = false;  // the last LoadModel took the binary image instead of parsing
     Scene(std::vector<std::vector<ptm::vec3>> &color_map, std::vector<std::vector<ptm::vec3>> &color2_map,
           std::vector<std::vector<int>> &samples_count);
     void LoadModel(std::string path);

@@ -23,6 +23,11 @@ public:
         SetNormal(n);
         square = ptm::length(n);
     }
+    // a triangle exactly as a previous constructor (+ SetNormal) call left it: the binary scene cache (scene.cpp)
+    Triangle(const float v9[9], const float plane4[4], float sq, int material_id)
+        : plane_(plane4[0], plane4[1], plane4[2], plane4[3]), material_id_(material_id), square(sq) {
+        for (size_t i = 0; i < 3; ++i) vertices_[i] = ptm::vec3(v9[3 * i], v9[3 * i + 1], v9[3 * i + 2]);
+    }
     ptm::vec4 GetNormal() const { return ptm::vec4(plane_.x, plane_.y, plane_.z, 0); }
     ptm::vec4 GetPlane() const { return plane_; }
     void SetNormal(ptm::vec3 normal) {

@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth"]
 
 
 class PtScene(C.Structure):
@@ -120,6 +120,7 @@ class Library:
         L.pt_render_image.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.POINTER(PtPostConfig), C.c_void_p,
                                       C.POINTER(PtDispersion)]
         L.pt_powf.argtypes = [C.c_void_p, C.c_int64, C.c_float, C.c_void_p]
+        L.pt_probe_read_bandwidth.argtypes = [C.c_size_t, C.c_int, C.POINTER(C.c_double)]
         L.pt_release_workspace.restype = None
 
     def last_phases(self):
@@ -231,6 +232,12 @@ class Library:
         self.check(self.lib.pt_powf(x.ctypes.data, x.size, y, out.ctypes.data))
         return out
 
+    def probe_read_bandwidth(self, footprint_bytes, passes=20):
+        """GB/s of streaming a buffer of that size `passes` times (L2 bandwidth when it fits in L2)"""
+        g = C.c_double(0.0)
+        self.check(self.lib.pt_probe_read_bandwidth(footprint_bytes, passes, C.byref(g)))
+        return g.value
+
     # ---- after the loop (main.cpp:162-201) ----
     @staticmethod
     def post_config(width, height, gamma=1 / 2.2, gauss=0, median=0):
@@ -325,11 +332,16 @@ class HostLoader:
         L.pth_copy_materials_ext.argtypes = [C.c_void_p]
         L.pth_triangle_setup.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.pth_parse_config.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(PtConfig)]
+        L.pth_set_cache_dir.argtypes = [C.c_char_p]
 
-    def load_obj(self, model_path, model_name):
+    def load_obj(self, model_path, model_name, cache_dir=""):
+        """cache_dir: the host side's -CACHE <dir> (binary image of the parsed model); sc["from_cache"] tells whether
+        this load took it"""
         if not model_path.endswith("/"):
             model_path += "/"
+        self.lib.pth_set_cache_dir(cache_dir.encode())
         n = self.lib.pth_load_obj(model_path.encode(), model_name.encode())
+        self.lib.pth_set_cache_dir(b"")
         if n < 0:
             raise FileNotFoundError(model_path + model_name)
         m = self.lib.pth_material_count()
@@ -342,6 +354,7 @@ class HostLoader:
         self.lib.pth_copy_materials_ext(ext.ctypes.data)
         sc["mats_ext"] = ext if self.lib.pth_has_refraction() else None
         sc["mats_ext_raw"] = ext
+        sc["from_cache"] = bool(self.lib.pth_loaded_from_cache())
         return sc
 
     def triangle_setup(self, verts, vn=None):

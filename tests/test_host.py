@@ -120,6 +120,48 @@ def test_fast_tokeniser_keeps_the_references_loader_semantics(loader, tmp_path):
         assert_bits_equal(sc["squares"], squares, "squares vs reference loader")
 
 
+def test_binary_scene_cache(loader, tmp_path):
+    """-CACHE <dir>: the second load takes the binary image and yields the same arrays bit for
+    bit; a changed OBJ or MTL, a truncated or foreign cache file fall back to parsing."""
+    d, cache = str(tmp_path), str(tmp_path / "cache")
+    os.mkdir(cache)
+    _write_awkward_obj(d, n_quads=500)
+    plain = loader.load_obj(d, "awk.obj")
+    first = loader.load_obj(d, "awk.obj", cache_dir=cache)
+    assert not plain["from_cache"] and not first["from_cache"]
+    img = os.path.join(cache, "awk.obj.ptscene")
+    assert os.path.exists(img) and not os.path.exists(img + ".tmp")
+    again = loader.load_obj(d, "awk.obj", cache_dir=cache)
+    assert again["from_cache"]
+    for k in ("verts", "planes", "squares", "mat_ids", "mats", "mats_ext_raw"):
+        assert_bits_equal(np.asarray(again[k]), np.asarray(plain[k]), k)
+    assert (again["mats_ext"] is None) == (plain["mats_ext"] is None)
+    # truncated image: ignored, rewritten
+    blob = open(img, "rb").read()
+    open(img, "wb").write(blob[: len(blob) // 2])
+    assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    assert open(img, "rb").read() == blob
+    # trailing garbage / foreign file
+    open(img, "wb").write(blob + b"x")
+    assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    open(img, "wb").write(b"not a cache")
+    assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    assert loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    # the MTL changes: stale
+    with open(os.path.join(d, "awk.mtl"), "a") as f:
+        f.write("\nnewmtl extra\nKd 0.1 0.2 0.3\n")
+    changed = loader.load_obj(d, "awk.obj", cache_dir=cache)
+    assert not changed["from_cache"] and changed["mats"].shape[0] == plain["mats"].shape[0] + 1
+    assert loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    # the OBJ changes: stale
+    with open(os.path.join(d, "awk.obj"), "a") as f:
+        f.write("f 1 2 3\n")
+    grown = loader.load_obj(d, "awk.obj", cache_dir=cache)
+    assert not grown["from_cache"] and grown["verts"].shape[0] == plain["verts"].shape[0] + 1
+    # an unwritable cache directory is not an error
+    assert not loader.load_obj(d, "awk.obj", cache_dir="/nonexistent/dir")["from_cache"]
+
+
 def test_loader_missing_file(loader):
     with pytest.raises(FileNotFoundError):
         loader.load_obj("/nonexistent", "x.obj")
