@@ -96,7 +96,12 @@ typedef struct PtConfig {
     int32_t device;       /* first CUDA device ordinal */
     int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant;
                              [1]: 0 = automatic, 1..6 = log2 of the samples per pixel one wavefront step carries;
-                             [2], [3] must be 0 */
+                             [2]: 1 = RESUME: the accumulator arrays passed to pt_render_accum(_w) /
+                                  pt_scene_render_device(_w) hold the loop's state after the samples before
+                                  sample_begin and the call continues from them, bit-identical to one call over all
+                                  samples (progressive refresh main.cpp:141-158, time limit main.cpp:111-114);
+                                  0 = start from zero;
+                             [3] must be 0 */
 } PtConfig;
 
 /* Statistics of the last render on a scene handle. */
@@ -186,6 +191,18 @@ int pt_postprocess_device(const float *d_sum3, const float *d_sum2_3, const int3
  * 3 bytes per pixel leave the device. */
 int pt_render_image(const PtScene *scene, const PtConfig *cfg, const PtPostConfig *post, uint8_t *rgb8,
                     PtDispersion *stats);
+
+/* The loop with the reference's refresh and time limit (main.cpp:111-114, 141-158): samples are rendered in blocks on
+ * device-resident accumulators (RESUME mode, bit-identical to one pt_render_image call when nothing stops it).
+ * update > 0: after the blocks ending behind sample 0, update, 2 update, ... `on_update(user, rgb8, samples)` gets the
+ * gamma-only image (no filter), `samples` = samples per pixel rendered so far; a non-zero return stops the loop.
+ * update == 0: no refresh.  time_limit_ms > 0: no new block starts once that much time has passed since the call
+ * (the reference checks before every sample; here before every block of `update` — or 64 — samples).
+ * rgb8 receives the final image (full post-loop stage), *samples_done the `rays_count` of the output file name. */
+typedef int (*PtPreviewFn)(void *user, const uint8_t *rgb8, int32_t samples);
+int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, const PtPostConfig *post, int update,
+                          int64_t time_limit_ms, PtPreviewFn on_update, void *user, uint8_t *rgb8,
+                          PtDispersion *stats, int32_t *samples_done);
 
 /* Nearest hit on an explicit ray set, exactly the loop scene.cpp:114-120: rays6 = n×(ox,oy,oz,dx,dy,dz) HOST
  * floats; the direction is normalised as Ray's constructor does (ray.h:21-25).  tri_id[i] = index in the

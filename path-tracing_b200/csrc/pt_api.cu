@@ -179,8 +179,9 @@ static int validate_config(const PtConfig *c) {
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
     if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
     if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
-    if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] || c->reserved[3])
-        return fail(PT_EINVAL, "reserved[1] must be 0..6 (log2 samples per wavefront step), reserved[2..3] zero");
+    if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] < 0 || c->reserved[2] > 1 || c->reserved[3])
+        return fail(PT_EINVAL, "reserved[1] must be 0..6 (log2 samples per wavefront step), reserved[2] 0/1 (resume), "
+                               "reserved[3] zero");
     return PT_OK;
 }
 
@@ -398,12 +399,13 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     // samples per wavefront step: reserved[1] = log2 (1..6) overrides; otherwise up to 64 for a flat-spp render (the
     // largest power of two <= the samples this rank traces), 4 when the adaptive rule can discard samples traced
     // ahead of it
-    const int per_rank = cfg->rays_per_pixel / (cfg->sample_step > 0 ? cfg->sample_step : 1);
+    const int per_rank = std::max(0, cfg->rays_per_pixel - cfg->sample_begin) / (cfg->sample_step > 0 ? cfg->sample_step : 1);
     int q_auto = 2;
     if (cfg->error < 0.0f) while (q_auto < 6 && (2 << q_auto) <= per_rank) ++q_auto;
     rp.q_shift = cfg->reserved[1] ? cfg->reserved[1] : q_auto;
     rp.rr_depth = cfg->rr_depth;
     rp.weight = d_weight;
+    rp.resume = cfg->reserved[2] == 1;
     return rp;
 }
 
@@ -453,7 +455,7 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     const SceneView &sc = ds->view;
     const int npc_max = (int)(ds->wf_slots >> rp.q_shift);
     int n = 0;
-    k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp.s_begin);
+    k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp);
     ++n;
     // timed mode: an event pair around every launch of a step, read back after the step
     const bool timed = ds->timed_classes;
@@ -545,6 +547,8 @@ extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, 
     int rc;
     if ((rc = validate_config(cfg))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
+    if (cfg->reserved[2] == 1 && (!d_sum3 || !d_sum2_3 || !d_count || (cfg->rr_depth > 0 && !d_weight)))
+        return fail(PT_EINVAL, "resume needs every accumulator (sum, sum2, count; weight under Russian roulette)");
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
     const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
     CK(cudaEventRecord(ds->ev0, st));
@@ -651,6 +655,14 @@ extern "C" int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, floa
     DevBuf<int> d_cnt;
     CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px));
     if (weight) CK(d_wt.alloc(px));
+    if (cfg->reserved[2] == 1) {  // resume: the caller's arrays are the state to continue from
+        if (!sum3 || !sum2_3 || !count || (cfg->rr_depth > 0 && !weight))
+            return fail(PT_EINVAL, "resume needs every accumulator (sum, sum2, count; weight under Russian roulette)");
+        CK(cudaMemcpy(d_sum.p, sum3, 3 * px * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_sum2.p, sum2_3, 3 * px * sizeof(float), cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(d_cnt.p, count, px * sizeof(int), cudaMemcpyHostToDevice));
+        if (weight) CK(cudaMemcpy(d_wt.p, weight, px * sizeof(float), cudaMemcpyHostToDevice));
+    }
     if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, weight ? d_wt.p : nullptr, nullptr))) return rc;
     CK(cudaDeviceSynchronize());
     if (weight) CK(cudaMemcpy(weight, d_wt.p, px * sizeof(float), cudaMemcpyDeviceToHost));
@@ -811,6 +823,70 @@ extern "C" int pt_render_image(const PtScene *scene, const PtConfig *cfg, const 
     if ((rc = pt_scene_render_device_w(ds, cfg, d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, nullptr))) return rc;
     if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, post, d_img.p, stats, nullptr))) return rc;
     CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
+    return PT_OK;
+}
+
+// The sample loop as the reference runs it — refresh of the image every `update` samples (main.cpp:141-158), stop at
+// a time limit (main.cpp:111-114) — on device-resident accumulators: blocks of samples rendered with the RESUME mode
+// of pt_scene_render_device, a gamma-only preview after the blocks the reference refreshes after (sample indices
+// 0, update, 2 update, ...), the full post-loop stage at the end.
+extern "C" int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, const PtPostConfig *post, int update,
+                                     int64_t time_limit_ms, PtPreviewFn on_update, void *user, uint8_t *rgb8,
+                                     PtDispersion *stats, int32_t *samples_done) {
+    int rc;
+    if (!rgb8) return fail(PT_EINVAL, "rgb8 is NULL");
+    if (update < 0 || time_limit_ms < 0) return fail(PT_EINVAL, "update and time_limit_ms must be >= 0");
+    if ((rc = validate_config(cfg)) || (rc = validate_scene(scene)) || (rc = validate_post(post))) return rc;
+    if (post->width != cfg->width || post->height != cfg->height) return fail(PT_EINVAL, "post and render sizes differ");
+    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
+    if (cfg->reserved[2]) return fail(PT_EINVAL, "pt_render_progressive manages the resume state itself");
+    if ((rc = check_device())) return rc;
+    CK(cudaSetDevice(cfg->device));
+    const auto t0 = std::chrono::steady_clock::now();
+    PtDeviceScene *ds = nullptr;
+    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
+    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    const size_t px = (size_t)cfg->width * cfg->height;
+    DevBuf<float> d_sum, d_sum2, d_wt;
+    DevBuf<int> d_cnt;
+    DevBuf<uint8_t> d_img;
+    CK(d_sum.alloc(3 * px)); CK(d_sum2.alloc(3 * px)); CK(d_cnt.alloc(px)); CK(d_img.alloc(3 * px)); CK(d_wt.alloc(px));
+    const bool rr = cfg->rr_depth > 0;
+    PtPostConfig preview = *post;  // main.cpp:144-150: gamma only
+    preview.gauss = 0; preview.median = 0;
+    const int step = cfg->sample_step > 0 ? cfg->sample_step : 1, spp = cfg->rays_per_pixel;
+    const int stride = (update > 0 ? update : 64) * step;  // samples of this partition per block
+    int done = cfg->sample_begin;                           // first sample index not yet rendered
+    bool first = true, stopped = false;
+    while (done < spp && !stopped) {
+        if (time_limit_ms > 0) {
+            const auto ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+            if (ms >= time_limit_ms) break;
+        }
+        // the reference refreshes after sample 0, update, 2 update, ...: the first block is one sample long
+        PtConfig c = *cfg;
+        c.sample_begin = done;
+        c.rays_per_pixel = std::min(spp, first && update > 0 ? done + step : done + stride);
+        c.reserved[2] = first ? 0 : 1;
+        if ((rc = pt_scene_render_device_w(ds, &c, d_sum.p, d_sum2.p, d_cnt.p, d_wt.p, nullptr))) return rc;
+        // next sample of the partition at or after the block's end
+        done += ((c.rays_per_pixel - done + step - 1) / step) * step;
+        const int k_done = (std::min(done, spp + step - 1) - cfg->sample_begin) / step;  // samples of the partition so far
+        if (update > 0 && on_update && (k_done - 1) % update == 0) {  // main.cpp:143: rays_count % update == 0
+            if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, &preview, d_img.p, nullptr, nullptr)))
+                return rc;
+            CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
+            stopped = on_update(user, rgb8, std::min(done, spp)) != 0;
+        }
+        first = false;
+    }
+    if (first) {  // nothing rendered (time limit already over, or no samples): empty accumulators
+        CK(cudaMemset(d_sum.p, 0, 3 * px * sizeof(float))); CK(cudaMemset(d_sum2.p, 0, 3 * px * sizeof(float)));
+        CK(cudaMemset(d_cnt.p, 0, px * sizeof(int))); CK(cudaMemset(d_wt.p, 0, px * sizeof(float)));
+    }
+    if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, post, d_img.p, stats, nullptr))) return rc;
+    CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
+    if (samples_done) *samples_done = std::min(done, spp);
     return PT_OK;
 }
 

@@ -29,6 +29,7 @@ struct RenderParams {
     int q_shift;    // wavefront pipeline: 2^q_shift consecutive samples of a pixel per step
     int rr_depth;   // extension: Russian roulette once Ray::depth >= rr_depth (0 = off, the reference)
     float *weight;  // extension: per-pixel sum of the contributing paths' RR weights (== count without RR)
+    int resume;     // the output buffers hold the accumulators after the samples before s_begin: continue from them
 };
 
 constexpr float kPi = 3.141593f;  // material.h:12
@@ -209,6 +210,12 @@ k_render_mega(SceneView sc, RenderParams rp) {
     int cnt = 0;
     float wsum = 0.0f;        // weight sum of the contributing paths (Russian roulette only)
     const bool rr_on = rp.rr_depth > 0;
+    if (rp.resume && in_image) {  // continue a render: the loop state after the samples before s_begin
+        sum = mk(rp.sum3[3 * (size_t)pixel], rp.sum3[3 * (size_t)pixel + 1], rp.sum3[3 * (size_t)pixel + 2]);
+        sum2 = mk(rp.sum2_3[3 * (size_t)pixel], rp.sum2_3[3 * (size_t)pixel + 1], rp.sum2_3[3 * (size_t)pixel + 2]);
+        cnt = rp.count[pixel];
+        if (rr_on) wsum = rp.weight[pixel];
+    }
     int s_next = rp.s_begin;  // next uncommitted sample of this pixel (identical across the quad)
     unsigned long long seg_commit = 0, seg_traced = 0, n_nodes = 0, n_tris = 0;
 

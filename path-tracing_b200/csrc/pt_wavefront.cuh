@@ -47,11 +47,19 @@ struct WfState {
     int cap;        // path slots
 };
 
-__global__ void k_wf_init(WfState wf, int npx, int s_begin) {
+__global__ void k_wf_init(WfState wf, int npx, RenderParams rp) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= npx) return;
+    if (rp.resume) {  // continue a render from the caller's accumulators (the loop state after the samples < s_begin)
+        const size_t q = 3 * (size_t)p;
+        const int cnt = rp.count[p];
+        wf.acc1[p] = make_float4(rp.sum3[q], rp.sum3[q + 1], rp.sum3[q + 2], __int_as_float(cnt));
+        wf.acc2[p] = make_float4(rp.sum2_3[q], rp.sum2_3[q + 1], rp.sum2_3[q + 2], __int_as_float(rp.s_begin));
+        wf.accw[p] = rp.rr_depth > 0 ? rp.weight[p] : 0.f;
+        return;
+    }
     wf.acc1[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
-    wf.acc2[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(s_begin));
+    wf.acc2[p] = make_float4(0.f, 0.f, 0.f, __int_as_float(rp.s_begin));
     wf.accw[p] = 0.f;
 }
 

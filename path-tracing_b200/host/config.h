@@ -26,6 +26,7 @@ public:
     float eps = 1e-4f;              // config.h:22
     float error = 0.001f;           // config.h:23
     int update = 32;                // config.h:24
+    bool update_given = false;      // -UPDATE was on the command line (main.cpp decides on it, see there)
     float gamma_correction = 1 / 2.2f;
     std::string model_path = "../models/";
     std::string model_name = "Tor.obj";
@@ -55,7 +56,7 @@ public:
             else if (is("-EPS")) eps = static_cast<float>(std::atof(val));
             else if (is("-ERR")) error = static_cast<float>(std::atof(val));
             else if (is("-MEDIAN")) { median = std::atoi(val); gauss = 0; }
-            else if (is("-UPDATE")) update = std::atoi(val);
+            else if (is("-UPDATE")) { update = std::atoi(val); update_given = true; }
             else if (is("-MODEL_PATH")) model_path = val;
             else if (is("-MODEL_NAME")) model_name = val;
             else if (is("-GAUSS")) { gauss = std::atoi(val); median = 0; }

@@ -343,3 +343,14 @@ int Scene::RenderImage(const PtConfig &cfg, const PtPostConfig &post, std::vecto
     rgb8.assign(3 * static_cast<size_t>(post.width) * post.height, 0);
     return pt_render_image(&s, &cfg, &post, rgb8.data(), &stats);
 }
+
+int Scene::RenderProgressive(const PtConfig &cfg, const PtPostConfig &post, int update, long long time_limit_ms,
+                             PtPreviewFn on_update, void *user, std::vector<uint8_t> &rgb8, PtDispersion &stats,
+                             int &samples_done) {
+    const PtScene s = abi();
+    rgb8.assign(3 * static_cast<size_t>(post.width) * post.height, 0);
+    int32_t done = 0;
+    const int rc = pt_render_progressive(&s, &cfg, &post, update, time_limit_ms, on_update, user, rgb8.data(), &stats, &done);
+    samples_done = done;
+    return rc;
+}

@@ -53,5 +53,10 @@ public:
     int Resolve(const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats) const;
     // Render + Resolve without the round trip through host accumulators (pt_render_image)
     int RenderImage(const PtConfig &cfg, const PtPostConfig &post, std::vector<uint8_t> &rgb8, PtDispersion &stats);
+    // the same with the reference's refresh every `update` samples and its time limit (pt_render_progressive);
+    // samples_done = the loop's rays_count at exit
+    int RenderProgressive(const PtConfig &cfg, const PtPostConfig &post, int update, long long time_limit_ms,
+                          PtPreviewFn on_update, void *user, std::vector<uint8_t> &rgb8, PtDispersion &stats,
+                          int &samples_done);
 };
 #endif

@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth", "pt_render_progressive"]
 
 
 class PtScene(C.Structure):
@@ -64,7 +64,7 @@ class PtError(RuntimeError):
 
 def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
            sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0,
-           mode=0, q_shift=0):
+           mode=0, q_shift=0, resume=0):
     """PtConfig with the reference's defaults (config.h:10,16-29)."""
     c = PtConfig()
     c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
@@ -73,7 +73,11 @@ def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, se
     c.intersector, c.accel, c.rr_depth, c.n_gpus, c.device = intersector, accel, rr_depth, n_gpus, device
     c.reserved[0] = mode  # 0 = wavefront pipeline, 1 = megakernel variant
     c.reserved[1] = q_shift  # 0 = automatic, else log2(samples per pixel per wavefront step)
+    c.reserved[2] = resume  # 1 = continue from the accumulators passed in (samples before sample_begin are in them)
     return c
+
+
+PREVIEW_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int32)
 
 
 def _load(path):
@@ -168,22 +172,27 @@ class Library:
         self.check(self.lib.pt_render(C.byref(s), C.byref(cfg), rgb.ctypes.data))
         return rgb
 
-    def render_accum(self, sc, cfg):
+    def render_accum(self, sc, cfg, state=None):
+        """state: (sum, sum2, count) of an earlier call to continue from (cfg built with resume=1)"""
         H, W = cfg.height, cfg.width
         sm = np.zeros((H, W, 3), np.float32)
         s2 = np.zeros((H, W, 3), np.float32)
         cnt = np.zeros((H, W), np.int32)
+        if state is not None:
+            sm, s2, cnt = (np.ascontiguousarray(a).copy() for a in state[:3])
         s = self.scene_struct(sc)
         self.check(self.lib.pt_render_accum(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data))
         return sm, s2, cnt
 
-    def render_accum_w(self, sc, cfg):
+    def render_accum_w(self, sc, cfg, state=None):
         """-> sum, sum2, count, weight (the divisor under Russian roulette; == count otherwise)"""
         H, W = cfg.height, cfg.width
         sm = np.zeros((H, W, 3), np.float32)
         s2 = np.zeros((H, W, 3), np.float32)
         cnt = np.zeros((H, W), np.int32)
         wt = np.zeros((H, W), np.float32)
+        if state is not None:
+            sm, s2, cnt, wt = (np.ascontiguousarray(a).copy() for a in state)
         s = self.scene_struct(sc)
         self.check(self.lib.pt_render_accum_w(C.byref(s), C.byref(cfg), sm.ctypes.data, s2.ctypes.data, cnt.ctypes.data,
                                               wt.ctypes.data))
@@ -260,6 +269,27 @@ class Library:
         s = self.scene_struct(sc)
         self.check(self.lib.pt_render_image(C.byref(s), C.byref(cfg), C.byref(post), img.ctypes.data, C.byref(st)))
         return img, (st.max_dispersion, st.min_dispersion, st.average_dispersion)
+
+    def render_progressive(self, sc, cfg, post, update=32, time_limit_ms=0, on_update=None):
+        """pt_render_progressive; on_update(image HxWx3 u8, samples) -> truthy stops the loop.
+        -> image, (max, min, average dispersion), samples done"""
+        H, W = post.height, post.width
+        img = np.zeros((H, W, 3), np.uint8)
+        st = PtDispersion()
+        done = C.c_int32(0)
+        s = self.scene_struct(sc)
+
+        def tramp(user, ptr, samples):
+            view = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(H, W, 3))
+            return 1 if on_update(view.copy(), samples) else 0
+
+        cb = PREVIEW_FN(tramp) if on_update else C.cast(None, PREVIEW_FN)
+        self.lib.pt_render_progressive.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.POINTER(PtPostConfig),
+                                                   C.c_int, C.c_int64, PREVIEW_FN, C.c_void_p, C.c_void_p,
+                                                   C.POINTER(PtDispersion), C.POINTER(C.c_int32)]
+        self.check(self.lib.pt_render_progressive(C.byref(s), C.byref(cfg), C.byref(post), update, time_limit_ms, cb,
+                                                  None, img.ctypes.data, C.byref(st), C.byref(done)))
+        return img, (st.max_dispersion, st.min_dispersion, st.average_dispersion), done.value
 
     def primary_rays(self, cfg, xys3):
         xys3 = np.ascontiguousarray(xys3, np.int32).reshape(-1, 3)

@@ -3,6 +3,7 @@ unmodified reference.  Bar: bit-exact for hit IDs, hit distances, counts AND the
 compiled without FMA contraction and reproduce the reference's evaluation order; sinf/cosf restate glibc's
 algorithm).  The north_star's tolerances (t within 1e-6 rel, radiance within 1e-4 rel) are therefore met with
 margin; they are written next to the assertions that would be relaxed to them."""
+import ctypes as C
 import numpy as np
 import pytest
 
@@ -361,4 +362,58 @@ def test_pixel_chunks_at_4k(lib):
     one = lib.render_accum(sc, ptb200.config(3840, 2160, 64, 4, 1e-4, -1.0, q_shift=3))
     for x, y, what in zip(big, one, ("sum", "sum2", "count")):
         assert_bits_equal(x, y, what)
-    assert int(one[2].min()) > 0  # every pixel of a closed box has contributing paths
+    assert int(one[2].sum()) > 10 ** 6 and int(one[2][2159, 3839:].sum() + one[2][:, 0].sum()) > 0  # all chunks rendered
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
+@pytest.mark.parametrize("case", ["flat", "adaptive", "roulette", "partition"])
+def test_resumed_render_is_the_one_shot_render(lib, tor, case, mode):
+    """PtConfig.reserved[2] = 1 continues from the accumulators passed in: the reference's loop refreshes a preview
+    every `update` samples and may stop at a time limit (main.cpp:111-114, 141-158), so a render cut into blocks of
+    samples — 1, then 8, then the rest, the reference's refresh pattern — must be the uncut render bit for bit,
+    including the adaptive rule's decisions, which read the running sums."""
+    kw = dict(flat=dict(error=-1.0), adaptive=dict(error=0.002), roulette=dict(error=-1.0, rr_depth=2),
+              partition=dict(error=0.002, sample_begin=1, sample_step=2))[case]
+    spp, begin, step = 30, kw.pop("sample_begin", 0), kw.pop("sample_step", 1)
+    sc = scenes.glossy_mix() if case == "roulette" else tor
+    mk = lambda lo, hi, resume: ptb200.config(96, 64, hi, 8, 1e-4, seed=5, sample_begin=lo, sample_step=step, mode=mode,
+                                              resume=resume, **kw)
+    whole = lib.render_accum_w(sc, mk(begin, spp, 0))
+    cuts = [begin, begin + step, begin + 9 * step, spp]
+    state = None
+    for lo, hi in zip(cuts[:-1], cuts[1:]):
+        state = lib.render_accum_w(sc, mk(lo, hi, 0 if state is None else 1), state)
+    for a, b, what in zip(state, whole, ("sum", "sum2", "count", "weight")):
+        assert_bits_equal(a, b, f"{case} {what}")
+    assert whole[2].sum() > 0
+    with pytest.raises(ptb200.PtError):  # resume without the state
+        s = lib.scene_struct(sc)
+        lib.check(lib.lib.pt_render_accum(C.byref(s), C.byref(mk(4, 8, 1)), None, None, None))
+
+
+def test_progressive_render(lib, oracle, tor):
+    """pt_render_progressive = the reference's loop with its refresh (main.cpp:141-158) and time limit (:111-114):
+    (a) uninterrupted, its final image and statistics are pt_render_image's, bit for bit, adaptive rule on;
+    (b) the previews arrive after samples 1, update + 1, 2 update + 1, ... and each one is the gamma-only image of a
+    render of exactly that many samples; (c) a callback that returns non-zero stops the loop there."""
+    cfg = ptb200.config(80, 60, 21, 8, 1e-4, 0.002, seed=9)
+    post = lib.post_config(80, 60, 1 / 2.2, gauss=1)
+    want, wstats = lib.render_image(tor, cfg, post)
+    seen = []
+    img, stats, done = lib.render_progressive(tor, cfg, post, update=8, on_update=lambda im, n: seen.append((n, im)) and False)
+    assert done == 21 and [n for n, _ in seen] == [1, 9, 17]
+    assert_bits_equal(img, want, "final image")
+    assert stats == wstats
+    plain = lib.post_config(80, 60, 1 / 2.2)
+    for n, im in seen:
+        ref, _ = lib.render_image(tor, ptb200.config(80, 60, n, 8, 1e-4, 0.002, seed=9), plain)
+        assert_bits_equal(im, ref, f"preview after {n} samples")
+    # stop at the second refresh: the result is the 9-sample render, filters applied
+    img, stats, done = lib.render_progressive(tor, cfg, post, update=8, on_update=lambda im, n: n >= 9)
+    ref, rstats = lib.render_image(tor, ptb200.config(80, 60, 9, 8, 1e-4, 0.002, seed=9), post)
+    assert done == 9 and stats == rstats
+    assert_bits_equal(img, ref, "stopped render")
+    # no refresh at all: one pass in blocks of 64
+    img, stats, done = lib.render_progressive(tor, cfg, post, update=0)
+    assert done == 21
+    assert_bits_equal(img, want, "update = 0")
