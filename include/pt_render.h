@@ -91,8 +91,11 @@ typedef struct PtConfig {
                              After each Reflect: p = clamp(max(T), 0.05, 1), survive when u < p (u = word 3 of the
                              bounce's Philox block), then T /= p and the path weight w /= p.  The estimator's divisor
                              (samples_count, main.cpp:180) becomes the sum of the contributing paths' weights. */
-    int32_t n_gpus;       /* pt_render only: 0/1 = current device; N>1 = split samples over N devices of this
-                             process and sum with one NCCL reduce */
+    int32_t n_gpus;       /* 0/1 = one device; N > 1 (pt_render, pt_render_accum(_w), pt_render_image): the samples are
+                             dealt round-robin to devices device .. device + N - 1 of this process (one host thread
+                             each, every device holds the whole scene), the partial accumulators are summed onto
+                             the first device over NVLink in rank order, then resolved there.  The
+                             one-process-per-GPU launch sets sample_begin / sample_step itself and leaves this 1. */
     int32_t device;       /* first CUDA device ordinal */
     int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant;
                              [1]: 0 = automatic, 1..6 = log2 of the samples per pixel one wavefront step carries;

@@ -8,6 +8,8 @@
 #include <chrono>
 #include <map>
 #include <mutex>
+#include <string>
+#include <thread>
 #include <stdlib.h>
 #include <vector>
 
@@ -635,6 +637,87 @@ extern "C" int pt_intersect(const PtScene *scene, const PtConfig *cfg, const flo
     return rc;
 }
 
+// ---- n_gpus > 1 inside one process ---------------------------------------------------------------------------
+// The samples of the caller's partition are dealt round-robin to N devices (device r renders sample_begin + r step,
+// then every N-th), one host thread per device — the render loop blocks on its own stream between steps, so the
+// devices need their own threads to run side by side.  Every device holds the whole scene and a full frame of
+// accumulators.  The exchange step is a sum of those frames onto the first device: the partial frames
+// come over NVLink with cudaMemcpyPeer and are added in rank order (deterministic, unlike a ring reduce).  The
+// one-process-per-GPU launch (bench.py under torchrun) does the same exchange with one NCCL reduce.
+struct FrameBufs {
+    DevBuf<float> sum, sum2, wt;
+    DevBuf<int> cnt;
+    cudaError_t alloc(size_t px) {
+        cudaError_t e;
+        if ((e = sum.alloc(3 * px)) || (e = sum2.alloc(3 * px)) || (e = wt.alloc(px)) || (e = cnt.alloc(px))) return e;
+        return cudaSuccess;
+    }
+};
+
+__global__ void __launch_bounds__(256)
+k_add_frame(float *__restrict__ sum, const float *__restrict__ o_sum, float *__restrict__ sum2,
+            const float *__restrict__ o_sum2, int *__restrict__ cnt, const int *__restrict__ o_cnt,
+            float *__restrict__ wt, const float *__restrict__ o_wt, long long px) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < 3 * px) { sum[i] += o_sum[i]; sum2[i] += o_sum2[i]; }
+    if (i < px) { cnt[i] += o_cnt[i]; wt[i] += o_wt[i]; }
+}
+
+// renders cfg (n_gpus = N > 1) and leaves the summed accumulators in `f`, allocated on device cfg->device
+static int render_frame_multi(const PtScene *scene, const PtConfig *cfg, FrameBufs &f) {
+    const int N = cfg->n_gpus, dev0 = cfg->device;
+    int have = 0;
+    CK(cudaGetDeviceCount(&have));
+    if (dev0 < 0 || dev0 + N > have) return fail(PT_EINVAL, "n_gpus = %d from device %d, but %d device(s) visible", N, dev0, have);
+    if (cfg->reserved[2]) return fail(PT_EINVAL, "resume is per device: not available with n_gpus > 1");
+    const size_t px = (size_t)cfg->width * cfg->height;
+    const int step = cfg->sample_step > 0 ? cfg->sample_step : 1;
+    std::vector<FrameBufs> part(N);
+    std::vector<int> rcs(N, PT_OK);
+    std::vector<std::string> errs(N);
+    auto work = [&](int r) {
+        auto run = [&]() -> int {
+            CK(cudaSetDevice(dev0 + r));
+            PtConfig c = *cfg;
+            c.device = dev0 + r;
+            c.n_gpus = 1;
+            c.sample_begin = cfg->sample_begin + r * step;
+            c.sample_step = step * N;
+            PtDeviceScene *ds = nullptr;
+            int rc;
+            if ((rc = pt_scene_create(scene, &c, 0, &ds))) return rc;
+            struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+            FrameBufs &b = r == 0 ? f : part[r];
+            CK(b.alloc(px));
+            if ((rc = pt_scene_render_device_w(ds, &c, b.sum.p, b.sum2.p, b.cnt.p, b.wt.p, nullptr))) return rc;
+            CK(cudaDeviceSynchronize());
+            return PT_OK;
+        };
+        rcs[r] = run();
+        if (rcs[r]) errs[r] = g_err;  // g_err is per thread
+    };
+    std::vector<std::thread> threads;
+    for (int r = 1; r < N; ++r) threads.emplace_back(work, r);
+    work(0);
+    for (std::thread &t : threads) t.join();
+    CK(cudaSetDevice(dev0));
+    for (int r = 0; r < N; ++r)
+        if (rcs[r]) return fail(rcs[r], "device %d: %s", dev0 + r, errs[r].c_str());
+    FrameBufs stage;
+    CK(stage.alloc(px));
+    for (int r = 1; r < N; ++r) {  // rank order
+        CK(cudaMemcpyPeer(stage.sum.p, dev0, part[r].sum.p, dev0 + r, 3 * px * sizeof(float)));
+        CK(cudaMemcpyPeer(stage.sum2.p, dev0, part[r].sum2.p, dev0 + r, 3 * px * sizeof(float)));
+        CK(cudaMemcpyPeer(stage.cnt.p, dev0, part[r].cnt.p, dev0 + r, px * sizeof(int)));
+        CK(cudaMemcpyPeer(stage.wt.p, dev0, part[r].wt.p, dev0 + r, px * sizeof(float)));
+        k_add_frame<<<blocks_for(3 * (long long)px, 256), 256>>>(f.sum.p, stage.sum.p, f.sum2.p, stage.sum2.p, f.cnt.p,
+                                                                 stage.cnt.p, f.wt.p, stage.wt.p, (long long)px);
+        CK(cudaGetLastError());
+    }
+    CK(cudaDeviceSynchronize());
+    return PT_OK;
+}
+
 extern "C" int pt_render_accum(const PtScene *scene, const PtConfig *cfg, float *sum3, float *sum2_3, int32_t *count) {
     return pt_render_accum_w(scene, cfg, sum3, sum2_3, count, nullptr);
 }
@@ -644,9 +727,18 @@ extern "C" int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, floa
     int rc;
     if ((rc = validate_config(cfg))) return rc;
     if ((rc = validate_scene(scene))) return rc;
-    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "n_gpus > 1: use pt_render (in-process NCCL) or one process per GPU");
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
+    if (cfg->n_gpus > 1) {
+        FrameBufs f;
+        if ((rc = render_frame_multi(scene, cfg, f))) return rc;
+        const size_t npx = (size_t)cfg->width * cfg->height;
+        if (weight) CK(cudaMemcpy(weight, f.wt.p, npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (sum3) CK(cudaMemcpy(sum3, f.sum.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (sum2_3) CK(cudaMemcpy(sum2_3, f.sum2.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (count) CK(cudaMemcpy(count, f.cnt.p, npx * sizeof(int), cudaMemcpyDeviceToHost));
+        return PT_OK;
+    }
     PtDeviceScene *ds = nullptr;
     if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
     struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
@@ -677,9 +769,18 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     if (!rgb) return fail(PT_EINVAL, "rgb is NULL");
     if ((rc = validate_config(cfg))) return rc;
     if ((rc = validate_scene(scene))) return rc;
-    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
+    if (cfg->n_gpus > 1) {
+        FrameBufs f;
+        if ((rc = render_frame_multi(scene, cfg, f))) return rc;
+        const size_t npx = (size_t)cfg->width * cfg->height;
+        DevBuf<float> d_out;
+        CK(d_out.alloc(3 * npx));
+        if ((rc = pt_resolve_device_w(f.sum.p, f.cnt.p, cfg->rr_depth > 0 ? f.wt.p : nullptr, (int64_t)npx, d_out.p, nullptr))) return rc;
+        CK(cudaMemcpy(rgb, d_out.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
+        return PT_OK;
+    }
     const bool prof = getenv("PT_PROFILE") != nullptr;  // wall-clock phase times on stderr
     using clk = std::chrono::steady_clock;
     auto t0 = clk::now();
@@ -807,9 +908,19 @@ extern "C" int pt_render_image(const PtScene *scene, const PtConfig *cfg, const 
     if (!rgb8) return fail(PT_EINVAL, "rgb8 is NULL");
     if ((rc = validate_config(cfg)) || (rc = validate_scene(scene)) || (rc = validate_post(post))) return rc;
     if (post->width != cfg->width || post->height != cfg->height) return fail(PT_EINVAL, "post and render sizes differ");
-    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
+    if (cfg->n_gpus > 1) {
+        FrameBufs f;
+        if ((rc = render_frame_multi(scene, cfg, f))) return rc;
+        const size_t npx = (size_t)cfg->width * cfg->height;
+        DevBuf<uint8_t> d_out;
+        CK(d_out.alloc(3 * npx));
+        if ((rc = pt_postprocess_device(f.sum.p, f.sum2.p, f.cnt.p, cfg->rr_depth > 0 ? f.wt.p : nullptr, post, d_out.p, stats, nullptr)))
+            return rc;
+        CK(cudaMemcpy(rgb8, d_out.p, 3 * npx, cudaMemcpyDeviceToHost));
+        return PT_OK;
+    }
     PtDeviceScene *ds = nullptr;
     if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
     struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};

@@ -417,3 +417,24 @@ def test_progressive_render(lib, oracle, tor):
     img, stats, done = lib.render_progressive(tor, cfg, post, update=0)
     assert done == 21
     assert_bits_equal(img, want, "update = 0")
+
+
+def test_in_process_multi_gpu(lib, tor):
+    """PtConfig.n_gpus = 2 inside one call: device r renders every second sample, the partial frames are summed on the
+    first device in rank order — exactly the sum of the two single-device partition renders (one fp32 add per
+    value), and the image calls resolve from that sum."""
+    if lib.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    for kw in (dict(error=-1.0), dict(error=0.002), dict(error=-1.0, rr_depth=2)):
+        parts = [lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, sample_begin=r, sample_step=2, **kw))
+                 for r in (0, 1)]
+        both = lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, n_gpus=2, **kw))
+        for a, b, c, what in zip(parts[0], parts[1], both, ("sum", "sum2", "count", "weight")):
+            assert_bits_equal(a + b, c, f"{kw} {what}")
+    cfg = ptb200.config(96, 64, 24, 8, 1e-4, -1.0, seed=3, n_gpus=2)
+    sm, _, cnt, _ = both = lib.render_accum_w(tor, cfg)
+    rgb = lib.render(tor, cfg)
+    want = np.where(cnt[..., None] > 0, sm / np.maximum(cnt, 1)[..., None].astype(np.float32), 0).astype(np.float32)
+    assert_bits_equal(rgb, want, "pt_render, n_gpus = 2")
+    with pytest.raises(ptb200.PtError):
+        lib.render(tor, ptb200.config(16, 16, 4, n_gpus=lib.device_count() + 1))
