@@ -438,3 +438,13 @@ def test_in_process_multi_gpu(lib, tor):
     assert_bits_equal(rgb, want, "pt_render, n_gpus = 2")
     with pytest.raises(ptb200.PtError):
         lib.render(tor, ptb200.config(16, 16, 4, n_gpus=lib.device_count() + 1))
+
+
+def test_read_bandwidth_probe(lib):
+    """pt_probe_read_bandwidth (bench.py's L2 peak): an L2-resident footprint reads faster than one that
+    has to come from HBM, and both are plausible for a B200."""
+    l2 = lib.probe_read_bandwidth(64 << 20, 20)
+    hbm = lib.probe_read_bandwidth(2 << 30, 2)
+    assert 2000 < hbm < 9000 and l2 > 1.5 * hbm, (l2, hbm)
+    with pytest.raises(ptb200.PtError):
+        lib.probe_read_bandwidth(16, 1)
