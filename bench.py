@@ -297,7 +297,7 @@ def main():
         with the device-resident entry points — pt_scene_create (upload + LBVH build), pt_scene_render_device on this
         rank's sample partition, one NCCL reduce of (sum, count), pt_resolve_device, download on rank 0."""
         if world == 1:
-            return lib.render(sc, cfg)
+            return lib.render(sc_pinned, cfg, out=rgb_pinned)
         h = lib.scene_create(sc, cfg)
         h.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
         acc[3 * n_px:].copy_(d_cnt_i)
@@ -312,6 +312,13 @@ def main():
         h.close()
         return out
 
+    # the host side of the call: scene arrays and the image live in page-locked host memory, as a host that renders
+    # frame after frame would keep them (and as the bench contract words it)
+    sc_pinned, rgb_pinned = sc, None
+    if world == 1:
+        pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+        sc_pinned = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in sc.items()}
+        rgb_pinned = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory().numpy()
     if args.warmup > 0:
         e2e_call()  # one untimed call: the library keeps its path-state workspace (GBs of HBM) between calls
     barrier()

@@ -166,8 +166,10 @@ class Library:
         return s
 
     # ---- host-buffer entry points (the drop-in boundary) ----
-    def render(self, sc, cfg):
-        rgb = np.zeros((cfg.height, cfg.width, 3), np.float32)
+    def render(self, sc, cfg, out=None):
+        """out: a caller-owned (H, W, 3) float32 array to fill (e.g. page-locked memory reused across frames)"""
+        rgb = np.zeros((cfg.height, cfg.width, 3), np.float32) if out is None else out
+        assert rgb.dtype == np.float32 and rgb.flags.c_contiguous and rgb.size == cfg.height * cfg.width * 3
         s = self.scene_struct(sc)
         self.check(self.lib.pt_render(C.byref(s), C.byref(cfg), rgb.ctypes.data))
         return rgb
