@@ -198,6 +198,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs only)")
     ap.add_argument("--accel", type=int, default=0)
     ap.add_argument("--mode", type=int, default=0, help="0 wavefront pipeline (default), 1 megakernel variant")
+    ap.add_argument("--error", type=float, default=None, help="override the adaptive threshold (tuning runs only)")
     ap.add_argument("--q-shift", type=int, default=0, help="log2 samples per wavefront step (0 = automatic; tuning runs only)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -220,6 +221,8 @@ def main():
     desc, W, H, spp, depth, error = WORKLOADS[args.workload]
     if args.spp:
         spp = args.spp
+    if args.error is not None:
+        error = args.error
     sc = make_scene(args.workload)
     lib = ptb200.Library()
     cfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,

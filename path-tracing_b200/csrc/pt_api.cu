@@ -398,13 +398,25 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     rp.seed = cfg->seed;
     rp.sum3 = d_sum3; rp.sum2_3 = d_sum2; rp.count = d_count;
     rp.stats = stats;
-    // samples per wavefront step: reserved[1] = log2 (1..6) overrides; otherwise up to 64 for a flat-spp render (the
-    // largest power of two <= the samples this rank traces), 4 when the adaptive rule can discard samples traced
-    // ahead of it
+    // Samples per wavefront step: reserved[1] = log2 (1..6) overrides.  Otherwise (measured,
+    // profiles/r01_sweep_samples_per_step.txt and r01_sweep_adaptive.txt):
+    //  * flat-spp render: the largest power of two <= the samples this rank traces, up to 64 — the traversal kernel's
+    //    throughput grows with the batch; a small frame (fewer than 6 M path slots per step) rounds UP instead, so
+    //    that e.g. 20 spp at 512 x 512 are one step of 32 slots per pixel rather than 16 + 4;
+    //  * adaptive rule on: samples traced ahead of the rule can be discarded, so a large frame carries 4 per step,
+    //    but a small one is bound by the number of launches (each at least one dependent-fetch chain long) and
+    //    takes as many as it needs to reach 6 M slots per step (512 x 512: 32).
     const int per_rank = std::max(0, cfg->rays_per_pixel - cfg->sample_begin) / (cfg->sample_step > 0 ? cfg->sample_step : 1);
+    const long long px = (long long)cfg->width * cfg->height, small_frame = 6000000;
     int q_auto = 2;
-    if (cfg->error < 0.0f) while (q_auto < 6 && (2 << q_auto) <= per_rank) ++q_auto;
+    if (cfg->error < 0.0f) {
+        while (q_auto < 6 && (2 << q_auto) <= per_rank) ++q_auto;
+        if (q_auto < 6 && (1 << q_auto) < per_rank && (px << q_auto) < small_frame) ++q_auto;
+    } else {
+        while (q_auto < 6 && (px << q_auto) < small_frame && (1 << q_auto) < per_rank) ++q_auto;
+    }
     rp.q_shift = cfg->reserved[1] ? cfg->reserved[1] : q_auto;
+    rp.sample_major = (1 << rp.q_shift) > per_rank;  // a partial step: idle sample positions become idle warps
     rp.rr_depth = cfg->rr_depth;
     rp.weight = d_weight;
     rp.resume = cfg->reserved[2] == 1;

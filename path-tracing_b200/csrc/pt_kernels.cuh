@@ -29,6 +29,7 @@ struct RenderParams {
     int q_shift;    // wavefront pipeline: 2^q_shift consecutive samples of a pixel per step
     int rr_depth;   // extension: Russian roulette once Ray::depth >= rr_depth (0 = off, the reference)
     float *weight;  // extension: per-pixel sum of the contributing paths' RR weights (== count without RR)
+    int sample_major;  // wavefront slot numbering, pt_wavefront.cuh slot_split
     int resume;     // the output buffers hold the accumulators after the samples before s_begin: continue from them
 };
 

@@ -162,7 +162,7 @@ def test_extensions_vs_oracle(lib, oracle, case, accel, mode):
     ds.close()
 
 
-@pytest.mark.parametrize("q_shift", [1, 3, 4, 5])
+@pytest.mark.parametrize("q_shift", [1, 3, 4, 5, 6])  # 6: more sample positions than samples -> sample-major slots
 @pytest.mark.parametrize("error", [-1.0, 0.001])
 def test_samples_per_step_do_not_change_the_result(lib, oracle, q_shift, error):
     """The wavefront pipeline carries 2^q_shift samples of every pixel per step; the ordered commit must make that
@@ -362,6 +362,11 @@ def test_pixel_chunks_at_4k(lib):
     one = lib.render_accum(sc, ptb200.config(3840, 2160, 64, 4, 1e-4, -1.0, q_shift=3))
     for x, y, what in zip(big, one, ("sum", "sum2", "count")):
         assert_bits_equal(x, y, what)
+    # 40 samples in steps of 64 positions: the sample-major slot numbering, in chunks
+    part = lib.render_accum(sc, ptb200.config(3840, 2160, 40, 4, 1e-4, -1.0, q_shift=6))
+    ref = lib.render_accum(sc, ptb200.config(3840, 2160, 40, 4, 1e-4, -1.0, q_shift=3))
+    for x, y, what in zip(part, ref, ("sum", "sum2", "count")):
+        assert_bits_equal(x, y, "sample-major " + what)
     assert int(one[2].sum()) > 10 ** 6 and int(one[2][2159, 3839:].sum() + one[2][:, 0].sum()) > 0  # all chunks rendered
 
 
