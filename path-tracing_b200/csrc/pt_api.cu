@@ -510,13 +510,13 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
     for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
         const int npix = (int)std::min<size_t>(npc_max, npx - pix0);
-        const int slot_blocks = blocks_for((long long)npix << rp.q_shift, 256);
+        const int slot_blocks = blocks_for((long long)npix << rp.q_shift, kWfBlock);
         int remaining = total;
         while (remaining > 0) {
             const int steps = (remaining + Q - 1) / Q;
             for (int i = 0; i < steps; ++i) {
                 if ((rc = tick(0))) return rc;
-                k_wf_begin<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                k_wf_begin<COUNT><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
                 if ((rc = tock())) return rc;
                 for (int b = 0; b < rp.max_depth; ++b) {
                     if (!sc.brute && sc.root != kRefEmpty) {
@@ -526,7 +526,7 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
                         ++n;
                     }
                     if ((rc = tick(2))) return rc;
-                    k_wf_bounce<COUNT><<<slot_blocks, 256, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    k_wf_bounce<COUNT><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
                     if ((rc = tock())) return rc;
                     ++n;
                 }

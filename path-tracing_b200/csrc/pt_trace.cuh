@@ -308,16 +308,21 @@ __device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o,
     return sp ? stack[--sp] : kRefEmpty;
 }
 
-// Whole nearest-hit query in one thread (pt_intersect, and the brute-force checker mode).
+// scene.cpp:114-120 as written: every triangle, in order (the checker mode, PT_ACCEL_BRUTE)
+template <bool COUNT>
+__device__ __forceinline__ Hit brute_hit(const SceneView &sc, V3 o, V3 d, float eps, unsigned long long &n_tris) {
+    Hit h = no_hit();
+    for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)k, k, o, d, eps, h);
+    if (COUNT) n_tris += sc.n_tri;
+    return h;
+}
+
+// Whole nearest-hit query in one thread (pt_intersect, the megakernel).
 template <bool COUNT>
 __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_large, V3 o, V3 d, float eps,
                                            unsigned long long &n_nodes, unsigned long long &n_tris) {
+    if (sc.brute) return brute_hit<COUNT>(sc, o, d, eps, n_tris);
     Hit h = no_hit();
-    if (sc.brute) {  // scene.cpp:114-120 as written: every triangle, in order
-        for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)k, k, o, d, eps, h);
-        if (COUNT) n_tris += sc.n_tri;
-        return h;
-    }
     large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
     if (COUNT) n_tris += sc.n_large;
     if (!reaches_root(sc, o, d, h.t)) return h;

@@ -54,6 +54,13 @@ __device__ __forceinline__ int slot_of(int i, int q, int npix, int q_shift, bool
     return sample_major ? q * npix + i : (i << q_shift) + q;
 }
 
+// threads per block of the per-slot kernels (begin, bounce): with the 55 registers ptxas gives k_wf_bounce, blocks of
+// 256 fit 4 to an SM (32 warps), blocks of 128 fit 9 (36 warps)
+#ifndef PT_WF_BLOCK
+#define PT_WF_BLOCK 256
+#endif
+constexpr int kWfBlock = PT_WF_BLOCK;
+
 struct WfState {
     float4 *oT;     // per slot: origin xyz, best hit distance t
     float4 *dR;     // per slot: direction xyz, bits(record index of the best hit, -1 = none)
@@ -93,7 +100,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
     if (active) {
         Hit h = no_hit();
         if (sc.brute) {
-            h = nearest_hit<COUNT>(sc, s_large, o, d, eps, n_nodes, n_tris);
+            h = brute_hit<COUNT>(sc, o, d, eps, n_tris);  // (not nearest_hit: its traversal stack would become this kernel's frame)
         } else {
             large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
             if (COUNT) n_tris += sc.n_large;
@@ -113,7 +120,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
 }
 
 template <bool COUNT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kWfBlock)
 k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
@@ -159,7 +166,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
 
 // bounce `b` (0-based): shades segment b of every live path and starts segment b+1; writes queue (b+1)&1
 template <bool COUNT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kWfBlock)
 k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
     __shared__ float4 s_large[kLargeRowsMax];
     // this thread's path state first: the loads are in flight while the block stages the shared-memory image
@@ -337,9 +344,10 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
         float wsum = rr_on ? __ldcs(&wf.accw[p]) : 0.0f;
         bool stop = false;
         const int Q = 1 << rp.q_shift;
+        const int slot0 = slot_of(i, 0, npix, rp.q_shift, rp.sample_major != 0), stride = rp.sample_major ? npix : 1;
 #pragma unroll 4
         for (int j = 0; j < Q; ++j) {
-            const int slot = slot_of(i, j, npix, rp.q_shift, rp.sample_major != 0);
+            const int slot = slot0 + j * stride;
             const int flags = __float_as_int(__ldcs(&wf.Tn[slot].w));
             const float4 c = __ldcs(&wf.cS[slot]);
             const int nseg = (flags & 0xffff) + ((flags & WF_SHADE_END) ? 1 : 0);
