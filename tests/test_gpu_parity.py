@@ -4,6 +4,7 @@ compiled without FMA contraction and reproduce the reference's evaluation order;
 algorithm).  The north_star's tolerances (t within 1e-6 rel, radiance within 1e-4 rel) are therefore met with
 margin; they are written next to the assertions that would be relaxed to them."""
 import ctypes as C
+import os
 import numpy as np
 import pytest
 
@@ -453,3 +454,44 @@ def test_read_bandwidth_probe(lib):
     assert 2000 < hbm < 9000 and l2 > 1.5 * hbm, (l2, hbm)
     with pytest.raises(ptb200.PtError):
         lib.probe_read_bandwidth(16, 1)
+
+
+def _read_bmp(path):
+    raw = open(path, "rb").read()
+    assert raw[:2] == b"BM" and int.from_bytes(raw[28:30], "little") == 24
+    off, W, H = (int.from_bytes(raw[a:a + 4], "little", signed=True) for a in (10, 18, 22))
+    stride = (3 * W + 3) & ~3
+    rows = np.frombuffer(raw, np.uint8, count=stride * abs(H), offset=off).reshape(abs(H), stride)[:, :3 * W]
+    img = rows.reshape(abs(H), W, 3)[:, :, ::-1]  # BGR -> RGB
+    return img[::-1] if H > 0 else img            # positive height = bottom-up
+
+
+def test_host_program_end_to_end(lib, tor, tmp_path):
+    """bin/ray_tracing — the reference's main() on this library — with the reference's flags: the one-shot run and the
+    run with -UPDATE (refresh of ../result.bmp after samples 1, 9, 17; main.cpp:141-158) write the same picture, which
+    is pt_render_image's; the file name carries `rays_count of rays_per_pixel` and the dispersion statistics; a second
+    run takes the scene from the -CACHE image."""
+    import glob
+    import subprocess
+    from util import ROOT
+    exe = os.path.join(ROOT, "path-tracing_b200", "bin", "ray_tracing")
+    assert os.path.exists(exe), "build with python __graft_entry__.py"
+    models = os.path.join(ROOT, "assets", "models") + "/"
+    base = [exe, "-MODEL_PATH", models, "-MODEL_NAME", "Tor.obj", "--W", "96", "--H", "64", "-RPP", "20", "-SEED", "5",
+            "-GAUSS", "1"]
+    gamma = float(np.float32(1) / np.float32(2.2))  # Config::gamma_correction = 1 / 2.2f, one ulp from float(1 / 2.2)
+    want, wstats = lib.render_image(tor, ptb200.config(96, 64, 20, 8, 1e-4, 0.001, seed=5), lib.post_config(96, 64, gamma, gauss=1))
+    for tag, extra, updates in (("oneshot", [], 0), ("progressive", ["-UPDATE", "8", "-CACHE", str(tmp_path)], 3),
+                                ("cached", ["-UPDATE", "8", "-CACHE", str(tmp_path)], 3)):
+        run = tmp_path / tag / "build"
+        os.makedirs(run)
+        r = subprocess.run(base + extra, cwd=run, capture_output=True, text=True, timeout=300)
+        assert r.returncode == 0, r.stderr
+        assert r.stderr.count("Image update") == updates, r.stderr
+        assert "20 rays per pixel were sent" in r.stderr
+        out = _read_bmp(str(tmp_path / tag / "result.bmp"))
+        assert_bits_equal(out, want, tag + " result.bmp")
+        named = glob.glob(str(run / "*.bmp"))
+        assert len(named) == 1 and "   20 of 20  max_disp " in named[0] and "aver_disp" in named[0], named
+        assert_bits_equal(_read_bmp(named[0]), want, tag + " dated file")
+    assert os.path.exists(tmp_path / "Tor.obj.ptscene")
