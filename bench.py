@@ -32,7 +32,10 @@ WORKLOADS = {
     "tor": ("configs[0]: models/Tor.obj 512x512 20 spp depth 8, adaptive error 0.001", 512, 512, 20, 8, 0.001),
     "composite4k": ("configs[3]: Tor.obj + the two Cornell boxes, 290 tris, 4K 1024 spp depth 8 (spp split across the ranks)", 3840, 2160, 1024, 8, -1.0),
     "glossy": ("configs[4]: mixed glossy materials, 1080p 64 spp depth 32 (no Russian roulette)", 1920, 1080, 64, 32, -1.0),
+    "glossy_rr": ("configs[4]: mixed glossy + refractive materials, 1080p 256 spp depth 32, Russian roulette from bounce 3 "
+                  "(extensions: no reference semantics, CPU leg = the oracle port)", 1920, 1080, 256, 32, -1.0),
 }
+RR_DEPTH = {"glossy_rr": 3}  # PtConfig.rr_depth per workload (0 = off)
 
 
 def make_scene(name):
@@ -44,6 +47,8 @@ def make_scene(name):
         return scenes.torus_room(1000, 500)
     if name == "glossy":
         return scenes.glossy_mix()
+    if name == "glossy_rr":
+        return scenes.glass_mix()
     if name == "composite4k":
         return scenes.composite(ptb200.HostLoader().load_obj(os.path.join(ROOT, "assets", "models"), "Tor.obj"))
     if name == "tor":
@@ -102,7 +107,7 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(hi), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=0):
+def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=0, rr_depth=0):
     """The reference's own CPU renderer (oracle/_ref: unmodified scene.cpp/triangles.h/material.h/ray.h + shims) when it
     was compiled, else the oracle's C port, on a bounded sample of the workload: the same scene and parameters at a
     reduced image size / spp, sized by a calibration pass to about `budget_s` seconds."""
@@ -111,7 +116,8 @@ def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=
     orc = Oracle()
     planes, squares = (sc["planes"], sc["squares"]) if sc.get("planes") is not None else (None, None)
     n_tri = sc["verts"].shape[0]
-    use_ref = Reference.available()
+    # the unmodified reference has neither roulette nor refraction: those workloads run on the oracle's port
+    use_ref = Reference.available() and rr_depth == 0 and sc.get("mats_ext") is None
     if use_ref:
         ref = Reference()
         threads = threads or ref.max_threads()
@@ -138,7 +144,7 @@ def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=
         osc = dict(sc, planes=planes, squares=squares)
 
         def run(w, h, s):
-            _, _, _, segs, sec = orc.render_accum(osc, orc.config(w, h, s, depth, 1e-4, error, 42), threads)
+            _, _, _, segs, sec = orc.render_accum(osc, orc.config(w, h, s, depth, 1e-4, error, 42, rr_depth=rr_depth), threads)
             return segs, sec
     # calibration: a thumbnail with the frame's aspect ratio, 1 sample
     w, h, s = max(16, W // 40), max(9, H // 40), 1
@@ -170,7 +176,7 @@ def run_reference_arm(args):
     runs = []
     per_step_budget = max(2.0, min(20.0, 120.0 / max(1, args.steps + args.warmup)))
     for i in range(args.warmup + args.steps):
-        r = cpu_reference_leg(args.workload, sc, W, H, spp, depth, error, budget_s=per_step_budget)
+        r = cpu_reference_leg(args.workload, sc, W, H, spp, depth, error, budget_s=per_step_budget, rr_depth=RR_DEPTH.get(args.workload, 0))
         if i >= args.warmup:
             runs.append(r)
     segs = sum(r["segments"] for r in runs)
@@ -225,14 +231,19 @@ def main():
         error = args.error
     sc = make_scene(args.workload)
     lib = ptb200.Library()
+    rr = RR_DEPTH.get(args.workload, 0)
+    if rr and world > 1:
+        raise SystemExit("the Russian-roulette workload reduces weight sums: run it on one GPU (or in-process, n_gpus)")
     cfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
-                        accel=args.accel, mode=args.mode, q_shift=args.q_shift)
+                        accel=args.accel, mode=args.mode, q_shift=args.q_shift, rr_depth=rr)
     ds = lib.scene_create(sc, cfg)
     n_px = W * H
     acc = torch.zeros(n_px * 4, device="cuda")            # [sum rgb (3*n_px) | count as f32 (n_px)] reduced together
     d_sum = acc[:3 * n_px]
     d_cnt_i = torch.zeros(n_px, dtype=torch.int32, device="cuda")
     d_rgb = torch.zeros(n_px * 3, device="cuda")
+    d_wt_t = torch.zeros(n_px, device="cuda") if rr else None  # the estimator's divisor under Russian roulette
+    d_wt = d_wt_t.data_ptr() if rr else 0
     h_rgb = torch.empty(n_px * 3, pin_memory=True) if world > 1 and rank == 0 else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
@@ -242,14 +253,14 @@ def main():
     def step():
         nonlocal launches_per_step
         flush.fill_(1)                                    # L2 flush between iterations
-        ds.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
+        ds.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream, d_wt)
         n = 1
         if world > 1:
             acc[3 * n_px:].copy_(d_cnt_i)                 # counts are exact in f32 up to 2^24 samples
             dist.reduce(acc, 0, op=dist.ReduceOp.SUM)     # one NCCL reduce over NVLink
             d_cnt_i.copy_(acc[3 * n_px:])
         if rank == 0:
-            ds.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream)
+            ds.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream, d_wt)
             n += 1
         launches_per_step = n - 1 + ds_launches()
 
@@ -344,7 +355,7 @@ def main():
     if rank == 0:
         cspp = max(world, min(spp, 64 * world))  # one full wavefront step of the production size per rank
         ccfg = ptb200.config(W, H, cspp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
-                             accel=args.accel, mode=args.mode, q_shift=args.q_shift)
+                             accel=args.accel, mode=args.mode, q_shift=args.q_shift, rr_depth=rr)
         # two instrumented frames (same image, cspp samples): one with traversal counters, one with CUDA events around
         # every launch (the counters' atomics would distort the timing)
         dsc = lib.scene_create(sc, ccfg, counters=True)
@@ -420,7 +431,7 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        cpu = cpu_reference_leg(args.workload, sc, W, H, spp, depth, error)
+        cpu = cpu_reference_leg(args.workload, sc, W, H, spp, depth, error, rr_depth=RR_DEPTH.get(args.workload, 0))
         cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
     if rank == 0:

@@ -104,7 +104,9 @@ typedef struct PtConfig {
                                   sample_begin and the call continues from them, bit-identical to one call over all
                                   samples (progressive refresh main.cpp:141-158, time limit main.cpp:111-114);
                                   0 = start from zero;
-                             [3] must be 0 */
+                             [3]: alive lists of the wavefront pipeline (bounce launches work on the paths still alive
+                                  instead of all path slots; same result either way): 0 = automatic (on under
+                                  Russian roulette, the adaptive rule or a skybox), 1 = on, 2 = off */
 } PtConfig;
 
 /* Statistics of the last render on a scene handle. */

@@ -181,9 +181,9 @@ static int validate_config(const PtConfig *c) {
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
     if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
     if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
-    if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] < 0 || c->reserved[2] > 1 || c->reserved[3])
+    if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] < 0 || c->reserved[2] > 1 || c->reserved[3] < 0 || c->reserved[3] > 2)
         return fail(PT_EINVAL, "reserved[1] must be 0..6 (log2 samples per wavefront step), reserved[2] 0/1 (resume), "
-                               "reserved[3] zero");
+                               "reserved[3] 0..2 (alive lists: automatic / on / off)");
     return PT_OK;
 }
 
@@ -417,19 +417,27 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     }
     rp.q_shift = cfg->reserved[1] ? cfg->reserved[1] : q_auto;
     rp.sample_major = (1 << rp.q_shift) > per_rank;  // a partial step: idle sample positions become idle warps
+    // alive lists: when paths are expected to end well before the depth limit — roulette, or the adaptive rule with
+    // enough samples for it to act (it never skips before sample 11); reserved[3]: 1 = on, 2 = off.  Measured in
+    // profiles/r01_sweep_alive_lists.txt.
+    rp.use_alive = cfg->reserved[3] == 1 ||
+                   (cfg->reserved[3] != 2 && (cfg->rr_depth > 0 || (cfg->error >= 0.0f && per_rank > 32)));
     rp.rr_depth = cfg->rr_depth;
     rp.weight = d_weight;
     rp.resume = cfg->reserved[2] == 1;
     return rp;
 }
 
-constexpr size_t kMaxSlots = (size_t)1 << 27;  // path slots in flight (64 B of state + 8 B of queue each: <= 9.7 GB)
+constexpr size_t kMaxSlots = (size_t)1 << 27;  // path slots in flight (64 B of state + 16 B of queues each: <= 10.8 GB)
 
 static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
     const size_t npc = std::min(npx, kMaxSlots >> q_shift), slots = npc << q_shift;
     const size_t npx4 = (npx + 3) & ~(size_t)3;  // keeps the queue 16-byte aligned behind the per-pixel weights
-    const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * npx * sizeof(float4) +
-                         npx4 * sizeof(float) + 256;
+    const size_t slot_blocks = (slots + kWfBlock - 1) / kWfBlock;
+    const size_t alive_seg = (slot_blocks + kAliveLists - 1) / kAliveLists * kWfBlock;  // capacity of one sub-list
+    const size_t alive_cap = alive_seg * kAliveLists;
+    const size_t bytes = slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * alive_cap * sizeof(int) +
+                         2 * npx * sizeof(float4) + npx4 * sizeof(float) + (kWfCounters + 3 * kAliveLists) * sizeof(int) + 256;
     if (!ds->wf_mem || ds->wf_bytes < bytes) {
         if (ds->wf_mem) { CK(cudaDeviceSynchronize()); pool_free(ds->wf_mem); ds->wf_mem = nullptr; ds->wf_bytes = 0; }
         CK(pool_alloc(&ds->wf_mem, bytes));
@@ -445,7 +453,10 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
     w.acc2 = (float4 *)p; p += npx * sizeof(float4);
     w.accw = (float *)p; p += npx4 * sizeof(float);
     w.queue = (int *)p; p += 2 * slots * sizeof(int);
-    w.counters = (int *)p;
+    w.alive = (int *)p; p += 2 * alive_cap * sizeof(int);
+    w.alive_seg = (int)alive_seg;
+    w.alive_cap = (int)alive_cap;
+    w.counters = (int *)p;  // kWfCounters ints, then the 3 x kAliveLists lengths of the alive sub-lists
     w.cap = (int)slots;
     ds->wf_slots = slots;
     ds->wf_pixels = npx;
@@ -506,7 +517,7 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
         ev_used = 0;
         return PT_OK;
     };
-    CK(cudaMemsetAsync(wf.counters, 0, 8 * sizeof(int), st));
+    CK(cudaMemsetAsync(wf.counters, 0, (kWfCounters + 3 * kAliveLists) * sizeof(int), st));
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
     for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
         const int npix = (int)std::min<size_t>(npc_max, npx - pix0);
@@ -516,7 +527,8 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
             const int steps = (remaining + Q - 1) / Q;
             for (int i = 0; i < steps; ++i) {
                 if ((rc = tick(0))) return rc;
-                k_wf_begin<COUNT><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                if (rp.use_alive) k_wf_begin<COUNT, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                else k_wf_begin<COUNT, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
                 if ((rc = tock())) return rc;
                 for (int b = 0; b < rp.max_depth; ++b) {
                     if (!sc.brute && sc.root != kRefEmpty) {
@@ -526,7 +538,8 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
                         ++n;
                     }
                     if ((rc = tick(2))) return rc;
-                    k_wf_bounce<COUNT><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    if (rp.use_alive) k_wf_bounce<COUNT, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    else k_wf_bounce<COUNT, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
                     if ((rc = tock())) return rc;
                     ++n;
                 }
@@ -564,7 +577,8 @@ extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, 
     if (cfg->reserved[2] == 1 && (!d_sum3 || !d_sum2_3 || !d_count || (cfg->rr_depth > 0 && !d_weight)))
         return fail(PT_EINVAL, "resume needs every accumulator (sum, sum2, count; weight under Russian roulette)");
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
-    const RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
+    RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
+    if (cfg->reserved[3] == 0 && ds->view.sky) rp.use_alive = 1;  // an open scene: every miss ends a path
     CK(cudaEventRecord(ds->ev0, st));
     int launches = 1;
     if (cfg->reserved[0] == 1) {  // megakernel variant

@@ -30,6 +30,7 @@ struct RenderParams {
     int rr_depth;   // extension: Russian roulette once Ray::depth >= rr_depth (0 = off, the reference)
     float *weight;  // extension: per-pixel sum of the contributing paths' RR weights (== count without RR)
     int sample_major;  // wavefront slot numbering, pt_wavefront.cuh slot_split
+    int use_alive;     // wavefront pipeline: bounce launches work on lists of the paths still alive (pt_wavefront.cuh)
     int resume;     // the output buffers hold the accumulators after the samples before s_begin: continue from them
 };
 

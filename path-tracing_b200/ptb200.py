@@ -64,7 +64,7 @@ class PtError(RuntimeError):
 
 def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
            sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0,
-           mode=0, q_shift=0, resume=0):
+           mode=0, q_shift=0, resume=0, alive=0):
     """PtConfig with the reference's defaults (config.h:10,16-29)."""
     c = PtConfig()
     c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
@@ -73,6 +73,7 @@ def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, se
     c.intersector, c.accel, c.rr_depth, c.n_gpus, c.device = intersector, accel, rr_depth, n_gpus, device
     c.reserved[0] = mode  # 0 = wavefront pipeline, 1 = megakernel variant
     c.reserved[1] = q_shift  # 0 = automatic, else log2(samples per pixel per wavefront step)
+    c.reserved[3] = alive  # alive lists of the wavefront pipeline: 0 automatic, 1 on, 2 off
     c.reserved[2] = resume  # 1 = continue from the accumulators passed in (samples before sample_begin are in them)
     return c
 

@@ -495,3 +495,24 @@ def test_host_program_end_to_end(lib, tor, tmp_path):
         assert len(named) == 1 and "   20 of 20  max_disp " in named[0] and "aver_disp" in named[0], named
         assert_bits_equal(_read_bmp(named[0]), want, tag + " dated file")
     assert os.path.exists(tmp_path / "Tor.obj.ptscene")
+
+
+@pytest.mark.parametrize("case", ["flat", "adaptive", "roulette", "sky", "chunks"])
+def test_alive_lists_do_not_change_the_result(lib, tor, case):
+    """PtConfig.reserved[3]: bounce launches over lists of the paths still alive (1) or over all path slots (2) — the
+    same accumulators bit for bit, whatever ends the paths: the depth limit, emitters, roulette, misses into a skybox,
+    samples the adaptive rule skipped; also across pixel chunks."""
+    kw, sc, size, spp = dict(error=-1.0), tor, (96, 64), 24
+    if case == "adaptive":
+        kw = dict(error=0.002)
+    elif case == "roulette":
+        kw, sc = dict(error=-1.0, rr_depth=2, max_depth=24), scenes.glass_mix()
+    elif case == "sky":
+        sc = dict(scenes.open_scene(), sky=scenes.sky_image())
+    elif case == "chunks":
+        sc, size, spp, kw = scenes.cornell(), (3840, 2160), 40, dict(error=-1.0, q_shift=6, max_depth=4)
+    depth = kw.pop("max_depth", 8)
+    out = [lib.render_accum_w(sc, ptb200.config(size[0], size[1], spp, depth, 1e-4, seed=11, alive=a, **kw)) for a in (1, 2)]
+    for x, y, what in zip(out[0], out[1], ("sum", "sum2", "count", "weight")):
+        assert_bits_equal(x, y, f"{case} {what}")
+    assert out[0][2].sum() > 0
