@@ -232,8 +232,6 @@ def main():
     sc = make_scene(args.workload)
     lib = ptb200.Library()
     rr = RR_DEPTH.get(args.workload, 0)
-    if rr and world > 1:
-        raise SystemExit("the Russian-roulette workload reduces weight sums: run it on one GPU (or in-process, n_gpus)")
     cfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, sample_begin=rank, sample_step=world, device=local,
                         accel=args.accel, mode=args.mode, q_shift=args.q_shift, rr_depth=rr)
     ds = lib.scene_create(sc, cfg)
@@ -256,9 +254,11 @@ def main():
         ds.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream, d_wt)
         n = 1
         if world > 1:
-            acc[3 * n_px:].copy_(d_cnt_i)                 # counts are exact in f32 up to 2^24 samples
+            # the divisor travels with the sums: counts (exact in f32 up to 2^24 samples), or under Russian roulette
+            # the weight sums (the resolve then reads them instead of the counts, which stay this rank's own)
+            acc[3 * n_px:].copy_(d_wt_t if rr else d_cnt_i)
             dist.reduce(acc, 0, op=dist.ReduceOp.SUM)     # one NCCL reduce over NVLink
-            d_cnt_i.copy_(acc[3 * n_px:])
+            (d_wt_t if rr else d_cnt_i).copy_(acc[3 * n_px:])
         if rank == 0:
             ds.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream, d_wt)
             n += 1
@@ -313,13 +313,13 @@ def main():
         if world == 1:
             return lib.render(sc_pinned, cfg, out=rgb_pinned)
         h = lib.scene_create(sc, cfg)
-        h.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream)
-        acc[3 * n_px:].copy_(d_cnt_i)
+        h.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream, d_wt)
+        acc[3 * n_px:].copy_(d_wt_t if rr else d_cnt_i)
         dist.reduce(acc, 0, op=dist.ReduceOp.SUM)
         out = None
         if rank == 0:
-            d_cnt_i.copy_(acc[3 * n_px:])
-            h.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream)
+            (d_wt_t if rr else d_cnt_i).copy_(acc[3 * n_px:])
+            h.resolve_device(d_sum.data_ptr(), d_cnt_i.data_ptr(), n_px, d_rgb.data_ptr(), stream, d_wt)
             h_rgb.copy_(d_rgb, non_blocking=True)  # pinned host buffer
             out = h_rgb
         torch.cuda.synchronize()

@@ -331,8 +331,11 @@ __global__ void k_resolve(const float *__restrict__ sum3, const int *__restrict_
     if (p >= n_pixels) return;
     const int c = count[p];
     const float fn = weight ? weight[p] : (float)c;
+    // "has samples": the count, or — when weight sums are the divisor (they may have been reduced over ranks while
+    // the counts stayed local) — a positive weight; the two agree on one device (weights are positive)
+    const bool has = weight ? fn > 0.0f : c != 0;
 #pragma unroll
-    for (int k = 0; k < 3; ++k) rgb[3 * p + k] = c ? sum3[3 * p + k] / fn : 0.0f;
+    for (int k = 0; k < 3; ++k) rgb[3 * p + k] = has ? sum3[3 * p + k] / fn : 0.0f;
 }
 
 // ---- parity probes ----------------------------------------------------------------------------------------
