@@ -232,7 +232,7 @@ int pt_powf(const float *x, int64_t n, float y, float *out); /* the device's res
 int pt_probe_read_bandwidth(size_t footprint_bytes, int passes, double *gb_per_s);
 int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
 
-/* pt_render / pt_scene_destroy keep the last path-state workspace (up to 9.7 GB of HBM) for the next call on the same
+/* pt_render / pt_scene_destroy keep the last path-state workspace (up to 10.8 GB of HBM) for the next call on the same
  * device; this frees it. */
 void pt_release_workspace(void);
 
