@@ -99,6 +99,25 @@ def test_render_golden(lib, name, accel, mode):
 
 
 @pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
+@pytest.mark.parametrize("name", ["tor", "cornell"])
+def test_converged_4096spp(lib, name, mode):
+    """north_star, third check: converged images at 4096 spp agree within RMSE 1e-3.  The golden images are the
+    unmodified reference's under the Philox contract (tests/golden/make_converged.py); 64 wavefront steps of 64
+    samples.  RMSE is the bar that is asserted first; the sums are in fact bit-identical."""
+    from test_oracle import CONVERGED_RMSE_TOL, converged_image
+    CV, img = converged_image(name)
+    W, H, spp, depth, seed = map(int, CV[name + "_cfg"])
+    sc = tor_scene() if name == "tor" else scenes.cornell()
+    cfg = ptb200.config(W, H, spp, depth, 1e-4, -1.0, seed=seed, mode=mode)
+    rgb = lib.render(sc, cfg)
+    rmse = float(np.sqrt(np.mean((rgb.astype(np.float64) - img) ** 2)))
+    assert rmse <= CONVERGED_RMSE_TOL, rmse
+    sm, _, cnt = lib.render_accum(sc, cfg)
+    assert_bits_equal(cnt, CV[name + "_count"], name + " count")
+    assert_bits_equal(sm, CV[name + "_sum"], name + " sum")
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
 def test_render_skybox(lib, mode):
     """scene.cpp:125-156.  acosf / atan2f are CUDA's here and glibc's in the reference: counts and segment counts
     must be exact, radiance within 1e-5 relative (RADIANCE_REL_TOL is 1e-4)."""
