@@ -339,7 +339,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         } else {
             CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb)); CK(children.alloc(nb)); CK(range.alloc(nb));
             CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
-            CK(pool_alloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
+            CK(pool_alloc((void **)&ds->nodes, 4 * (size_t)(nb - 1 + kTopNodes) * sizeof(float4)));  // + the top table (variant)
             CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
             k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
             k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
@@ -347,6 +347,17 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             launches += 3;
             v.root = 0;
             ds->n_nodes = nb - 1;
+#if PT_TOP_NODES
+            {
+                DevBuf<int> d_ntop;
+                CK(d_ntop.alloc(1));
+                float4 *top = ds->nodes + 4 * (size_t)(nb - 1);
+                k_top_tree<<<1, 1>>>(ds->nodes, top, d_ntop.p);
+                ++launches;
+                CK(cudaMemcpy(&v.n_top, d_ntop.p, sizeof(int), cudaMemcpyDeviceToHost));
+                v.top = top;
+            }
+#endif
         }
         if (nb > 0) {
             k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, node_lo.p, node_hi.p, d_root.p);

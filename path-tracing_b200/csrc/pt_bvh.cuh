@@ -264,6 +264,34 @@ __global__ void k_emit_nodes(int n, const int2 *__restrict__ children, const int
     o[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
 }
 
+#if PT_TOP_NODES
+// Breadth-first table of the first kTopNodes inner nodes below the root (node 0) for the shared-memory variant of
+// k_wf_traverse: row layout of `nodes`, child refs that point to a node inside the table become kTopBit | index.
+// One thread: a few hundred dependent 64-byte reads, once per scene.
+__global__ void k_top_tree(const float4 *__restrict__ nodes, float4 *__restrict__ top, int *__restrict__ n_top) {
+    int gq[kTopNodes];  // node index of table entry i
+    int n = 1;
+    gq[0] = 0;
+    for (int i = 0; i < n; ++i) {
+        const float4 *nd = nodes + 4 * (size_t)gq[i];
+        const float4 r0 = nd[0], r1 = nd[1], r2 = nd[2], r3 = nd[3];
+        int c[2] = {__float_as_int(r3.x), __float_as_int(r3.y)};
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+            if (c[k] >= 0 && c[k] != kRefEmpty && n < kTopNodes) {
+                gq[n] = c[k];
+                c[k] = kTopBit | n;
+                ++n;
+            }
+        top[4 * i] = r0;
+        top[4 * i + 1] = r1;
+        top[4 * i + 2] = r2;
+        top[4 * i + 3] = make_float4(__int_as_float(c[0]), __int_as_float(c[1]), 0.0f, 0.0f);
+    }
+    *n_top = n;
+}
+#endif
+
 // triangle records in sorted order (vals == nullptr: caller order)
 __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__restrict__ planes,
                             const float *__restrict__ squares, const int *__restrict__ mat_ids,

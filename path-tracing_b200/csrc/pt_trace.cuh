@@ -63,13 +63,51 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
                  : "l"(p));
 }
 
+// Compile-time variants of the cache policy (tools/ab_variants.sh; 0 = the default build): PT_TRI_NOALLOC fetches
+// triangle records without allocating them in L1 (a record is rarely read twice; the nodes are), PT_NODE_EVICT_LAST
+// marks inner nodes evict-last in L1.
+#ifndef PT_TRI_NOALLOC
+#define PT_TRI_NOALLOC 0
+#endif
+#ifndef PT_NODE_EVICT_LAST
+#define PT_NODE_EVICT_LAST 0
+#endif
+__device__ __forceinline__ void ldg256_tri(const float4 *p, float4 &a, float4 &b) {
+#if PT_TRI_NOALLOC
+    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+#else
+    ldg256(p, a, b);
+#endif
+}
+__device__ __forceinline__ float4 ldg128_tri(const float4 *p) {
+#if PT_TRI_NOALLOC
+    float4 a;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(p));
+    return a;
+#else
+    return __ldg(p);
+#endif
+}
+__device__ __forceinline__ void ldg256_node(const float4 *p, float4 &a, float4 &b) {
+#if PT_NODE_EVICT_LAST
+    asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+                 : "l"(p));
+#else
+    ldg256(p, a, b);
+#endif
+}
+
 // Triangle::Intersect (triangles.h:48-73) on record `rec` (4 float4 at r).  Differences from the reference, both
 // outside its defined behaviour: a NaN distance (0/0: ray in the plane) is rejected instead of accepted, and equal
 // distances go to the lower caller index explicitly.
 __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o, V3 d, float eps, Hit &h) {
     float4 pl, a, b, c;
-    ldg256(r, pl, a);
-    ldg256(r + 2, b, c);
+    ldg256_tri(r, pl, a);
+    ldg256_tri(r + 2, b, c);
     const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
     const int idx = __float_as_int(b.w);
@@ -258,7 +296,7 @@ __device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3
     float4 pl[kLeafMax];
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k)
-        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        pl[k] = k < cnt ? ldg128_tri(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k) {
         const float nd = plane_distance(pl[k], o, d);
@@ -279,8 +317,8 @@ __device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 
     {
         const float4 *nd = sc.nodes + 4 * (size_t)cur;
         float4 n0, n1, n2, n3;
-        ldg256(nd, n0, n1);
-        ldg256(nd + 2, n2, n3);
+        ldg256_node(nd, n0, n1);
+        ldg256_node(nd + 2, n2, n3);
         if (COUNT) ++n_nodes;
         // box_entry clips against h.t with <=, so that an equal-distance lower index is still found; +inf = miss
         const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
@@ -297,6 +335,37 @@ __device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 
         return sp ? stack[--sp] : kRefEmpty;
     }
 }
+
+#if PT_TOP_NODES
+// node_step of the shared-memory variant: a ref with kTopBit reads its node from the block's copy of the top table
+// (four LDS.128, no L1 tag lookup), any other node ref from global memory as above.
+template <bool COUNT>
+__device__ __forceinline__ int node_step_top(const SceneView &sc, const float4 *s_top, int cur, V3 o, V3 inv,
+                                             const Hit &h, int *stack, int &sp, unsigned long long &n_nodes) {
+    float4 n0, n1, n2, n3;
+    if (cur & kTopBit) {
+        const float4 *nd = s_top + 4 * (cur & ~kTopBit);
+        n0 = nd[0]; n1 = nd[1]; n2 = nd[2]; n3 = nd[3];
+    } else {
+        const float4 *nd = sc.nodes + 4 * (size_t)cur;
+        ldg256_node(nd, n0, n1);
+        ldg256_node(nd + 2, n2, n3);
+    }
+    if (COUNT) ++n_nodes;
+    const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
+    const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
+    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
+    if (g0 && g1) {
+        const bool swap = t1 < t0;
+        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
+        return swap ? c1 : c0;
+    }
+    if (g0) return c0;
+    if (g1) return c1;
+    return sp ? stack[--sp] : kRefEmpty;
+}
+#endif
 
 // One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
 template <bool COUNT>

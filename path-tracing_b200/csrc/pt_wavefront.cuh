@@ -303,6 +303,11 @@ __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
     const int count = wf.counters[2 * set];
     if (count == 0) return;
+#if PT_TOP_NODES
+    __shared__ float4 s_top[4 * kTopNodes];  // (count is the same for every thread: no one left before the barrier)
+    for (int k = threadIdx.x; k < 4 * sc.n_top; k += blockDim.x) s_top[k] = sc.top[k];
+    __syncthreads();
+#endif
     int *head = &wf.counters[2 * set + 1];
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
@@ -340,7 +345,11 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
                     h.t = ot.w;
                     h.rec = __float_as_int(dr.w);
                     h.idx = h.rec >= 0 ? __float_as_int(__ldg(sc.tris + 4 * (size_t)h.rec + 2).w) : -1;
+#if PT_TOP_NODES
+                    cur = sc.n_top > 0 ? kTopBit : sc.root;  // table entry 0 is the root node
+#else
                     cur = sc.root;
+#endif
                     sp = 0;
                     ray_nodes0 = n_nodes;
                 } else {
@@ -359,7 +368,11 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             const bool can = cur >= 0 && cur != kRefEmpty;
             const unsigned cm = __ballot_sync(0xffffffffu, can);
             if (cm == 0u || (it > 0 && __popc(cm) < kMinNodeLanes)) break;
+#if PT_TOP_NODES
+            if (can) cur = node_step_top<COUNT>(sc, s_top, cur, o, inv, h, stack, sp, n_nodes);
+#else
             if (can) cur = node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
+#endif
         }
         if (cur < 0 && leaf == 0) {
             leaf = cur;

@@ -1,0 +1,61 @@
+"""Quick A/B of compile-time variants built by `tools/ab_variants.sh build`, in ONE process (a GPU-box call of well
+under a minute):  python tools/ab_quick.py base top128 top320
+For each variant: accumulators of two small renders must equal the first variant's bit for bit (the first one is the
+default build, which the goldens pin), then the 1M-triangle scene (C3) at 1080p, 128 spp: 1 warm-up + 3 timed
+frames with per-class event timing."""
+import os
+import sys
+import time
+
+HERE = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(HERE, "path-tracing_b200"))
+import numpy as np  # noqa: E402
+import ptb200  # noqa: E402
+import scenes  # noqa: E402
+
+CLASSES = ("begin", "traverse", "bounce", "commit")
+
+
+def main():
+    names = sys.argv[1:] or ["base"]
+    t00 = time.time()
+    big, small = scenes.torus_room(1000, 500), scenes.torus_room(40, 20)
+    print(f"scenes built in {time.time() - t00:.1f} s", flush=True)
+    ref = None
+    lines = []
+    for name in names:
+        ptb200.RENDER_SO = os.path.join(HERE, "path-tracing_b200", "lib", "variants", f"libptrender_{name}.so")
+        lib = ptb200.Library()
+        outs = [lib.render_accum(small, ptb200.config(64, 64, 16, 8, 1e-4, -1.0, seed=42)),
+                lib.render_accum(big, ptb200.config(320, 180, 8, 8, 1e-4, -1.0, seed=42)),
+                lib.render_accum(big, ptb200.config(96, 54, 24, 8, 1e-4, 0.001, seed=7))]
+        flat = [np.ascontiguousarray(a).view(np.uint32).ravel() for o in outs for a in o]
+        if ref is None:
+            ref, parity = flat, "reference"
+        else:
+            parity = "bit-equal" if all(np.array_equal(a, b) for a, b in zip(flat, ref)) else "DIFFERS"
+        cfg = ptb200.config(1920, 1080, 128, 8, 1e-4, -1.0, seed=42)
+        ds = lib.scene_create(big, cfg, timed=True)
+        ms, cls = [], np.zeros(4)
+        for i in range(4):
+            ds.render_device(cfg)
+            st = ds.stats()
+            if i:
+                ms.append(st["kernel_ms"])
+                cls += np.array(st["class_ms"][:4])
+        segs = st["segments"]
+        ds.close()
+        lib.lib.pt_release_workspace()
+        line = (f"{name:8s} parity {parity:9s} frame {np.mean(ms):7.2f} ms (min {min(ms):.2f})  "
+                f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " +
+                "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)))
+        print(line, flush=True)
+        lines.append(line)
+    os.makedirs(os.path.join(HERE, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(HERE, "gpurun_out", "ab_quick.txt"), "a") as f:
+        f.write("\n".join(lines) + "\n")
+    print(f"total {time.time() - t00:.1f} s")
+
+
+if __name__ == "__main__":
+    main()
