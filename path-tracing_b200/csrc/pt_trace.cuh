@@ -20,6 +20,17 @@
 
 namespace ptd {
 
+#ifndef PT_LAZY_IDX
+#define PT_LAZY_IDX 1
+#endif
+#ifndef PT_SLAB_FMA
+#define PT_SLAB_FMA 0
+#endif
+#ifndef PT_LEAF_RCP
+#define PT_LEAF_RCP 1
+#endif
+constexpr int kIdxLazy = (int)0x80000000;  // Hit::idx not fetched yet (PT_LAZY_IDX); caller indices are >= 0
+
 struct Hit {
     float t;   // best distance so far (+inf = none)
     int idx;   // caller's triangle index of the best hit (-1 = none)
@@ -111,7 +122,14 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
     const int idx = __float_as_int(b.w);
+#if PT_LAZY_IDX
+    if (nd == h.t) {  // a tie: now the caller index of the best hit so far is needed (k_wf_traverse left it unfetched)
+        if (h.idx == kIdxLazy) h.idx = __float_as_int(__ldg(r - 4 * (ptrdiff_t)rec + 4 * (ptrdiff_t)h.rec + 2).w);
+        if (!(idx < h.idx)) return;
+    }
+#else
     if (nd == h.t && !(idx < h.idx)) return;  // also rejects nd == +inf against the initial (inf, -1)
+#endif
     if (!inside_test(a, b, c, o, d, nd, eps)) return;
     h.t = nd;
     h.idx = idx;
@@ -297,11 +315,26 @@ __device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k)
         pl[k] = k < cnt ? ldg128_tri(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+#if PT_LEAF_RCP
+    // Compile-time variant: the plane pass with an approximate reciprocal (MUFU.RCP, within 2^-21 of the IEEE quotient
+    // for the reference's own numerator and denominator) and a range widened by 2e-6 relative, as in scan_singles;
+    // conservative — the exact test below repeats the IEEE division for the triangles it marks.  A NaN marks.
+    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
+#pragma unroll
+    for (int k = 0; k < kLeafMax; ++k) {
+        const float4 p = pl[k];
+        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
+        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+        const float t = num * rcp_approx(sd);
+        mask |= (unsigned)(k < cnt && !((t > t_hi) | (t < t_lo))) << k;
+    }
+#else
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k) {
         const float nd = plane_distance(pl[k], o, d);
         mask |= (unsigned)(k < cnt && nd <= h.t && !(nd < eps)) << k;
     }
+#endif
     while (mask) {
         const int k = __ffs(mask) - 1;
         mask &= mask - 1u;
@@ -354,6 +387,75 @@ __device__ __forceinline__ int node_step_top(const SceneView &sc, const float4 *
     if (COUNT) ++n_nodes;
     const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
     const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
+    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
+    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
+    if (g0 && g1) {
+        const bool swap = t1 < t0;
+        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
+        return swap ? c1 : c0;
+    }
+    if (g0) return c0;
+    if (g1) return c1;
+    return sp ? stack[--sp] : kRefEmpty;
+}
+#endif
+
+#if PT_QNODES
+// node_step on the 32-byte quantised copy of the nodes (pt_scene.cuh): one 256-bit load, twelve decodes
+template <bool COUNT>
+__device__ __forceinline__ int node_step_q(const SceneView &sc, int cur, V3 o, V3 inv, const Hit &h, int *stack, int &sp,
+                                           unsigned long long &n_nodes) {
+    uint4 a, b;
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
+                 : "l"(sc.qnodes + 2 * (size_t)cur));
+    if (COUNT) ++n_nodes;
+    const float sx = sc.q_scale.x, sy = sc.q_scale.y, sz = sc.q_scale.z;
+    const float bx = sc.q_base.x, by = sc.q_base.y, bz = sc.q_base.z;
+    const float t0 = box_entry(q_decode(a.x & 0xffffu, sx, bx), q_decode(a.x >> 16, sx, bx),
+                               q_decode(a.y & 0xffffu, sy, by), q_decode(a.y >> 16, sy, by),
+                               q_decode(a.z & 0xffffu, sz, bz), q_decode(a.z >> 16, sz, bz), o, inv, h.t);
+    const float t1 = box_entry(q_decode(a.w & 0xffffu, sx, bx), q_decode(a.w >> 16, sx, bx),
+                               q_decode(b.x & 0xffffu, sy, by), q_decode(b.x >> 16, sy, by),
+                               q_decode(b.y & 0xffffu, sz, bz), q_decode(b.y >> 16, sz, bz), o, inv, h.t);
+    const int c0 = (int)b.z, c1 = (int)b.w;
+    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
+    if (g0 && g1) {
+        const bool swap = t1 < t0;
+        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
+        return swap ? c1 : c0;
+    }
+    if (g0) return c0;
+    if (g1) return c1;
+    return sp ? stack[--sp] : kRefEmpty;
+}
+#endif
+
+#if PT_SLAB_FMA
+// Compile-time variant -DPT_SLAB_FMA=1: the slab distances as one FMA each, lo * inv + noi with noi = -(o * inv)
+// computed once per ray, instead of (lo - o) * inv: 12 instructions fewer per node visit.  In position terms the result
+// differs from the subtract-multiply form by about one ulp of the origin's coordinate (the rounding of o * inv),
+// inside the 32 ulp the leaf boxes are padded with (pt_bvh.cuh k_tri_boxes_keys).  inf - inf (inv = inf, or o * inv
+// overflowing) is NaN and drops the axis, as 0 * inf does in box_entry.
+__device__ __forceinline__ float box_entry_fma(float lox, float hix, float loy, float hiy, float loz, float hiz, V3 noi,
+                                               V3 inv, float tmax) {
+    const float x0 = __fmaf_rn(lox, inv.x, noi.x), x1 = __fmaf_rn(hix, inv.x, noi.x);
+    const float y0 = __fmaf_rn(loy, inv.y, noi.y), y1 = __fmaf_rn(hiy, inv.y, noi.y);
+    const float z0 = __fmaf_rn(loz, inv.z, noi.z), z1 = __fmaf_rn(hiz, inv.z, noi.z);
+    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
+    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
+    return tn <= tf * 1.0000003f ? tn : __int_as_float(0x7f800000);
+}
+template <bool COUNT>
+__device__ __forceinline__ int node_step_fma(const SceneView &sc, int cur, V3 noi, V3 inv, const Hit &h, int *stack,
+                                             int &sp, unsigned long long &n_nodes) {
+    const float4 *nd = sc.nodes + 4 * (size_t)cur;
+    float4 n0, n1, n2, n3;
+    ldg256(nd, n0, n1);
+    ldg256(nd + 2, n2, n3);
+    if (COUNT) ++n_nodes;
+    const float t0 = box_entry_fma(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, noi, inv, h.t);
+    const float t1 = box_entry_fma(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, noi, inv, h.t);
     const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
     const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
     if (g0 && g1) {

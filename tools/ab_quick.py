@@ -16,39 +16,45 @@ import scenes  # noqa: E402
 CLASSES = ("begin", "traverse", "bounce", "commit")
 
 
+def run_variant(name, big, small, state):
+    ptb200.RENDER_SO = os.path.join(HERE, "path-tracing_b200", "lib", "variants", f"libptrender_{name}.so")
+    lib = ptb200.Library()
+    outs = [lib.render_accum(small, ptb200.config(64, 64, 16, 8, 1e-4, -1.0, seed=42)),
+            lib.render_accum(big, ptb200.config(320, 180, 8, 8, 1e-4, -1.0, seed=42)),
+            lib.render_accum(big, ptb200.config(96, 54, 24, 8, 1e-4, 0.001, seed=7))]
+    flat = [np.ascontiguousarray(a).view(np.uint32).ravel() for o in outs for a in o]
+    if state["ref"] is None:
+        state["ref"], parity = flat, "reference"
+    else:
+        parity = "bit-equal" if all(np.array_equal(a, b) for a, b in zip(flat, state["ref"])) else "DIFFERS"
+    cfg = ptb200.config(1920, 1080, 128, 8, 1e-4, -1.0, seed=42)
+    ds = lib.scene_create(big, cfg, timed=True)
+    ms, cls = [], np.zeros(4)
+    for i in range(4):
+        ds.render_device(cfg)
+        st = ds.stats()
+        if i:
+            ms.append(st["kernel_ms"])
+            cls += np.array(st["class_ms"][:4])
+    segs = st["segments"]
+    ds.close()
+    lib.lib.pt_release_workspace()
+    return (f"{name:8s} parity {parity:9s} frame {np.mean(ms):7.2f} ms (min {min(ms):.2f})  "
+            f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " + "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)))
+
+
 def main():
     names = sys.argv[1:] or ["base"]
     t00 = time.time()
     big, small = scenes.torus_room(1000, 500), scenes.torus_room(40, 20)
     print(f"scenes built in {time.time() - t00:.1f} s", flush=True)
-    ref = None
+    state = {"ref": None}
     lines = []
     for name in names:
-        ptb200.RENDER_SO = os.path.join(HERE, "path-tracing_b200", "lib", "variants", f"libptrender_{name}.so")
-        lib = ptb200.Library()
-        outs = [lib.render_accum(small, ptb200.config(64, 64, 16, 8, 1e-4, -1.0, seed=42)),
-                lib.render_accum(big, ptb200.config(320, 180, 8, 8, 1e-4, -1.0, seed=42)),
-                lib.render_accum(big, ptb200.config(96, 54, 24, 8, 1e-4, 0.001, seed=7))]
-        flat = [np.ascontiguousarray(a).view(np.uint32).ravel() for o in outs for a in o]
-        if ref is None:
-            ref, parity = flat, "reference"
-        else:
-            parity = "bit-equal" if all(np.array_equal(a, b) for a, b in zip(flat, ref)) else "DIFFERS"
-        cfg = ptb200.config(1920, 1080, 128, 8, 1e-4, -1.0, seed=42)
-        ds = lib.scene_create(big, cfg, timed=True)
-        ms, cls = [], np.zeros(4)
-        for i in range(4):
-            ds.render_device(cfg)
-            st = ds.stats()
-            if i:
-                ms.append(st["kernel_ms"])
-                cls += np.array(st["class_ms"][:4])
-        segs = st["segments"]
-        ds.close()
-        lib.lib.pt_release_workspace()
-        line = (f"{name:8s} parity {parity:9s} frame {np.mean(ms):7.2f} ms (min {min(ms):.2f})  "
-                f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " +
-                "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)))
+        try:
+            line = run_variant(name, big, small, state)
+        except Exception as e:  # a broken variant must not take the rest of the session with it
+            line = f"{name:8s} FAILED: {e}"
         print(line, flush=True)
         lines.append(line)
     os.makedirs(os.path.join(HERE, "gpurun_out"), exist_ok=True)
