@@ -53,13 +53,6 @@ int check_device() {
     return PT_OK;
 }
 
-// Compile-time variant -DPT_L2_PERSIST=1|2 (0 = off, the default build): k_wf_traverse is launched with an access
-// policy window that keeps the LBVH nodes (1) or the nodes and the triangle records (2, one block) in the persisting
-// part of L2, sized to the device's maximum set-aside; everything else the launch touches is streaming.
-#ifndef PT_L2_PERSIST
-#define PT_L2_PERSIST 0
-#endif
-
 inline int blocks_for(long long n, int bs) { return (int)((n + bs - 1) / bs); }
 
 // ---- device memory pool ---------------------------------------------------------------------------------------------
@@ -163,11 +156,6 @@ struct PtDeviceScene {
     size_t wf_slots = 0, wf_pixels = 0, wf_bytes = 0;
     int *h_counters = nullptr;  // pinned, 6 ints
     int traverse_blocks = 0;
-#if PT_L2_PERSIST
-    bool nodes_in_tris = false;  // mode 2: nodes live behind the triangle records in one block
-    void *l2_base = nullptr;     // access-policy window of the traversal launches
-    size_t l2_bytes = 0;
-#endif
 };
 
 static int validate_scene(const PtScene *s) {
@@ -228,9 +216,6 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     };
     cudaDeviceSynchronize();  // blocks go back to the pool: nothing may still be using them (cudaFree used to wait)
     pool_free(ds->tris);
-#if PT_L2_PERSIST
-    if (ds->nodes_in_tris) ds->nodes = nullptr;
-#endif
     pool_free(ds->nodes);
     pool_free(ds->mats);
     pool_free(ds->lrecs);
@@ -298,11 +283,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     }
     CK(pool_alloc((void **)&ds->mats, (m ? 3 * (size_t)m : 1) * sizeof(float4)));
     if (m) { k_pack_materials<<<blocks_for(m, 128), 128>>>(d_mats10.p, d_ext2.p, m, ds->mats); ++launches; }
-#if PT_L2_PERSIST == 2
-    CK(pool_alloc((void **)&ds->tris, (n ? 8 * (size_t)n : 1) * sizeof(float4)));  // records, then room for the nodes
-#else
     CK(pool_alloc((void **)&ds->tris, (n ? 4 * (size_t)n : 1) * sizeof(float4)));
-#endif
     CK(pool_alloc((void **)&ds->stats, kStatWords * sizeof(unsigned long long)));
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
 
@@ -358,13 +339,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         } else {
             CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb)); CK(children.alloc(nb)); CK(range.alloc(nb));
             CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
-#if PT_L2_PERSIST == 2
-            ds->nodes = ds->tris + 4 * (size_t)n;
-            ds->nodes_in_tris = true;
-#else
-            // (+ the top table / the 32-byte copy of the nodes in the compile-time variants)
-            CK(pool_alloc((void **)&ds->nodes, (4 * (size_t)(nb - 1 + kTopNodes) + (PT_QNODES ? 2 * (size_t)(nb - 1) : 0)) * sizeof(float4)));
-#endif
+            CK(pool_alloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
             CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
             k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
             k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
@@ -372,30 +347,6 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             launches += 3;
             v.root = 0;
             ds->n_nodes = nb - 1;
-#if PT_L2_PERSIST
-            {
-                cudaDeviceProp prop;
-                CK(cudaGetDeviceProperties(&prop, ds->device));
-                CK(cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)prop.persistingL2CacheMaxSize));
-                ds->l2_base = PT_L2_PERSIST == 2 ? (void *)ds->tris : (void *)ds->nodes;
-                ds->l2_bytes = (PT_L2_PERSIST == 2 ? 4 * (size_t)n + 4 * (size_t)(nb - 1) : 4 * (size_t)(nb - 1)) * sizeof(float4);
-                ds->l2_bytes = std::min(ds->l2_bytes, (size_t)prop.accessPolicyMaxWindowSize);
-                if (getenv("PT_PROFILE"))
-                    fprintf(stderr, "[l2 persist] set-aside max %d MB, window max %d MB, window %zu MB\n",
-                            prop.persistingL2CacheMaxSize >> 20, prop.accessPolicyMaxWindowSize >> 20, ds->l2_bytes >> 20);
-            }
-#endif
-#if PT_TOP_NODES
-            {
-                DevBuf<int> d_ntop;
-                CK(d_ntop.alloc(1));
-                float4 *top = ds->nodes + 4 * (size_t)(nb - 1);
-                k_top_tree<<<1, 1>>>(ds->nodes, top, d_ntop.p);
-                ++launches;
-                CK(cudaMemcpy(&v.n_top, d_ntop.p, sizeof(int), cudaMemcpyDeviceToHost));
-                v.top = top;
-            }
-#endif
         }
         if (nb > 0) {
             k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, node_lo.p, node_hi.p, d_root.p);
@@ -409,23 +360,6 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
                 CK(cudaMemcpy(rn, ds->nodes, sizeof rn, cudaMemcpyDeviceToHost));
                 v.root_n0 = rn[0]; v.root_n1 = rn[1]; v.root_n2 = rn[2];
             }
-#if PT_QNODES
-            if (v.root == 0) {  // grid: 65000 cells across the root box per axis, 4 cells of margin below it
-                const float lo[3] = {rb[0].x, rb[0].y, rb[0].z}, hi[3] = {rb[1].x, rb[1].y, rb[1].z};
-                float qs[3], qb[3];
-                for (int k = 0; k < 3; ++k) {
-                    const float amax = std::max(fabsf(lo[k]), fabsf(hi[k]));
-                    qs[k] = std::max((hi[k] - lo[k]) / 65000.0f, amax * 1e-6f + 1e-30f);
-                    qb[k] = lo[k] - 4.0f * qs[k];
-                }
-                uint4 *qn = (uint4 *)(ds->nodes + 4 * (size_t)(nb - 1 + kTopNodes));
-                v.q_scale = make_float4(qs[0], qs[1], qs[2], 0.f);
-                v.q_base = make_float4(qb[0], qb[1], qb[2], 0.f);
-                k_quant_nodes<<<blocks_for(nb - 1, 256), 256>>>(nb - 1, range.p, ds->nodes, v.q_base, v.q_scale, qn);
-                ++launches;
-                v.qnodes = qn;
-            }
-#endif
         }
         ds->accel = PT_ACCEL_LBVH;
         CK(cudaDeviceSynchronize());  // scratch buffers are freed on scope exit
@@ -599,26 +533,7 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
                 for (int b = 0; b < rp.max_depth; ++b) {
                     if (!sc.brute && sc.root != kRefEmpty) {
                         if ((rc = tick(1))) return rc;
-#if PT_L2_PERSIST
-                        {
-                            cudaLaunchConfig_t lc{};
-                            lc.gridDim = dim3(ds->traverse_blocks);
-                            lc.blockDim = dim3(128);
-                            lc.stream = st;
-                            cudaLaunchAttribute at[1];
-                            at[0].id = cudaLaunchAttributeAccessPolicyWindow;
-                            at[0].val.accessPolicyWindow.base_ptr = ds->l2_base;
-                            at[0].val.accessPolicyWindow.num_bytes = ds->l2_bytes;
-                            at[0].val.accessPolicyWindow.hitRatio = 1.0f;
-                            at[0].val.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
-                            at[0].val.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
-                            lc.attrs = at;
-                            lc.numAttrs = ds->l2_bytes ? 1 : 0;
-                            CK(cudaLaunchKernelEx(&lc, k_wf_traverse<COUNT>, sc, wf, b & 1, rp.eps, rp.stats));
-                        }
-#else
                         k_wf_traverse<COUNT><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
-#endif
                         if ((rc = tock())) return rc;
                         ++n;
                     }

@@ -264,69 +264,6 @@ __global__ void k_emit_nodes(int n, const int2 *__restrict__ children, const int
     o[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
 }
 
-#if PT_TOP_NODES
-// Breadth-first table of the first kTopNodes inner nodes below the root (node 0) for the shared-memory variant of
-// k_wf_traverse: row layout of `nodes`, child refs that point to a node inside the table become kTopBit | index.
-// One thread: a few hundred dependent 64-byte reads, once per scene.
-__global__ void k_top_tree(const float4 *__restrict__ nodes, float4 *__restrict__ top, int *__restrict__ n_top) {
-    int gq[kTopNodes];  // node index of table entry i
-    int n = 1;
-    gq[0] = 0;
-    for (int i = 0; i < n; ++i) {
-        const float4 *nd = nodes + 4 * (size_t)gq[i];
-        const float4 r0 = nd[0], r1 = nd[1], r2 = nd[2], r3 = nd[3];
-        int c[2] = {__float_as_int(r3.x), __float_as_int(r3.y)};
-#pragma unroll
-        for (int k = 0; k < 2; ++k)
-            if (c[k] >= 0 && c[k] != kRefEmpty && n < kTopNodes) {
-                gq[n] = c[k];
-                c[k] = kTopBit | n;
-                ++n;
-            }
-        top[4 * i] = r0;
-        top[4 * i + 1] = r1;
-        top[4 * i + 2] = r2;
-        top[4 * i + 3] = make_float4(__int_as_float(c[0]), __int_as_float(c[1]), 0.0f, 0.0f);
-    }
-    *n_top = n;
-}
-#endif
-
-#if PT_QNODES
-// grid coordinate whose decoded value is <= x (q_lo) / >= x (q_hi), with one cell of slack where the grid allows it
-__device__ __forceinline__ unsigned q_lo(float x, float s, float base) {
-    int q = (int)fminf(fmaxf(floorf((x - base) / s) - 1.0f, 0.0f), 65535.0f);
-    while (q > 0 && q_decode((unsigned)q, s, base) > x) --q;
-    return (unsigned)q;
-}
-__device__ __forceinline__ unsigned q_hi(float x, float s, float base) {
-    int q = (int)fminf(fmaxf(ceilf((x - base) / s) + 1.0f, 0.0f), 65535.0f);
-    while (q < 65535 && q_decode((unsigned)q, s, base) < x) ++q;
-    return (unsigned)q;
-}
-// 32-byte copy of every emitted node (layout: pt_scene.cuh)
-__global__ void k_quant_nodes(int n_nodes, const int2 *__restrict__ range, const float4 *__restrict__ nodes, float4 qb,
-                              float4 qs, uint4 *__restrict__ qnodes) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_nodes) return;
-    const int2 r = range[i];
-    if (r.y - r.x + 1 <= kLeafMax) return;  // swallowed by a leaf above: never emitted, never referenced
-    const float4 *nd = nodes + 4 * (size_t)i;
-    const float4 n0 = nd[0], n1 = nd[1], n2 = nd[2], n3 = nd[3];
-    uint4 a, b;
-    a.x = q_lo(n0.x, qs.x, qb.x) | (q_hi(n0.y, qs.x, qb.x) << 16);
-    a.y = q_lo(n0.z, qs.y, qb.y) | (q_hi(n0.w, qs.y, qb.y) << 16);
-    a.z = q_lo(n2.x, qs.z, qb.z) | (q_hi(n2.y, qs.z, qb.z) << 16);
-    a.w = q_lo(n1.x, qs.x, qb.x) | (q_hi(n1.y, qs.x, qb.x) << 16);
-    b.x = q_lo(n1.z, qs.y, qb.y) | (q_hi(n1.w, qs.y, qb.y) << 16);
-    b.y = q_lo(n2.z, qs.z, qb.z) | (q_hi(n2.w, qs.z, qb.z) << 16);
-    b.z = (unsigned)__float_as_int(n3.x);
-    b.w = (unsigned)__float_as_int(n3.y);
-    qnodes[2 * (size_t)i] = a;
-    qnodes[2 * (size_t)i + 1] = b;
-}
-#endif
-
 // triangle records in sorted order (vals == nullptr: caller order)
 __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__restrict__ planes,
                             const float *__restrict__ squares, const int *__restrict__ mat_ids,

@@ -34,29 +34,6 @@ constexpr int kLargeRowsMax = 4 * kMaxLarge + kSingleRows * kMaxLarge;  // worst
 constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
 constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
-// Compile-time variant (tools/ab_variants.sh, -DPT_TOP_NODES=K; 0 = off, the default build): the first K nodes of the
-// LBVH in breadth-first order are copied behind the node array with their child refs renumbered (k_top_tree), and
-// every block of k_wf_traverse stages that table in shared memory.  A ref with kTopBit set is an index into the table
-// (node indices stay below 2^28, so the bit is free; such a ref is positive and != kRefEmpty).
-#ifndef PT_TOP_NODES
-#define PT_TOP_NODES 0
-#endif
-constexpr int kTopNodes = PT_TOP_NODES;
-constexpr int kTopBit = 0x40000000;
-// Compile-time variant -DPT_QNODES=1 (0 = off, the default build): k_wf_traverse walks a 32-byte copy of the nodes —
-// both child boxes as 16-bit grid coordinates of the LBVH root box, rounded outwards (k_quant_nodes), then the two
-// child refs — fetched with ONE 256-bit load per visit instead of two.  The decoded box contains the fp32 box bit for
-// bit (the builder checks it with the very function the walk decodes with), so the walk stays conservative.
-//   row 0 (uint4): child0 x, y, z, child1 x       row 1 (uint4): child1 y, z, ref0, ref1      (lo | hi << 16 each)
-#ifndef PT_QNODES
-#define PT_QNODES 0
-#endif
-#if PT_QNODES
-__device__ __forceinline__ float q_decode(unsigned q, float s, float base) {
-    // 0x4B000000 | q is the float 2^23 + q (q < 2^16): exact int -> float without I2F
-    return __fmaf_rn(__uint_as_float(0x4B000000u | q) - 8388608.0f, s, base);
-}
-#endif
 
 // lobe kinds built by Factory (material.h:58-106)
 // MAT_MULTI (extension): a material with the refractive lobe; its lobe set is the mask in row 2 (1 mirror, 2 diffuse, 4 refract)
@@ -89,14 +66,6 @@ struct SceneView {
     const unsigned char *sky;  // equirect skybox, 24-bit BGR rows top-down (bitmap_image's layout); nullptr = none
     int sky_w, sky_h;
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
-#if PT_QNODES
-    const uint4 *qnodes;     // 2 x uint4 per node (layout above); nullptr when the tree has no inner node
-    float4 q_base, q_scale;  // grid origin and cell size per axis
-#endif
-#if PT_TOP_NODES
-    const float4 *top;  // breadth-first table of the first n_top nodes (node layout, child refs renumbered)
-    int n_top;          // 0: no table (tree is one leaf or empty)
-#endif
 };
 
 }  // namespace ptd

@@ -20,20 +20,13 @@
 
 namespace ptd {
 
-#ifndef PT_LAZY_IDX
-#define PT_LAZY_IDX 1
-#endif
-#ifndef PT_SLAB_FMA
-#define PT_SLAB_FMA 0
-#endif
-#ifndef PT_LEAF_RCP
-#define PT_LEAF_RCP 1
-#endif
-constexpr int kIdxLazy = (int)0x80000000;  // Hit::idx not fetched yet (PT_LAZY_IDX); caller indices are >= 0
+// Hit::idx value "not fetched yet": k_wf_traverse takes a ray over with the record of its best hit so far and reads that
+// record's caller index only if a candidate ties with it (one dependent fetch less per ray); caller indices are >= 0
+constexpr int kIdxLazy = (int)0x80000000;
 
 struct Hit {
     float t;   // best distance so far (+inf = none)
-    int idx;   // caller's triangle index of the best hit (-1 = none)
+    int idx;   // caller's triangle index of the best hit (-1 = none, kIdxLazy = look it up in record `rec`)
     int rec;   // record index of the best hit in SceneView::tris
 };
 
@@ -74,62 +67,20 @@ __device__ __forceinline__ void ldg256(const float4 *p, float4 &a, float4 &b) {
                  : "l"(p));
 }
 
-// Compile-time variants of the cache policy (tools/ab_variants.sh; 0 = the default build): PT_TRI_NOALLOC fetches
-// triangle records without allocating them in L1 (a record is rarely read twice; the nodes are), PT_NODE_EVICT_LAST
-// marks inner nodes evict-last in L1.
-#ifndef PT_TRI_NOALLOC
-#define PT_TRI_NOALLOC 0
-#endif
-#ifndef PT_NODE_EVICT_LAST
-#define PT_NODE_EVICT_LAST 0
-#endif
-__device__ __forceinline__ void ldg256_tri(const float4 *p, float4 &a, float4 &b) {
-#if PT_TRI_NOALLOC
-    asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-                 : "l"(p));
-#else
-    ldg256(p, a, b);
-#endif
-}
-__device__ __forceinline__ float4 ldg128_tri(const float4 *p) {
-#if PT_TRI_NOALLOC
-    float4 a;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
-                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(p));
-    return a;
-#else
-    return __ldg(p);
-#endif
-}
-__device__ __forceinline__ void ldg256_node(const float4 *p, float4 &a, float4 &b) {
-#if PT_NODE_EVICT_LAST
-    asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
-                 : "l"(p));
-#else
-    ldg256(p, a, b);
-#endif
-}
-
 // Triangle::Intersect (triangles.h:48-73) on record `rec` (4 float4 at r).  Differences from the reference, both
 // outside its defined behaviour: a NaN distance (0/0: ray in the plane) is rejected instead of accepted, and equal
 // distances go to the lower caller index explicitly.
 __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o, V3 d, float eps, Hit &h) {
     float4 pl, a, b, c;
-    ldg256_tri(r, pl, a);
-    ldg256_tri(r + 2, b, c);
+    ldg256(r, pl, a);
+    ldg256(r + 2, b, c);
     const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
     const int idx = __float_as_int(b.w);
-#if PT_LAZY_IDX
-    if (nd == h.t) {  // a tie: now the caller index of the best hit so far is needed (k_wf_traverse left it unfetched)
+    if (nd == h.t) {  // a tie goes to the lower caller index; also rejects nd == +inf against the initial (inf, -1)
         if (h.idx == kIdxLazy) h.idx = __float_as_int(__ldg(r - 4 * (ptrdiff_t)rec + 4 * (ptrdiff_t)h.rec + 2).w);
         if (!(idx < h.idx)) return;
     }
-#else
-    if (nd == h.t && !(idx < h.idx)) return;  // also rejects nd == +inf against the initial (inf, -1)
-#endif
     if (!inside_test(a, b, c, o, d, nd, eps)) return;
     h.t = nd;
     h.idx = idx;
@@ -314,11 +265,12 @@ __device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3
     float4 pl[kLeafMax];
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k)
-        pl[k] = k < cnt ? ldg128_tri(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-#if PT_LEAF_RCP
-    // Compile-time variant: the plane pass with an approximate reciprocal (MUFU.RCP, within 2^-21 of the IEEE quotient
-    // for the reference's own numerator and denominator) and a range widened by 2e-6 relative, as in scan_singles;
-    // conservative — the exact test below repeats the IEEE division for the triangles it marks.  A NaN marks.
+        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    // The plane pass with an approximate reciprocal instead of up to kLeafMax IEEE divisions: numerator and denominator
+    // are the reference's own, MUFU.RCP is within 2^-21 of the IEEE quotient and the range is widened by 2e-6 relative
+    // (as in scan_singles), so every triangle the exact test can accept is marked; the exact test repeats the division
+    // for the marked ones.  A NaN marks.  (-3.7 % traversal time on the 1M-triangle scene: the leaf phase, with its
+    // divisions, square roots and few active lanes, is where the walk is short of issue slots.)
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
 #pragma unroll
     for (int k = 0; k < kLeafMax; ++k) {
@@ -328,13 +280,6 @@ __device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3
         const float t = num * rcp_approx(sd);
         mask |= (unsigned)(k < cnt && !((t > t_hi) | (t < t_lo))) << k;
     }
-#else
-#pragma unroll
-    for (int k = 0; k < kLeafMax; ++k) {
-        const float nd = plane_distance(pl[k], o, d);
-        mask |= (unsigned)(k < cnt && nd <= h.t && !(nd < eps)) << k;
-    }
-#endif
     while (mask) {
         const int k = __ffs(mask) - 1;
         mask &= mask - 1u;
@@ -350,8 +295,8 @@ __device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 
     {
         const float4 *nd = sc.nodes + 4 * (size_t)cur;
         float4 n0, n1, n2, n3;
-        ldg256_node(nd, n0, n1);
-        ldg256_node(nd + 2, n2, n3);
+        ldg256(nd, n0, n1);
+        ldg256(nd + 2, n2, n3);
         if (COUNT) ++n_nodes;
         // box_entry clips against h.t with <=, so that an equal-distance lower index is still found; +inf = miss
         const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
@@ -368,106 +313,6 @@ __device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 
         return sp ? stack[--sp] : kRefEmpty;
     }
 }
-
-#if PT_TOP_NODES
-// node_step of the shared-memory variant: a ref with kTopBit reads its node from the block's copy of the top table
-// (four LDS.128, no L1 tag lookup), any other node ref from global memory as above.
-template <bool COUNT>
-__device__ __forceinline__ int node_step_top(const SceneView &sc, const float4 *s_top, int cur, V3 o, V3 inv,
-                                             const Hit &h, int *stack, int &sp, unsigned long long &n_nodes) {
-    float4 n0, n1, n2, n3;
-    if (cur & kTopBit) {
-        const float4 *nd = s_top + 4 * (cur & ~kTopBit);
-        n0 = nd[0]; n1 = nd[1]; n2 = nd[2]; n3 = nd[3];
-    } else {
-        const float4 *nd = sc.nodes + 4 * (size_t)cur;
-        ldg256_node(nd, n0, n1);
-        ldg256_node(nd + 2, n2, n3);
-    }
-    if (COUNT) ++n_nodes;
-    const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
-    const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
-    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
-    if (g0 && g1) {
-        const bool swap = t1 < t0;
-        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
-        return swap ? c1 : c0;
-    }
-    if (g0) return c0;
-    if (g1) return c1;
-    return sp ? stack[--sp] : kRefEmpty;
-}
-#endif
-
-#if PT_QNODES
-// node_step on the 32-byte quantised copy of the nodes (pt_scene.cuh): one 256-bit load, twelve decodes
-template <bool COUNT>
-__device__ __forceinline__ int node_step_q(const SceneView &sc, int cur, V3 o, V3 inv, const Hit &h, int *stack, int &sp,
-                                           unsigned long long &n_nodes) {
-    uint4 a, b;
-    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-                 : "=r"(a.x), "=r"(a.y), "=r"(a.z), "=r"(a.w), "=r"(b.x), "=r"(b.y), "=r"(b.z), "=r"(b.w)
-                 : "l"(sc.qnodes + 2 * (size_t)cur));
-    if (COUNT) ++n_nodes;
-    const float sx = sc.q_scale.x, sy = sc.q_scale.y, sz = sc.q_scale.z;
-    const float bx = sc.q_base.x, by = sc.q_base.y, bz = sc.q_base.z;
-    const float t0 = box_entry(q_decode(a.x & 0xffffu, sx, bx), q_decode(a.x >> 16, sx, bx),
-                               q_decode(a.y & 0xffffu, sy, by), q_decode(a.y >> 16, sy, by),
-                               q_decode(a.z & 0xffffu, sz, bz), q_decode(a.z >> 16, sz, bz), o, inv, h.t);
-    const float t1 = box_entry(q_decode(a.w & 0xffffu, sx, bx), q_decode(a.w >> 16, sx, bx),
-                               q_decode(b.x & 0xffffu, sy, by), q_decode(b.x >> 16, sy, by),
-                               q_decode(b.y & 0xffffu, sz, bz), q_decode(b.y >> 16, sz, bz), o, inv, h.t);
-    const int c0 = (int)b.z, c1 = (int)b.w;
-    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
-    if (g0 && g1) {
-        const bool swap = t1 < t0;
-        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
-        return swap ? c1 : c0;
-    }
-    if (g0) return c0;
-    if (g1) return c1;
-    return sp ? stack[--sp] : kRefEmpty;
-}
-#endif
-
-#if PT_SLAB_FMA
-// Compile-time variant -DPT_SLAB_FMA=1: the slab distances as one FMA each, lo * inv + noi with noi = -(o * inv)
-// computed once per ray, instead of (lo - o) * inv: 12 instructions fewer per node visit.  In position terms the result
-// differs from the subtract-multiply form by about one ulp of the origin's coordinate (the rounding of o * inv),
-// inside the 32 ulp the leaf boxes are padded with (pt_bvh.cuh k_tri_boxes_keys).  inf - inf (inv = inf, or o * inv
-// overflowing) is NaN and drops the axis, as 0 * inf does in box_entry.
-__device__ __forceinline__ float box_entry_fma(float lox, float hix, float loy, float hiy, float loz, float hiz, V3 noi,
-                                               V3 inv, float tmax) {
-    const float x0 = __fmaf_rn(lox, inv.x, noi.x), x1 = __fmaf_rn(hix, inv.x, noi.x);
-    const float y0 = __fmaf_rn(loy, inv.y, noi.y), y1 = __fmaf_rn(hiy, inv.y, noi.y);
-    const float z0 = __fmaf_rn(loz, inv.z, noi.z), z1 = __fmaf_rn(hiz, inv.z, noi.z);
-    const float tn = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), 0.0f));
-    const float tf = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), tmax));
-    return tn <= tf * 1.0000003f ? tn : __int_as_float(0x7f800000);
-}
-template <bool COUNT>
-__device__ __forceinline__ int node_step_fma(const SceneView &sc, int cur, V3 noi, V3 inv, const Hit &h, int *stack,
-                                             int &sp, unsigned long long &n_nodes) {
-    const float4 *nd = sc.nodes + 4 * (size_t)cur;
-    float4 n0, n1, n2, n3;
-    ldg256(nd, n0, n1);
-    ldg256(nd + 2, n2, n3);
-    if (COUNT) ++n_nodes;
-    const float t0 = box_entry_fma(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, noi, inv, h.t);
-    const float t1 = box_entry_fma(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, noi, inv, h.t);
-    const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-    const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
-    if (g0 && g1) {
-        const bool swap = t1 < t0;
-        if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
-        return swap ? c1 : c0;
-    }
-    if (g0) return c0;
-    if (g1) return c1;
-    return sp ? stack[--sp] : kRefEmpty;
-}
-#endif
 
 // One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
 template <bool COUNT>

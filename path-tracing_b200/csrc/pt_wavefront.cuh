@@ -290,20 +290,10 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
 #ifndef PT_TRAV_MIN_BLOCKS
 #define PT_TRAV_MIN_BLOCKS 10  // resident blocks of 128 threads per SM the traversal kernel is compiled for
 #endif
-constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
-// Compile-time variants of the ray refill (tools/ab_variants.sh; the defaults give the build as measured so far).  A
-// refill is a chain of dependent round trips — atomicAdd on the queue head, the queue entry, the ray's state, the
-// caller index of its best hit so far — that the whole warp waits for, and with 32 rays of ~34 steps each some lane
-// finishes in almost every iteration:
-//   PT_REFILL_MIN   refill only when at least this many lanes are idle (or no lane has work left): fewer chains
-//   PT_TRAV_CHUNK   a warp reserves this many queue entries per atomicAdd and hands them out from registers
-//   PT_LAZY_IDX     the caller index of the best hit is fetched only when a candidate ties with it (pt_trace.cuh)
 #ifndef PT_REFILL_MIN
-#define PT_REFILL_MIN 4
+#define PT_REFILL_MIN 4       // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
 #endif
-#ifndef PT_TRAV_CHUNK
-#define PT_TRAV_CHUNK 0
-#endif
+constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
 
 // persistent warps over queue `set`: one ray per lane, refilled as lanes finish.
 // while-while with a postponed leaf (Aila & Laine 2009, "speculative traversal"): a lane that reaches a leaf parks
@@ -316,24 +306,13 @@ __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
     const int count = wf.counters[2 * set];
     if (count == 0) return;
-#if PT_TOP_NODES
-    __shared__ float4 s_top[4 * kTopNodes];  // (count is the same for every thread: no one left before the barrier)
-    for (int k = threadIdx.x; k < 4 * sc.n_top; k += blockDim.x) s_top[k] = sc.top[k];
-    __syncthreads();
-#endif
     int *head = &wf.counters[2 * set + 1];
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
     int stack[kStackDepth];
     int sp = 0, cur = kRefEmpty, leaf = 0, slot = -1;  // leaf refs are negative: 0 = no parked leaf
-#if PT_TRAV_CHUNK
-    int chunk_next = 0, chunk_end = 0;
-#endif
     bool done = false;
     V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 1);
-#if PT_SLAB_FMA
-    V3 noi = mk(0, 0, 0);
-#endif
     Hit h = no_hit();
     unsigned long long n_nodes = 0, n_tris = 0, ray_nodes0 = 0;
     while (true) {
@@ -349,28 +328,12 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         }
         const unsigned m = __ballot_sync(0xffffffffu, need);
 #if PT_REFILL_MIN > 1
+        // a refill is a chain of dependent fetches (queue head, queue entry, ray state) the whole warp sits through
         const unsigned busy = __ballot_sync(0xffffffffu, !need && !done);
         if (m && (__popc(m) >= PT_REFILL_MIN || busy == 0u)) {
 #else
         if (m) {
 #endif
-#if PT_TRAV_CHUNK
-            // entries [chunk_next, chunk_end) are this warp's; a new chunk is reserved when they do not cover the request
-            const int want = __popc(m), avail = chunk_end - chunk_next, rank = __popc(m & ((1u << lane) - 1u));
-            int qi = chunk_next + rank;
-            if (want > avail) {
-                int base = 0;
-                if (lane == 0) base = atomicAdd(head, PT_TRAV_CHUNK);
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (rank >= avail) qi = base + (rank - avail);
-                chunk_next = base + (want - avail);
-                chunk_end = base + PT_TRAV_CHUNK;
-            } else {
-                chunk_next += want;
-            }
-            if (need) {
-                if (qi < count) {
-#else
             const int leader = __ffs(m) - 1;
             int base = 0;
             if (lane == leader) base = atomicAdd(head, __popc(m));
@@ -378,27 +341,15 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             if (need) {
                 const int qi = base + __popc(m & ((1u << lane) - 1u));
                 if (qi < count) {
-#endif
                     slot = __ldcs(&queue[qi]);
                     const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
                     o = mk(ot.x, ot.y, ot.z);
                     d = mk(dr.x, dr.y, dr.z);
                     inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-#if PT_SLAB_FMA
-                    noi = mk(-(o.x * inv.x), -(o.y * inv.y), -(o.z * inv.z));
-#endif
                     h.t = ot.w;
                     h.rec = __float_as_int(dr.w);
-#if PT_LAZY_IDX
                     h.idx = h.rec >= 0 ? kIdxLazy : -1;
-#else
-                    h.idx = h.rec >= 0 ? __float_as_int(__ldg(sc.tris + 4 * (size_t)h.rec + 2).w) : -1;
-#endif
-#if PT_TOP_NODES
-                    cur = sc.n_top > 0 ? kTopBit : sc.root;  // table entry 0 is the root node
-#else
                     cur = sc.root;
-#endif
                     sp = 0;
                     ray_nodes0 = n_nodes;
                 } else {
@@ -417,15 +368,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             const bool can = cur >= 0 && cur != kRefEmpty;
             const unsigned cm = __ballot_sync(0xffffffffu, can);
             if (cm == 0u || (it > 0 && __popc(cm) < kMinNodeLanes)) break;
-#if PT_TOP_NODES
-            if (can) cur = node_step_top<COUNT>(sc, s_top, cur, o, inv, h, stack, sp, n_nodes);
-#elif PT_QNODES
-            if (can) cur = node_step_q<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
-#elif PT_SLAB_FMA
-            if (can) cur = node_step_fma<COUNT>(sc, cur, noi, inv, h, stack, sp, n_nodes);
-#else
             if (can) cur = node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
-#endif
         }
         if (cur < 0 && leaf == 0) {
             leaf = cur;
