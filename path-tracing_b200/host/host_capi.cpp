@@ -30,6 +30,7 @@ PTH_API int pth_load_obj(const char *model_path, const char *model_name) {
 // -CACHE <dir> ("" = off); pth_loaded_from_cache: did the last pth_load_obj take the binary image?
 PTH_API void pth_set_cache_dir(const char *dir) { Config::get().cache = dir ? dir : ""; }
 PTH_API int pth_loaded_from_cache(void) { return g_scene && g_scene->loaded_from_cache; }
+PTH_API int pth_parsed_in_pieces(void) { return g_scene ? g_scene->parsed_in_pieces : 0; }
 PTH_API int pth_material_count(void) { return g_scene ? g_view.n_materials : 0; }
 PTH_API void pth_copy_scene(float *vertices9, float *planes4, float *squares, int32_t *mat_ids, float *mats10) {
     const size_t n = g_view.n_triangles, m = g_view.n_materials;

@@ -7,13 +7,20 @@
 // material by its ordinal.  An unopenable OBJ is fatal (exit(1)), as scene.cpp:32-35.
 #include "scene.h"
 
+#include <fcntl.h>
 #include <sys/stat.h>
+#include <unistd.h>
 
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <fstream>
+#include <algorithm>
+#include <chrono>
 #include <iostream>
+#include <memory>
+#include <thread>
+#include <utility>
 
 using ptm::vec3;
 using ptm::vec4;
@@ -78,21 +85,16 @@ namespace {
 // no locale, sentry and stream-state work per token: a 1 M-triangle OBJ (40 MB) loads in a fraction of a second
 // instead of the seconds the stream extraction takes.
 class TokenStream {
-    std::string buf_;
-    const char *p_, *end_;
+    const char *p_, *end_;  // the buffer is followed by one ' ': strtof / strtol stop there
 
 public:
-    explicit TokenStream(std::ifstream &in) {
-        in.seekg(0, std::ios::end);
-        const std::streamoff n = in.tellg();
-        in.seekg(0, std::ios::beg);
-        buf_.resize(n > 0 ? static_cast<size_t>(n) : 0);
-        if (n > 0) in.read(&buf_[0], n);
-        buf_.push_back(' ');  // strtof / strtol stop here
-        p_ = buf_.data();
-        end_ = p_ + buf_.size() - 1;
-    }
+    TokenStream(const char *begin, const char *end) : p_(begin), end_(end) {}
     static bool space(char c) { return c == ' ' || c == '\n' || c == '\t' || c == '\r' || c == '\v' || c == '\f'; }
+    // start of the next token (end of the buffer if there is none)
+    const char *peek() {
+        while (p_ < end_ && space(*p_)) ++p_;
+        return p_;
+    }
     // next token as [b, e); false at end of file
     bool next(const char *&b, const char *&e) {
         while (p_ < end_ && space(*p_)) ++p_;
@@ -123,6 +125,41 @@ public:
         return static_cast<int>(v);
     }
 };
+// The whole file followed by one ' ' (strtof / strtol stop there), read with pread by a few threads into memory that
+// is not zero-filled first (a 135 MB model: 35 ms instead of 220 ms through ifstream into a resized string).
+struct FileText {
+    std::unique_ptr<char[]> data;
+    size_t size = 0;  // without the trailing ' '
+    bool ok = false;
+};
+FileText slurp(const std::string &path) {
+    FileText t;
+    const int fd = ::open(path.c_str(), O_RDONLY);
+    if (fd < 0) return t;
+    struct stat st;
+    if (::fstat(fd, &st) != 0 || st.st_size < 0) { ::close(fd); return t; }
+    t.size = static_cast<size_t>(st.st_size);
+    t.data.reset(new char[t.size + 1]);
+    const size_t parts = t.size >= (size_t{8} << 20) ? std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 8) : 1;
+    std::vector<char> good(parts, 1);
+    auto read_part = [&](size_t i) {
+        size_t off = t.size / parts * i;
+        const size_t stop = i + 1 == parts ? t.size : t.size / parts * (i + 1);
+        while (off < stop) {
+            const ssize_t n = ::pread(fd, t.data.get() + off, stop - off, static_cast<off_t>(off));
+            if (n <= 0) { good[i] = 0; return; }
+            off += static_cast<size_t>(n);
+        }
+    };
+    std::vector<std::thread> th;
+    for (size_t i = 1; i < parts; ++i) th.emplace_back(read_part, i);
+    read_part(0);
+    for (std::thread &x : th) x.join();
+    ::close(fd);
+    t.data[t.size] = ' ';
+    t.ok = std::all_of(good.begin(), good.end(), [](char g) { return g != 0; });
+    return t;
+}
 inline bool is_tok(const char *b, const char *e, const char *lit) {
     const size_t n = std::strlen(lit);
     return static_cast<size_t>(e - b) == n && std::memcmp(b, lit, n) == 0;
@@ -228,6 +265,174 @@ bool Scene::LoadCache(const std::string &cache_file, const std::string &obj_path
     return true;
 }
 
+// ---- parallel parse ----------------------------------------------------------------------------
+// The reference's loader is a state machine over whitespace-separated tokens: a keyword token, then its arguments,
+// wherever the line breaks are; every other token is skipped.  A large file is cut after line breaks into one piece
+// per thread, and every piece is parsed from its first token as if a statement began there, running past its end to
+// finish a statement it has started.  That guess is checked, not trusted: the pieces are consistent when each one
+// stopped exactly at the token the next one started from; then the sequential machine would have gone through the
+// same states.  Vertex and normal indices are resolved after a prefix sum over the pieces, with the bound the
+// sequential loader's `positions.at()` would have applied at that point of the file (no forward references).
+// Anything else — an inconsistent cut, an index out of range, a face cut short by the end of the file — falls back to
+// the sequential loop, which then behaves (and throws) exactly as before.
+namespace {
+struct FaceRec {
+    int idx[3][3];
+    uint32_t npos, nnrm;  // vertices / normals of THIS piece defined before the face
+};
+struct Piece {
+    const char *begin = nullptr, *limit = nullptr;     // statements starting in [begin, limit) are this piece's
+    const char *first_tok = nullptr, *end_tok = nullptr;
+    std::vector<vec4> positions;
+    std::vector<vec3> normals;
+    std::vector<FaceRec> faces;
+    std::vector<std::pair<size_t, int>> usemtl;         // (faces before the statement, ordinal)
+    std::vector<std::string> mtllibs;
+    std::vector<Triangle> triangles;
+    bool truncated = false;                             // the file ended inside a statement
+};
+
+void parse_piece(Piece &pc, const char *file_end) {
+    // room for the densest files (short `v` / `f` lines) up front: untouched pages cost nothing, regrowth does
+    const size_t bytes = static_cast<size_t>(pc.limit - pc.begin);
+    pc.positions.reserve(bytes / 12);
+    pc.faces.reserve(bytes / 10);
+    TokenStream ts(pc.begin, file_end);
+    pc.first_tok = ts.peek();
+    const char *b, *e;
+    while (ts.peek() < pc.limit && ts.next(b, e)) {
+        if (is_tok(b, e, "mtllib")) {
+            if (!ts.next(b, e)) { pc.truncated = true; break; }
+            pc.mtllibs.emplace_back(b, e);
+        } else if (is_tok(b, e, "v")) {
+            vec4 p(1);
+            p.x = ts.next_float(); p.y = ts.next_float(); p.z = ts.next_float();
+            pc.positions.push_back(p);
+        } else if (is_tok(b, e, "vt")) {
+            ts.next_float(); ts.next_float();
+        } else if (is_tok(b, e, "vn")) {
+            vec3 n;
+            n.x = ts.next_float(); n.y = ts.next_float(); n.z = ts.next_float();
+            pc.normals.push_back(n);
+        } else if (is_tok(b, e, "f")) {
+            FaceRec f;
+            for (int i = 0; i < 3; ++i) {
+                if (!ts.next(b, e)) { pc.truncated = true; b = e = ""; }
+                corner(b, e, f.idx[i]);
+            }
+            f.npos = static_cast<uint32_t>(pc.positions.size());
+            f.nnrm = static_cast<uint32_t>(pc.normals.size());
+            pc.faces.push_back(f);
+        } else if (is_tok(b, e, "usemtl")) {
+            pc.usemtl.emplace_back(pc.faces.size(), ts.next_int());
+        }
+    }
+    pc.end_tok = ts.peek();
+}
+
+struct Lap {  // PT_PROFILE=1: where LoadModel spends its time, on stderr
+    bool on = std::getenv("PT_PROFILE") != nullptr;
+    std::chrono::steady_clock::time_point t = std::chrono::steady_clock::now();
+    void operator()(const char *what) {
+        if (!on) return;
+        const auto n = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[LoadModel] %-18s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(n - t).count());
+        t = n;
+    }
+};
+
+template <class F> void run_threads(size_t n, F f) {
+    std::vector<std::thread> th;
+    for (size_t i = 1; i < n; ++i) th.emplace_back([&f, i] { f(i); });
+    f(0);
+    for (std::thread &t : th) t.join();
+}
+}  // namespace
+
+bool Scene::LoadModelParallel(const char *text, size_t size) {
+    // tuning knobs for the tests: PT_LOADER_THREADS (0 / 1 = sequential), PT_LOADER_MIN_BYTES (smallest file cut up)
+    const char *env_t = std::getenv("PT_LOADER_THREADS"), *env_b = std::getenv("PT_LOADER_MIN_BYTES");
+    size_t threads = env_t ? static_cast<size_t>(std::atol(env_t)) : std::min<size_t>(std::thread::hardware_concurrency(), 32);
+    const size_t min_bytes = env_b ? static_cast<size_t>(std::atol(env_b)) : (size_t{4} << 20);
+    if (threads < 2 || size < min_bytes || size < 2 * threads) return false;
+    const char *base = text, *end = base + size;
+    std::vector<Piece> pieces(threads);
+    const char *cut = base;
+    for (size_t i = 0; i < threads; ++i) {
+        pieces[i].begin = cut;
+        const char *want = base + size / threads * (i + 1);
+        if (i + 1 == threads || want >= end) {
+            cut = end;
+        } else {
+            if (want < cut) want = cut;
+            const void *nl = std::memchr(want, '\n', static_cast<size_t>(end - want));
+            cut = nl ? static_cast<const char *>(nl) + 1 : end;
+        }
+        pieces[i].limit = cut;
+    }
+    Lap lap;
+    run_threads(threads, [&](size_t i) { parse_piece(pieces[i], end); });
+    lap("parse pieces");
+    // the guess behind the cuts: every piece stopped at the token the next one started from
+    for (size_t i = 0; i < threads; ++i) {
+        if (pieces[i].truncated) return false;
+        if (i + 1 < threads && pieces[i].end_tok != pieces[i + 1].first_tok) return false;
+    }
+    // prefix sums, then the bounds `positions.at()` / `normals.at()` would have checked at that point of the file
+    std::vector<size_t> pos0(threads + 1, 0), nrm0(threads + 1, 0), tri0(threads + 1, 0);
+    for (size_t i = 0; i < threads; ++i) {
+        pos0[i + 1] = pos0[i] + pieces[i].positions.size();
+        nrm0[i + 1] = nrm0[i] + pieces[i].normals.size();
+        tri0[i + 1] = tri0[i] + pieces[i].faces.size();
+    }
+    std::vector<char> bad(threads, 0);
+    run_threads(threads, [&](size_t i) {
+        for (const FaceRec &f : pieces[i].faces) {
+            const long long np = static_cast<long long>(pos0[i] + f.npos), nn = static_cast<long long>(nrm0[i] + f.nnrm);
+            for (int k = 0; k < 3; ++k)
+                if (f.idx[k][0] < 0 || f.idx[k][0] >= np) bad[i] = 1;
+            if (f.idx[0][2] >= nn) bad[i] = 1;
+        }
+    });
+    for (char b : bad)
+        if (b) return false;
+    lap("check");
+    // from here on nothing can fail: materials in file order, then the triangles
+    for (const Piece &pc : pieces)
+        for (const std::string &name : pc.mtllibs) {
+            mtl_files_.push_back(Config::get().model_path + name);
+            read_mtl(mtl_files_.back(), *this);
+        }
+    lap("materials");
+    std::vector<vec4> positions(pos0[threads]);
+    std::vector<vec3> normals(nrm0[threads]);
+    std::vector<int> mat_in(threads + 1, 0);  // current_material at the start of each piece
+    for (size_t i = 0; i < threads; ++i) mat_in[i + 1] = pieces[i].usemtl.empty() ? mat_in[i] : pieces[i].usemtl.back().second;
+    run_threads(threads, [&](size_t i) {
+        std::copy(pieces[i].positions.begin(), pieces[i].positions.end(), positions.begin() + pos0[i]);
+        std::copy(pieces[i].normals.begin(), pieces[i].normals.end(), normals.begin() + nrm0[i]);
+    });
+    run_threads(threads, [&](size_t i) {
+        Piece &pc = pieces[i];
+        pc.triangles.reserve(pc.faces.size());
+        int material = mat_in[i];
+        size_t ev = 0;
+        for (size_t k = 0; k < pc.faces.size(); ++k) {
+            while (ev < pc.usemtl.size() && pc.usemtl[ev].first <= k) material = pc.usemtl[ev++].second;
+            const FaceRec &f = pc.faces[k];
+            Triangle t({positions[f.idx[0][0]], positions[f.idx[1][0]], positions[f.idx[2][0]]}, material);
+            if (f.idx[0][2] >= 0) t.SetNormal(normals[f.idx[0][2]]);
+            pc.triangles.push_back(t);
+        }
+    });
+    lap("triangles");
+    triangles_.reserve(triangles_.size() + tri0[threads]);
+    for (const Piece &pc : pieces) triangles_.insert(triangles_.end(), pc.triangles.begin(), pc.triangles.end());
+    lap("append");
+    parsed_in_pieces = static_cast<int>(threads);
+    return true;
+}
+
 void Scene::LoadModel(std::string path) {
     std::ifstream file(path, std::ios::binary);
     if (!file.is_open()) {
@@ -235,6 +440,7 @@ void Scene::LoadModel(std::string path) {
         std::exit(1);
     }
     loaded_from_cache = false;
+    parsed_in_pieces = 0;
     const std::string &cache_dir = Config::get().cache;
     const bool fresh = triangles_.empty() && materials_.empty();  // the image describes a whole scene, not an increment
     if (!cache_dir.empty() && fresh && LoadCache(cache_name(cache_dir, path), path)) {
@@ -242,37 +448,47 @@ void Scene::LoadModel(std::string path) {
         return;
     }
     mtl_files_.clear();
-    TokenStream ts(file);
-    std::vector<vec4> positions;
-    std::vector<vec3> normals;
-    int current_material = 0;
-    const char *b, *e;
-    while (ts.next(b, e)) {
-        if (is_tok(b, e, "mtllib")) {
-            if (!ts.next(b, e)) break;
-            mtl_files_.push_back(Config::get().model_path + std::string(b, e));
-            read_mtl(mtl_files_.back(), *this);
-        } else if (is_tok(b, e, "v")) {
-            vec4 p(1);
-            p.x = ts.next_float(); p.y = ts.next_float(); p.z = ts.next_float();
-            positions.push_back(p);
-        } else if (is_tok(b, e, "vt")) {
-            ts.next_float(); ts.next_float();
-        } else if (is_tok(b, e, "vn")) {
-            vec3 n;
-            n.x = ts.next_float(); n.y = ts.next_float(); n.z = ts.next_float();
-            normals.push_back(n);
-        } else if (is_tok(b, e, "f")) {
-            int idx[3][3];
-            for (int i = 0; i < 3; ++i) {
-                if (!ts.next(b, e)) { b = e = ""; }
-                corner(b, e, idx[i]);
+    Lap lap;
+    file.close();
+    const FileText text = slurp(path);
+    if (!text.ok) {
+        std::cerr << "Impossible to open the file !" << std::endl;
+        std::exit(1);
+    }
+    lap("read file");
+    if (!LoadModelParallel(text.data.get(), text.size)) {
+        TokenStream ts(text.data.get(), text.data.get() + text.size);
+        std::vector<vec4> positions;
+        std::vector<vec3> normals;
+        int current_material = 0;
+        const char *b, *e;
+        while (ts.next(b, e)) {
+            if (is_tok(b, e, "mtllib")) {
+                if (!ts.next(b, e)) break;
+                mtl_files_.push_back(Config::get().model_path + std::string(b, e));
+                read_mtl(mtl_files_.back(), *this);
+            } else if (is_tok(b, e, "v")) {
+                vec4 p(1);
+                p.x = ts.next_float(); p.y = ts.next_float(); p.z = ts.next_float();
+                positions.push_back(p);
+            } else if (is_tok(b, e, "vt")) {
+                ts.next_float(); ts.next_float();
+            } else if (is_tok(b, e, "vn")) {
+                vec3 n;
+                n.x = ts.next_float(); n.y = ts.next_float(); n.z = ts.next_float();
+                normals.push_back(n);
+            } else if (is_tok(b, e, "f")) {
+                int idx[3][3];
+                for (int i = 0; i < 3; ++i) {
+                    if (!ts.next(b, e)) { b = e = ""; }
+                    corner(b, e, idx[i]);
+                }
+                Triangle t({positions.at(idx[0][0]), positions.at(idx[1][0]), positions.at(idx[2][0])}, current_material);
+                if (idx[0][2] >= 0) t.SetNormal(normals.at(idx[0][2]));
+                triangles_.push_back(t);
+            } else if (is_tok(b, e, "usemtl")) {
+                current_material = ts.next_int();
             }
-            Triangle t({positions.at(idx[0][0]), positions.at(idx[1][0]), positions.at(idx[2][0])}, current_material);
-            if (idx[0][2] >= 0) t.SetNormal(normals.at(idx[0][2]));
-            triangles_.push_back(t);
-        } else if (is_tok(b, e, "usemtl")) {
-            current_material = ts.next_int();
         }
     }
     if (!cache_dir.empty() && fresh) SaveCache(cache_name(cache_dir, path), path);
@@ -283,15 +499,19 @@ PtScene Scene::abi() const {
     vertices_.resize(9 * n); planes_.resize(4 * n); squares_.resize(n); mat_ids_.resize(n); mats_.resize(10 * m);
     mats_ext_.resize(2 * m);
     bool any_refract = false;
-    for (size_t i = 0; i < n; ++i) {
-        const Triangle &t = triangles_[i];
-        for (int k = 0; k < 3; ++k)
-            for (int a = 0; a < 3; ++a) vertices_[9 * i + 3 * k + a] = t.GetVertices()[k][a];
-        const vec4 p = t.GetPlane();
-        planes_[4 * i] = p.x; planes_[4 * i + 1] = p.y; planes_[4 * i + 2] = p.z; planes_[4 * i + 3] = p.w;
-        squares_[i] = t.GetSquare();
-        mat_ids_[i] = t.GetMaterialId();
-    }
+    auto flatten = [&](size_t i0, size_t i1) {
+        for (size_t i = i0; i < i1; ++i) {
+            const Triangle &t = triangles_[i];
+            for (int k = 0; k < 3; ++k)
+                for (int a = 0; a < 3; ++a) vertices_[9 * i + 3 * k + a] = t.GetVertices()[k][a];
+            const vec4 p = t.GetPlane();
+            planes_[4 * i] = p.x; planes_[4 * i + 1] = p.y; planes_[4 * i + 2] = p.z; planes_[4 * i + 3] = p.w;
+            squares_[i] = t.GetSquare();
+            mat_ids_[i] = t.GetMaterialId();
+        }
+    };
+    const size_t parts = n >= 200000 ? std::min<size_t>(std::max(1u, std::thread::hardware_concurrency()), 16) : 1;
+    run_threads(parts, [&](size_t k) { flatten(n / parts * k, k + 1 == parts ? n : n / parts * (k + 1)); });
     for (size_t j = 0; j < m; ++j) {
         const MaterialCharacteristics &c = materials_[j].GetCharacteristics();
         const float row[10] = {c.Ke.x, c.Ke.y, c.Ke.z, c.Kd.x, c.Kd.y, c.Kd.z, c.Ks.x, c.Ks.y, c.Ks.z, c.Ns};

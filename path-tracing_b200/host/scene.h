@@ -31,9 +31,13 @@ class Scene {
     bool LoadCache(const std::string &cache_file, const std::string &obj_path);
     void SaveCache(const std::string &cache_file, const std::string &obj_path) const;
     std::vector<std::string> mtl_files_;  // the MTL files LoadModel read, for the cache's validity record
+    // the OBJ text (`size` bytes followed by one ' ') parsed by several threads; false = not attempted or the cuts did
+    // not line up with the statements, nothing changed: the caller parses sequentially (scene.cpp)
+    bool LoadModelParallel(const char *text, size_t size);
 
 public:
     bool loaded_from_cache = false;  // the last LoadModel took the binary image instead of parsing
+    int parsed_in_pieces = 0;        // threads the last LoadModel parsed the OBJ with (0 = the sequential loop)
     Scene(std::vector<std::vector<ptm::vec3>> &color_map, std::vector<std::vector<ptm::vec3>> &color2_map,
           std::vector<std::vector<int>> &samples_count);
     void LoadModel(std::string path);

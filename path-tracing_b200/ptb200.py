@@ -388,6 +388,7 @@ class HostLoader:
         sc["mats_ext"] = ext if self.lib.pth_has_refraction() else None
         sc["mats_ext_raw"] = ext
         sc["from_cache"] = bool(self.lib.pth_loaded_from_cache())
+        sc["parse_pieces"] = int(self.lib.pth_parsed_in_pieces())  # threads the OBJ was parsed with (0 = sequential)
         return sc
 
     def triangle_setup(self, verts, vn=None):

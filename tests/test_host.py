@@ -120,6 +120,68 @@ def test_fast_tokeniser_keeps_the_references_loader_semantics(loader, tmp_path):
         assert_bits_equal(sc["squares"], squares, "squares vs reference loader")
 
 
+LOADER_KEYS = ("verts", "planes", "squares", "mat_ids", "mats", "mats_ext_raw")
+
+
+def _load_with(loader, d, name, threads, min_bytes=1):
+    os.environ["PT_LOADER_THREADS"], os.environ["PT_LOADER_MIN_BYTES"] = str(threads), str(min_bytes)
+    try:
+        return loader.load_obj(d, name)
+    finally:
+        del os.environ["PT_LOADER_THREADS"], os.environ["PT_LOADER_MIN_BYTES"]
+
+
+def test_parallel_parse_is_the_sequential_parse(loader, tmp_path):
+    """A large OBJ is cut after line breaks and parsed by several threads (host/scene.cpp LoadModelParallel); the
+    result must be the sequential token machine's, bit for bit — here forced onto a small file, for several cuts."""
+    d = str(tmp_path)
+    _write_awkward_obj(d, n_quads=3000)
+    seq = _load_with(loader, d, "awk.obj", 1)
+    assert seq["parse_pieces"] == 0
+    for threads in (2, 3, 7, 16):
+        par = _load_with(loader, d, "awk.obj", threads)
+        assert par["parse_pieces"] == threads
+        for k in LOADER_KEYS:
+            assert_bits_equal(np.asarray(par[k]), np.asarray(seq[k]), f"{k} with {threads} threads")
+    assert loader.load_obj(d, "awk.obj")["parse_pieces"] == 0  # default: small files are not cut up
+
+
+def test_parallel_parse_falls_back_when_the_cuts_do_not_fit(loader, tmp_path):
+    """The loader's grammar is token based: statements may span lines and keywords inside "comments" count
+    (scene.cpp:37-38).  Where a cut after a line break lands inside a statement, or an index points at a vertex the
+    sequential loader would not have seen yet in another piece's range, the pieces are discarded and the sequential
+    loop runs."""
+    d = str(tmp_path)
+    rng = np.random.default_rng(4)
+    v = rng.uniform(-5, 5, (600, 3)).astype(np.float32)
+    with open(os.path.join(d, "m.mtl"), "w") as f:
+        f.write("newmtl a\nKd 1 0 0\nnewmtl b\nKd 0 1 0\n")
+    # every vertex statement spans three lines: any cut after a line break is inside one with probability 2/3
+    lines = ["mtllib m.mtl", "# v 9 9 9 is a vertex too: the reference reads tokens, not lines"]
+    for x, y, z in v:
+        lines += [f"v {x:.9g}", f"{y:.9g}", f"{z:.9g}"]
+    lines += ["usemtl 1"] + [f"f {3 * k + 2} {3 * k + 3}\n{3 * k + 4}" for k in range(199)]
+    open(os.path.join(d, "span.obj"), "w").write("\n".join(lines) + "\n")
+    seq = _load_with(loader, d, "span.obj", 1)
+    assert seq["verts"].shape[0] == 199 and seq["verts"][0][0] == v[0][0]  # vertex 1 is the comment's (9, 9, 9)
+    hit_fallback = False
+    for threads in (2, 3, 5, 8, 13):
+        par = _load_with(loader, d, "span.obj", threads)
+        hit_fallback |= par["parse_pieces"] == 0
+        for k in LOADER_KEYS:
+            assert_bits_equal(np.asarray(par[k]), np.asarray(seq[k]), f"{k} with {threads} threads")
+    assert hit_fallback
+    # one statement per line, but the faces come BEFORE their vertices in file order only for the last one: the
+    # sequential loader throws there (positions.at), so this file keeps every face behind its vertices
+    lines = [f"v {x:.9g} {y:.9g} {z:.9g}" for x, y, z in v] + [f"f {k + 1} {k + 2} {k + 3}" for k in range(0, 597, 3)]
+    open(os.path.join(d, "plain.obj"), "w").write("\n".join(lines) + "\n")
+    seq = _load_with(loader, d, "plain.obj", 1)
+    par = _load_with(loader, d, "plain.obj", 6)
+    assert par["parse_pieces"] == 6 and par["mats"].shape[0] == 0
+    for k in ("verts", "planes", "squares", "mat_ids"):
+        assert_bits_equal(np.asarray(par[k]), np.asarray(seq[k]), k)
+
+
 def test_binary_scene_cache(loader, tmp_path):
     """-CACHE <dir>: the second load takes the binary image and yields the same arrays bit for
     bit; a changed OBJ or MTL, a truncated or foreign cache file fall back to parsing."""
