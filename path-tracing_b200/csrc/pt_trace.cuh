@@ -45,10 +45,35 @@ __device__ __forceinline__ float plane_distance(float4 p, V3 o, V3 d) {
 }
 
 // the area-sum inside test of triangles.h:56-70 for the plane hit at distance nd; a = (v0, S), b = (v1, .), c = (v2, .)
+// Compile-time variant -DPT_INSIDE_APPROX=1 (0 = off, the default build; NOT yet measured — prepared for the next GPU
+// session, tools/ab_quick.py): the three areas first with MUFU.RSQ instead of three IEEE square roots.  The staged
+// test below accepts exactly when |S - (s1 + s2 + s3)| <= eps (the early exits follow from it, the areas being
+// non-negative), so a sum that misses the threshold by more than a margin covering every rounding on either side —
+// rsqrt.approx is within 2^-22, the sums within a few 2^-24 of S + s1 + s2 + s3 — decides; anything closer to the
+// threshold, and any NaN, goes through the exact test.
+#ifndef PT_INSIDE_APPROX
+#define PT_INSIDE_APPROX 0
+#endif
+__device__ __forceinline__ float rsqrt_approx(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ bool inside_test(float4 a, float4 b, float4 c, V3 o, V3 d, float nd, float eps) {
     const float S = a.w;
     const V3 P = mk(o.x + d.x * nd, o.y + d.y * nd, o.z + d.z * nd);
     const V3 f0 = P - mk(a.x, a.y, a.z), f1 = P - mk(b.x, b.y, b.z), f2 = P - mk(c.x, c.y, c.z);
+#if PT_INSIDE_APPROX
+    {
+        const V3 c1 = cross3(f0, f1), c2 = cross3(f0, f2), c3 = cross3(f2, f1);
+        const float q1 = dot3(c1, c1), q2 = dot3(c2, c2), q3 = dot3(c3, c3);
+        const float sum = q1 * rsqrt_approx(q1) + q2 * rsqrt_approx(q2) + q3 * rsqrt_approx(q3);  // 0 * inf = NaN: exact path
+        const float dev = fabsf(S - sum), margin = 8e-6f * (S + sum);
+        if (dev > eps + margin) return false;
+        if (dev < eps - margin) return true;
+    }
+#endif
     const float s1 = length3(cross3(f0, f1));
     if (s1 > S + eps) return false;
     const float s2 = length3(cross3(f0, f2));
