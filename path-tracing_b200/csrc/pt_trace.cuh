@@ -54,6 +54,16 @@ __device__ __forceinline__ float plane_distance(float4 p, V3 o, V3 d) {
 #ifndef PT_INSIDE_APPROX
 #define PT_INSIDE_APPROX 0
 #endif
+#ifndef PT_TRI_PREREJECT
+#define PT_TRI_PREREJECT 0
+#endif
+// MUFU.RCP: at most 1 ulp from 1/x (PTX ISA, rcp.approx.ftz.f32); denormal inputs flush to zero -> +-inf
+__device__ __forceinline__ float rcp_approx(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+
 __device__ __forceinline__ float rsqrt_approx(float x) {
     float r;
     asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -99,6 +109,33 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     float4 pl, a, b, c;
     ldg256(r, pl, a);
     ldg256(r + 2, b, c);
+#if PT_TRI_PREREJECT
+    // Compile-time variant (0 = off, the default build; NOT yet measured — prepared for the next GPU session): most
+    // candidates of a leaf fail the inside test, and they pay an IEEE division and up to three IEEE square roots to be
+    // told so (ncu: a third of the kernel's warp instructions, 6.7 of 32 lanes active).  Here the hit point comes from
+    // MUFU.RCP and the three areas from MUFU.RSQ; the candidate leaves when that area sum misses S by more than eps
+    // plus a bound on everything that separates it from the exact evaluation:
+    //   8e-6 (S + sum)     rsqrt (2^-22), the roundings of the sums on both sides
+    //   per * dP           the hit point moves by dP <= 1e-6 (|t| + |o|_1) (quotient within 2^-21, roundings of o + d t
+    //                      and of P - v), every area by at most dP times its edge; per <= 2 l1, l1 = sum of |P - v_k|_1
+    //   1e-6 l1^2          the products of the cross products round independently on both sides
+    // A NaN fails the comparison and goes on to the exact test.
+    {
+        const float sd = d.x * pl.x + d.y * pl.y + d.z * pl.z;
+        const float num = -(o.x * pl.x + o.y * pl.y + o.z * pl.z + pl.w);
+        const float tq = num * rcp_approx(sd);
+        const V3 Pq = mk(o.x + d.x * tq, o.y + d.y * tq, o.z + d.z * tq);
+        const V3 g0 = Pq - mk(a.x, a.y, a.z), g1 = Pq - mk(b.x, b.y, b.z), g2 = Pq - mk(c.x, c.y, c.z);
+        const V3 c1 = cross3(g0, g1), c2 = cross3(g0, g2), c3 = cross3(g2, g1);
+        const float q1 = dot3(c1, c1), q2 = dot3(c2, c2), q3 = dot3(c3, c3);
+        const float sum = q1 * rsqrt_approx(q1) + q2 * rsqrt_approx(q2) + q3 * rsqrt_approx(q3);
+        const float l1 = fabsf(g0.x) + fabsf(g0.y) + fabsf(g0.z) + fabsf(g1.x) + fabsf(g1.y) + fabsf(g1.z) + fabsf(g2.x) +
+                         fabsf(g2.y) + fabsf(g2.z);
+        const float dP = 1e-6f * (fabsf(tq) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+        const float margin = 8e-6f * (a.w + sum) + 2.0f * l1 * dP + 1e-6f * l1 * l1;
+        if (fabsf(a.w - sum) > eps + margin) return;
+    }
+#endif
     const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
     const int idx = __float_as_int(b.w);
@@ -110,13 +147,6 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     h.t = nd;
     h.idx = idx;
     h.rec = rec;
-}
-
-// MUFU.RCP: at most 1 ulp from 1/x (PTX ISA, rcp.approx.ftz.f32); denormal inputs flush to zero -> +-inf
-__device__ __forceinline__ float rcp_approx(float x) {
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
 }
 
 // ---- large triangles from shared memory (image layout: pt_scene.cuh, built by k_large_pack) ------------------
