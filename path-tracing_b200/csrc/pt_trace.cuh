@@ -57,6 +57,9 @@ __device__ __forceinline__ float plane_distance(float4 p, V3 o, V3 d) {
 #ifndef PT_TRI_PREREJECT
 #define PT_TRI_PREREJECT 0
 #endif
+#ifndef PT_COOP_EXACT
+#define PT_COOP_EXACT 0
+#endif
 // MUFU.RCP: at most 1 ulp from 1/x (PTX ISA, rcp.approx.ftz.f32); denormal inputs flush to zero -> +-inf
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
@@ -342,6 +345,103 @@ __device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3
     }
     if (COUNT) n_tris += cnt;
 }
+
+#if PT_COOP_EXACT
+// Compile-time variant (0 = off, the default build; NOT yet measured — prepared for the next GPU session): the exact
+// tests of a warp's leaf phase shared out over all 32 lanes.  As written above every lane runs its own candidates one
+// after the other — ncu: a third of the kernel's warp instructions at 6.7 active lanes.  Here the (ray, candidate)
+// pairs of the warp are numbered by a prefix sum over the lanes' candidate counts, lane i tests pair base + i with
+// the owner's ray fetched by shuffles, and every owner merges the results of its pairs (minimum t, ties to the lower
+// caller index: the nearest-hit rule does not depend on the order, pt_trace.cuh header).  All candidates of a leaf see
+// the t the ray came in with, so a hit no longer prunes its neighbours' inside tests — they run side by side instead.
+
+// the plane pass of leaf_step: candidate mask of leaf `ref` for this lane's ray
+template <bool COUNT>
+__device__ __forceinline__ unsigned leaf_candidates(const SceneView &sc, int ref, V3 o, V3 d, float eps, const Hit &h,
+                                                    unsigned long long &n_tris) {
+    const int first = leaf_first(ref), cnt = leaf_count(ref);
+    unsigned mask = 0u;
+    float4 pl[kLeafMax];
+#pragma unroll
+    for (int k = 0; k < kLeafMax; ++k)
+        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
+#pragma unroll
+    for (int k = 0; k < kLeafMax; ++k) {
+        const float4 p = pl[k];
+        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
+        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+        const float t = num * rcp_approx(sd);
+        mask |= (unsigned)(k < cnt && !((t > t_hi) | (t < t_lo))) << k;
+    }
+    if (COUNT) n_tris += cnt;
+    return mask;
+}
+
+// an accepted candidate (t, caller index, record) against the best hit so far
+__device__ __forceinline__ void hit_merge(const float4 *tris, Hit &h, float t, int idx, int rec) {
+    if (!(t <= h.t)) return;
+    if (t == h.t) {
+        if (h.idx == kIdxLazy) h.idx = __float_as_int(__ldg(tris + 4 * (size_t)h.rec + 2).w);
+        if (!(idx < h.idx)) return;
+    }
+    h.t = t;
+    h.idx = idx;
+    h.rec = rec;
+}
+
+// Must be reached by all 32 lanes.  mask / first: this lane's candidates (bit k = record first + k), 0 = none.
+__device__ __forceinline__ void coop_exact(const SceneView &sc, unsigned mask, int first, V3 o, V3 d, float eps, Hit &h) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int mycnt = __popc(mask);
+    int incl = mycnt;  // inclusive prefix sum of the candidate counts
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(full, incl, off);
+        if (lane >= off) incl += v;
+    }
+    const int start = incl - mycnt, total = __shfl_sync(full, incl, 31);
+    for (int base = 0; base < total; base += 32) {  // the same trip count for every lane
+        const int pair = base + lane;
+        // owner of the pair: the first lane whose inclusive sum exceeds it
+        int owner = 0;
+#pragma unroll
+        for (int step = 16; step; step >>= 1) {
+            const int v = __shfl_sync(full, incl, owner + step - 1);
+            if (v <= pair) owner += step;
+        }
+        const bool valid = pair < total;
+        owner = min(owner, 31);
+        int j = pair - __shfl_sync(full, start, owner);  // which of the owner's candidates
+        unsigned om = __shfl_sync(full, mask, owner);
+        const int ofirst = __shfl_sync(full, first, owner);
+        const V3 oo = mk(__shfl_sync(full, o.x, owner), __shfl_sync(full, o.y, owner), __shfl_sync(full, o.z, owner));
+        const V3 dd = mk(__shfl_sync(full, d.x, owner), __shfl_sync(full, d.y, owner), __shfl_sync(full, d.z, owner));
+        Hit hh;
+        hh.t = __shfl_sync(full, h.t, owner);
+        hh.idx = __shfl_sync(full, h.idx, owner);
+        hh.rec = __shfl_sync(full, h.rec, owner);
+        int got = -1;  // record of the accepted candidate
+        if (valid) {
+            for (; j > 0; --j) om &= om - 1u;
+            const int rec = ofirst + __ffs(om) - 1;
+            tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, oo, dd, eps, hh);
+            if (hh.rec == rec) got = rec;
+        }
+        // every owner collects the results of its pairs that were tested in this round
+#pragma unroll
+        for (int q = 0; q < kLeafMax; ++q) {
+            const int src = start - base + q;
+            const bool mine = q < mycnt && src >= 0 && src < 32;
+            const int s = mine ? src : lane;
+            const float rt = __shfl_sync(full, hh.t, s);
+            const int ri = __shfl_sync(full, hh.idx, s), rr = __shfl_sync(full, got, s);
+            if (mine && rr >= 0) hit_merge(sc.tris, h, rt, ri, rr);
+        }
+    }
+}
+#endif
 
 // One step on the inner node `cur` (>= 0); returns the next ref: a node, a leaf (< 0) or kRefEmpty when the stack ran out.
 template <bool COUNT>

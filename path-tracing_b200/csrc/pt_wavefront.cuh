@@ -375,12 +375,25 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             cur = sp ? stack[--sp] : kRefEmpty;
         }
         // ---- leaf phase: every parked leaf
+#if PT_COOP_EXACT
+        if (__any_sync(0xffffffffu, leaf != 0)) {
+            unsigned cand = 0u;
+            int first = 0;
+            if (leaf != 0) {
+                cand = leaf_candidates<COUNT>(sc, leaf, o, d, eps, h, n_tris);
+                first = leaf_first(leaf);
+                leaf = 0;
+            }
+            coop_exact(sc, cand, first, o, d, eps, h);
+        }
+#else
         if (__any_sync(0xffffffffu, leaf != 0)) {
             if (leaf != 0) {
                 leaf_step<COUNT>(sc, leaf, o, d, eps, h, n_tris);
                 leaf = 0;
             }
         }
+#endif
     }
     if (COUNT && stats) {
         for (int o2 = 16; o2; o2 >>= 1) {
