@@ -4,6 +4,8 @@
 
 #include "scene.h"
 
+void pth_check_fast_strtof_impl(const char *text, int64_t *counts);  // scene.cpp
+
 namespace {
 Image g_c, g_c2;
 std::vector<std::vector<int>> g_n;
@@ -57,6 +59,9 @@ PTH_API void pth_triangle_setup(const float *v9, int has_vn, const float *vn3, f
     plane4[0] = p.x; plane4[1] = p.y; plane4[2] = p.z; plane4[3] = p.w;
     *square = t.GetSquare();
 }
+// the loader's fast float conversion against strtof on every whitespace-separated token of `text` (NUL-terminated):
+// counts[0] tokens, [1] taken by the fast path, [2] mismatches (value bits or end of the number); test hook
+PTH_API void pth_check_fast_strtof(const char *text, int64_t *counts) { pth_check_fast_strtof_impl(text, counts); }
 // Config::set_config on an argv vector; copies the resulting PtConfig out
 PTH_API void pth_parse_config(int argc, char **argv, PtConfig *out) {
     Config::get().set_config(argc, argv);

@@ -84,6 +84,75 @@ namespace {
 // separated; scene.cpp:37-38), same numeric conversion (strtof / strtol are what libstdc++'s operator>> ends in), but
 // no locale, sentry and stream-state work per token: a 1 M-triangle OBJ (40 MB) loads in a fraction of a second
 // instead of the seconds the stream extraction takes.
+// strtof for the common case, bit for bit.  A decimal with at most 15 significant digits and a power of ten within
+// 10^+-22 converts to double with ONE rounding (digits and power are exact doubles: Clinger's fast path), and that
+// double rounds to the float strtof returns unless it sits exactly on the midpoint of two floats — if the exact value
+// and its double were on different sides of a midpoint, the midpoint, itself a double, would be the nearer double.
+// On a midpoint bit pattern, or for anything else this does not take (hex, inf / nan, long digit strings, large
+// exponents), the caller calls strtof.  p[...] is readable up to a terminating non-numeric character.
+inline bool fast_strtof(const char *p, float *out, const char **endp) {
+    static const double kPow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
+                                      1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
+    const char *q = p;
+    bool neg = false;
+    if (*q == '-' || *q == '+') neg = *q++ == '-';
+    if (!((*q >= '0' && *q <= '9') || *q == '.')) return false;
+    if (*q == '0' && (q[1] == 'x' || q[1] == 'X')) return false;
+    uint64_t mant = 0;
+    int sig = 0, frac = 0;
+    bool any = false;
+    for (; *q >= '0' && *q <= '9'; ++q) {
+        any = true;
+        if (sig || *q != '0') {
+            if (sig == 15) return false;
+            mant = mant * 10 + static_cast<uint64_t>(*q - '0');
+            ++sig;
+        }
+    }
+    if (*q == '.') {
+        for (++q; *q >= '0' && *q <= '9'; ++q) {
+            any = true;
+            ++frac;
+            if (sig || *q != '0') {
+                if (sig == 15) return false;
+                mant = mant * 10 + static_cast<uint64_t>(*q - '0');
+                ++sig;
+            }
+        }
+    }
+    if (!any) return false;
+    int e10 = 0;
+    if (*q == 'e' || *q == 'E') {
+        const char *r = q + 1;
+        bool eneg = false;
+        if (*r == '-' || *r == '+') eneg = *r++ == '-';
+        if (*r >= '0' && *r <= '9') {
+            int digits = 0;
+            for (; *r >= '0' && *r <= '9'; ++r) {
+                if (++digits > 4) return false;
+                e10 = e10 * 10 + (*r - '0');
+            }
+            if (eneg) e10 = -e10;
+            q = r;
+        }  // no digits: the number ends before the 'e', as for strtof
+    }
+    float f;
+    if (mant == 0) {
+        f = 0.0f;
+    } else {
+        const int k = e10 - frac;
+        if (k < -22 || k > 22) return false;
+        const double d = k < 0 ? static_cast<double>(mant) / kPow10[-k] : static_cast<double>(mant) * kPow10[k];
+        uint64_t bits;
+        std::memcpy(&bits, &d, sizeof bits);
+        if ((bits & 0x1fffffffull) == 0x10000000ull) return false;  // a float midpoint: let strtof look at the digits
+        f = static_cast<float>(d);
+    }
+    *out = neg ? -f : f;
+    *endp = q;
+    return true;
+}
+
 class TokenStream {
     const char *p_, *end_;  // the buffer is followed by one ' ': strtof / strtol stop there
 
@@ -106,6 +175,12 @@ public:
     }
     float next_float() {  // like `file >> f`: skips whitespace, converts the longest numeric prefix
         while (p_ < end_ && space(*p_)) ++p_;
+        float fast;
+        const char *fe;
+        if (fast_strtof(p_, &fast, &fe)) {
+            p_ = fe;
+            return fast;
+        }
         char *q = nullptr;
         const float f = std::strtof(p_, &q);
         if (q == p_) {  // not a number: the stream would fail here; consume the token, value 0
@@ -165,6 +240,25 @@ inline bool is_tok(const char *b, const char *e, const char *lit) {
     return static_cast<size_t>(e - b) == n && std::memcmp(b, lit, n) == 0;
 }
 }  // namespace
+
+void pth_check_fast_strtof_impl(const char *text, int64_t *counts) {
+    counts[0] = counts[1] = counts[2] = 0;
+    const char *p = text;
+    while (true) {
+        while (*p && TokenStream::space(*p)) ++p;
+        if (!*p) break;
+        ++counts[0];
+        float fast = 0;
+        const char *fe = nullptr;
+        if (fast_strtof(p, &fast, &fe)) {
+            ++counts[1];
+            char *q = nullptr;
+            const float f = std::strtof(p, &q);
+            if (q != fe || std::memcmp(&f, &fast, sizeof f) != 0) ++counts[2];
+        }
+        while (*p && !TokenStream::space(*p)) ++p;
+    }
+}
 
 // ---- binary scene cache (extension; -CACHE <dir>) ------------------------------------------------------------
 // What LoadModel produces — triangles as constructed (vertices, plane, area, material ordinal) and the material
@@ -288,7 +382,6 @@ struct Piece {
     std::vector<FaceRec> faces;
     std::vector<std::pair<size_t, int>> usemtl;         // (faces before the statement, ordinal)
     std::vector<std::string> mtllibs;
-    std::vector<Triangle> triangles;
     bool truncated = false;                             // the file ended inside a statement
 };
 
@@ -404,31 +497,36 @@ bool Scene::LoadModelParallel(const char *text, size_t size) {
             read_mtl(mtl_files_.back(), *this);
         }
     lap("materials");
-    std::vector<vec4> positions(pos0[threads]);
-    std::vector<vec3> normals(nrm0[threads]);
     std::vector<int> mat_in(threads + 1, 0);  // current_material at the start of each piece
     for (size_t i = 0; i < threads; ++i) mat_in[i + 1] = pieces[i].usemtl.empty() ? mat_in[i] : pieces[i].usemtl.back().second;
+    // global (file order) vertex / normal index -> the piece that parsed it
+    auto position = [&](int g) -> const vec4 & {
+        const size_t p = static_cast<size_t>(std::upper_bound(pos0.begin() + 1, pos0.end(), static_cast<size_t>(g)) - pos0.begin() - 1);
+        return pieces[p].positions[static_cast<size_t>(g) - pos0[p]];
+    };
+    auto normal = [&](int g) -> const vec3 & {
+        const size_t p = static_cast<size_t>(std::upper_bound(nrm0.begin() + 1, nrm0.end(), static_cast<size_t>(g)) - nrm0.begin() - 1);
+        return pieces[p].normals[static_cast<size_t>(g) - nrm0[p]];
+    };
+    // room first (one serial fill: std::vector cannot grow without constructing), then every piece writes its own range
+    const size_t t_base = triangles_.size();
+    const float zero9[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0}, zero4[4] = {0, 0, 0, 0};
+    triangles_.resize(t_base + tri0[threads], Triangle(zero9, zero4, 0.0f, 0));
+    lap("room");
     run_threads(threads, [&](size_t i) {
-        std::copy(pieces[i].positions.begin(), pieces[i].positions.end(), positions.begin() + pos0[i]);
-        std::copy(pieces[i].normals.begin(), pieces[i].normals.end(), normals.begin() + nrm0[i]);
-    });
-    run_threads(threads, [&](size_t i) {
-        Piece &pc = pieces[i];
-        pc.triangles.reserve(pc.faces.size());
+        const Piece &pc = pieces[i];
+        Triangle *dst = triangles_.data() + t_base + tri0[i];
         int material = mat_in[i];
         size_t ev = 0;
         for (size_t k = 0; k < pc.faces.size(); ++k) {
             while (ev < pc.usemtl.size() && pc.usemtl[ev].first <= k) material = pc.usemtl[ev++].second;
             const FaceRec &f = pc.faces[k];
-            Triangle t({positions[f.idx[0][0]], positions[f.idx[1][0]], positions[f.idx[2][0]]}, material);
-            if (f.idx[0][2] >= 0) t.SetNormal(normals[f.idx[0][2]]);
-            pc.triangles.push_back(t);
+            Triangle t({position(f.idx[0][0]), position(f.idx[1][0]), position(f.idx[2][0])}, material);
+            if (f.idx[0][2] >= 0) t.SetNormal(normal(f.idx[0][2]));
+            dst[k] = t;
         }
     });
     lap("triangles");
-    triangles_.reserve(triangles_.size() + tri0[threads]);
-    for (const Piece &pc : pieces) triangles_.insert(triangles_.end(), pc.triangles.begin(), pc.triangles.end());
-    lap("append");
     parsed_in_pieces = static_cast<int>(threads);
     return true;
 }

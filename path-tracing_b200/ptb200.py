@@ -391,6 +391,12 @@ class HostLoader:
         sc["parse_pieces"] = int(self.lib.pth_parsed_in_pieces())  # threads the OBJ was parsed with (0 = sequential)
         return sc
 
+    def check_fast_strtof(self, text):
+        """The loader's fast float conversion against strtof on every token of `text`: (tokens, fast, mismatches)."""
+        counts = (C.c_int64 * 3)()
+        self.lib.pth_check_fast_strtof(C.c_char_p(text.encode()), counts)
+        return tuple(counts)
+
     def triangle_setup(self, verts, vn=None):
         v = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
         n = v.shape[0]

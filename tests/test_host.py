@@ -182,6 +182,32 @@ def test_parallel_parse_falls_back_when_the_cuts_do_not_fit(loader, tmp_path):
         assert_bits_equal(np.asarray(par[k]), np.asarray(seq[k]), k)
 
 
+def test_fast_float_conversion_is_strtof(loader):
+    """host/scene.cpp fast_strtof converts short decimals through one double operation and must return strtof's float
+    bit for bit, ending at the same character; everything it cannot guarantee goes to strtof (hex, inf / nan, more
+    than 15 digits, large exponents, doubles that sit on a float midpoint)."""
+    rng = np.random.default_rng(11)
+    toks = ["0", "-0", "+0.0", ".5", "5.", "-.5e-3", "1e", "1e+", "1.e5", "12abc", "1.5e3x", "0x10", "0x1p3", "inf", "-inf",
+            "nan", "+nan", "infinity", ".", "-", "+.e5", "1e5000", "1e-5000", "123456789012345", "1234567890123456",
+            "0.000000000000000000001", "1e22", "1e23", "1e-22", "1e-23", "3.4028235e38", "1.17549435e-38", "1e-45",
+            "00000000000000000000001.5", "9007199254740993", "16777217", "16777217.0", "33554434.0000001",
+            "0.1", "0.2", "0.30000001", "1.00000005960464477539", "1.000000059604645", "1.00000005960464"]
+    x = np.concatenate([rng.uniform(-30, 30, 200000), rng.normal(size=100000) * 1e-3, rng.uniform(-1, 1, 100000) * 1e6,
+                        10.0 ** rng.uniform(-30, 30, 100000)])
+    fmts = ["%.9g", "%.6f", "%.8e", "%.7g", "%+.12g", "%.15g", "%.17g", "%.3f", "%E", "%.10f"]
+    for i, v in enumerate(x):
+        toks.append(fmts[i % len(fmts)] % v)
+    # decimals at and next to float midpoints: the double-rounding hazard the guard is there for
+    f = np.abs(rng.normal(size=50000).astype(np.float32) * np.float32(10.0)) + np.float32(1e-3)
+    mid = (f.astype(np.float64) + np.nextafter(f, np.float32(np.inf)).astype(np.float64)) / 2
+    for m in mid:
+        toks += ["%.15g" % m, "%.14g" % m, "%.13g" % m, repr(float(m)), "%.15g" % np.nextafter(m, np.inf), "%.15g" % np.nextafter(m, -np.inf)]
+    n, fast, bad = loader.check_fast_strtof(" ".join(toks))
+    assert n == len(toks)
+    assert bad == 0
+    assert fast > 0.6 * n  # the fast path is what usually runs
+
+
 def test_binary_scene_cache(loader, tmp_path):
     """-CACHE <dir>: the second load takes the binary image and yields the same arrays bit for
     bit; a changed OBJ or MTL, a truncated or foreign cache file fall back to parsing."""
