@@ -59,6 +59,43 @@ PTH_API void pth_triangle_setup(const float *v9, int has_vn, const float *vn3, f
     plane4[0] = p.x; plane4[1] = p.y; plane4[2] = p.z; plane4[3] = p.w;
     *square = t.GetSquare();
 }
+// the same for n triangles (has_vn / vn3 may be NULL)
+PTH_API void pth_triangle_setup_n(const float *v9, const uint8_t *has_vn, const float *vn3, int64_t n, float *planes4,
+                                  float *squares) {
+    for (int64_t i = 0; i < n; ++i)
+        pth_triangle_setup(v9 + 9 * i, has_vn && vn3 && has_vn[i], vn3 ? vn3 + 3 * i : v9, planes4 + 4 * i, squares + i);
+}
+// Scene::Intersect on the loaded scene: rays6 = n x (origin, direction) -> Ray objects -> pt_intersect
+PTH_API int pth_intersect(const float *rays6, int64_t n, const PtConfig *cfg, int32_t *ids, float *t) {
+    if (!g_scene) return PT_EINVAL;
+    std::vector<Ray> rays;
+    rays.reserve(n);
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = rays6 + 6 * i;
+        rays.emplace_back(ptm::vec4(r[0], r[1], r[2], 1), ptm::vec4(r[3], r[4], r[5], 0), 0, 0, 0);
+    }
+    std::vector<int32_t> vi;
+    std::vector<float> vt;
+    const int rc = g_scene->Intersect(rays, *cfg, vi, vt);
+    if (rc) return rc;
+    std::memcpy(ids, vi.data(), n * sizeof(int32_t));
+    std::memcpy(t, vt.data(), n * sizeof(float));
+    return 0;
+}
+// Ray::Reflect (ray.h:45-50) on raw arrays: state = (begin4, direction4, color3, depth) in / out
+PTH_API void pth_ray_reflect(float *begin4, float *dir4, float *color3, int *depth, const float *nbegin4, const float *ndir4,
+                             const float *tint3) {
+    Ray r(ptm::vec4(begin4[0], begin4[1], begin4[2], begin4[3]), ptm::vec4(dir4[0], dir4[1], dir4[2], dir4[3]), *depth, 0, 0);
+    r.SetColor(ptm::vec3(color3[0], color3[1], color3[2]));
+    r.Reflect(ptm::vec4(nbegin4[0], nbegin4[1], nbegin4[2], nbegin4[3]), ptm::vec4(ndir4[0], ndir4[1], ndir4[2], ndir4[3]),
+              ptm::vec3(tint3[0], tint3[1], tint3[2]));
+    const ptm::vec4 b = r.GetBegin(), d = r.GetDirection();
+    const ptm::vec3 c = r.GetColor();
+    begin4[0] = b.x; begin4[1] = b.y; begin4[2] = b.z; begin4[3] = b.w;
+    dir4[0] = d.x; dir4[1] = d.y; dir4[2] = d.z; dir4[3] = d.w;
+    color3[0] = c.x; color3[1] = c.y; color3[2] = c.z;
+    *depth = r.GetDepth();
+}
 // the loader's fast float conversion against strtof on every whitespace-separated token of `text` (NUL-terminated):
 // counts[0] tokens, [1] taken by the fast path, [2] mismatches (value bits or end of the number); test hook
 PTH_API void pth_check_fast_strtof(const char *text, int64_t *counts) { pth_check_fast_strtof_impl(text, counts); }

@@ -1,6 +1,7 @@
-// ray.h — Ray with the reference's surface (ray.h:11-57).  On the device the same state lives in registers
-// (origin, unit direction, depth, pixel, RGB throughput); this host type exists for callers that build explicit ray
-// sets for pt_intersect and for API parity.
+// ray.h — Ray with the reference's surface (ray.h:11-57).  On the device the same state lives in registers / 64 B of
+// HBM per path (origin, unit direction, depth, pixel, RGB throughput); on the host this type is what
+// Scene::Intersect(std::vector<Ray>) takes — explicit ray sets for the nearest-hit query (pt_intersect) — and Reflect
+// is the reference's bounce step for callers that drive a path by hand.
 #ifndef PT_B200_HOST_RAY_H
 #define PT_B200_HOST_RAY_H
 #include "config.h"
@@ -32,6 +33,13 @@ public:
     int GetY() const { return coord_y_; }
     ptm::vec3 GetColor() const { return color_; }
     void SetColor(ptm::vec3 c) { color_ = c; }
+    // ray.h:45-50: new origin, re-normalised direction, throughput times the closure's tint, one bounce deeper
+    void Reflect(ptm::vec4 begin, ptm::vec4 direction, ptm::vec3 color) {
+        begin_ = begin;
+        direction_ = unit(direction);
+        color_ = color_ * color;
+        ++depth_;
+    }
     bool IsValid() const { return depth_ < Config::get().max_ray_reflections && color_ != ptm::vec3(0); }
     void MakeInvalid() { depth_ = Config::get().max_ray_reflections; }
 };

@@ -632,6 +632,19 @@ PtScene Scene::abi() const {
     return s;
 }
 
+int Scene::Intersect(const std::vector<Ray> &rays, const PtConfig &cfg, std::vector<int32_t> &ids, std::vector<float> &t) const {
+    const PtScene s = abi();
+    std::vector<float> rays6(6 * rays.size());
+    for (size_t i = 0; i < rays.size(); ++i) {  // Ray keeps a unit direction (ray.h:21-25); pt_intersect normalises again: a no-op
+        const vec4 o = rays[i].GetBegin(), d = rays[i].GetDirection();
+        rays6[6 * i] = o.x; rays6[6 * i + 1] = o.y; rays6[6 * i + 2] = o.z;
+        rays6[6 * i + 3] = d.x; rays6[6 * i + 4] = d.y; rays6[6 * i + 5] = d.z;
+    }
+    ids.assign(rays.size(), -1);
+    t.assign(rays.size(), 0.0f);
+    return pt_intersect(&s, &cfg, rays6.data(), static_cast<int64_t>(rays.size()), ids.data(), t.data());
+}
+
 int Scene::Render(const PtConfig &cfg) {
     const PtScene s = abi();
     const size_t W = cfg.width, H = cfg.height;

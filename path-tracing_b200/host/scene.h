@@ -49,6 +49,9 @@ public:
     const std::vector<Material> &Materials() const { return materials_; }
 
     PtScene abi() const;  // plain-data view for the C-ABI; valid until the scene is modified
+    // Nearest hit of every ray, exactly the loop scene.cpp:114-120 (pt_intersect): ids[i] = index into Triangles()
+    // (-1 = miss), t[i] = hit distance (+inf = miss).  Uses cfg.eps and cfg.accel.  Returns a PT_* code.
+    int Intersect(const std::vector<Ray> &rays, const PtConfig &cfg, std::vector<int32_t> &ids, std::vector<float> &t) const;
     int Render(const PtConfig &cfg);  // the loop main.cpp:107-160 on the GPU; returns a PT_* code
     // per-pixel divisor for the resolve, row-major [y][x]: samples_count, or the weight sum of a Russian-roulette render
     const std::vector<float> &Weights() const { return weight_; }

@@ -364,6 +364,9 @@ class HostLoader:
         L.pth_copy_scene.argtypes = [C.c_void_p] * 5
         L.pth_copy_materials_ext.argtypes = [C.c_void_p]
         L.pth_triangle_setup.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pth_triangle_setup_n.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pth_intersect.argtypes = [C.c_void_p, C.c_int64, C.POINTER(PtConfig), C.c_void_p, C.c_void_p]
+        L.pth_ray_reflect.argtypes = [C.c_void_p] * 7
         L.pth_parse_config.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.POINTER(PtConfig)]
         L.pth_set_cache_dir.argtypes = [C.c_char_p]
 
@@ -410,6 +413,41 @@ class HostLoader:
             self.lib.pth_triangle_setup(v[i].ctypes.data, int(has), nn.ctypes.data, planes[i].ctypes.data, C.byref(sq))
             squares[i] = sq.value
         return planes, squares
+
+    def triangle_setup_bulk(self, verts, vn=None, has_vn=None):
+        """Triangle's constructor (+ SetNormal where has_vn) for n triangles in one call"""
+        v = np.ascontiguousarray(verts, np.float32).reshape(-1, 9)
+        n = v.shape[0]
+        planes = np.zeros((n, 4), np.float32)
+        squares = np.zeros(n, np.float32)
+        hp = vp = None
+        if vn is not None:
+            vn = np.ascontiguousarray(vn, np.float32).reshape(-1, 3)
+            has_vn = np.ascontiguousarray(has_vn if has_vn is not None else np.ones(n), np.uint8)
+            hp, vp = has_vn.ctypes.data, vn.ctypes.data
+        self.lib.pth_triangle_setup_n(v.ctypes.data, hp, vp, n, planes.ctypes.data, squares.ctypes.data)
+        return planes, squares
+
+    def intersect_loaded(self, rays6, cfg=None):
+        """Scene::Intersect(std::vector<Ray>) on the scene of the last load_obj (needs a GPU)"""
+        cfg = cfg or config()
+        rays6 = np.ascontiguousarray(rays6, np.float32).reshape(-1, 6)
+        n = rays6.shape[0]
+        ids = np.empty(n, np.int32)
+        t = np.empty(n, np.float32)
+        rc = self.lib.pth_intersect(rays6.ctypes.data, n, C.byref(cfg), ids.ctypes.data, t.ctypes.data)
+        if rc:
+            raise PtError(rc, "Scene::Intersect")
+        return ids, t
+
+    def ray_reflect(self, begin4, dir4, color3, depth, nbegin4, ndir4, tint3):
+        """Ray::Reflect on a Ray built from (begin, direction, colour, depth): -> the Ray's state afterwards"""
+        b, d, c = (np.array(a, np.float32) for a in (begin4, dir4, color3))
+        nb, nd, tn = (np.ascontiguousarray(a, np.float32) for a in (nbegin4, ndir4, tint3))
+        dep = C.c_int(depth)
+        self.lib.pth_ray_reflect(b.ctypes.data, d.ctypes.data, c.ctypes.data, C.addressof(dep), nb.ctypes.data, nd.ctypes.data,
+                                 tn.ctypes.data)
+        return b, d, c, dep.value
 
     def parse_config(self, argv):
         arr = (C.c_char_p * len(argv))(*[a.encode() for a in argv])

@@ -15,6 +15,7 @@ from util import GOLDEN, assert_bits_equal, with_planes
 
 pytestmark = pytest.mark.gpu
 G = np.load(GOLDEN + "/golden.npz")
+GB = np.load(GOLDEN + "/golden_big.npz")  # pins of BASELINE configs[2] / configs[3] on the unmodified reference
 BRUTE, LBVH = ptb200.PT_ACCEL_BRUTE, ptb200.PT_ACCEL_LBVH
 
 T_REL_TOL = 1e-6         # north_star: hit distance t within 1e-6 relative
@@ -49,10 +50,11 @@ def test_triangle_setup_device(lib, tor):
     p, s = lib.triangle_setup(sc["verts"])
     assert_bits_equal(p, G["cornell_planes"])
     assert_bits_equal(s, G["cornell_squares"])
-    # `vn` override path: feed each Tor.obj triangle's stored unit normal back in as its vn
-    p2, s2 = lib.triangle_setup(tor["verts"], vn=tor["planes"][:, :3].copy())
-    assert_bits_equal(s2, tor["squares"])
-    np.testing.assert_allclose(p2, tor["planes"], rtol=0, atol=2e-6)
+    # `vn` override path (scene.cpp:102-104): Tor.obj's raw vn values -> the planes the reference's loader stored
+    p2, s2 = lib.triangle_setup(GB["torvn_verts"], vn=GB["torvn_vn"], has_vn=GB["torvn_has"])
+    assert_bits_equal(s2, GB["torvn_squares"], "squares")
+    assert_bits_equal(p2, GB["torvn_planes"], "vn planes")
+    assert_bits_equal(GB["torvn_planes"], tor["planes"], "the product's loader")
 
 
 def test_primary_rays_device(lib):
@@ -70,7 +72,7 @@ def test_nearest_hit_golden(lib, oracle, name, accel):
     assert_bits_equal(t, G[name + "_t"], name + " t")           # (tolerance allowed: T_REL_TOL)
 
 
-def run_case(lib, sc, name, accel, mode):
+def run_case(lib, sc, name, accel, mode, G=G):
     W, H, spp, depth, seed, sb, ss = map(int, G[name + "_cfg"])
     cfg = ptb200.config(W, H, spp, depth, 1e-4, float(G[name + "_error"]), seed, sb, ss, accel=accel, mode=mode)
     ds = lib.scene_create(sc, cfg)
@@ -96,6 +98,43 @@ def test_render_golden(lib, name, accel, mode):
     sc = {"tor_flat": tor_scene, "tor_adapt": tor_scene, "tor_part": tor_scene, "cornell": scenes.cornell,
           "glossy": scenes.glossy_mix, "torus40": lambda: scenes.torus_room(40, 20)}[name]()
     run_case(lib, sc, name, accel, mode)
+
+
+@pytest.fixture(scope="module")
+def big_scenes(tor):
+    return {"torus1m": scenes.torus_room(1000, 500), "composite": scenes.composite(tor)}
+
+
+@pytest.mark.parametrize("accel", [BRUTE, LBVH])
+@pytest.mark.parametrize("name", ["torus1m", "composite"])
+def test_nearest_hit_golden_big(lib, big_scenes, name, accel):
+    """BASELINE configs[2]'s own scene (1,000,014 triangles) and configs[3]'s composite against the unmodified
+    reference's brute-force answer (tests/golden/make_golden_big.py): camera rays, uniform rays and — for the torus —
+    8192 rays aimed at the mesh itself."""
+    ids, t = lib.intersect(big_scenes[name], GB[name + "_rays"], ptb200.config(accel=accel))
+    assert_bits_equal(ids, GB[name + "_ids"], name + " ids")     # north_star: IDs bit-exact
+    assert_bits_equal(t, GB[name + "_t"], name + " t")           # (tolerance allowed: T_REL_TOL)
+    if name == "torus1m":
+        assert ((ids >= 0) & (ids < 1000000)).mean() > 0.6
+
+
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
+@pytest.mark.parametrize("accel", [BRUTE, LBVH])
+@pytest.mark.parametrize("name", ["torus1m", "composite", "composite_part"])
+def test_render_golden_big(lib, big_scenes, name, accel, mode):
+    """Accumulators of small frames of C3's and C4's scenes (C4 also as one 1-of-4 sample partition, the multi-GPU
+    split) against the unmodified reference under the Philox contract, bit for bit."""
+    if name == "torus1m" and accel == BRUTE and mode == 1:
+        pytest.skip("brute force over 1M triangles in the megakernel: minutes; the wavefront pipeline covers it")
+    run_case(lib, big_scenes[name.split("_")[0]], name, accel, mode, GB)
+
+
+def test_host_scene_intersect_takes_rays(lib, loader, tor):
+    """host Scene::Intersect(std::vector<Ray>) (host/ray.h, host/scene.h) -> pt_intersect: the golden answer."""
+    loader.load_obj(os.path.join(os.path.dirname(GOLDEN), "..", "assets", "models"), "Tor.obj")
+    ids, t = loader.intersect_loaded(G["tor_rnd_rays"], ptb200.config())
+    assert_bits_equal(ids, G["tor_rnd_ids"])
+    assert_bits_equal(t, G["tor_rnd_t"])
 
 
 @pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])

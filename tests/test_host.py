@@ -267,3 +267,28 @@ def test_config_parser(loader):
                              "-EPS"])  # trailing unpaired flag is ignored (config.h:36)
     assert (c.width, c.height, c.rays_per_pixel, c.max_ray_reflections, c.seed) == (1920, 1080, 256, 8, 7)
     assert c.error == -1.0 and abs(c.eps - 1e-4) < 1e-10
+
+
+def test_host_ray_reflect(loader):
+    """host/ray.h Ray::Reflect = ray.h:45-50: new origin, glm::normalize(vec4) of the direction ((x+y)+(z+w) dot,
+    v * (1 / sqrt)), throughput times the tint, depth + 1."""
+    f = np.float32
+    rng = np.random.default_rng(8)
+    for _ in range(200):
+        nd = rng.normal(size=4).astype(np.float32)
+        nd[3] = 0
+        nb = np.append(rng.normal(size=3), 1).astype(np.float32)
+        col, tint = rng.random(3).astype(np.float32), rng.random(3).astype(np.float32)
+        b, d, c, depth = loader.ray_reflect([0, 0, -20, 1], [0, 0, 1, 0], col, 3, nb, nd, tint)
+        inv = f(1) / np.sqrt(f(f(nd[0] * nd[0]) + f(nd[1] * nd[1])) + f(f(nd[2] * nd[2]) + f(nd[3] * nd[3])))
+        assert_bits_equal(d, (nd * inv).astype(np.float32), "direction")
+        assert_bits_equal(b, nb, "begin")
+        assert_bits_equal(c, col * tint, "colour")
+        assert depth == 4
+
+
+def test_host_triangle_constructor_bulk(loader):
+    GB = np.load(GOLDEN + "/golden_big.npz")
+    p, s = loader.triangle_setup_bulk(GB["torvn_verts"], GB["torvn_vn"], GB["torvn_has"])
+    assert_bits_equal(p, GB["torvn_planes"], "vn planes")
+    assert_bits_equal(s, GB["torvn_squares"], "squares")

@@ -7,6 +7,7 @@ import scenes
 from util import GOLDEN, MODELS, assert_bits_equal, with_planes
 
 G = np.load(GOLDEN + "/golden.npz")
+GB = np.load(GOLDEN + "/golden_big.npz")  # BASELINE configs[2] / configs[3] pins, tests/golden/make_golden_big.py
 
 
 def tor_scene():
@@ -80,6 +81,54 @@ def test_render_tor(oracle, name):
                                        ("torus40", lambda: scenes.torus_room(40, 20))])
 def test_render_synthetic(oracle, name, make):
     render_case(oracle, with_planes(make(), oracle), name)
+
+
+def composite_scene(loader):
+    """BASELINE configs[3] (C4): Tor.obj as the product's loader reads it + the two Cornell boxes, 290 triangles."""
+    return scenes.composite(loader.load_obj(MODELS, "Tor.obj"))
+
+
+def render_case_big(oracle, sc, name):
+    W, H, spp, depth, seed, sb, ss = map(int, GB[name + "_cfg"])
+    sm, s2, cnt, segs, _ = oracle.render_accum(sc, oracle.config(W, H, spp, depth, 1e-4, float(GB[name + "_error"]), seed, sb, ss))
+    assert_bits_equal(cnt, GB[name + "_count"], name + " count")
+    assert_bits_equal(sm, GB[name + "_sum"], name + " sum")
+    assert_bits_equal(s2, GB[name + "_sum2"], name + " sum2")
+    assert segs == int(GB[name + "_segments"])
+
+
+def test_composite_c4_golden(oracle, loader):
+    """C4's scene: ray set, a 32x32x16 frame and one 1-of-4 sample partition of it, against the unmodified reference."""
+    sc = with_planes(composite_scene(loader), oracle)
+    ids, t = oracle.intersect(sc, GB["composite_rays"])
+    assert_bits_equal(ids, GB["composite_ids"], "composite ids")
+    assert_bits_equal(t, GB["composite_t"], "composite t")
+    render_case_big(oracle, sc, "composite")
+    render_case_big(oracle, sc, "composite_part")
+
+
+def test_torus1m_c3_golden_subset(oracle):
+    """C3's own scene (1,000,014 triangles): every 16th ray of the golden set (the oracle is brute force like the
+    reference: the whole set takes the host cores half a minute; the GPU test runs all of it)."""
+    sc = scenes.torus_room(1000, 500)
+    import ptb200
+    planes, squares = ptb200.HostLoader().triangle_setup_bulk(sc["verts"])
+    sc = dict(sc, planes=planes, squares=squares)
+    sel = slice(5, None, 16)
+    ids, t = oracle.intersect(sc, GB["torus1m_rays"][sel])
+    assert_bits_equal(ids, GB["torus1m_ids"][sel], "torus1m ids")
+    assert_bits_equal(t, GB["torus1m_t"][sel], "torus1m t")
+    assert ((ids >= 0) & (ids < 1000000)).mean() > 0.5  # most of these rays end on the torus itself
+
+
+def test_vn_planes_golden(oracle):
+    """Triangle ctor + the `vn` override of scene.cpp:102-104 from Tor.obj's raw vn values: bit-exact planes."""
+    vn = [v if h else None for v, h in zip(GB["torvn_vn"], GB["torvn_has"])]
+    planes, squares = oracle.triangle_setup(GB["torvn_verts"], vn)
+    assert GB["torvn_has"].all()
+    assert_bits_equal(planes, GB["torvn_planes"], "vn planes")
+    assert_bits_equal(squares, GB["torvn_squares"], "squares")
+    assert_bits_equal(GB["torvn_planes"], G["tor_planes"])
 
 
 CONVERGED_RMSE_TOL = 1e-3  # north_star: converged images at 4096 spp agree within RMSE 1e-3
