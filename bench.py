@@ -107,6 +107,18 @@ class ClockSampler:
         return {"sm_mhz": statistics.median(hi), "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_threads():
+    """CPUs this process may run on.  NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1 to its workers, which
+    made round 1's multi-rank reference arm single-threaded; the harnesses take an explicit num_threads clause."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+REF_RELEASE_THREADS = 4  # the reference's own release build: THREADS_TO_RUN=4 (CMakeLists.txt:10)
+
+
 def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=0, rr_depth=0):
     """The reference's own CPU renderer (oracle/_ref: unmodified scene.cpp/triangles.h/material.h/ray.h + shims) when it
     was compiled, else the oracle's C port, on a bounded sample of the workload: the same scene and parameters at a
@@ -120,18 +132,18 @@ def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=
     use_ref = Reference.available() and rr_depth == 0 and sc.get("mats_ext") is None
     if use_ref:
         ref = Reference()
-        threads = threads or ref.max_threads()
+        threads = threads or host_threads()
 
-        def run(w, h, s):
+        def run(w, h, s, nthreads=None):
             ref.set_config(w, h, s, depth, 1e-4, error)
             if planes is None:
                 ref.from_arrays(sc["verts"], sc["mat_ids"], sc["mats"])
             else:  # scenes that came from the OBJ loader carry `vn` planes: rebuild through the reference's loader
                 ref.load_obj(os.path.join(ROOT, "assets", "models"), "Tor.obj")
-            _, _, _, segs, sec = ref.render_accum(seed=42, threads=threads)
+            _, _, _, segs, sec = ref.render_accum(seed=42, threads=nthreads or threads)
             return segs, sec
     else:
-        threads = threads or orc.max_threads()
+        threads = threads or host_threads()
         if planes is None:
             planes, squares = np.zeros((n_tri, 4), np.float32), np.zeros(n_tri, np.float32)
             import ctypes as C
@@ -143,8 +155,8 @@ def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=
                 squares[i] = sq.value
         osc = dict(sc, planes=planes, squares=squares)
 
-        def run(w, h, s):
-            _, _, _, segs, sec = orc.render_accum(osc, orc.config(w, h, s, depth, 1e-4, error, 42, rr_depth=rr_depth), threads)
+        def run(w, h, s, nthreads=None):
+            _, _, _, segs, sec = orc.render_accum(osc, orc.config(w, h, s, depth, 1e-4, error, 42, rr_depth=rr_depth), nthreads or threads)
             return segs, sec
     # calibration: a thumbnail with the frame's aspect ratio, 1 sample
     w, h, s = max(16, W // 40), max(9, H // 40), 1
@@ -161,7 +173,18 @@ def cpu_reference_leg(name, sc, W, H, spp, depth, error, budget_s=12.0, threads=
         w2, h2 = int(min(W, max(w, w * scale))), int(min(H, max(h, h * scale)))
         s2 = int(max(1, min(spp, want / (per_px * w2 * h2))))
         segs, sec = run(w2, h2, s2)
+    # the same sample at the reference's own release thread count (CMakeLists.txt:10: THREADS_TO_RUN=4), scaled down so
+    # that it takes about a quarter of the budget
+    rel = None
+    if threads > REF_RELEASE_THREADS:
+        frac = min(1.0, 0.25 * budget_s / max(sec, 1e-6) * REF_RELEASE_THREADS / threads)
+        s4 = max(1, int(s2 * frac))
+        h4 = h2 if s2 * frac >= 1 else max(1, int(h2 * s2 * frac))
+        segs4, sec4 = run(w2, h4, s4, REF_RELEASE_THREADS)
+        rel = {"value": segs4 / sec4 / 1e6, "unit": "Mrays/s", "cores": REF_RELEASE_THREADS,
+               "what": f"THREADS_TO_RUN=4 (the reference's release setting): {w2}x{h4}, {s4} spp, {segs4} segments in {sec4:.2f} s"}
     return {"value": segs / sec / 1e6, "unit": "Mrays/s", "cores": int(threads), "kind": "reference" if use_ref else "port",
+            "release_threads": rel, "host_cpus": host_threads(),
             "sample": f"{name}: same scene/depth at {w2}x{h2}, {s2} spp ({segs} segments in {sec:.2f} s); "
                       f"full frame extrapolates to {(W * H * spp) * (segs / (w2 * h2 * s2)) / (segs / sec) :.0f} s",
             "segments": int(segs), "seconds": sec}
@@ -187,7 +210,8 @@ def run_reference_arm(args):
            "warmup": args.warmup, "ms_per_step": 1e3 * sec / len(runs), "higher_is_better": True, "scaling": "strong",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": desc, "sample": last["sample"]},
-           "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"]},
+           "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": last["cores"], "kind": last["kind"], "sample": last["sample"],
+                            "release_threads": last["release_threads"], "host_cpus": last["host_cpus"]},
            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out))
@@ -198,7 +222,8 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="cornell", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="torus1m", choices=sorted(WORKLOADS),
+                    help="default: BASELINE configs[2], the configuration the >= 1 Gray/s target is quoted on")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--spp", type=int, default=0, help="override samples per pixel (profiling runs only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs only)")
@@ -432,7 +457,7 @@ def main():
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference_leg(args.workload, sc, W, H, spp, depth, error, rr_depth=RR_DEPTH.get(args.workload, 0))
-        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample", "release_threads", "host_cpus")}
 
     if rank == 0:
         st = ds.stats()

@@ -68,7 +68,8 @@ enum {
 };
 /* acceleration modes */
 enum {
-    PT_ACCEL_AUTO = 0,  /* = PT_ACCEL_LBVH: GPU LBVH, with the few scene-sized triangles (walls) in shared memory */
+    PT_ACCEL_AUTO = 0,  /* = PT_ACCEL_LBVH (GPU-built 8-wide BVH, the few scene-sized triangles (walls) in shared memory),
+                           falling back to PT_ACCEL_BRUTE for a tree deeper than the traversal stack allows */
     PT_ACCEL_BRUTE = 1, /* every triangle in index order, as scene.cpp:114-120 (checker mode) */
     PT_ACCEL_LBVH = 2
 };
@@ -113,8 +114,8 @@ typedef struct PtConfig {
 typedef struct PtStats {
     uint64_t segments;        /* committed TraceRay-equivalents (what the reference's loop would have traced) */
     uint64_t segments_traced; /* traced on the device, including speculative samples the adaptive rule discarded */
-    uint64_t nodes_visited;   /* BVH nodes fetched (0 unless the scene was built with counters on) */
-    uint64_t tris_tested;     /* triangle tests run */
+    uint64_t nodes_visited;   /* 8-wide BVH nodes fetched (0 unless the scene was built with counters on) */
+    uint64_t tris_tested;     /* triangle tests run: shared-memory triangles + scan records of BVH triangles */
     float kernel_ms;          /* device time of the render kernel(s), CUDA events */
     float build_ms;           /* device time of the LBVH build */
     float upload_ms;
@@ -131,7 +132,9 @@ typedef struct PtStats {
     uint64_t rays_queued;
     uint64_t node_hist[16];
     int32_t n_quads;          /* of the n_large shared-memory triangles, 2 n_quads are scanned as quad units */
-    int32_t reserved0;
+    int32_t n_levels;         /* levels of the 8-wide BVH (the traversal stack holds two entries per level) */
+    uint64_t exact_tests;     /* counters mode: BVH triangles whose scan record passed, i.e. runs of the reference's
+                                 exact test (triangles.h:48-73) during the tree walk */
 } PtStats;
 
 typedef struct PtDeviceScene PtDeviceScene; /* opaque: device-resident SoA triangles, materials, LBVH */

@@ -133,6 +133,7 @@ struct PtDeviceScene {
     int device = 0;
     int n_tri = 0, n_mat = 0;
     float4 *tris = nullptr;
+    float4 *scans = nullptr;
     float4 *nodes = nullptr;
     float4 *mats = nullptr;
     float4 *lrecs = nullptr;
@@ -144,7 +145,7 @@ struct PtDeviceScene {
     float class_ms[4] = {0, 0, 0, 0};
     int class_launches[4] = {0, 0, 0, 0};
     std::vector<cudaEvent_t> class_events;  // pairs, recycled every step
-    int n_nodes = 0;
+    int n_nodes = 0, n_levels = 0;
     float build_ms = 0.f, upload_ms = 0.f, kernel_ms = 0.f;
     int launches = 0;
     int accel = PT_ACCEL_BRUTE;
@@ -216,6 +217,7 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     };
     cudaDeviceSynchronize();  // blocks go back to the pool: nothing may still be using them (cudaFree used to wait)
     pool_free(ds->tris);
+    pool_free(ds->scans);
     pool_free(ds->nodes);
     pool_free(ds->mats);
     pool_free(ds->lrecs);
@@ -297,15 +299,17 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         v.n_bvh = 0; v.n_large = 0; v.root = kRefEmpty;
         ds->accel = PT_ACCEL_BRUTE;
     } else {
-        // ---- LBVH ----
+        // ---- BVH: Morton sort -> Karras binary tree -> fit -> 8-wide collapse, level by level ----
         DevBuf<BuildScratch> d_scr;
         DevBuf<float4> box_lo, box_hi, node_lo, node_hi;
         DevBuf<uint64_t> keys, keys2;
-        DevBuf<int> vals, vals2, parent, flags;
+        DevBuf<int> vals, vals2, parent, flags, perm, order;
         DevBuf<int2> children, range;
         DevBuf<unsigned char> tmp;
         DevBuf<float4> d_root;
-        CK(d_root.alloc(2));
+        DevBuf<WideItem> items_a, items_b;
+        DevBuf<CollapseCounters> d_ctr;
+        CK(d_root.alloc(5));
         CK(pool_alloc((void **)&ds->lrecs, (size_t)kLargeRowsMax * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
         CK(vals.alloc(n)); CK(vals2.alloc(n));
@@ -330,37 +334,73 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             CK(cudaMemcpy(&scr, d_scr.p, sizeof scr, cudaMemcpyDeviceToHost));
             v.n_quads = scr.n_quads;
         }
-        k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, vals2.p, n, ds->tris);
-        ++launches;
+        int levels = 0;
         if (nb == 0) {
             v.root = kRefEmpty;
-        } else if (nb <= kLeafMax) {
-            v.root = leaf_ref(0, nb);
         } else {
-            CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb)); CK(children.alloc(nb)); CK(range.alloc(nb));
-            CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
-            CK(pool_alloc((void **)&ds->nodes, 4 * (size_t)(nb - 1) * sizeof(float4)));
-            CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
-            k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
-            k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
-            k_emit_nodes<<<blocks_for(nb - 1, 256), 256>>>(nb, children.p, range.p, vals2.p, box_lo.p, box_hi.p, node_lo.p, node_hi.p, ds->nodes);
-            launches += 3;
-            v.root = 0;
-            ds->n_nodes = nb - 1;
-        }
-        if (nb > 0) {
-            k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, node_lo.p, node_hi.p, d_root.p);
-            ++launches;
-            float4 rb[2];
-            CK(cudaMemcpy(rb, d_root.p, sizeof rb, cudaMemcpyDeviceToHost));
-            v.root_lo = rb[0];
-            v.root_hi = rb[1];
-            if (v.root == 0) {
-                float4 rn[3];
-                CK(cudaMemcpy(rn, ds->nodes, sizeof rn, cudaMemcpyDeviceToHost));
-                v.root_n0 = rn[0]; v.root_n1 = rn[1]; v.root_n2 = rn[2];
+            CK(children.alloc(nb)); CK(range.alloc(nb)); CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
+            if (nb >= 2) {
+                CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb));
+                CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
+                k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
+                k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
+                launches += 2;
             }
+            // every wide node has at least min(8, kLeafMax + 1) children (k_collapse), every leaf child a triangle
+            const size_t max_nodes = (size_t)nb / (std::min(8, kLeafMax + 1) - 1) + 2;
+            const size_t max_items = (size_t)nb / (kLeafMax + 1) + 2;
+            CK(pool_alloc((void **)&ds->nodes, kNodeRows * max_nodes * sizeof(float4)));
+            CK(items_a.alloc(max_items)); CK(items_b.alloc(max_items)); CK(d_ctr.alloc(1)); CK(perm.alloc(nb)); CK(order.alloc(n));
+            const WideItem root_item{0, nb >= 2 ? 0 : ~0};
+            CollapseCounters ctr{1, 0, 0, 0};
+            CK(cudaMemcpy(items_a.p, &root_item, sizeof root_item, cudaMemcpyHostToDevice));
+            CK(cudaMemcpy(d_ctr.p, &ctr, sizeof ctr, cudaMemcpyHostToDevice));
+            const BinTree bt{children.p, range.p, vals2.p, box_lo.p, box_hi.p, node_lo.p, node_hi.p};
+            WideItem *in = items_a.p, *out_items = items_b.p;
+            int n_in = 1;
+            while (n_in > 0) {
+                k_collapse<<<blocks_for(n_in, 128), 128>>>(in, n_in, out_items, d_ctr.p, bt, ds->nodes, perm.p);
+                ++launches;
+                ++levels;
+                CK(cudaMemcpy(&ctr, d_ctr.p, sizeof ctr, cudaMemcpyDeviceToHost));
+                n_in = ctr.n_out;
+                if ((size_t)n_in > max_items || (size_t)ctr.n_nodes > max_nodes)
+                    return fail(PT_ECUDA, "BVH collapse overran its buffers (%d items, %d nodes)", n_in, ctr.n_nodes);
+                CK(cudaMemsetAsync(&d_ctr.p->n_out, 0, sizeof(int)));
+                std::swap(in, out_items);
+            }
+            if (ctr.tri_cursor != nb) return fail(PT_ECUDA, "BVH collapse placed %d of %d triangles", ctr.tri_cursor, nb);
+            ds->n_nodes = ctr.n_nodes;
+            ds->n_levels = levels;
+            v.root = 0;
+            k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, node_lo.p, node_hi.p, d_root.p);
+            ++launches;
+            float4 rb[5];
+            CK(cudaMemcpy(rb, d_root.p, sizeof rb, cudaMemcpyDeviceToHost));
+            v.root_lo = rb[0]; v.root_hi = rb[1];
+            v.root_n0 = rb[2]; v.root_n1 = rb[3]; v.root_n2 = rb[4];
+            // records in wide-node order: the BVH triangles through perm, the large ones behind them as sorted
+            k_compose_order<<<blocks_for(nb, 256), 256>>>(perm.p, vals2.p, nb, order.p);
+            if (n_large) CK(cudaMemcpyAsync(order.p + nb, vals2.p + nb, (size_t)n_large * sizeof(int), cudaMemcpyDeviceToDevice));
+            CK(pool_alloc((void **)&ds->scans, 4 * (size_t)nb * sizeof(float4)));
+            k_pack_scans<<<blocks_for(nb, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, order.p, nb, eps, d_scr.p, ds->scans);
+            launches += 2;
         }
+        k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb ? order.p : vals2.p, n, ds->tris);
+        ++launches;
+        if (levels > kMaxLevels) {
+            // the traversal stack holds two entries per level: a deeper tree (adversarial centroid spacing) is not walked.
+            // PT_ACCEL_AUTO renders it with the brute-force scan instead (correct, slow); an explicit LBVH request fails.
+            if (want == PT_ACCEL_LBVH)
+                return fail(PT_EINVAL, "the scene needs a %d-level BVH (max %d): use PT_ACCEL_AUTO or PT_ACCEL_BRUTE", levels, kMaxLevels);
+            CK(cudaDeviceSynchronize());
+            k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nullptr, n, ds->tris);
+            ++launches;
+            v.brute = 1;
+            v.n_bvh = 0; v.n_large = 0; v.n_quads = 0; v.root = kRefEmpty;
+            ds->accel = PT_ACCEL_BRUTE;
+            ds->n_nodes = 0;
+        } else
         ds->accel = PT_ACCEL_LBVH;
         CK(cudaDeviceSynchronize());  // scratch buffers are freed on scope exit
     }
@@ -370,6 +410,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     CK(cudaEventElapsedTime(&ds->upload_ms, e0, e1));
     CK(cudaEventElapsedTime(&ds->build_ms, e1, e2));
     v.tris = ds->tris;
+    v.scans = ds->scans;
     v.nodes = ds->nodes;
     v.mats = ds->mats;
     v.lrecs = ds->lrecs;
@@ -625,6 +666,8 @@ extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
     out->launches = ds->launches;
     out->rays_queued = st[4];
     out->n_quads = ds->view.n_quads;
+    out->n_levels = ds->n_levels;
+    out->exact_tests = st[21];
     for (int c = 0; c < 16; ++c) out->node_hist[c] = st[5 + c];
     for (int c = 0; c < 4; ++c) { out->class_ms[c] = ds->class_ms[c]; out->class_launches[c] = ds->class_launches[c]; }
     return PT_OK;

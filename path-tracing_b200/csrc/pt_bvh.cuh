@@ -1,4 +1,5 @@
-// pt_bvh.cuh — SoA repack + GPU LBVH build (Morton codes -> radix sort -> Karras 2012 hierarchy -> bottom-up fit).
+// pt_bvh.cuh — SoA repack + GPU BVH build: Morton codes -> radix sort -> Karras 2012 binary hierarchy -> bottom-up fit
+// -> collapse into an 8-wide tree with quantised child boxes (k_collapse, level by level) -> records in node order.
 //
 // The reference has no acceleration structure (scene.cpp:114-120 tests every triangle); the LBVH must therefore
 // return exactly the brute-force answer of the reference's intersector.  That intersector (triangles.h:48-73) is
@@ -230,40 +231,6 @@ __global__ void k_fit(const int *__restrict__ vals, const float4 *__restrict__ b
     }
 }
 
-// final 64-byte nodes; a subtree of at most kLeafMax triangles becomes one leaf (its records are contiguous)
-__global__ void k_emit_nodes(int n, const int2 *__restrict__ children, const int2 *__restrict__ range,
-                             const int *__restrict__ vals, const float4 *__restrict__ box_lo,
-                             const float4 *__restrict__ box_hi, const float4 *__restrict__ node_lo,
-                             const float4 *__restrict__ node_hi, float4 *__restrict__ nodes) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n - 1) return;
-    const int2 r = range[i];
-    if (r.y - r.x + 1 <= kLeafMax) return;  // swallowed by a leaf above
-    const int2 c = children[i];
-    float4 l[2], h[2];
-    int ref[2];
-#pragma unroll
-    for (int k = 0; k < 2; ++k) {
-        const int ck = k ? c.y : c.x;
-        if (ck >= 0) {
-            l[k] = node_lo[ck];
-            h[k] = node_hi[ck];
-            const int2 rr = range[ck];
-            const int cnt = rr.y - rr.x + 1;
-            ref[k] = cnt <= kLeafMax ? leaf_ref(rr.x, cnt) : ck;
-        } else {
-            l[k] = box_lo[vals[~ck]];
-            h[k] = box_hi[vals[~ck]];
-            ref[k] = leaf_ref(~ck, 1);
-        }
-    }
-    float4 *o = nodes + 4 * (size_t)i;
-    o[0] = make_float4(l[0].x, h[0].x, l[0].y, h[0].y);
-    o[1] = make_float4(l[1].x, h[1].x, l[1].y, h[1].y);
-    o[2] = make_float4(l[0].z, h[0].z, l[1].z, h[1].z);
-    o[3] = make_float4(__int_as_float(ref[0]), __int_as_float(ref[1]), 0.0f, 0.0f);
-}
-
 // triangle records in sorted order (vals == nullptr: caller order)
 __global__ void k_pack_tris(const float *__restrict__ verts, const float4 *__restrict__ planes,
                             const float *__restrict__ squares, const int *__restrict__ mat_ids,
@@ -434,22 +401,229 @@ k_large_pack(int *__restrict__ vals, const float *__restrict__ verts, const floa
         for (int j = 0; j < 3; ++j) o[1 + j] = edge_plane(t, j, ng, ok, e, slack);
     }
 }
+// ---- collapse of the binary tree into the 8-wide tree (layout: pt_scene.cuh) -----------------------------------------
+// A binary ref is an inner node index (>= 0) or ~k for the leaf at sorted position k.
+struct WideItem {
+    int node;  // index of the wide node to emit
+    int ref;   // binary ref whose subtree it covers
+};
+struct CollapseCounters {
+    int n_nodes;    // wide nodes allocated so far
+    int n_out;      // work items appended for the next level
+    int tri_cursor; // triangle records placed so far
+    int pad;
+};
+
+struct BinTree {
+    const int2 *children, *range;
+    const int *vals;
+    const float4 *box_lo, *box_hi, *node_lo, *node_hi;
+    __device__ __forceinline__ int count(int ref) const { return ref >= 0 ? range[ref].y - range[ref].x + 1 : 1; }
+    __device__ __forceinline__ int first(int ref) const { return ref >= 0 ? range[ref].x : ~ref; }
+    __device__ __forceinline__ void box(int ref, V3 *lo, V3 *hi) const {
+        const float4 l = ref >= 0 ? node_lo[ref] : box_lo[vals[~ref]], h = ref >= 0 ? node_hi[ref] : box_hi[vals[~ref]];
+        *lo = mk(l.x, l.y, l.z);
+        *hi = mk(h.x, h.y, h.z);
+    }
+    __device__ __forceinline__ float area(int ref) const {
+        V3 lo, hi;
+        box(ref, &lo, &hi);
+        const V3 e = hi - lo;
+        return e.x * e.y + e.y * e.z + e.z * e.x;
+    }
+};
+
+// decode of a quantised plane as the builder checks it: p + q s with one rounding
+__device__ __forceinline__ float q_decode(int q, float s, float p) { return __fmaf_rn((float)q, s, p); }
+
+// One thread per wide node of the current level.  Its children: start from the subtree's two binary children and keep
+// replacing the child with the largest box by its own two children — first among the subtrees that are too big for a
+// leaf (> kLeafMax triangles), then, while slots are free, among the leaves themselves (a slot costs the same whether
+// it is used or not) — until there are 8.  Subtrees of <= kLeafMax triangles become leaf children (their triangles are
+// contiguous in the sorted order), the others inner children, numbered in slot order from child_base and queued for
+// the next level.  Quantisation: q_lo = floor, q_hi = ceil on the grid p + q s, s = extent / 255, pushed outwards until
+// the DECODED plane (q_decode) encloses the child box with a margin of 2^-7 of a grid step: node8_visit
+// (pt_trace.cuh) evaluates (p + q s - o) / d in a different association (one FMA on a 2^15-scaled grid) whose rounding
+// stays below 2^-9 of a step plus a few ulp of |p - o| / |d|; the latter are covered by the 32-ulp padding every
+// triangle box already carries (k_tri_boxes_keys).
+__global__ void __launch_bounds__(128)
+k_collapse(const WideItem *__restrict__ in, int n_in, WideItem *__restrict__ out, CollapseCounters *ctr, BinTree bt,
+           float4 *__restrict__ nodes, int *__restrict__ perm) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_in) return;
+    const WideItem item = in[t];
+    int refs[8];
+    float area[8];
+    int n;
+    if (item.ref >= 0) {
+        const int2 c = bt.children[item.ref];
+        refs[0] = c.x; refs[1] = c.y;
+        n = 2;
+    } else {  // a one-triangle tree
+        refs[0] = item.ref;
+        n = 1;
+    }
+    for (int i = 0; i < n; ++i) area[i] = bt.area(refs[i]);
+    for (int phase = 0; phase < 2 && n < 8; ++phase) {
+        const int min_cnt = phase == 0 ? kLeafMax + 1 : 2;
+        while (n < 8) {
+            int best = -1;
+            float best_a = -1.0f;
+            for (int i = 0; i < n; ++i)
+                if (refs[i] >= 0 && bt.count(refs[i]) >= min_cnt && area[i] > best_a) { best = i; best_a = area[i]; }
+            if (best < 0) break;
+            const int2 c = bt.children[refs[best]];
+            refs[best] = c.x; area[best] = bt.area(c.x);
+            refs[n] = c.y; area[n] = bt.area(c.y);
+            ++n;
+        }
+    }
+    // child boxes, node box
+    V3 clo[8], chi[8];
+    V3 lo = mk(FLT_MAX, FLT_MAX, FLT_MAX), hi = mk(-FLT_MAX, -FLT_MAX, -FLT_MAX);
+    for (int i = 0; i < n; ++i) {
+        bt.box(refs[i], &clo[i], &chi[i]);
+        lo = mk(fminf(lo.x, clo[i].x), fminf(lo.y, clo[i].y), fminf(lo.z, clo[i].z));
+        hi = mk(fmaxf(hi.x, chi[i].x), fmaxf(hi.y, chi[i].y), fmaxf(hi.z, chi[i].z));
+    }
+    // slot assignment: greedy on dot(child centre - node centre, octant direction of the slot)
+    int slot_of_child[8], child_in_slot[8];
+    for (int i = 0; i < 8; ++i) { slot_of_child[i] = -1; child_in_slot[i] = -1; }
+    const V3 ctr_n = (lo + hi) * 0.5f;
+    for (int round = 0; round < n; ++round) {
+        int bc = -1, bs = -1;
+        float bv = -FLT_MAX;
+        for (int i = 0; i < n; ++i) {
+            if (slot_of_child[i] >= 0) continue;
+            const V3 c = (clo[i] + chi[i]) * 0.5f - ctr_n;
+            for (int sl = 0; sl < 8; ++sl) {
+                if (child_in_slot[sl] >= 0) continue;
+                const float v = ((sl & 1) ? c.x : -c.x) + ((sl & 2) ? c.y : -c.y) + ((sl & 4) ? c.z : -c.z);
+                if (v > bv || bc < 0) { bv = v; bc = i; bs = sl; }
+            }
+        }
+        slot_of_child[bc] = bs;
+        child_in_slot[bs] = bc;
+    }
+    // grid: the origin one step below the node box and 253 steps across it, so that every child plane has a grid
+    // plane strictly outside it on either side (the outward margins below)
+    float p[3], sc[3];
+    const float lo3[3] = {lo.x, lo.y, lo.z}, hi3[3] = {hi.x, hi.y, hi.z};
+    for (int a = 0; a < 3; ++a) {
+        float sa = fmaxf((hi3[a] - lo3[a]) * (1.0f / 252.0f), 1e-30f);
+        p[a] = lo3[a] - sa;
+        while (q_decode(255, sa, p[a]) < hi3[a] + sa * 0.0078125f) sa *= 1.0000005f;
+        sc[a] = sa;
+    }
+    // inner / leaf children in slot order
+    int n_inner = 0, n_tri = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        const int i = child_in_slot[sl];
+        if (i < 0) continue;
+        const int c = bt.count(refs[i]);
+        if (c > kLeafMax) ++n_inner; else n_tri += c;
+    }
+    const int child_base = n_inner ? atomicAdd(&ctr->n_nodes, n_inner) : 0;
+    const int out_base = n_inner ? atomicAdd(&ctr->n_out, n_inner) : 0;
+    const int tri_base = n_tri ? atomicAdd(&ctr->tri_cursor, n_tri) : 0;
+    unsigned meta[2] = {0u, 0u}, imask = 0u;
+    unsigned q[6][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};  // qlo x y z, qhi x y z; slots 0..3, 4..7
+    int k_inner = 0, k_tri = 0;
+    for (int sl = 0; sl < 8; ++sl) {
+        const int i = child_in_slot[sl];
+        const int sh = 8 * (sl & 3), w = sl >> 2;
+        if (i < 0) {  // empty slot: meta 0 contributes no hit bits whatever the box test says
+            for (int a = 0; a < 3; ++a) q[a][w] |= 255u << sh;
+            continue;
+        }
+        const int c = bt.count(refs[i]);
+        if (c > kLeafMax) {
+            meta[w] |= (0x38u + (unsigned)sl) << sh;
+            imask |= 1u << sl;
+            out[out_base + k_inner] = WideItem{child_base + k_inner, refs[i]};
+            ++k_inner;
+        } else {
+            meta[w] |= ((((1u << c) - 1u) << 5) | (unsigned)k_tri) << sh;
+            const int f = bt.first(refs[i]);
+            for (int j = 0; j < c; ++j) perm[tri_base + k_tri + j] = f + j;
+            k_tri += c;
+        }
+        const float l3[3] = {clo[i].x, clo[i].y, clo[i].z}, h3[3] = {chi[i].x, chi[i].y, chi[i].z};
+        for (int a = 0; a < 3; ++a) {
+            const float margin = sc[a] * 0.0078125f;  // 2^-7 of a step
+            int ql = (int)floorf((l3[a] - p[a]) / sc[a]);
+            ql = max(0, min(255, ql));
+            while (ql > 0 && q_decode(ql, sc[a], p[a]) > l3[a] - margin) --ql;
+            int qh = (int)ceilf((h3[a] - p[a]) / sc[a]);
+            qh = max(0, min(255, qh));
+            while (qh < 255 && q_decode(qh, sc[a], p[a]) < h3[a] + margin) ++qh;
+            q[a][w] |= (unsigned)ql << sh;
+            q[3 + a][w] |= (unsigned)qh << sh;
+        }
+    }
+    float4 *o = nodes + kNodeRows * (size_t)item.node;
+    o[0] = make_float4(p[0], p[1], p[2], sc[0]);
+    o[1] = make_float4(sc[1], sc[2], __int_as_float(child_base), __int_as_float(tri_base));
+    o[2] = make_float4(__uint_as_float(meta[0]), __uint_as_float(meta[1]), __uint_as_float(imask), 0.0f);
+    o[3] = make_float4(__uint_as_float(q[0][0]), __uint_as_float(q[0][1]), __uint_as_float(q[1][0]), __uint_as_float(q[1][1]));
+    o[4] = make_float4(__uint_as_float(q[2][0]), __uint_as_float(q[2][1]), __uint_as_float(q[3][0]), __uint_as_float(q[3][1]));
+    o[5] = make_float4(__uint_as_float(q[4][0]), __uint_as_float(q[4][1]), __uint_as_float(q[5][0]), __uint_as_float(q[5][1]));
+}
+
+// final order of the BVH triangles: wide-node order (perm over the sorted positions) composed with the sort
+__global__ void k_compose_order(const int *__restrict__ perm, const int *__restrict__ vals, int nb, int *__restrict__ out) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < nb) out[k] = vals[perm[k]];
+}
+
+// scan records of the BVH triangles, in record order: the plane and the three edge planes of scan_singles (pt_trace.cuh)
+__global__ void k_pack_scans(const float *__restrict__ verts, const float4 *__restrict__ planes,
+                             const float *__restrict__ squares, const int *__restrict__ order, int nb, float eps,
+                             const BuildScratch *__restrict__ s, float4 *__restrict__ scans) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= nb) return;
+    const float amax = fmaxf(20.0f, fmaxf(fmaxf(fmaxf(fabsf(ord2f(s->lo[0])), fabsf(ord2f(s->hi[0]))),
+                                                fmaxf(fabsf(ord2f(s->lo[1])), fabsf(ord2f(s->hi[1])))),
+                                          fmaxf(fabsf(ord2f(s->lo[2])), fabsf(ord2f(s->hi[2])))));
+    const float slack = amax * (64.0f * 1.1920929e-7f);
+    const int i = order[k];
+    const float *v = verts + 9 * (size_t)i;
+    LargeTri t;
+    t.p[0] = mk(v[0], v[1], v[2]); t.p[1] = mk(v[3], v[4], v[5]); t.p[2] = mk(v[6], v[7], v[8]);
+    t.plane = planes[i];
+    t.S = squares[i];
+    t.idx = i;
+    t.mat = 0;
+    const V3 ng = normalize3(cross3(t.p[1] - t.p[0], t.p[2] - t.p[0]));
+    const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x;
+    const float e = tri_e(t, eps);
+    float4 *o = scans + 4 * (size_t)k;
+    o[0] = t.plane;
+    for (int j = 0; j < 3; ++j) o[1 + j] = edge_plane(t, j, ng, ok, e, slack);
+}
+
+// box of the whole tree and the two child boxes of the binary root (node layout of the root test, pt_scene.cuh)
 __global__ void k_root_box(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
-                           const float4 *__restrict__ box_hi, int nb, const float4 *__restrict__ node_lo,
-                           const float4 *__restrict__ node_hi, float4 *__restrict__ out2) {
-    if (nb > kLeafMax) {  // internal root: node 0
-        out2[0] = node_lo[0];
-        out2[1] = node_hi[0];
-        return;
+                           const float4 *__restrict__ box_hi, int nb, const int2 *__restrict__ children,
+                           const float4 *__restrict__ node_lo, const float4 *__restrict__ node_hi,
+                           float4 *__restrict__ out5) {
+    float4 l[2], h[2];
+    if (nb >= 2) {
+        const int2 c = children[0];
+        for (int k = 0; k < 2; ++k) {
+            const int ck = k ? c.y : c.x;
+            l[k] = ck >= 0 ? node_lo[ck] : box_lo[vals[~ck]];
+            h[k] = ck >= 0 ? node_hi[ck] : box_hi[vals[~ck]];
+        }
+    } else {
+        l[0] = l[1] = box_lo[vals[0]];
+        h[0] = h[1] = box_hi[vals[0]];
     }
-    float4 l = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.0f), h = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.0f);
-    for (int k = 0; k < nb; ++k) {
-        const float4 a = box_lo[vals[k]], b = box_hi[vals[k]];
-        l = make_float4(fminf(l.x, a.x), fminf(l.y, a.y), fminf(l.z, a.z), 0.0f);
-        h = make_float4(fmaxf(h.x, b.x), fmaxf(h.y, b.y), fmaxf(h.z, b.z), 0.0f);
-    }
-    out2[0] = l;
-    out2[1] = h;
+    out5[0] = make_float4(fminf(l[0].x, l[1].x), fminf(l[0].y, l[1].y), fminf(l[0].z, l[1].z), 0.0f);
+    out5[1] = make_float4(fmaxf(h[0].x, h[1].x), fmaxf(h[0].y, h[1].y), fmaxf(h[0].z, h[1].z), 0.0f);
+    out5[2] = make_float4(l[0].x, h[0].x, l[0].y, h[0].y);
+    out5[3] = make_float4(l[1].x, h[1].x, l[1].y, h[1].y);
+    out5[4] = make_float4(l[0].z, h[0].z, l[1].z, h[1].z);
 }
 
 // Factory (material.h:58-106) as data: which closures exist and the mirror's selection chance

@@ -1,15 +1,27 @@
 // pt_scene.cuh — device-resident scene layout shared by the LBVH builder and the render kernels.
 //
-// HBM layout (all 16-byte aligned, read with LDG.128):
-//   tris   4 x float4 per triangle, in BVH (Morton) order, the "large" triangles last:
+// HBM layout (all 32-byte aligned, read with 256-bit loads):
+//   tris   4 x float4 per triangle, in BVH (wide-node) order, the "large" triangles last — the EXACT record:
 //            [0] Triangle::plane_            (nx, ny, nz, w)            triangles.h:21,40-44
 //            [1] vertices_[0], square        (x, y, z, S)               triangles.h:23-24
 //            [2] vertices_[1], caller index  (x, y, z, bits(int))
 //            [3] vertices_[2], material id   (x, y, z, bits(int))
-//   nodes  4 x float4 per BVH2 node (both child boxes live in the parent, one 64-byte fetch per visit):
-//            [0] child0 lo.x hi.x lo.y hi.y   [1] child1 lo.x hi.x lo.y hi.y
-//            [2] child0 lo.z hi.z, child1 lo.z hi.z      [3] bits: child0 ref, child1 ref, 0, 0
-//          child ref >= 0: node index; < 0: leaf, bits 0..27 = first triangle record, bits 28..30 = count-1
+//   scans  4 x float4 per BVH triangle (records [0, n_bvh)) — the SCAN record, a conservative test in front of the
+//          exact one: [0] the plane again, [1..3] the three edge planes (m, w) of pt_bvh.cuh edge_plane: every point
+//          the reference's Intersect can accept satisfies m . P + w >= 0
+//   nodes  6 x float4 (96 bytes, three 256-bit loads) per 8-wide BVH node, child boxes quantised to 8 bits per plane
+//          on the node's own grid (Ylitie, Karras, Laine 2017, "Efficient incoherent ray traversal on GPUs through
+//          compressed wide BVHs" — layout adapted: float scales instead of exponents, 96-byte nodes):
+//            [0] origin p.xyz, scale s.x           [1] s.y, s.z, bits(child_base), bits(tri_base)
+//            [2] bits: meta[0..3], meta[4..7], imask, 0
+//            [3] bits: qlo.x[0..3], qlo.x[4..7], qlo.y[0..3], qlo.y[4..7]
+//            [4] bits: qlo.z[0..3], qlo.z[4..7], qhi.x[0..3], qhi.x[4..7]
+//            [5] bits: qhi.y[0..3], qhi.y[4..7], qhi.z[0..3], qhi.z[4..7]
+//          child box k = p + q[k] * s (lo rounded down, hi rounded up: k_collapse).  meta[k]: 0 = empty slot;
+//          inner child: 0x38 + k (its node index is child_base + number of inner children in lower slots, imask has
+//          bit k set); leaf child: (unary triangle count 1 / 3 / 7) << 5 | offset — its records are tri_base + offset ..
+//          Children sit in the slot whose octant (bit 0 x, bit 1 y, bit 2 z; set = towards +) matches the direction
+//          from the node's centre to theirs, so slot ^ (octant of the ray) orders them roughly front to back.
 //   mats   3 x float4 per material: (Kd.xyz, bits(lobe kind)), (Ks.xyz, mirror chance), (Ni, Tr, bits(lobe mask),
 //          diffuse chance) — the third row is read for MAT_MULTI (refractive extension) only
 #pragma once
@@ -19,9 +31,11 @@
 namespace ptd {
 
 #ifndef PT_LEAF_MAX
-#define PT_LEAF_MAX 4
+#define PT_LEAF_MAX 3
 #endif
-constexpr int kLeafMax = PT_LEAF_MAX;  // triangles per LBVH leaf (<= 8: leaf_count)
+constexpr int kLeafMax = PT_LEAF_MAX;  // triangles per leaf child of a wide node (1..3: unary count in meta)
+static_assert(PT_LEAF_MAX >= 1 && PT_LEAF_MAX <= 3, "a leaf child holds 1..3 triangles");
+constexpr int kNodeRows = 6;           // float4 rows per wide node
 constexpr int kMaxLarge = 64;        // triangles kept out of the LBVH and tested from shared memory first
 constexpr int kAllLargeMax = 48;     // scenes up to this size keep every triangle in shared memory (no LBVH)
 // Shared-memory image of the large triangles (k_large_pack), rows of float4:
@@ -31,19 +45,17 @@ constexpr int kAllLargeMax = 48;     // scenes up to this size keep every triang
 //   then n_single x kSingleRows  scan units of the remaining triangles (records 2 n_quads + s): plane, 3 edge planes
 constexpr int kQuadRows = 7, kSingleRows = 4;
 constexpr int kLargeRowsMax = 4 * kMaxLarge + kSingleRows * kMaxLarge;  // worst case: no pairs
-constexpr int kStackDepth = 96;      // traversal stack entries (LBVH depth <= 63 key bits + index tie-break bits)
-constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray
+// Traversal stack: uint2 entries (a group of inner children, or a group of triangles, still to visit).  A ray holds at
+// most two entries per level of the wide tree, and the builder knows the number of levels: a tree deeper than
+// kMaxLevels is refused at pt_scene_create (PT_ACCEL_AUTO then falls back to the brute-force scan) — never a silent drop.
+constexpr int kMaxLevels = 24;
+constexpr int kStackDepth = 2 * kMaxLevels;
+constexpr int kStatWords = 24;       // device statistics: 4 totals, queued rays, 16 log2 buckets of nodes per queued ray, [21] exact tests
 constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack sentinel
 
 // lobe kinds built by Factory (material.h:58-106)
 // MAT_MULTI (extension): a material with the refractive lobe; its lobe set is the mask in row 2 (1 mirror, 2 diffuse, 4 refract)
 enum : int { MAT_EMISSIVE = 0, MAT_NONE = 1, MAT_MIRROR = 2, MAT_DIFFUSE = 3, MAT_BOTH = 4, MAT_MULTI = 5 };
-
-__host__ __device__ __forceinline__ int leaf_ref(int first, int count) {
-    return (int)(0x80000000u | ((uint32_t)(count - 1) << 28) | (uint32_t)first);
-}
-__host__ __device__ __forceinline__ int leaf_first(int ref) { return ref & 0x0fffffff; }
-__host__ __device__ __forceinline__ int leaf_count(int ref) { return ((ref >> 28) & 7) + 1; }
 
 struct SceneView;
 __host__ __device__ __forceinline__ int large_rows(int n_large, int n_quads) {
@@ -51,18 +63,21 @@ __host__ __device__ __forceinline__ int large_rows(int n_large, int n_quads) {
 }
 
 struct SceneView {
-    const float4 *tris;
-    const float4 *nodes;
+    const float4 *tris;   // exact records
+    const float4 *scans;  // scan records of the BVH triangles
+    const float4 *nodes;  // wide nodes, node 0 = root
     const float4 *mats;
     int n_tri;    // all triangle records
     int n_bvh;    // records [0, n_bvh) are in the LBVH
     int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
     int n_quads;  // of which the first 2 n_quads form quad scan units
-    int root;     // child ref of the LBVH root (kRefEmpty if n_bvh == 0)
+    int root;     // 0 = wide node 0 is the root; kRefEmpty if n_bvh == 0
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)
     const float4 *lrecs;     // shared-memory image of the large triangles (layout above), large_rows() float4
-    float4 root_lo, root_hi; // box of the LBVH root
-    float4 root_n0, root_n1, root_n2;  // the root node's two child boxes (node layout rows 0..2) when root == 0
+    float4 root_lo, root_hi; // box of the BVH root
+    // the two child boxes of the binary tree's root (the whole box twice for a one-triangle tree), for the "does this
+    // ray have to walk the tree at all" test: n0 = child 0 (lo.x hi.x lo.y hi.y), n1 = child 1, n2 = (lo.z hi.z) x 2
+    float4 root_n0, root_n1, root_n2;
     const unsigned char *sky;  // equirect skybox, 24-bit BGR rows top-down (bitmap_image's layout); nullptr = none
     int sky_w, sky_h;
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off

@@ -13,7 +13,9 @@
 //                expensive inside test (3 cross products, 3 IEEE square roots) is DEFERRED: candidates are marked in
 //                a per-lane bit mask and resolved together after the scan, so that lanes whose candidates sit at
 //                different triangle indices still run the inside test in the same instructions.
-//   traverse     stack-based BVH2 traversal over the LBVH for rays whose t-range still reaches the root box.
+//   traverse     stack-based walk of the 8-wide BVH (node8_visit, bvh8_traverse) for rays whose t-range still reaches
+//                the root's boxes; a leaf triangle goes through its conservative scan record first (tri_test) and
+//                through the reference's exact test only if that marks it.
 #pragma once
 #include "pt_math.cuh"
 #include "pt_scene.cuh"
@@ -44,22 +46,6 @@ __device__ __forceinline__ float plane_distance(float4 p, V3 o, V3 d) {
     return -(o.x * p.x + o.y * p.y + o.z * p.z + p.w) / sd;
 }
 
-// the area-sum inside test of triangles.h:56-70 for the plane hit at distance nd; a = (v0, S), b = (v1, .), c = (v2, .)
-// Compile-time variant -DPT_INSIDE_APPROX=1 (0 = off, the default build; NOT yet measured — prepared for the next GPU
-// session, tools/ab_quick.py): the three areas first with MUFU.RSQ instead of three IEEE square roots.  The staged
-// test below accepts exactly when |S - (s1 + s2 + s3)| <= eps (the early exits follow from it, the areas being
-// non-negative), so a sum that misses the threshold by more than a margin covering every rounding on either side —
-// rsqrt.approx is within 2^-22, the sums within a few 2^-24 of S + s1 + s2 + s3 — decides; anything closer to the
-// threshold, and any NaN, goes through the exact test.
-#ifndef PT_INSIDE_APPROX
-#define PT_INSIDE_APPROX 0
-#endif
-#ifndef PT_TRI_PREREJECT
-#define PT_TRI_PREREJECT 0
-#endif
-#ifndef PT_COOP_EXACT
-#define PT_COOP_EXACT 0
-#endif
 // MUFU.RCP: at most 1 ulp from 1/x (PTX ISA, rcp.approx.ftz.f32); denormal inputs flush to zero -> +-inf
 __device__ __forceinline__ float rcp_approx(float x) {
     float r;
@@ -67,26 +53,11 @@ __device__ __forceinline__ float rcp_approx(float x) {
     return r;
 }
 
-__device__ __forceinline__ float rsqrt_approx(float x) {
-    float r;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-
+// the area-sum inside test of triangles.h:56-70 for the plane hit at distance nd; a = (v0, S), b = (v1, .), c = (v2, .)
 __device__ __forceinline__ bool inside_test(float4 a, float4 b, float4 c, V3 o, V3 d, float nd, float eps) {
     const float S = a.w;
     const V3 P = mk(o.x + d.x * nd, o.y + d.y * nd, o.z + d.z * nd);
     const V3 f0 = P - mk(a.x, a.y, a.z), f1 = P - mk(b.x, b.y, b.z), f2 = P - mk(c.x, c.y, c.z);
-#if PT_INSIDE_APPROX
-    {
-        const V3 c1 = cross3(f0, f1), c2 = cross3(f0, f2), c3 = cross3(f2, f1);
-        const float q1 = dot3(c1, c1), q2 = dot3(c2, c2), q3 = dot3(c3, c3);
-        const float sum = q1 * rsqrt_approx(q1) + q2 * rsqrt_approx(q2) + q3 * rsqrt_approx(q3);  // 0 * inf = NaN: exact path
-        const float dev = fabsf(S - sum), margin = 8e-6f * (S + sum);
-        if (dev > eps + margin) return false;
-        if (dev < eps - margin) return true;
-    }
-#endif
     const float s1 = length3(cross3(f0, f1));
     if (s1 > S + eps) return false;
     const float s2 = length3(cross3(f0, f2));
@@ -112,33 +83,6 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     float4 pl, a, b, c;
     ldg256(r, pl, a);
     ldg256(r + 2, b, c);
-#if PT_TRI_PREREJECT
-    // Compile-time variant (0 = off, the default build; NOT yet measured — prepared for the next GPU session): most
-    // candidates of a leaf fail the inside test, and they pay an IEEE division and up to three IEEE square roots to be
-    // told so (ncu: a third of the kernel's warp instructions, 6.7 of 32 lanes active).  Here the hit point comes from
-    // MUFU.RCP and the three areas from MUFU.RSQ; the candidate leaves when that area sum misses S by more than eps
-    // plus a bound on everything that separates it from the exact evaluation:
-    //   8e-6 (S + sum)     rsqrt (2^-22), the roundings of the sums on both sides
-    //   per * dP           the hit point moves by dP <= 1e-6 (|t| + |o|_1) (quotient within 2^-21, roundings of o + d t
-    //                      and of P - v), every area by at most dP times its edge; per <= 2 l1, l1 = sum of |P - v_k|_1
-    //   1e-6 l1^2          the products of the cross products round independently on both sides
-    // A NaN fails the comparison and goes on to the exact test.
-    {
-        const float sd = d.x * pl.x + d.y * pl.y + d.z * pl.z;
-        const float num = -(o.x * pl.x + o.y * pl.y + o.z * pl.z + pl.w);
-        const float tq = num * rcp_approx(sd);
-        const V3 Pq = mk(o.x + d.x * tq, o.y + d.y * tq, o.z + d.z * tq);
-        const V3 g0 = Pq - mk(a.x, a.y, a.z), g1 = Pq - mk(b.x, b.y, b.z), g2 = Pq - mk(c.x, c.y, c.z);
-        const V3 c1 = cross3(g0, g1), c2 = cross3(g0, g2), c3 = cross3(g2, g1);
-        const float q1 = dot3(c1, c1), q2 = dot3(c2, c2), q3 = dot3(c3, c3);
-        const float sum = q1 * rsqrt_approx(q1) + q2 * rsqrt_approx(q2) + q3 * rsqrt_approx(q3);
-        const float l1 = fabsf(g0.x) + fabsf(g0.y) + fabsf(g0.z) + fabsf(g1.x) + fabsf(g1.y) + fabsf(g1.z) + fabsf(g2.x) +
-                         fabsf(g2.y) + fabsf(g2.z);
-        const float dP = 1e-6f * (fabsf(tq) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
-        const float margin = 8e-6f * (a.w + sum) + 2.0f * l1 * dP + 1e-6f * l1 * l1;
-        if (fabsf(a.w - sum) > eps + margin) return;
-    }
-#endif
     const float nd = plane_distance(pl, o, d);
     if (!(nd <= h.t) || nd < eps) return;
     const int idx = __float_as_int(b.w);
@@ -299,184 +243,196 @@ __device__ __forceinline__ float box_entry(float lox, float hix, float loy, floa
     return tn <= tf * 1.0000003f ? tn : __int_as_float(0x7f800000);
 }
 
-// Does the ray [0, tmax] have to walk the tree?  Tested against the root's two child boxes (tighter than the root
-// box: on the 1M-triangle scene half of the rays that enter the root box leave it without entering a child).
+// Does the ray [0, tmax] have to walk the tree?  Tested against the two child boxes of the binary tree's root (tighter
+// than the root box: on the 1M-triangle scene half of the rays that enter the root box leave it without entering one).
 __device__ __forceinline__ bool reaches_root(const SceneView &sc, V3 o, V3 d, float tmax) {
     if (sc.root == kRefEmpty) return false;
     const float inf = __int_as_float(0x7f800000);
     const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    if (sc.root < 0)  // the whole tree is one leaf
-        return box_entry(sc.root_lo.x, sc.root_hi.x, sc.root_lo.y, sc.root_hi.y, sc.root_lo.z, sc.root_hi.z, o, inv, tmax) < inf;
     const float4 n0 = sc.root_n0, n1 = sc.root_n1, n2 = sc.root_n2;
     return box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, tmax) < inf ||
            box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, tmax) < inf;
 }
 
-// The triangles of one leaf: plane distances of all of them first (cheap, same instructions for every lane), then
-// the reference's exact test on those whose distance can still win (up to kLeafMax records, contiguous).
-template <bool COUNT>
-__device__ __forceinline__ void leaf_step(const SceneView &sc, int ref, V3 o, V3 d, float eps, Hit &h,
-                                          unsigned long long &n_tris) {
-    const int first = leaf_first(ref), cnt = leaf_count(ref);
-    unsigned mask = 0u;
-    // all plane rows first (independent loads in flight together), then the arithmetic
-    float4 pl[kLeafMax];
+// ---- 8-wide BVH (node layout: pt_scene.cuh, builder: pt_bvh.cuh k_collapse) ---------------------------------------
+__device__ __forceinline__ float fmin3(float a, float b, float c) {  // FMNMX3 (sm_100)
+    float r;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) {
+    float r;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c));
+    return r;
+}
+
+struct Ray8 {
+    V3 o, d;
+    V3 idir;        // 1 / d with |d| clamped away from 0: the slab arithmetic below must stay finite
+    unsigned oct4;  // octant of the direction (bit 0 x, 1 y, 2 z; set = non-negative), replicated into the 4 bytes
+};
+__device__ __forceinline__ float clamped_rcp(float d) {
+    // a component below 1e-18 moves the ray by less than 1e-16 over any distance inside the scene: far below the
+    // padding of the boxes
+    return 1.0f / (fabsf(d) > 1e-18f ? d : copysignf(1e-18f, d));
+}
+__device__ __forceinline__ void ray8_setup(V3 o, V3 d, Ray8 &r) {
+    r.o = o;
+    r.d = d;
+    r.idir = mk(clamped_rcp(d.x), clamped_rcp(d.y), clamped_rcp(d.z));
+    const unsigned oct = (r.idir.x >= 0.0f ? 1u : 0u) | (r.idir.y >= 0.0f ? 2u : 0u) | (r.idir.z >= 0.0f ? 4u : 0u);
+    r.oct4 = oct * 0x01010101u;
+}
+
+// 0xff in every byte of x whose top bit is set (PRMT's sign-replicate mode: selector nibbles 8 + i.  __byte_perm masks
+// the selector to 3 bits per nibble, so this has to be the PTX instruction itself)
+__device__ __forceinline__ unsigned sign_bytes(unsigned x) {
+    unsigned r;
+    asm("prmt.b32 %0, %1, 0, 0xba98;" : "=r"(r) : "r"(x));
+    return r;
+}
+
+// byte k of w as the float 1 + q 2^-15 (q in mantissa bits 8..15): one PRMT instead of a conversion
+template <int K>
+__device__ __forceinline__ float qfloat(unsigned w) {
+    return __uint_as_float(__byte_perm(w, 0x3f800000u, 0x7604 | (K << 4)));
+}
+
+// four children (one meta word, slots 4 W .. 4 W + 3) against the ray; returns their hit bits
+template <int K>
+__device__ __forceinline__ unsigned child_hit(unsigned nx, unsigned fx, unsigned ny, unsigned fy, unsigned nz, unsigned fz,
+                                              float Ax, float Bx, float Ay, float By, float Az, float Bz, float tmax,
+                                              unsigned child_bits4, unsigned bit_index4) {
+    // slab distances on the 2^15-scaled grid: (p + q s - o) / d = (1 + q 2^-15) (2^15 s / d) + ((p - o) / d - 2^15 s / d)
+    const float tlx = __fmaf_rn(qfloat<K>(nx), Ax, Bx), thx = __fmaf_rn(qfloat<K>(fx), Ax, Bx);
+    const float tly = __fmaf_rn(qfloat<K>(ny), Ay, By), thy = __fmaf_rn(qfloat<K>(fy), Ay, By);
+    const float tlz = __fmaf_rn(qfloat<K>(nz), Az, Bz), thz = __fmaf_rn(qfloat<K>(fz), Az, Bz);
+    const float tn = fmaxf(fmax3(tlx, tly, tlz), 0.0f);
+    const float tf = fminf(fmin3(thx, thy, thz), tmax);  // clipped against the best t with <=: equal distances are kept
+    const unsigned bits = (child_bits4 >> (8 * K)) & 0xffu, idx = (bit_index4 >> (8 * K)) & 0xffu;
+    return tn <= tf ? bits << idx : 0u;
+}
+
+// Visit of wide node `ni`: all 8 child boxes against the ray [0, tmax].  Returns the hit mask — bits 24..31 the inner
+// children, at position 24 + (slot ^ octant) so that the highest bit is the child to enter first; bits 0..23 the
+// triangles of the hit leaf children (record tri_base + bit) — and the node's child_base / tri_base / imask.
+// Conservative by construction of the grid (k_collapse) and the padding of the triangle boxes.
+__device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes, int ni, const Ray8 &r, float tmax,
+                                                unsigned &child_base, unsigned &tri_base, unsigned &imask) {
+    const float4 *nd = nodes + kNodeRows * (size_t)ni;
+    float4 r0, r1, r2, r3, r4, r5;
+    ldg256(nd, r0, r1);
+    ldg256(nd + 2, r2, r3);
+    ldg256(nd + 4, r4, r5);
+    child_base = __float_as_uint(r1.z);
+    tri_base = __float_as_uint(r1.w);
+    imask = __float_as_uint(r2.z);
+    const float Ax = r0.w * r.idir.x * 32768.0f, Ay = r1.x * r.idir.y * 32768.0f, Az = r1.y * r.idir.z * 32768.0f;
+    const float Bx = (r0.x - r.o.x) * r.idir.x - Ax, By = (r0.y - r.o.y) * r.idir.y - Ay, Bz = (r0.z - r.o.z) * r.idir.z - Az;
+    // near / far planes per axis by the direction's sign
+    const bool px = (r.oct4 & 1u) != 0u, py = (r.oct4 & 2u) != 0u, pz = (r.oct4 & 4u) != 0u;
+    const unsigned lx0 = __float_as_uint(r3.x), lx1 = __float_as_uint(r3.y), ly0 = __float_as_uint(r3.z), ly1 = __float_as_uint(r3.w);
+    const unsigned lz0 = __float_as_uint(r4.x), lz1 = __float_as_uint(r4.y), hx0 = __float_as_uint(r4.z), hx1 = __float_as_uint(r4.w);
+    const unsigned hy0 = __float_as_uint(r5.x), hy1 = __float_as_uint(r5.y), hz0 = __float_as_uint(r5.z), hz1 = __float_as_uint(r5.w);
+    unsigned hits = 0u;
 #pragma unroll
-    for (int k = 0; k < kLeafMax; ++k)
-        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    // The plane pass with an approximate reciprocal instead of up to kLeafMax IEEE divisions: numerator and denominator
-    // are the reference's own, MUFU.RCP is within 2^-21 of the IEEE quotient and the range is widened by 2e-6 relative
-    // (as in scan_singles), so every triangle the exact test can accept is marked; the exact test repeats the division
-    // for the marked ones.  A NaN marks.  (-3.7 % traversal time on the 1M-triangle scene: the leaf phase, with its
-    // divisions, square roots and few active lanes, is where the walk is short of issue slots.)
+    for (int w = 0; w < 2; ++w) {
+        const unsigned meta4 = __float_as_uint(w ? r2.y : r2.x);
+        const unsigned is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;           // low 5 bits >= 24
+        const unsigned inner_mask4 = sign_bytes(is_inner4 << 3);                    // 0xff in the bytes of inner children
+        const unsigned bit_index4 = (meta4 ^ (r.oct4 & inner_mask4)) & 0x1f1f1f1fu;  // inner: 24 + (slot ^ octant); leaf: offset
+        const unsigned child_bits4 = (meta4 >> 5) & 0x07070707u;                    // inner: 1; leaf: unary triangle count
+        const unsigned nx = w ? (px ? lx1 : hx1) : (px ? lx0 : hx0), fx = w ? (px ? hx1 : lx1) : (px ? hx0 : lx0);
+        const unsigned ny = w ? (py ? ly1 : hy1) : (py ? ly0 : hy0), fy = w ? (py ? hy1 : ly1) : (py ? hy0 : ly0);
+        const unsigned nz = w ? (pz ? lz1 : hz1) : (pz ? lz0 : hz0), fz = w ? (pz ? hz1 : lz1) : (pz ? hz0 : lz0);
+        hits |= child_hit<0>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
+        hits |= child_hit<1>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
+        hits |= child_hit<2>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
+        hits |= child_hit<3>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
+    }
+    return hits;
+}
+
+// One BVH triangle: its scan record (plane + three edge planes, the conservative test of scan_singles with the same
+// tolerances: approximate reciprocal, range widened by 2e-6 relative, edge planes already dilated by the builder; a
+// NaN anywhere marks), then the reference's exact test if marked.  Returns whether the exact test ran.
+__device__ __forceinline__ bool tri_test(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
+    const float4 *s = sc.scans + 4 * (size_t)rec;
+    float4 p, e0, e1, e2;
+    ldg256(s, p, e0);
+    ldg256(s + 2, e1, e2);
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
-#pragma unroll
-    for (int k = 0; k < kLeafMax; ++k) {
-        const float4 p = pl[k];
-        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
-        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
-        const float t = num * rcp_approx(sd);
-        mask |= (unsigned)(k < cnt && !((t > t_hi) | (t < t_lo))) << k;
-    }
-    while (mask) {
-        const int k = __ffs(mask) - 1;
-        mask &= mask - 1u;
-        tri_intersect_ref(sc.tris + 4 * (size_t)(first + k), first + k, o, d, eps, h);
-    }
-    if (COUNT) n_tris += cnt;
+    const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
+    const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
+    const float t = num * rcp_approx(sd);
+    const float tol = fabsf(t) * 2e-6f;
+    const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
+    const float g0 = __fmaf_rn(e0.x, Px, __fmaf_rn(e0.y, Py, __fmaf_rn(e0.z, Pz, e0.w)));
+    const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
+    const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
+    const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
+    if (out) return false;
+    tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, o, d, eps, h);
+    return true;
 }
 
-#if PT_COOP_EXACT
-// Compile-time variant (0 = off, the default build; NOT yet measured — prepared for the next GPU session): the exact
-// tests of a warp's leaf phase shared out over all 32 lanes.  As written above every lane runs its own candidates one
-// after the other — ncu: a third of the kernel's warp instructions at 6.7 active lanes.  Here the (ray, candidate)
-// pairs of the warp are numbered by a prefix sum over the lanes' candidate counts, lane i tests pair base + i with
-// the owner's ray fetched by shuffles, and every owner merges the results of its pairs (minimum t, ties to the lower
-// caller index: the nearest-hit rule does not depend on the order, pt_trace.cuh header).  All candidates of a leaf see
-// the t the ray came in with, so a hit no longer prunes its neighbours' inside tests — they run side by side instead.
+// Traversal state of one ray: a group of inner children still to enter (x = child_base, y = hit bits 24..31 | imask)
+// and a group of triangles still to test (x = tri_base, y = bits 0..23).  Stack entries are one or the other, told
+// apart by y > 0x00ffffff.
+__device__ __forceinline__ bool has_inner(uint2 g) { return g.y > 0x00ffffffu; }
 
-// the plane pass of leaf_step: candidate mask of leaf `ref` for this lane's ray
+// takes the nearest inner child out of node group `ng` (re-pushing the rest), visits it and leaves its hits in ng / tg
 template <bool COUNT>
-__device__ __forceinline__ unsigned leaf_candidates(const SceneView &sc, int ref, V3 o, V3 d, float eps, const Hit &h,
-                                                    unsigned long long &n_tris) {
-    const int first = leaf_first(ref), cnt = leaf_count(ref);
-    unsigned mask = 0u;
-    float4 pl[kLeafMax];
-#pragma unroll
-    for (int k = 0; k < kLeafMax; ++k)
-        pl[k] = k < cnt ? __ldg(sc.tris + 4 * (size_t)(first + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
-    const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
-#pragma unroll
-    for (int k = 0; k < kLeafMax; ++k) {
-        const float4 p = pl[k];
-        const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
-        const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
-        const float t = num * rcp_approx(sd);
-        mask |= (unsigned)(k < cnt && !((t > t_hi) | (t < t_lo))) << k;
-    }
-    if (COUNT) n_tris += cnt;
-    return mask;
+__device__ __forceinline__ void enter_child(const SceneView &sc, const Ray8 &r, float tmax, uint2 &ng, uint2 &tg,
+                                            uint2 *stack, int &sp, unsigned long long &n_nodes) {
+    const unsigned hits = ng.y;
+    const int bit = 31 - __clz((int)hits);
+    ng.y &= ~(1u << bit);
+    if (has_inner(ng)) stack[sp++] = ng;
+    const unsigned slot = (unsigned)(bit - 24) ^ (r.oct4 & 7u);
+    const int ni = (int)ng.x + __popc(hits & 0xffu & ~(0xffffffffu << slot));
+    unsigned cb, tb, im;
+    const unsigned hm = node8_visit(sc.nodes, ni, r, tmax, cb, tb, im);
+    if (COUNT) ++n_nodes;
+    ng = make_uint2(cb, (hm & 0xff000000u) | im);
+    tg = make_uint2(tb, hm & 0x00ffffffu);
 }
 
-// an accepted candidate (t, caller index, record) against the best hit so far
-__device__ __forceinline__ void hit_merge(const float4 *tris, Hit &h, float t, int idx, int rec) {
-    if (!(t <= h.t)) return;
-    if (t == h.t) {
-        if (h.idx == kIdxLazy) h.idx = __float_as_int(__ldg(tris + 4 * (size_t)h.rec + 2).w);
-        if (!(idx < h.idx)) return;
-    }
-    h.t = t;
-    h.idx = idx;
-    h.rec = rec;
-}
-
-// Must be reached by all 32 lanes.  mask / first: this lane's candidates (bit k = record first + k), 0 = none.
-__device__ __forceinline__ void coop_exact(const SceneView &sc, unsigned mask, int first, V3 o, V3 d, float eps, Hit &h) {
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const int mycnt = __popc(mask);
-    int incl = mycnt;  // inclusive prefix sum of the candidate counts
-#pragma unroll
-    for (int off = 1; off < 32; off <<= 1) {
-        const int v = __shfl_up_sync(full, incl, off);
-        if (lane >= off) incl += v;
-    }
-    const int start = incl - mycnt, total = __shfl_sync(full, incl, 31);
-    for (int base = 0; base < total; base += 32) {  // the same trip count for every lane
-        const int pair = base + lane;
-        // owner of the pair: the first lane whose inclusive sum exceeds it
-        int owner = 0;
-#pragma unroll
-        for (int step = 16; step; step >>= 1) {
-            const int v = __shfl_sync(full, incl, owner + step - 1);
-            if (v <= pair) owner += step;
-        }
-        const bool valid = pair < total;
-        owner = min(owner, 31);
-        int j = pair - __shfl_sync(full, start, owner);  // which of the owner's candidates
-        unsigned om = __shfl_sync(full, mask, owner);
-        const int ofirst = __shfl_sync(full, first, owner);
-        const V3 oo = mk(__shfl_sync(full, o.x, owner), __shfl_sync(full, o.y, owner), __shfl_sync(full, o.z, owner));
-        const V3 dd = mk(__shfl_sync(full, d.x, owner), __shfl_sync(full, d.y, owner), __shfl_sync(full, d.z, owner));
-        Hit hh;
-        hh.t = __shfl_sync(full, h.t, owner);
-        hh.idx = __shfl_sync(full, h.idx, owner);
-        hh.rec = __shfl_sync(full, h.rec, owner);
-        int got = -1;  // record of the accepted candidate
-        if (valid) {
-            for (; j > 0; --j) om &= om - 1u;
-            const int rec = ofirst + __ffs(om) - 1;
-            tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, oo, dd, eps, hh);
-            if (hh.rec == rec) got = rec;
-        }
-        // every owner collects the results of its pairs that were tested in this round
-#pragma unroll
-        for (int q = 0; q < kLeafMax; ++q) {
-            const int src = start - base + q;
-            const bool mine = q < mycnt && src >= 0 && src < 32;
-            const int s = mine ? src : lane;
-            const float rt = __shfl_sync(full, hh.t, s);
-            const int ri = __shfl_sync(full, hh.idx, s), rr = __shfl_sync(full, got, s);
-            if (mine && rr >= 0) hit_merge(sc.tris, h, rt, ri, rr);
-        }
-    }
-}
-#endif
-
-// One step on the inner node `cur` (>= 0); returns the next ref: a node, a leaf (< 0) or kRefEmpty when the stack ran out.
+// all triangles of group tg
 template <bool COUNT>
-__device__ __forceinline__ int node_step(const SceneView &sc, int cur, V3 o, V3 inv, const Hit &h, int *stack, int &sp,
-                                         unsigned long long &n_nodes) {
-    {
-        const float4 *nd = sc.nodes + 4 * (size_t)cur;
-        float4 n0, n1, n2, n3;
-        ldg256(nd, n0, n1);
-        ldg256(nd + 2, n2, n3);
-        if (COUNT) ++n_nodes;
-        // box_entry clips against h.t with <=, so that an equal-distance lower index is still found; +inf = miss
-        const float t0 = box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, h.t);
-        const float t1 = box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, h.t);
-        const int c0 = __float_as_int(n3.x), c1 = __float_as_int(n3.y);
-        const bool g0 = t0 < __int_as_float(0x7f800000), g1 = t1 < __int_as_float(0x7f800000);
-        if (g0 && g1) {
-            const bool swap = t1 < t0;
-            if (sp < kStackDepth) stack[sp++] = swap ? c0 : c1;
-            return swap ? c1 : c0;
-        }
-        if (g0) return c0;
-        if (g1) return c1;
-        return sp ? stack[--sp] : kRefEmpty;
+__device__ __forceinline__ void test_group(const SceneView &sc, const Ray8 &r, float eps, Hit &h, uint2 &tg,
+                                           unsigned long long &n_tris, unsigned long long &n_exact) {
+    while (tg.y) {
+        const int j = 31 - __clz((int)tg.y);
+        tg.y &= ~(1u << j);
+        const bool exact = tri_test(sc, (int)tg.x + j, r.o, r.d, eps, h);
+        if (COUNT) { ++n_tris; n_exact += exact ? 1u : 0u; }
     }
 }
 
-// One traversal step on `cur` (a node or a leaf ref); returns the next ref (kRefEmpty when the stack is empty).
+// the whole walk in one thread (pt_intersect, the megakernel)
 template <bool COUNT>
-__device__ __forceinline__ int traverse_step(const SceneView &sc, int cur, V3 o, V3 d, V3 inv, float eps, Hit &h,
-                                             int *stack, int &sp, unsigned long long &n_nodes,
-                                             unsigned long long &n_tris) {
-    if (cur >= 0) return node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
-    leaf_step<COUNT>(sc, cur, o, d, eps, h, n_tris);
-    return sp ? stack[--sp] : kRefEmpty;
+__device__ __forceinline__ void bvh8_traverse(const SceneView &sc, V3 o, V3 d, float eps, Hit &h,
+                                              unsigned long long &n_nodes, unsigned long long &n_tris) {
+    Ray8 r;
+    ray8_setup(o, d, r);
+    uint2 stack[kStackDepth];
+    int sp = 0;
+    uint2 ng = make_uint2(0u, 0x80000000u), tg = make_uint2(0u, 0u);  // the root as the only child of a virtual group
+    unsigned long long n_exact = 0;
+    while (true) {
+        if (has_inner(ng)) {
+            enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
+        } else {  // a triangle group popped from the stack
+            tg = ng;
+            ng = make_uint2(0u, 0u);
+        }
+        test_group<COUNT>(sc, r, eps, h, tg, n_tris, n_exact);
+        if (!has_inner(ng)) {
+            if (sp == 0) break;
+            ng = stack[--sp];
+        }
+    }
 }
 
 // scene.cpp:114-120 as written: every triangle, in order (the checker mode, PT_ACCEL_BRUTE)
@@ -497,11 +453,7 @@ __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_
     large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
     if (COUNT) n_tris += sc.n_large;
     if (!reaches_root(sc, o, d, h.t)) return h;
-    const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
-    int stack[kStackDepth];
-    int sp = 0;
-    int cur = sc.root;
-    while (cur != kRefEmpty) cur = traverse_step<COUNT>(sc, cur, o, d, inv, eps, h, stack, sp, n_nodes, n_tris);
+    bvh8_traverse<COUNT>(sc, o, d, eps, h, n_nodes, n_tris);
     return h;
 }
 

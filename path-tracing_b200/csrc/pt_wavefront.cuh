@@ -10,8 +10,9 @@
 //                  accumulators, jittered primary ray (main.cpp:118-129), then `front`:
 //     front        large triangles from shared memory (pt_trace.cuh large_phase), LBVH root test, and a
 //                  warp-ballot compaction of the rays that must walk the tree into a global queue
-//   k_wf_traverse  persistent warps drain the queue: every lane walks one ray and fetches the next one as soon as it
-//                  finishes (dynamic fetch), so the walk runs with full warps whatever fraction of rays got here
+//   k_wf_traverse  persistent warps drain the queue: every lane walks one ray through the 8-wide BVH and fetches the
+//                  next one as soon as it finishes (dynamic fetch), so the walk runs with full warps whatever
+//                  fraction of rays got here
 //   k_wf_bounce    per path slot: shade the hit (Material::Process and the closures, pt_kernels.cuh shade), spawn the
 //                  next segment and run `front` on it
 //   k_wf_commit    per pixel: the ordered commit of the Q samples (see pt_kernels.cuh header): exact replay of the
@@ -281,26 +282,21 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
     }
 }
 
-#ifndef PT_NODE_BURST
-#define PT_NODE_BURST 8      // upper bound of inner-node steps between two refill checks
-#endif
-#ifndef PT_MIN_NODE_LANES
-#define PT_MIN_NODE_LANES 8   // the node phase ends when fewer lanes than this can still take a node step
-#endif
 #ifndef PT_TRAV_MIN_BLOCKS
 #define PT_TRAV_MIN_BLOCKS 10  // resident blocks of 128 threads per SM the traversal kernel is compiled for
 #endif
 #ifndef PT_REFILL_MIN
-#define PT_REFILL_MIN 4       // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
+#define PT_REFILL_MIN 4        // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
 #endif
-constexpr int kNodeBurst = PT_NODE_BURST, kMinNodeLanes = PT_MIN_NODE_LANES;
+#ifndef PT_TRI_LANES
+#define PT_TRI_LANES 1         // lanes with triangles to test before the warp enters the triangle phase (1 = at once)
+#endif
 
-// persistent warps over queue `set`: one ray per lane, refilled as lanes finish.
-// while-while with a postponed leaf (Aila & Laine 2009, "speculative traversal"): a lane that reaches a leaf parks
-// it and keeps walking inner nodes until it reaches a second one; the warp switches to the leaf phase only when few
-// lanes can still take a node step, so that the expensive exact triangle tests run with most lanes active (the
-// first version of this kernel ran them with 3 of 32, profiles/r01_wf_sass_traverse_torus1m.txt).  Walking on
-// with a not-yet-shortened t only visits extra nodes: the nearest-hit rule is order independent (pt_trace.cuh).
+// persistent warps over queue `set`: one ray per lane, refilled as lanes finish (dynamic fetch).  Every round of the
+// loop a lane enters at most one wide node (node phase) and tests the triangles that node handed it (triangle phase);
+// with PT_TRI_LANES > 1 the triangle phase waits until that many lanes have triangles (the group is parked on the
+// lane's stack meanwhile, Ylitie et al. 2017) — walking on with a not-yet-shortened t only visits extra nodes, the
+// nearest-hit rule is order independent (pt_trace.cuh).
 template <bool COUNT>
 __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
@@ -309,14 +305,19 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     int *head = &wf.counters[2 * set + 1];
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
-    int stack[kStackDepth];
-    int sp = 0, cur = kRefEmpty, leaf = 0, slot = -1;  // leaf refs are negative: 0 = no parked leaf
+    uint2 stack[kStackDepth];
+    int sp = 0, slot = -1;
+    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
     bool done = false;
-    V3 o = mk(0, 0, 0), d = mk(0, 0, 1), inv = mk(0, 0, 1);
+    Ray8 r;
+    ray8_setup(mk(0, 0, 0), mk(0, 0, 1), r);
     Hit h = no_hit();
-    unsigned long long n_nodes = 0, n_tris = 0, ray_nodes0 = 0;
+    unsigned long long n_nodes = 0, n_tris = 0, n_exact = 0, ray_nodes0 = 0;
+#if PT_TRI_LANES > 1
+    unsigned round = 0;
+#endif
     while (true) {
-        const bool need = !done && cur == kRefEmpty && leaf == 0;
+        const bool need = !done && !has_inner(ng) && tg.y == 0u && sp == 0;
         if (need && slot >= 0) {  // retire the finished ray
             if (COUNT && stats) {
                 atomicAdd(&stats[4], 1ull);
@@ -327,13 +328,9 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             slot = -1;
         }
         const unsigned m = __ballot_sync(0xffffffffu, need);
-#if PT_REFILL_MIN > 1
         // a refill is a chain of dependent fetches (queue head, queue entry, ray state) the whole warp sits through
         const unsigned busy = __ballot_sync(0xffffffffu, !need && !done);
         if (m && (__popc(m) >= PT_REFILL_MIN || busy == 0u)) {
-#else
-        if (m) {
-#endif
             const int leader = __ffs(m) - 1;
             int base = 0;
             if (lane == leader) base = atomicAdd(head, __popc(m));
@@ -343,14 +340,11 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
                 if (qi < count) {
                     slot = __ldcs(&queue[qi]);
                     const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
-                    o = mk(ot.x, ot.y, ot.z);
-                    d = mk(dr.x, dr.y, dr.z);
-                    inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+                    ray8_setup(mk(ot.x, ot.y, ot.z), mk(dr.x, dr.y, dr.z), r);
                     h.t = ot.w;
                     h.rec = __float_as_int(dr.w);
                     h.idx = h.rec >= 0 ? kIdxLazy : -1;
-                    cur = sc.root;
-                    sp = 0;
+                    ng = make_uint2(0u, 0x80000000u);  // the root as the only child of a virtual group
                     ray_nodes0 = n_nodes;
                 } else {
                     done = true;
@@ -358,49 +352,39 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             }
         }
         if (__all_sync(0xffffffffu, done)) break;
-        // ---- node phase
-#pragma unroll 1
-        for (int it = 0; it < kNodeBurst; ++it) {
-            if (cur < 0 && leaf == 0) {  // park the leaf, go on with the next subtree
-                leaf = cur;
-                cur = sp ? stack[--sp] : kRefEmpty;
-            }
-            const bool can = cur >= 0 && cur != kRefEmpty;
-            const unsigned cm = __ballot_sync(0xffffffffu, can);
-            if (cm == 0u || (it > 0 && __popc(cm) < kMinNodeLanes)) break;
-            if (can) cur = node_step<COUNT>(sc, cur, o, inv, h, stack, sp, n_nodes);
+        // ---- pop: a lane with nothing in hand takes the top of its stack
+        if (!has_inner(ng) && tg.y == 0u && sp > 0) {
+            const uint2 e = stack[--sp];
+            if (has_inner(e)) ng = e; else tg = e;
         }
-        if (cur < 0 && leaf == 0) {
-            leaf = cur;
-            cur = sp ? stack[--sp] : kRefEmpty;
-        }
-        // ---- leaf phase: every parked leaf
-#if PT_COOP_EXACT
-        if (__any_sync(0xffffffffu, leaf != 0)) {
-            unsigned cand = 0u;
-            int first = 0;
-            if (leaf != 0) {
-                cand = leaf_candidates<COUNT>(sc, leaf, o, d, eps, h, n_tris);
-                first = leaf_first(leaf);
-                leaf = 0;
-            }
-            coop_exact(sc, cand, first, o, d, eps, h);
-        }
-#else
-        if (__any_sync(0xffffffffu, leaf != 0)) {
-            if (leaf != 0) {
-                leaf_step<COUNT>(sc, leaf, o, d, eps, h, n_tris);
-                leaf = 0;
-            }
+#if PT_TRI_LANES > 1
+        else if (!has_inner(ng) && sp > 0 && has_inner(stack[sp - 1])) {  // waiting triangles: swap them for the node group below
+            const uint2 e = stack[sp - 1];
+            stack[sp - 1] = tg;
+            tg.y = 0u;
+            ng = e;
         }
 #endif
+        // ---- node phase: one wide node per lane
+        if (has_inner(ng)) {
+            if (tg.y) { stack[sp++] = tg; tg.y = 0u; }  // parked triangles (PT_TRI_LANES > 1 only)
+            enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
+        }
+        // ---- triangle phase
+#if PT_TRI_LANES > 1
+        const unsigned mt = __ballot_sync(0xffffffffu, tg.y != 0u), mn = __ballot_sync(0xffffffffu, has_inner(ng));
+        ++round;
+        if (__popc(mt) >= PT_TRI_LANES || mn == 0u || (round & 7u) == 0u)
+#endif
+            test_group<COUNT>(sc, r, eps, h, tg, n_tris, n_exact);
     }
     if (COUNT && stats) {
         for (int o2 = 16; o2; o2 >>= 1) {
             n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
             n_tris += __shfl_xor_sync(0xffffffffu, n_tris, o2);
+            n_exact += __shfl_xor_sync(0xffffffffu, n_exact, o2);
         }
-        if (lane == 0) { atomicAdd(&stats[2], n_nodes); atomicAdd(&stats[3], n_tris); }
+        if (lane == 0) { atomicAdd(&stats[2], n_nodes); atomicAdd(&stats[3], n_tris); atomicAdd(&stats[21], n_exact); }
     }
 }
 

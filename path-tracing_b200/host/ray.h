@@ -9,6 +9,8 @@
 
 class Ray {
     ptm::vec4 begin_, direction_;
+    ptm::vec4 given_direction_;  // the direction as handed in, before normalisation: what Scene::Intersect passes on
+                                 // (pt_intersect normalises as the constructor does; normalising twice moves the last bit)
     int depth_ = 0;
     int coord_x_ = 0, coord_y_ = 0;
     ptm::vec3 color_ = ptm::vec3(1);
@@ -22,11 +24,12 @@ class Ray {
 public:
     Ray() = default;
     Ray(ptm::vec4 begin, ptm::vec4 direction, int depth, int px, int py)
-        : begin_(begin), direction_(unit(direction)), depth_(depth), coord_x_(px), coord_y_(py) {}
+        : begin_(begin), direction_(unit(direction)), given_direction_(direction), depth_(depth), coord_x_(px), coord_y_(py) {}
     ptm::vec4 GetBegin() const { return begin_; }
     void SetBegin(ptm::vec4 b) { begin_ = b; }
     ptm::vec4 GetDirection() const { return direction_; }
-    void SetDirection(ptm::vec4 d) { direction_ = unit(d); }
+    void SetDirection(ptm::vec4 d) { direction_ = unit(d); given_direction_ = d; }
+    ptm::vec4 GetGivenDirection() const { return given_direction_; }
     int GetDepth() const { return depth_; }
     void SetDepth(int d) { depth_ = d; }
     int GetX() const { return coord_x_; }
@@ -37,6 +40,7 @@ public:
     void Reflect(ptm::vec4 begin, ptm::vec4 direction, ptm::vec3 color) {
         begin_ = begin;
         direction_ = unit(direction);
+        given_direction_ = direction;
         color_ = color_ * color;
         ++depth_;
     }

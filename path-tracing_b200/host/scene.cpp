@@ -635,8 +635,8 @@ PtScene Scene::abi() const {
 int Scene::Intersect(const std::vector<Ray> &rays, const PtConfig &cfg, std::vector<int32_t> &ids, std::vector<float> &t) const {
     const PtScene s = abi();
     std::vector<float> rays6(6 * rays.size());
-    for (size_t i = 0; i < rays.size(); ++i) {  // Ray keeps a unit direction (ray.h:21-25); pt_intersect normalises again: a no-op
-        const vec4 o = rays[i].GetBegin(), d = rays[i].GetDirection();
+    for (size_t i = 0; i < rays.size(); ++i) {  // pt_intersect normalises the direction exactly as Ray's constructor did (ray.h:21-25)
+        const vec4 o = rays[i].GetBegin(), d = rays[i].GetGivenDirection();
         rays6[6 * i] = o.x; rays6[6 * i + 1] = o.y; rays6[6 * i + 2] = o.z;
         rays6[6 * i + 3] = d.x; rays6[6 * i + 4] = d.y; rays6[6 * i + 5] = d.z;
     }

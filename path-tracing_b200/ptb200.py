@@ -44,7 +44,8 @@ class PtStats(C.Structure):
                 ("tris_tested", C.c_uint64), ("kernel_ms", C.c_float), ("build_ms", C.c_float),
                 ("upload_ms", C.c_float), ("n_nodes", C.c_int32), ("n_large", C.c_int32), ("accel", C.c_int32),
                 ("launches", C.c_int32), ("class_ms", C.c_float * 4), ("class_launches", C.c_int32 * 4),
-                ("rays_queued", C.c_uint64), ("node_hist", C.c_uint64 * 16), ("n_quads", C.c_int32), ("reserved0", C.c_int32)]
+                ("rays_queued", C.c_uint64), ("node_hist", C.c_uint64 * 16), ("n_quads", C.c_int32), ("n_levels", C.c_int32),
+                ("exact_tests", C.c_uint64)]
 
 
 class PtPostConfig(C.Structure):
