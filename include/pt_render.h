@@ -92,11 +92,18 @@ typedef struct PtConfig {
                              After each Reflect: p = clamp(max(T), 0.05, 1), survive when u < p (u = word 3 of the
                              bounce's Philox block), then T /= p and the path weight w /= p.  The estimator's divisor
                              (samples_count, main.cpp:180) becomes the sum of the contributing paths' weights. */
-    int32_t n_gpus;       /* 0/1 = one device; N > 1 (pt_render, pt_render_accum(_w), pt_render_image): the samples are
-                             dealt round-robin to devices device .. device + N - 1 of this process (one host thread
-                             each, every device holds the whole scene), the partial accumulators are summed onto
-                             the first device over NVLink in rank order, then resolved there.  The
-                             one-process-per-GPU launch sets sample_begin / sample_step itself and leaves this 1. */
+    int32_t n_gpus;       /* 0/1 = one device; N > 1 (pt_render, pt_render_accum(_w), pt_render_image): devices device ..
+                             device + N - 1 of this process share the frame (one host thread each, every device holds
+                             the whole scene and a full frame of accumulators), then ONE NCCL sum-reduce over NVLink
+                             brings (color_map, color2_map, samples_count, weights) onto the first device, where the
+                             frame is resolved.  Flat-spp renders (error < 0) deal the SAMPLES round-robin to the
+                             devices.  With the adaptive rule on (error >= 0) a sample's fate depends on the pixel's
+                             earlier samples (main.cpp:118-125), so the devices take bands of image ROWS instead and
+                             every pixel sees all of its samples in order: the result is bit-identical to one
+                             device (the reduce then only adds zeros).  PT_ENCCL if libnccl.so.2 cannot be loaded
+                             (searched: $PT_NCCL_LIB, an NCCL already in the process, the system library) or a
+                             collective fails.  The one-process-per-GPU launch sets sample_begin / sample_step
+                             (or row_begin / row_end) itself and leaves this 1. */
     int32_t device;       /* first CUDA device ordinal */
     int32_t reserved[4];  /* [0]: 0 = wavefront pipeline (default), 1 = megakernel variant;
                              [1]: 0 = automatic, 1..6 = log2 of the samples per pixel one wavefront step carries;
@@ -108,6 +115,9 @@ typedef struct PtConfig {
                              [3]: alive lists of the wavefront pipeline (bounce launches work on the paths still alive
                                   instead of all path slots; same result either way): 0 = automatic (on under
                                   Russian roulette, the adaptive rule or a skybox), 1 = on, 2 = off */
+    int32_t row_begin, row_end; /* image rows [row_begin, row_end) traced by this call; 0, 0 = all rows.  The other
+                                   pixels come back zero (in RESUME mode: unchanged).  The partition a multi-GPU host
+                                   uses when the adaptive rule is on (see n_gpus). */
 } PtConfig;
 
 /* Statistics of the last render on a scene handle. */

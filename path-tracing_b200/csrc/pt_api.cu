@@ -1,6 +1,8 @@
 // pt_api.cu — the C-ABI of include/pt_render.h: scene upload + SoA repack + LBVH build, render, intersect.
 // Compiled for sm_100a only, with -fmad=false (see pt_math.cuh).  There is no CPU path in this library.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
 #include <stdarg.h>
 #include <stdio.h>
 #include <string.h>
@@ -182,6 +184,8 @@ static int validate_config(const PtConfig *c) {
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
     if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
     if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
+    if ((c->row_begin != 0 || c->row_end != 0) && (c->row_begin < 0 || c->row_end > c->height || c->row_begin > c->row_end))
+        return fail(PT_EINVAL, "row range [%d, %d) outside the image (height %d)", c->row_begin, c->row_end, c->height);
     if (c->reserved[1] < 0 || c->reserved[1] > 6 || c->reserved[2] < 0 || c->reserved[2] > 1 || c->reserved[3] < 0 || c->reserved[3] > 2)
         return fail(PT_EINVAL, "reserved[1] must be 0..6 (log2 samples per wavefront step), reserved[2] 0/1 (resume), "
                                "reserved[3] 0..2 (alive lists: automatic / on / off)");
@@ -197,7 +201,10 @@ extern "C" int pt_device_count(void) {
     return n;
 }
 
+namespace { void drop_cached_scenes(); void drop_nccl_comms(); }
 extern "C" void pt_release_workspace(void) {
+    drop_cached_scenes();
+    drop_nccl_comms();
     std::lock_guard<std::mutex> lock(g_pool.m);
     for (auto &kv : g_pool.free_blocks) cudaFree(kv.second);
     g_pool.free_blocks.clear();
@@ -215,7 +222,11 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
         fprintf(stderr, "[pt_scene_destroy] %-12s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
         t0 = t1;
     };
-    cudaDeviceSynchronize();  // blocks go back to the pool: nothing may still be using them (cudaFree used to wait)
+    // blocks go back to the pool keyed by THEIR device: wait for that device, whichever one is current
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (cur != ds->device) cudaSetDevice(ds->device);
+    cudaDeviceSynchronize();
     pool_free(ds->tris);
     pool_free(ds->scans);
     pool_free(ds->nodes);
@@ -231,6 +242,7 @@ extern "C" void pt_scene_destroy(PtDeviceScene *ds) {
     if (ds->ev0) cudaEventDestroy(ds->ev0);
     if (ds->ev1) cudaEventDestroy(ds->ev1);
     for (cudaEvent_t e : ds->class_events) cudaEventDestroy(e);
+    if (cur != ds->device) cudaSetDevice(cur);
     delete ds;
 }
 
@@ -427,6 +439,167 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     return PT_OK;
 }
 
+// ---- device-scene cache ---------------------------------------------------------------------------------------------
+// The host-scene entry points (pt_render, pt_render_accum, pt_render_image, pt_intersect, ...) used to upload the scene
+// and rebuild the BVH on every call and on every device: 15 ms for the 1M-triangle scene, a quarter of its 8-GPU
+// frame.  A frame loop passes the same arrays again and again, so the built PtDeviceScene is kept per device, keyed
+// by the CONTENT of the caller's arrays (a 64-bit hash of every byte, computed once per call on several host threads:
+// about 1 ms for 40 MB) together with everything else the build depends on.  A call whose scene is not there builds it
+// and evicts the least recently used one (2 per device).  pt_release_workspace() empties the cache.
+namespace {
+
+inline uint64_t mix64(uint64_t h, uint64_t w) {
+    h ^= w;
+    h *= 0x9E3779B97F4A7C15ull;
+    return h ^ (h >> 29);
+}
+uint64_t hash_block(const unsigned char *p, size_t n) {
+    uint64_t h0 = 0x243F6A8885A308D3ull, h1 = 0x13198A2E03707344ull, h2 = 0xA4093822299F31D0ull, h3 = 0x082EFA98EC4E6C89ull;
+    size_t i = 0;
+    for (; i + 32 <= n; i += 32) {
+        uint64_t w[4];
+        memcpy(w, p + i, 32);
+        h0 = mix64(h0, w[0]); h1 = mix64(h1, w[1]); h2 = mix64(h2, w[2]); h3 = mix64(h3, w[3]);
+    }
+    if (i < n) {  // the last partial 32 bytes, zero padded
+        uint64_t w[4] = {0, 0, 0, 0};
+        memcpy(w, p + i, n - i);
+        h0 = mix64(h0, w[0]); h1 = mix64(h1, w[1]); h2 = mix64(h2, w[2]); h3 = mix64(h3, w[3]);
+    }
+    return mix64(mix64(mix64(mix64(h0, h1), h2), h3), n);
+}
+uint64_t hash_array(const void *ptr, size_t bytes, uint64_t seed) {
+    if (!ptr || !bytes) return mix64(seed, 0x5bd1e995u);
+    const unsigned char *p = (const unsigned char *)ptr;
+    const size_t chunk = (size_t)1 << 20;
+    const size_t n_chunks = (bytes + chunk - 1) / chunk;
+    std::vector<uint64_t> part(n_chunks);
+    auto work = [&](size_t c0, size_t c1) {
+        for (size_t c = c0; c < c1; ++c) part[c] = hash_block(p + c * chunk, std::min(chunk, bytes - c * chunk));
+    };
+    const size_t n_thr = std::min<size_t>(std::min<size_t>(8, std::max(1u, std::thread::hardware_concurrency())), n_chunks / 4);
+    if (n_thr <= 1) {
+        work(0, n_chunks);
+    } else {
+        std::vector<std::thread> th;
+        for (size_t t = 0; t < n_thr; ++t) th.emplace_back(work, n_chunks * t / n_thr, n_chunks * (t + 1) / n_thr);
+        for (std::thread &t : th) t.join();
+    }
+    uint64_t h = mix64(seed, bytes);
+    for (uint64_t v : part) h = mix64(h, v);
+    return h;
+}
+
+struct SceneKey {
+    uint64_t hash = 0;
+    int n_tri = 0, n_mat = 0, sky_w = 0, sky_h = 0, accel = 0;
+    float eps = 0.f;
+    bool operator==(const SceneKey &o) const {
+        return hash == o.hash && n_tri == o.n_tri && n_mat == o.n_mat && sky_w == o.sky_w && sky_h == o.sky_h &&
+               accel == o.accel && memcmp(&eps, &o.eps, sizeof eps) == 0;
+    }
+};
+SceneKey scene_key(const PtScene *s, const PtConfig *cfg) {
+    SceneKey k;
+    k.n_tri = s->n_triangles; k.n_mat = s->n_materials;
+    k.accel = cfg ? cfg->accel : PT_ACCEL_AUTO;
+    k.eps = cfg ? cfg->eps : 1e-4f;
+    const size_t n = (size_t)s->n_triangles, m = (size_t)s->n_materials;
+    uint64_t h = 0x6a09e667f3bcc908ull;
+    h = hash_array(s->vertices, 36 * n, h);
+    h = hash_array(s->planes, s->planes ? 16 * n : 0, h);
+    h = hash_array(s->squares, s->squares ? 4 * n : 0, h);
+    h = hash_array(s->material_ids, 4 * n, h);
+    h = hash_array(s->materials, 40 * m, h);
+    h = hash_array(s->materials_ext, s->materials_ext ? 8 * m : 0, h);
+    if (s->sky_bgr && s->sky_width > 0 && s->sky_height > 0) {
+        k.sky_w = s->sky_width; k.sky_h = s->sky_height;
+        h = hash_array(s->sky_bgr, (size_t)s->sky_width * s->sky_height * 3, h);
+    }
+    k.hash = h;
+    return k;
+}
+
+struct CachedScene {
+    SceneKey key;
+    PtDeviceScene *ds = nullptr;
+    int device = 0;
+    bool in_use = false;
+    uint64_t stamp = 0;
+};
+std::mutex g_cache_m;
+std::vector<CachedScene> g_cache;
+uint64_t g_cache_clock = 0;
+constexpr int kCachePerDevice = 2;
+
+// the built scene for `key` on the current device: from the cache, or built now (validated by the caller)
+int acquire_scene(const PtScene *scene, const PtConfig *cfg, const SceneKey &key, PtDeviceScene **out) {
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    {
+        std::lock_guard<std::mutex> lock(g_cache_m);
+        for (CachedScene &c : g_cache)
+            if (!c.in_use && c.device == dev && c.key == key) {
+                c.in_use = true;
+                c.stamp = ++g_cache_clock;
+                *out = c.ds;
+                (*out)->upload_ms = 0.f;  // nothing was uploaded or built for this call
+                (*out)->build_ms = 0.f;
+                return PT_OK;
+            }
+    }
+    PtDeviceScene *ds = nullptr;
+    int rc = pt_scene_create(scene, cfg, 0, &ds);
+    if (rc) return rc;
+    std::vector<PtDeviceScene *> evict;
+    {
+        std::lock_guard<std::mutex> lock(g_cache_m);
+        int n_dev = 0;
+        for (const CachedScene &c : g_cache) n_dev += c.device == dev;
+        while (n_dev >= kCachePerDevice) {  // drop the least recently used idle entry of this device
+            int victim = -1;
+            for (size_t i = 0; i < g_cache.size(); ++i)
+                if (g_cache[i].device == dev && !g_cache[i].in_use && (victim < 0 || g_cache[i].stamp < g_cache[victim].stamp)) victim = (int)i;
+            if (victim < 0) break;
+            evict.push_back(g_cache[victim].ds);
+            g_cache.erase(g_cache.begin() + victim);
+            --n_dev;
+        }
+        CachedScene c;
+        c.key = key; c.ds = ds; c.device = dev; c.in_use = true; c.stamp = ++g_cache_clock;
+        g_cache.push_back(c);
+    }
+    for (PtDeviceScene *e : evict) pt_scene_destroy(e);
+    *out = ds;
+    return PT_OK;
+}
+// hands the scene back (the work issued on it must have been waited for, as for pt_scene_destroy)
+void release_scene(PtDeviceScene *ds) {
+    if (!ds) return;
+    std::lock_guard<std::mutex> lock(g_cache_m);
+    for (CachedScene &c : g_cache)
+        if (c.ds == ds) { c.in_use = false; return; }
+}
+void drop_cached_scenes() {
+    std::vector<PtDeviceScene *> all;
+    {
+        std::lock_guard<std::mutex> lock(g_cache_m);
+        for (size_t i = 0; i < g_cache.size();)
+            if (!g_cache[i].in_use) { all.push_back(g_cache[i].ds); g_cache.erase(g_cache.begin() + i); } else ++i;
+    }
+    for (PtDeviceScene *e : all) pt_scene_destroy(e);
+}
+struct SceneLease {  // RAII: wait for the device (an error path may leave work in flight), then hand the scene back
+    PtDeviceScene *p = nullptr;
+    ~SceneLease() {
+        if (!p) return;
+        cudaDeviceSynchronize();
+        release_scene(p);
+    }
+};
+
+}  // namespace
+
 static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum2, int *d_count, float *d_weight,
                                 unsigned long long *stats) {
     RenderParams rp{};
@@ -448,7 +621,8 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     //    but a small one is bound by the number of launches (each at least one dependent-fetch chain long) and
     //    takes as many as it needs to reach 6 M slots per step (512 x 512: 32).
     const int per_rank = std::max(0, cfg->rays_per_pixel - cfg->sample_begin) / (cfg->sample_step > 0 ? cfg->sample_step : 1);
-    const long long px = (long long)cfg->width * cfg->height, small_frame = 6000000;
+    const int rows = (cfg->row_begin != 0 || cfg->row_end != 0) ? cfg->row_end - cfg->row_begin : cfg->height;
+    const long long px = (long long)cfg->width * rows, small_frame = 6000000;
     int q_auto = 2;
     if (cfg->error < 0.0f) {
         while (q_auto < 6 && (2 << q_auto) <= per_rank) ++q_auto;
@@ -466,13 +640,16 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     rp.rr_depth = cfg->rr_depth;
     rp.weight = d_weight;
     rp.resume = cfg->reserved[2] == 1;
+    rp.row0 = 0; rp.row1 = cfg->height;
+    if (cfg->row_begin != 0 || cfg->row_end != 0) { rp.row0 = cfg->row_begin; rp.row1 = cfg->row_end; }
     return rp;
 }
 
 constexpr size_t kMaxSlots = (size_t)1 << 27;  // path slots in flight (64 B of state + 16 B of queues each: <= 10.8 GB)
 
-static int wf_reserve(PtDeviceScene *ds, size_t npx, int q_shift) {
-    const size_t npc = std::min(npx, kMaxSlots >> q_shift), slots = npc << q_shift;
+// npx: pixels of the frame (accumulators), npx_traced: pixels of the rows this call traces (path slots)
+static int wf_reserve(PtDeviceScene *ds, size_t npx, size_t npx_traced, int q_shift) {
+    const size_t npc = std::min(std::max<size_t>(npx_traced, 1), kMaxSlots >> q_shift), slots = npc << q_shift;
     const size_t npx4 = (npx + 3) & ~(size_t)3;  // keeps the queue 16-byte aligned behind the per-pixel weights
     const size_t slot_blocks = (slots + kWfBlock - 1) / kWfBlock;
     const size_t alive_seg = (slot_blocks + kAliveLists - 1) / kAliveLists * kWfBlock;  // capacity of one sub-list
@@ -515,7 +692,7 @@ template <bool COUNT>
 static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStream_t st, int *launches) {
     const size_t npx = (size_t)rp.W * rp.H;
     int rc;
-    if ((rc = wf_reserve(ds, npx, rp.q_shift))) return rc;
+    if ((rc = wf_reserve(ds, npx, (size_t)(rp.row1 - rp.row0) * rp.W, rp.q_shift))) return rc;
     const int Q = 1 << rp.q_shift;
     const WfState wf = ds->wf;
     const SceneView &sc = ds->view;
@@ -560,8 +737,9 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     };
     CK(cudaMemsetAsync(wf.counters, 0, (kWfCounters + 3 * kAliveLists) * sizeof(int), st));
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
-    for (size_t pix0 = 0; pix0 < npx && total > 0; pix0 += npc_max) {
-        const int npix = (int)std::min<size_t>(npc_max, npx - pix0);
+    const size_t pix_end = (size_t)rp.row1 * rp.W;  // the rows this call traces (PtConfig::row_begin / row_end)
+    for (size_t pix0 = (size_t)rp.row0 * rp.W; pix0 < pix_end && total > 0; pix0 += npc_max) {
+        const int npix = (int)std::min<size_t>(npc_max, pix_end - pix0);
         const int slot_blocks = blocks_for((long long)npix << rp.q_shift, kWfBlock);
         int remaining = total;
         while (remaining > 0) {
@@ -698,39 +876,127 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
 
 extern "C" int pt_intersect(const PtScene *scene, const PtConfig *cfg, const float *rays6, int64_t n, int32_t *tri_id,
                             float *t) {
-    PtDeviceScene *ds = nullptr;
-    int rc = pt_scene_create(scene, cfg, 0, &ds);
-    if (rc) return rc;
-    rc = pt_scene_intersect(ds, cfg, rays6, n, tri_id, t);
-    pt_scene_destroy(ds);
-    return rc;
+    int rc;
+    if ((rc = validate_scene(scene)) || (rc = check_device())) return rc;
+    if (cfg) CK(cudaSetDevice(cfg->device));
+    SceneLease lease;
+    if ((rc = acquire_scene(scene, cfg, scene_key(scene, cfg), &lease.p))) return rc;
+    return pt_scene_intersect(lease.p, cfg, rays6, n, tri_id, t);
 }
 
 // ---- n_gpus > 1 inside one process ---------------------------------------------------------------------------
-// The samples of the caller's partition are dealt round-robin to N devices (device r renders sample_begin + r step,
-// then every N-th), one host thread per device — the render loop blocks on its own stream between steps, so the
-// devices need their own threads to run side by side.  Every device holds the whole scene and a full frame of
-// accumulators.  The exchange step is a sum of those frames onto the first device: the partial frames
-// come over NVLink with cudaMemcpyPeer and are added in rank order (deterministic, unlike a ring reduce).  The
-// one-process-per-GPU launch (bench.py under torchrun) does the same exchange with one NCCL reduce.
+// N devices share one frame: one host thread per device (the render loop blocks on its own stream between steps, so
+// the devices need their own threads to run side by side), every device with the whole scene (from the scene cache)
+// and a full frame of accumulators, then ONE NCCL sum-reduce of those frames onto the first device over NVLink
+// (north_star).  What is split depends on the adaptive rule (main.cpp:118-125):
+//   error < 0   flat spp: device r renders samples sample_begin + r step, then every N-th.  Sums and counts are
+//               reduced, never normalised images (the estimator divides by the contributing-path count).
+//   error >= 0  a sample's fate depends on the running statistics of ALL earlier samples of its pixel, so a sample
+//               split would change which samples are traced (one device's partition holds too few samples to estimate a
+//               variance: high-variance pixels would stop early).  The devices take bands of image rows instead, every
+//               pixel keeps its whole ordered sample sequence, and the reduce adds zeros: bit-identical to one device.
+// NCCL is loaded at run time (dlopen): this library also lives in processes that carry their own NCCL (PyTorch's),
+// and must load on a box without one.
+namespace {
+
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*Reduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    std::string error;
+};
+std::mutex g_nccl_m;
+NcclApi g_nccl;
+struct NcclComms {
+    int dev0 = 0, n = 0;
+    std::vector<ncclComm_t> comm;
+};
+std::vector<NcclComms> g_comms;
+
+int nccl_load() {  // g_nccl_m held
+    if (g_nccl.lib) return PT_OK;
+    if (!g_nccl.error.empty()) return fail(PT_ENCCL, "%s", g_nccl.error.c_str());
+    const char *env = getenv("PT_NCCL_LIB");
+    const char *names[] = {env && *env ? env : nullptr, "libnccl.so.2", "libnccl.so"};
+    void *lib = nullptr;
+    for (const char *nm : names) {
+        if (!nm) continue;
+        lib = dlopen(nm, RTLD_NOW | RTLD_LOCAL);  // a copy already in the process (same soname) is reused
+        if (lib) break;
+    }
+    if (!lib) {
+        g_nccl.error = std::string("NCCL not available: ") + (dlerror() ? dlerror() : "libnccl.so.2 not found") +
+                       " (set PT_NCCL_LIB to the library's path)";
+        return fail(PT_ENCCL, "%s", g_nccl.error.c_str());
+    }
+    auto sym = [&](const char *nm) { return dlsym(lib, nm); };
+    g_nccl.CommInitAll = (decltype(g_nccl.CommInitAll))sym("ncclCommInitAll");
+    g_nccl.CommDestroy = (decltype(g_nccl.CommDestroy))sym("ncclCommDestroy");
+    g_nccl.Reduce = (decltype(g_nccl.Reduce))sym("ncclReduce");
+    g_nccl.GroupStart = (decltype(g_nccl.GroupStart))sym("ncclGroupStart");
+    g_nccl.GroupEnd = (decltype(g_nccl.GroupEnd))sym("ncclGroupEnd");
+    g_nccl.GetErrorString = (decltype(g_nccl.GetErrorString))sym("ncclGetErrorString");
+    if (!g_nccl.CommInitAll || !g_nccl.CommDestroy || !g_nccl.Reduce || !g_nccl.GroupStart || !g_nccl.GroupEnd || !g_nccl.GetErrorString) {
+        dlclose(lib);
+        g_nccl.error = "NCCL library lacks a required symbol";
+        return fail(PT_ENCCL, "%s", g_nccl.error.c_str());
+    }
+    g_nccl.lib = lib;
+    return PT_OK;
+}
+
+#define NCK(call)                                                                                             \
+    do {                                                                                                      \
+        ncclResult_t r_ = (call);                                                                             \
+        if (r_ != ncclSuccess) return fail(PT_ENCCL, "%s:%d %s: %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); \
+    } while (0)
+
+// communicators over devices dev0 .. dev0 + n - 1, created once and kept (ncclCommInitAll takes ~0.1-1 s)
+int nccl_comms(int dev0, int n, ncclComm_t **out) {  // g_nccl_m held
+    int rc;
+    if ((rc = nccl_load())) return rc;
+    for (NcclComms &c : g_comms)
+        if (c.dev0 == dev0 && c.n == n) { *out = c.comm.data(); return PT_OK; }
+    NcclComms c;
+    c.dev0 = dev0; c.n = n;
+    c.comm.resize(n);
+    std::vector<int> devs(n);
+    for (int r = 0; r < n; ++r) devs[r] = dev0 + r;
+    NCK(g_nccl.CommInitAll(c.comm.data(), n, devs.data()));
+    g_comms.push_back(std::move(c));
+    *out = g_comms.back().comm.data();
+    return PT_OK;
+}
+
+void drop_nccl_comms() {
+    std::lock_guard<std::mutex> lock(g_nccl_m);
+    for (NcclComms &c : g_comms)
+        for (ncclComm_t k : c.comm) g_nccl.CommDestroy(k);
+    g_comms.clear();
+}
+
+}  // namespace
+
+// One frame of accumulators on one device: [color_map 3 px | color2_map 3 px | weight px] floats in one block (one
+// reduce), samples_count px ints in another.
 struct FrameBufs {
-    DevBuf<float> sum, sum2, wt;
+    DevBuf<float> f;
     DevBuf<int> cnt;
-    cudaError_t alloc(size_t px) {
+    size_t px = 0;
+    cudaError_t alloc(size_t n_px) {
+        px = n_px;
         cudaError_t e;
-        if ((e = sum.alloc(3 * px)) || (e = sum2.alloc(3 * px)) || (e = wt.alloc(px)) || (e = cnt.alloc(px))) return e;
+        if ((e = f.alloc(7 * n_px)) || (e = cnt.alloc(n_px))) return e;
         return cudaSuccess;
     }
+    float *sum() const { return f.p; }
+    float *sum2() const { return f.p + 3 * px; }
+    float *wt() const { return f.p + 6 * px; }
 };
-
-__global__ void __launch_bounds__(256)
-k_add_frame(float *__restrict__ sum, const float *__restrict__ o_sum, float *__restrict__ sum2,
-            const float *__restrict__ o_sum2, int *__restrict__ cnt, const int *__restrict__ o_cnt,
-            float *__restrict__ wt, const float *__restrict__ o_wt, long long px) {
-    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
-    if (i < 3 * px) { sum[i] += o_sum[i]; sum2[i] += o_sum2[i]; }
-    if (i < px) { cnt[i] += o_cnt[i]; wt[i] += o_wt[i]; }
-}
 
 // renders cfg (n_gpus = N > 1) and leaves the summed accumulators in `f`, allocated on device cfg->device
 static int render_frame_multi(const PtScene *scene, const PtConfig *cfg, FrameBufs &f) {
@@ -739,9 +1005,19 @@ static int render_frame_multi(const PtScene *scene, const PtConfig *cfg, FrameBu
     CK(cudaGetDeviceCount(&have));
     if (dev0 < 0 || dev0 + N > have) return fail(PT_EINVAL, "n_gpus = %d from device %d, but %d device(s) visible", N, dev0, have);
     if (cfg->reserved[2]) return fail(PT_EINVAL, "resume is per device: not available with n_gpus > 1");
+    const bool by_rows = cfg->error >= 0.0f;  // adaptive rule on: split the image, not the samples
+    const int row0 = (cfg->row_begin || cfg->row_end) ? cfg->row_begin : 0, row1 = (cfg->row_begin || cfg->row_end) ? cfg->row_end : cfg->height;
     const size_t px = (size_t)cfg->width * cfg->height;
     const int step = cfg->sample_step > 0 ? cfg->sample_step : 1;
+    const SceneKey key = scene_key(scene, cfg);  // hashed once for all devices
+    ncclComm_t *comm = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_nccl_m);
+        int rc;
+        if ((rc = nccl_comms(dev0, N, &comm))) return rc;
+    }
     std::vector<FrameBufs> part(N);
+    std::vector<PtDeviceScene *> scenes(N, nullptr);
     std::vector<int> rcs(N, PT_OK);
     std::vector<std::string> errs(N);
     auto work = [&](int r) {
@@ -750,17 +1026,24 @@ static int render_frame_multi(const PtScene *scene, const PtConfig *cfg, FrameBu
             PtConfig c = *cfg;
             c.device = dev0 + r;
             c.n_gpus = 1;
-            c.sample_begin = cfg->sample_begin + r * step;
-            c.sample_step = step * N;
-            PtDeviceScene *ds = nullptr;
+            if (by_rows) {
+                const int rows = row1 - row0;
+                c.row_begin = row0 + (int)((long long)rows * r / N);
+                c.row_end = row0 + (int)((long long)rows * (r + 1) / N);
+            } else {
+                c.sample_begin = cfg->sample_begin + r * step;
+                c.sample_step = step * N;
+            }
             int rc;
-            if ((rc = pt_scene_create(scene, &c, 0, &ds))) return rc;
-            struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+            if ((rc = acquire_scene(scene, &c, key, &scenes[r]))) return rc;
             FrameBufs &b = r == 0 ? f : part[r];
             CK(b.alloc(px));
-            if ((rc = pt_scene_render_device_w(ds, &c, b.sum.p, b.sum2.p, b.cnt.p, b.wt.p, nullptr))) return rc;
-            CK(cudaDeviceSynchronize());
-            return PT_OK;
+            if (by_rows && c.row_begin == c.row_end) {  // more devices than rows: an empty band
+                CK(cudaMemsetAsync(b.f.p, 0, 7 * px * sizeof(float)));
+                CK(cudaMemsetAsync(b.cnt.p, 0, px * sizeof(int)));
+                return PT_OK;
+            }
+            return pt_scene_render_device_w(scenes[r], &c, b.sum(), b.sum2(), b.cnt.p, b.wt(), nullptr);
         };
         rcs[r] = run();
         if (rcs[r]) errs[r] = g_err;  // g_err is per thread
@@ -769,21 +1052,30 @@ static int render_frame_multi(const PtScene *scene, const PtConfig *cfg, FrameBu
     for (int r = 1; r < N; ++r) threads.emplace_back(work, r);
     work(0);
     for (std::thread &t : threads) t.join();
-    CK(cudaSetDevice(dev0));
+    struct Cleanup {  // wait for every device, hand the scenes back
+        int dev0, N;
+        std::vector<PtDeviceScene *> &sc;
+        ~Cleanup() {
+            for (int r = 0; r < N; ++r) { cudaSetDevice(dev0 + r); cudaDeviceSynchronize(); release_scene(sc[r]); }
+            cudaSetDevice(dev0);
+        }
+    } cleanup{dev0, N, scenes};
     for (int r = 0; r < N; ++r)
         if (rcs[r]) return fail(rcs[r], "device %d: %s", dev0 + r, errs[r].c_str());
-    FrameBufs stage;
-    CK(stage.alloc(px));
-    for (int r = 1; r < N; ++r) {  // rank order
-        CK(cudaMemcpyPeer(stage.sum.p, dev0, part[r].sum.p, dev0 + r, 3 * px * sizeof(float)));
-        CK(cudaMemcpyPeer(stage.sum2.p, dev0, part[r].sum2.p, dev0 + r, 3 * px * sizeof(float)));
-        CK(cudaMemcpyPeer(stage.cnt.p, dev0, part[r].cnt.p, dev0 + r, px * sizeof(int)));
-        CK(cudaMemcpyPeer(stage.wt.p, dev0, part[r].wt.p, dev0 + r, px * sizeof(float)));
-        k_add_frame<<<blocks_for(3 * (long long)px, 256), 256>>>(f.sum.p, stage.sum.p, f.sum2.p, stage.sum2.p, f.cnt.p,
-                                                                 stage.cnt.p, f.wt.p, stage.wt.p, (long long)px);
-        CK(cudaGetLastError());
+    // the exchange step: one grouped sum-reduce onto the first device, on the streams the renders were issued on
+    {
+        std::lock_guard<std::mutex> lock(g_nccl_m);
+        NCK(g_nccl.GroupStart());
+        for (int r = 0; r < N; ++r) {
+            FrameBufs &b = r == 0 ? f : part[r];
+            CK(cudaSetDevice(dev0 + r));
+            NCK(g_nccl.Reduce(b.f.p, r == 0 ? f.f.p : nullptr, 7 * px, ncclFloat, ncclSum, 0, comm[r], nullptr));
+            NCK(g_nccl.Reduce(b.cnt.p, r == 0 ? f.cnt.p : nullptr, px, ncclInt32, ncclSum, 0, comm[r], nullptr));
+        }
+        NCK(g_nccl.GroupEnd());
     }
-    CK(cudaDeviceSynchronize());
+    for (int r = 0; r < N; ++r) { CK(cudaSetDevice(dev0 + r)); CK(cudaDeviceSynchronize()); }
+    CK(cudaSetDevice(dev0));
     return PT_OK;
 }
 
@@ -802,15 +1094,15 @@ extern "C" int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, floa
         FrameBufs f;
         if ((rc = render_frame_multi(scene, cfg, f))) return rc;
         const size_t npx = (size_t)cfg->width * cfg->height;
-        if (weight) CK(cudaMemcpy(weight, f.wt.p, npx * sizeof(float), cudaMemcpyDeviceToHost));
-        if (sum3) CK(cudaMemcpy(sum3, f.sum.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
-        if (sum2_3) CK(cudaMemcpy(sum2_3, f.sum2.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (weight) CK(cudaMemcpy(weight, f.wt(), npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (sum3) CK(cudaMemcpy(sum3, f.sum(), 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
+        if (sum2_3) CK(cudaMemcpy(sum2_3, f.sum2(), 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
         if (count) CK(cudaMemcpy(count, f.cnt.p, npx * sizeof(int), cudaMemcpyDeviceToHost));
         return PT_OK;
     }
-    PtDeviceScene *ds = nullptr;
-    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
-    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    SceneLease lease;
+    if ((rc = acquire_scene(scene, cfg, scene_key(scene, cfg), &lease.p))) return rc;
+    PtDeviceScene *ds = lease.p;
     const size_t px = (size_t)cfg->width * cfg->height;
     DevBuf<float> d_sum, d_sum2, d_wt;
     DevBuf<int> d_cnt;
@@ -846,7 +1138,7 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
         const size_t npx = (size_t)cfg->width * cfg->height;
         DevBuf<float> d_out;
         CK(d_out.alloc(3 * npx));
-        if ((rc = pt_resolve_device_w(f.sum.p, f.cnt.p, cfg->rr_depth > 0 ? f.wt.p : nullptr, (int64_t)npx, d_out.p, nullptr))) return rc;
+        if ((rc = pt_resolve_device_w(f.sum(), f.cnt.p, cfg->rr_depth > 0 ? f.wt() : nullptr, (int64_t)npx, d_out.p, nullptr))) return rc;
         CK(cudaMemcpy(rgb, d_out.p, 3 * npx * sizeof(float), cudaMemcpyDeviceToHost));
         return PT_OK;
     }
@@ -863,9 +1155,9 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
         if (prof) fprintf(stderr, "[pt_render] %-14s %8.2f ms\n", what, ms);
         t0 = t1;
     };
-    PtDeviceScene *ds = nullptr;
-    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
-    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    SceneLease lease;
+    if ((rc = acquire_scene(scene, cfg, scene_key(scene, cfg), &lease.p))) return rc;
+    PtDeviceScene *ds = lease.p;
     lap("scene_create");
     const size_t px = (size_t)cfg->width * cfg->height;
     DevBuf<float> d_sum, d_rgb, d_wt;
@@ -879,8 +1171,8 @@ extern "C" int pt_render(const PtScene *scene, const PtConfig *cfg, float *rgb) 
     if ((rc = pt_resolve_device_w(d_sum.p, d_cnt.p, rr ? d_wt.p : nullptr, (int64_t)px, d_rgb.p, nullptr))) return rc;
     CK(cudaMemcpy(rgb, d_rgb.p, 3 * px * sizeof(float), cudaMemcpyDeviceToHost));
     lap("resolve + d2h");
-    pt_scene_destroy(ds);
-    guard.p = nullptr;
+    release_scene(ds);  // the download above waited for the device
+    lease.p = nullptr;
     d_sum.free(); d_rgb.free(); d_wt.free(); d_cnt.free();
     lap("release");
     return PT_OK;
@@ -985,14 +1277,14 @@ extern "C" int pt_render_image(const PtScene *scene, const PtConfig *cfg, const 
         const size_t npx = (size_t)cfg->width * cfg->height;
         DevBuf<uint8_t> d_out;
         CK(d_out.alloc(3 * npx));
-        if ((rc = pt_postprocess_device(f.sum.p, f.sum2.p, f.cnt.p, cfg->rr_depth > 0 ? f.wt.p : nullptr, post, d_out.p, stats, nullptr)))
+        if ((rc = pt_postprocess_device(f.sum(), f.sum2(), f.cnt.p, cfg->rr_depth > 0 ? f.wt() : nullptr, post, d_out.p, stats, nullptr)))
             return rc;
         CK(cudaMemcpy(rgb8, d_out.p, 3 * npx, cudaMemcpyDeviceToHost));
         return PT_OK;
     }
-    PtDeviceScene *ds = nullptr;
-    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
-    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    SceneLease lease;
+    if ((rc = acquire_scene(scene, cfg, scene_key(scene, cfg), &lease.p))) return rc;
+    PtDeviceScene *ds = lease.p;
     const size_t px = (size_t)cfg->width * cfg->height;
     DevBuf<float> d_sum, d_sum2, d_wt;
     DevBuf<int> d_cnt;
@@ -1023,9 +1315,9 @@ extern "C" int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, 
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
     const auto t0 = std::chrono::steady_clock::now();
-    PtDeviceScene *ds = nullptr;
-    if ((rc = pt_scene_create(scene, cfg, 0, &ds))) return rc;
-    struct Guard { PtDeviceScene *p; ~Guard() { pt_scene_destroy(p); } } guard{ds};
+    SceneLease lease;
+    if ((rc = acquire_scene(scene, cfg, scene_key(scene, cfg), &lease.p))) return rc;
+    PtDeviceScene *ds = lease.p;
     const size_t px = (size_t)cfg->width * cfg->height;
     DevBuf<float> d_sum, d_sum2, d_wt;
     DevBuf<int> d_cnt;

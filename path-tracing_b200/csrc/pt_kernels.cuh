@@ -32,6 +32,8 @@ struct RenderParams {
     int sample_major;  // wavefront slot numbering, pt_wavefront.cuh slot_split
     int use_alive;     // wavefront pipeline: bounce launches work on lists of the paths still alive (pt_wavefront.cuh)
     int resume;     // the output buffers hold the accumulators after the samples before s_begin: continue from them
+    int row0, row1; // image rows [row0, row1) are traced (PtConfig::row_begin / row_end); the others keep their
+                    // initial accumulators (zero, or the caller's in resume mode)
 };
 
 constexpr float kPi = 3.141593f;  // material.h:12
@@ -221,9 +223,10 @@ k_render_mega(SceneView sc, RenderParams rp) {
     int s_next = rp.s_begin;  // next uncommitted sample of this pixel (identical across the quad)
     unsigned long long seg_commit = 0, seg_traced = 0, n_nodes = 0, n_tris = 0;
 
-    while (__any_sync(0xffffffffu, in_image && s_next < rp.spp)) {
+    const bool in_band = in_image && y >= rp.row0 && y < rp.row1;
+    while (__any_sync(0xffffffffu, in_band && s_next < rp.spp)) {
         const int s = s_next + qi * rp.s_step;
-        const bool live = in_image && s_next < rp.spp && s < rp.spp;
+        const bool live = in_band && s_next < rp.spp && s < rp.spp;
         const bool traced = live && !adaptive_skip(s, rr_on ? wsum : (float)cnt, sum, sum2, rp.error);
         V3 c = mk(0, 0, 0);
         int nseg = 0;

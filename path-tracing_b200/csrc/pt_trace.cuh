@@ -292,21 +292,28 @@ __device__ __forceinline__ unsigned sign_bytes(unsigned x) {
     return r;
 }
 
-// byte k of w as the float 1 + q 2^-15 (q in mantissa bits 8..15): one PRMT instead of a conversion
+// byte k of w as the float 1 + q 2^-15 (q in mantissa bits 8..15): one PRMT instead of a conversion.  `one` holds
+// 0x3f800000 in a register the compiler cannot fold (float_one_bits): PRMT takes one immediate, and with the constant as
+// the immediate the four selectors lived in registers that were re-materialised 45 times per node visit (ncu source view).
 template <int K>
-__device__ __forceinline__ float qfloat(unsigned w) {
-    return __uint_as_float(__byte_perm(w, 0x3f800000u, 0x7604 | (K << 4)));
+__device__ __forceinline__ float qfloat(unsigned w, unsigned one) {
+    return __uint_as_float(__byte_perm(w, one, 0x7604 | (K << 4)));
+}
+__device__ __forceinline__ unsigned float_one_bits() {
+    unsigned r;
+    asm("mov.b32 %0, 0x3f800000;" : "=r"(r));
+    return r;
 }
 
 // four children (one meta word, slots 4 W .. 4 W + 3) against the ray; returns their hit bits
 template <int K>
 __device__ __forceinline__ unsigned child_hit(unsigned nx, unsigned fx, unsigned ny, unsigned fy, unsigned nz, unsigned fz,
                                               float Ax, float Bx, float Ay, float By, float Az, float Bz, float tmax,
-                                              unsigned child_bits4, unsigned bit_index4) {
+                                              unsigned child_bits4, unsigned bit_index4, unsigned one) {
     // slab distances on the 2^15-scaled grid: (p + q s - o) / d = (1 + q 2^-15) (2^15 s / d) + ((p - o) / d - 2^15 s / d)
-    const float tlx = __fmaf_rn(qfloat<K>(nx), Ax, Bx), thx = __fmaf_rn(qfloat<K>(fx), Ax, Bx);
-    const float tly = __fmaf_rn(qfloat<K>(ny), Ay, By), thy = __fmaf_rn(qfloat<K>(fy), Ay, By);
-    const float tlz = __fmaf_rn(qfloat<K>(nz), Az, Bz), thz = __fmaf_rn(qfloat<K>(fz), Az, Bz);
+    const float tlx = __fmaf_rn(qfloat<K>(nx, one), Ax, Bx), thx = __fmaf_rn(qfloat<K>(fx, one), Ax, Bx);
+    const float tly = __fmaf_rn(qfloat<K>(ny, one), Ay, By), thy = __fmaf_rn(qfloat<K>(fy, one), Ay, By);
+    const float tlz = __fmaf_rn(qfloat<K>(nz, one), Az, Bz), thz = __fmaf_rn(qfloat<K>(fz, one), Az, Bz);
     const float tn = fmaxf(fmax3(tlx, tly, tlz), 0.0f);
     const float tf = fminf(fmin3(thx, thy, thz), tmax);  // clipped against the best t with <=: equal distances are kept
     const unsigned bits = (child_bits4 >> (8 * K)) & 0xffu, idx = (bit_index4 >> (8 * K)) & 0xffu;
@@ -335,6 +342,7 @@ __device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes
     const unsigned lz0 = __float_as_uint(r4.x), lz1 = __float_as_uint(r4.y), hx0 = __float_as_uint(r4.z), hx1 = __float_as_uint(r4.w);
     const unsigned hy0 = __float_as_uint(r5.x), hy1 = __float_as_uint(r5.y), hz0 = __float_as_uint(r5.z), hz1 = __float_as_uint(r5.w);
     unsigned hits = 0u;
+    const unsigned one = float_one_bits();
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
         const unsigned meta4 = __float_as_uint(w ? r2.y : r2.x);
@@ -345,18 +353,18 @@ __device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes
         const unsigned nx = w ? (px ? lx1 : hx1) : (px ? lx0 : hx0), fx = w ? (px ? hx1 : lx1) : (px ? hx0 : lx0);
         const unsigned ny = w ? (py ? ly1 : hy1) : (py ? ly0 : hy0), fy = w ? (py ? hy1 : ly1) : (py ? hy0 : ly0);
         const unsigned nz = w ? (pz ? lz1 : hz1) : (pz ? lz0 : hz0), fz = w ? (pz ? hz1 : lz1) : (pz ? hz0 : lz0);
-        hits |= child_hit<0>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
-        hits |= child_hit<1>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
-        hits |= child_hit<2>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
-        hits |= child_hit<3>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4);
+        hits |= child_hit<0>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4, one);
+        hits |= child_hit<1>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4, one);
+        hits |= child_hit<2>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4, one);
+        hits |= child_hit<3>(nx, fx, ny, fy, nz, fz, Ax, Bx, Ay, By, Az, Bz, tmax, child_bits4, bit_index4, one);
     }
     return hits;
 }
 
-// One BVH triangle: its scan record (plane + three edge planes, the conservative test of scan_singles with the same
-// tolerances: approximate reciprocal, range widened by 2e-6 relative, edge planes already dilated by the builder; a
-// NaN anywhere marks), then the reference's exact test if marked.  Returns whether the exact test ran.
-__device__ __forceinline__ bool tri_test(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
+// The scan record of one BVH triangle (plane + three edge planes): the conservative test of scan_singles with the same
+// tolerances — approximate reciprocal, range widened by 2e-6 relative, edge planes already dilated by the builder; a
+// NaN anywhere marks.  true = the reference's exact test has to decide.
+__device__ __forceinline__ bool scan_pass(const SceneView &sc, int rec, V3 o, V3 d, float eps, const Hit &h) {
     const float4 *s = sc.scans + 4 * (size_t)rec;
     float4 p, e0, e1, e2;
     ldg256(s, p, e0);
@@ -371,7 +379,12 @@ __device__ __forceinline__ bool tri_test(const SceneView &sc, int rec, V3 o, V3 
     const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
     const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
     const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
-    if (out) return false;
+    return !out;
+}
+
+// One BVH triangle: scan record first, the reference's exact test if that marks it.  Returns whether the exact test ran.
+__device__ __forceinline__ bool tri_test(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
+    if (!scan_pass(sc, rec, o, d, eps, h)) return false;
     tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, o, d, eps, h);
     return true;
 }

@@ -288,15 +288,22 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
 #ifndef PT_REFILL_MIN
 #define PT_REFILL_MIN 4        // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
 #endif
-#ifndef PT_TRI_LANES
-#define PT_TRI_LANES 1         // lanes with triangles to test before the warp enters the triangle phase (1 = at once)
+#ifndef PT_EXACT_LANES
+#define PT_EXACT_LANES 6       // lanes with a candidate for the exact test before the warp runs it (see below)
 #endif
 
-// persistent warps over queue `set`: one ray per lane, refilled as lanes finish (dynamic fetch).  Every round of the
-// loop a lane enters at most one wide node (node phase) and tests the triangles that node handed it (triangle phase);
-// with PT_TRI_LANES > 1 the triangle phase waits until that many lanes have triangles (the group is parked on the
-// lane's stack meanwhile, Ylitie et al. 2017) — walking on with a not-yet-shortened t only visits extra nodes, the
-// nearest-hit rule is order independent (pt_trace.cuh).
+// persistent warps over queue `set`: one ray per lane, refilled as lanes finish (dynamic fetch).
+// Every round of the loop a lane does ONE unit of its ray's work, and the warp runs each kind of unit once for all the
+// lanes that are up to it:
+//   exact   the reference's exact test (IEEE division, three IEEE square roots) on the lane's pending candidate — run
+//           when PT_EXACT_LANES lanes have one (or nothing else is left to do): a lane with a candidate waits, because
+//           its ray's t must be settled before it goes on (front to back);
+//   scan    the scan record of one triangle of the lane's triangle group; a marked triangle becomes the candidate;
+//   node    one wide node (node8_visit), when the lane has no triangles left.
+// The first version tested a node's triangles in a per-lane loop right after the visit: ncu's source view put 31 % of
+// the kernel's warp instructions in that loop at 3.0 active lanes and 23 % in the exact test at 1.0 — a node hands a
+// lane 0..6 triangles, so the loop ran for the unluckiest lane.  One unit per round keeps the scan at whatever share of
+// the lanes has triangles at all, and the exact test at >= PT_EXACT_LANES lanes.
 template <bool COUNT>
 __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
@@ -306,18 +313,15 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
     uint2 stack[kStackDepth];
-    int sp = 0, slot = -1;
+    int sp = 0, slot = -1, pend = -1;  // pend: record that passed its scan and waits for the exact test
     uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
     bool done = false;
     Ray8 r;
     ray8_setup(mk(0, 0, 0), mk(0, 0, 1), r);
     Hit h = no_hit();
     unsigned long long n_nodes = 0, n_tris = 0, n_exact = 0, ray_nodes0 = 0;
-#if PT_TRI_LANES > 1
-    unsigned round = 0;
-#endif
     while (true) {
-        const bool need = !done && !has_inner(ng) && tg.y == 0u && sp == 0;
+        const bool need = !done && !has_inner(ng) && tg.y == 0u && sp == 0 && pend < 0;
         if (need && slot >= 0) {  // retire the finished ray
             if (COUNT && stats) {
                 atomicAdd(&stats[4], 1ull);
@@ -353,30 +357,32 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         }
         if (__all_sync(0xffffffffu, done)) break;
         // ---- pop: a lane with nothing in hand takes the top of its stack
-        if (!has_inner(ng) && tg.y == 0u && sp > 0) {
+        if (!has_inner(ng) && tg.y == 0u && pend < 0 && sp > 0) {
             const uint2 e = stack[--sp];
             if (has_inner(e)) ng = e; else tg = e;
         }
-#if PT_TRI_LANES > 1
-        else if (!has_inner(ng) && sp > 0 && has_inner(stack[sp - 1])) {  // waiting triangles: swap them for the node group below
-            const uint2 e = stack[sp - 1];
-            stack[sp - 1] = tg;
-            tg.y = 0u;
-            ng = e;
+        // ---- exact phase
+        const unsigned me = __ballot_sync(0xffffffffu, pend >= 0);
+        if (me) {
+            const unsigned other = __ballot_sync(0xffffffffu, pend < 0 && (tg.y != 0u || has_inner(ng)));
+            if (__popc(me) >= PT_EXACT_LANES || other == 0u) {
+                if (pend >= 0) {
+                    tri_intersect_ref(sc.tris + 4 * (size_t)pend, pend, r.o, r.d, eps, h);
+                    pend = -1;
+                    if (COUNT) ++n_exact;
+                }
+            }
         }
-#endif
-        // ---- node phase: one wide node per lane
-        if (has_inner(ng)) {
-            if (tg.y) { stack[sp++] = tg; tg.y = 0u; }  // parked triangles (PT_TRI_LANES > 1 only)
-            enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
+        // ---- scan phase: one triangle of the lane's group
+        if (pend < 0 && tg.y != 0u) {
+            const int j = 31 - __clz((int)tg.y);
+            tg.y &= ~(1u << j);
+            const int rec = (int)tg.x + j;
+            if (scan_pass(sc, rec, r.o, r.d, eps, h)) pend = rec;
+            if (COUNT) ++n_tris;
         }
-        // ---- triangle phase
-#if PT_TRI_LANES > 1
-        const unsigned mt = __ballot_sync(0xffffffffu, tg.y != 0u), mn = __ballot_sync(0xffffffffu, has_inner(ng));
-        ++round;
-        if (__popc(mt) >= PT_TRI_LANES || mn == 0u || (round & 7u) == 0u)
-#endif
-            test_group<COUNT>(sc, r, eps, h, tg, n_tris, n_exact);
+        // ---- node phase: one wide node
+        if (pend < 0 && tg.y == 0u && has_inner(ng)) enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
     }
     if (COUNT && stats) {
         for (int o2 = 16; o2; o2 >>= 1) {

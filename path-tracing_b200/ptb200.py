@@ -36,7 +36,7 @@ class PtConfig(C.Structure):
                 ("max_ray_reflections", C.c_int32), ("eps", C.c_float), ("error", C.c_float), ("seed", C.c_uint32),
                 ("sample_begin", C.c_int32), ("sample_step", C.c_int32), ("intersector", C.c_int32),
                 ("accel", C.c_int32), ("rr_depth", C.c_int32), ("n_gpus", C.c_int32), ("device", C.c_int32),
-                ("reserved", C.c_int32 * 4)]
+                ("reserved", C.c_int32 * 4), ("row_begin", C.c_int32), ("row_end", C.c_int32)]
 
 
 class PtStats(C.Structure):
@@ -65,7 +65,7 @@ class PtError(RuntimeError):
 
 def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, seed=42, sample_begin=0,
            sample_step=1, accel=PT_ACCEL_AUTO, intersector=PT_ISECT_REFERENCE, device=0, n_gpus=1, rr_depth=0,
-           mode=0, q_shift=0, resume=0, alive=0):
+           mode=0, q_shift=0, resume=0, alive=0, rows=None):
     """PtConfig with the reference's defaults (config.h:10,16-29)."""
     c = PtConfig()
     c.width, c.height, c.rays_per_pixel, c.max_ray_reflections = width, height, spp, max_depth
@@ -76,10 +76,30 @@ def config(width=512, height=512, spp=20, max_depth=8, eps=1e-4, error=0.001, se
     c.reserved[1] = q_shift  # 0 = automatic, else log2(samples per pixel per wavefront step)
     c.reserved[3] = alive  # alive lists of the wavefront pipeline: 0 automatic, 1 on, 2 off
     c.reserved[2] = resume  # 1 = continue from the accumulators passed in (samples before sample_begin are in them)
+    if rows is not None:    # image rows [begin, end) traced by this call
+        c.row_begin, c.row_end = rows
     return c
 
 
 PREVIEW_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_void_p, C.c_int32)
+
+
+def _point_at_bundled_nccl():
+    """PtConfig.n_gpus > 1 loads NCCL at run time (dlopen, $PT_NCCL_LIB first).  A Python process that also imports
+    PyTorch should end up with ONE libnccl.so.2: point the library at the wheel's copy (nvidia/nccl/lib) when there is
+    one and the caller has not chosen; otherwise the system library is used."""
+    if os.environ.get("PT_NCCL_LIB"):
+        return
+    try:
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for root in (spec.submodule_search_locations if spec else []):
+            cand = os.path.join(root, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["PT_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
 
 
 def _load(path):
@@ -94,6 +114,7 @@ class Library:
     verts (n,9) f32, planes (n,4) f32 | None, squares (n,) f32 | None, mat_ids (n,) i32, mats (m,10) f32."""
 
     def __init__(self):
+        _point_at_bundled_nccl()
         L = self.lib = _load(RENDER_SO)
         L.pt_last_error.restype = C.c_char_p
         L.pt_version.restype = C.c_char_p

@@ -483,25 +483,89 @@ def test_progressive_render(lib, oracle, tor):
     assert_bits_equal(img, want, "update = 0")
 
 
+@pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
+def test_row_bands_are_the_frame(lib, tor, mode):
+    """PtConfig.row_begin / row_end: a band render is the rows of the whole-frame render (pixels are independent given
+    the counter-based streams), zero elsewhere — with the adaptive rule on, which is what the multi-GPU row split
+    relies on (pt_render_accum with n_gpus > 1 and error >= 0)."""
+    W, H, spp = 48, 37, 24
+    full = lib.render_accum_w(tor, ptb200.config(W, H, spp, 8, 1e-4, 0.002, seed=3, mode=mode))
+    acc = [np.zeros_like(a) for a in full]
+    for r0, r1 in ((0, 12), (12, 13), (13, 37)):
+        band = lib.render_accum_w(tor, ptb200.config(W, H, spp, 8, 1e-4, 0.002, seed=3, mode=mode, rows=(r0, r1)))
+        for a, b in zip(acc, band):
+            assert not b[:r0].any() and not b[r1:].any()
+            a += b
+    for a, b, what in zip(acc, full, ("sum", "sum2", "count", "weight")):
+        assert_bits_equal(a, b, what)
+    with pytest.raises(ptb200.PtError):
+        lib.render_accum(tor, ptb200.config(W, H, spp, rows=(5, H + 1)))
+
+
 def test_in_process_multi_gpu(lib, tor):
-    """PtConfig.n_gpus = 2 inside one call: device r renders every second sample, the partial frames are summed on the
-    first device in rank order — exactly the sum of the two single-device partition renders (one fp32 add per
-    value), and the image calls resolve from that sum."""
-    if lib.device_count() < 2:
+    """PtConfig.n_gpus = N inside one call (every N the box allows): one host thread per device, one NCCL sum-reduce of
+    the accumulators onto the first device.
+    Flat spp: the samples are dealt round-robin — counts are exactly the sum of the single-device partition renders,
+    sums equal it bit for bit at N = 2 (one fp32 add per value) and to rounding beyond (NCCL's reduction order).
+    Adaptive rule on: the devices take bands of rows instead, and the result is the ONE-device render bit for bit."""
+    n_dev = lib.device_count()
+    if n_dev < 2:
         pytest.skip("needs two GPUs")
-    for kw in (dict(error=-1.0), dict(error=0.002), dict(error=-1.0, rr_depth=2)):
-        parts = [lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, sample_begin=r, sample_step=2, **kw))
-                 for r in (0, 1)]
-        both = lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, n_gpus=2, **kw))
-        for a, b, c, what in zip(parts[0], parts[1], both, ("sum", "sum2", "count", "weight")):
-            assert_bits_equal(a + b, c, f"{kw} {what}")
+    for N in [n for n in (2, 4, 8) if n <= n_dev]:
+        for kw in (dict(error=-1.0), dict(error=-1.0, rr_depth=2)):
+            parts = [lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, sample_begin=r, sample_step=N, **kw))
+                     for r in range(N)]
+            both = lib.render_accum_w(tor, ptb200.config(96, 64, 24, 8, 1e-4, seed=3, n_gpus=N, **kw))
+            want = [sum(p[k].astype(np.float64) for p in parts) for k in range(4)]
+            assert_bits_equal(both[2], want[2].astype(np.int32), f"N={N} {kw} count")
+            for k, what in ((0, "sum"), (1, "sum2"), (3, "weight")):
+                if N == 2:
+                    assert_bits_equal(both[k], parts[0][k] + parts[1][k], f"N=2 {kw} {what}")
+                else:
+                    np.testing.assert_allclose(both[k], want[k], rtol=2e-6, atol=1e-7, err_msg=f"N={N} {kw} {what}")
+        one = lib.render_accum_w(tor, ptb200.config(96, 61, 24, 8, 1e-4, 0.002, seed=3))
+        many = lib.render_accum_w(tor, ptb200.config(96, 61, 24, 8, 1e-4, 0.002, seed=3, n_gpus=N))
+        for a, b, what in zip(one, many, ("sum", "sum2", "count", "weight")):
+            assert_bits_equal(a, b, f"adaptive rule, N={N}: {what}")
+        assert one[2].sum() > 0
     cfg = ptb200.config(96, 64, 24, 8, 1e-4, -1.0, seed=3, n_gpus=2)
-    sm, _, cnt, _ = both = lib.render_accum_w(tor, cfg)
+    sm, _, cnt, _ = lib.render_accum_w(tor, cfg)
     rgb = lib.render(tor, cfg)
     want = np.where(cnt[..., None] > 0, sm / np.maximum(cnt, 1)[..., None].astype(np.float32), 0).astype(np.float32)
     assert_bits_equal(rgb, want, "pt_render, n_gpus = 2")
+    img, _ = lib.render_image(tor, cfg, lib.post_config(96, 64))
+    img1, _ = lib.postprocess(*lib.render_accum(tor, cfg), lib.post_config(96, 64))
+    assert np.array_equal(img, img1)
     with pytest.raises(ptb200.PtError):
-        lib.render(tor, ptb200.config(16, 16, 4, n_gpus=lib.device_count() + 1))
+        lib.render(tor, ptb200.config(16, 16, 4, n_gpus=n_dev + 1))
+
+
+def test_scene_cache_is_keyed_by_content(lib, tor):
+    """The host-scene entry points keep the built device scene between calls, keyed by a hash of the caller's arrays:
+    the same arrays again reuse it; a changed vertex (same buffer, same sizes) must not."""
+    cfg = ptb200.config(64, 48, 8, 8, 1e-4, -1.0, seed=2)
+    a = lib.render_accum(tor, cfg)
+    b = lib.render_accum(tor, cfg)
+    for x, y in zip(a, b):
+        assert_bits_equal(x, y)
+    moved = dict(tor, verts=tor["verts"].copy())
+    moved["verts"][:256] += np.float32(0.37)          # the torus, shifted; planes recomputed on the device
+    moved["planes"] = moved["squares"] = None
+    ref = dict(tor, planes=None, squares=None)
+    c, d = lib.render_accum(moved, cfg), lib.render_accum(ref, cfg)
+    assert not np.array_equal(c[0], d[0])
+    ds = lib.scene_create(moved, cfg)                 # an uncached handle gives the same picture
+    import torch
+    sm = torch.zeros(48, 64, 3, device="cuda")
+    cnt = torch.zeros(48, 64, dtype=torch.int32, device="cuda")
+    ds.render_device(cfg, sm.data_ptr(), 0, cnt.data_ptr())
+    torch.cuda.synchronize()
+    assert_bits_equal(sm.cpu().numpy(), c[0])
+    ds.close()
+    lib.lib.pt_release_workspace()
+    e = lib.render_accum(tor, cfg)
+    for x, y in zip(a, e):
+        assert_bits_equal(x, y)
 
 
 def test_read_bandwidth_probe(lib):

@@ -24,7 +24,7 @@ def test_library_exports_every_declared_symbol(lib):
 
 
 def test_struct_layouts_match_header():
-    assert C.sizeof(ptb200.PtConfig) == 4 * 18
+    assert C.sizeof(ptb200.PtConfig) == 4 * 20
     assert C.sizeof(ptb200.PtScene) == 80
     assert C.sizeof(ptb200.PtStats) == 4 * 8 + 3 * 4 + 4 * 4 + 8 * 4 + 4 + 17 * 8 + 8 + 8  # 8-byte aligned
 
