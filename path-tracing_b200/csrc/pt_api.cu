@@ -305,6 +305,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
     SceneView v{};
     v.n_tri = n;
     v.counters = nullptr;
+    v.one_bits = 0x3f800000u;
     if (brute) {
         if (n) { k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nullptr, n, ds->tris); ++launches; }
         v.brute = 1;
@@ -358,8 +359,8 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
                 k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
                 launches += 2;
             }
-            // every wide node has at least min(8, kLeafMax + 1) children (k_collapse), every leaf child a triangle
-            const size_t max_nodes = (size_t)nb / (std::min(8, kLeafMax + 1) - 1) + 2;
+            // every wide node has at least two children (k_collapse), every leaf child a triangle
+            const size_t max_nodes = (size_t)nb + 2;
             const size_t max_items = (size_t)nb / (kLeafMax + 1) + 2;
             CK(pool_alloc((void **)&ds->nodes, kNodeRows * max_nodes * sizeof(float4)));
             CK(items_a.alloc(max_items)); CK(items_b.alloc(max_items)); CK(d_ctr.alloc(1)); CK(perm.alloc(nb)); CK(order.alloc(n));

@@ -437,11 +437,9 @@ struct BinTree {
 __device__ __forceinline__ float q_decode(int q, float s, float p) { return __fmaf_rn((float)q, s, p); }
 
 // One thread per wide node of the current level.  Its children: start from the subtree's two binary children and keep
-// replacing the child with the largest box by its own two children — first among the subtrees that are too big for a
-// leaf (> kLeafMax triangles), then, while slots are free, among the leaves themselves (a slot costs the same whether
-// it is used or not) — until there are 8.  Subtrees of <= kLeafMax triangles become leaf children (their triangles are
-// contiguous in the sorted order), the others inner children, numbered in slot order from child_base and queued for
-// the next level.  Quantisation: q_lo = floor, q_hi = ceil on the grid p + q s, s = extent / 255, pushed outwards until
+// replacing a child by its own two children until there are 8 or nothing is left to open (largest box first).
+// Subtrees of <= kLeafMax triangles become leaf children (their triangles are contiguous in the sorted order), the
+// others inner children, numbered in slot order from child_base and queued for the next level.  Quantisation: q_lo = floor, q_hi = ceil on the grid p + q s, s = extent / 255, pushed outwards until
 // the DECODED plane (q_decode) encloses the child box with a margin of 2^-7 of a grid step: node8_visit
 // (pt_trace.cuh) evaluates (p + q s - o) / d in a different association (one FMA on a 2^15-scaled grid) whose rounding
 // stays below 2^-9 of a step plus a few ulp of |p - o| / |d|; the latter are covered by the 32-ulp padding every
@@ -464,6 +462,11 @@ k_collapse(const WideItem *__restrict__ in, int n_in, WideItem *__restrict__ out
         n = 1;
     }
     for (int i = 0; i < n; ++i) area[i] = bt.area(refs[i]);
+    // Which children are opened up: largest box first, among the subtrees that are too big for a leaf (> kLeafMax
+    // triangles); then, while slots are free — a slot costs the same whether it is used or not — among the leaves
+    // themselves.  (Measured alternative, profiles/r02_sweep_bvh8.txt: opening only children above a size target
+    // kLeafMax 8^k, which makes a BALANCED tree divide by exactly 8 per level, gave 13 levels and 13.1 node visits per
+    // ray on the torus instead of 9 and 11.5 — the Karras tree over a curved surface is not balanced in counts.)
     for (int phase = 0; phase < 2 && n < 8; ++phase) {
         const int min_cnt = phase == 0 ? kLeafMax + 1 : 2;
         while (n < 8) {

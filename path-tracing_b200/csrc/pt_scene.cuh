@@ -81,6 +81,7 @@ struct SceneView {
     const unsigned char *sky;  // equirect skybox, 24-bit BGR rows top-down (bitmap_image's layout); nullptr = none
     int sky_w, sky_h;
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
+    unsigned one_bits;  // 0x3f800000, deliberately a run-time value: see qfloat (pt_trace.cuh)
 };
 
 }  // namespace ptd

@@ -292,18 +292,15 @@ __device__ __forceinline__ unsigned sign_bytes(unsigned x) {
     return r;
 }
 
-// byte k of w as the float 1 + q 2^-15 (q in mantissa bits 8..15): one PRMT instead of a conversion.  `one` holds
-// 0x3f800000 in a register the compiler cannot fold (float_one_bits): PRMT takes one immediate, and with the constant as
-// the immediate the four selectors lived in registers that were re-materialised 45 times per node visit (ncu source view).
+// byte k of w as the float 1 + q 2^-15 (q in mantissa bits 8..15): one PRMT instead of a conversion.  `one` is
+// 0x3f800000 handed in through SceneView::one_bits, i.e. a value neither nvcc nor ptxas can fold: PRMT takes one
+// immediate, and with the constant as the immediate the four selectors lived in registers that were re-materialised 45
+// times per node visit (ncu source view: 40 IMAD.U32 R, RZ, RZ, UR per visit).
 template <int K>
 __device__ __forceinline__ float qfloat(unsigned w, unsigned one) {
     return __uint_as_float(__byte_perm(w, one, 0x7604 | (K << 4)));
 }
-__device__ __forceinline__ unsigned float_one_bits() {
-    unsigned r;
-    asm("mov.b32 %0, 0x3f800000;" : "=r"(r));
-    return r;
-}
+
 
 // four children (one meta word, slots 4 W .. 4 W + 3) against the ray; returns their hit bits
 template <int K>
@@ -324,8 +321,8 @@ __device__ __forceinline__ unsigned child_hit(unsigned nx, unsigned fx, unsigned
 // children, at position 24 + (slot ^ octant) so that the highest bit is the child to enter first; bits 0..23 the
 // triangles of the hit leaf children (record tri_base + bit) — and the node's child_base / tri_base / imask.
 // Conservative by construction of the grid (k_collapse) and the padding of the triangle boxes.
-__device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes, int ni, const Ray8 &r, float tmax,
-                                                unsigned &child_base, unsigned &tri_base, unsigned &imask) {
+__device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes, unsigned one, int ni, const Ray8 &r,
+                                                float tmax, unsigned &child_base, unsigned &tri_base, unsigned &imask) {
     const float4 *nd = nodes + kNodeRows * (size_t)ni;
     float4 r0, r1, r2, r3, r4, r5;
     ldg256(nd, r0, r1);
@@ -342,7 +339,6 @@ __device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes
     const unsigned lz0 = __float_as_uint(r4.x), lz1 = __float_as_uint(r4.y), hx0 = __float_as_uint(r4.z), hx1 = __float_as_uint(r4.w);
     const unsigned hy0 = __float_as_uint(r5.x), hy1 = __float_as_uint(r5.y), hz0 = __float_as_uint(r5.z), hz1 = __float_as_uint(r5.w);
     unsigned hits = 0u;
-    const unsigned one = float_one_bits();
 #pragma unroll
     for (int w = 0; w < 2; ++w) {
         const unsigned meta4 = __float_as_uint(w ? r2.y : r2.x);
@@ -405,7 +401,7 @@ __device__ __forceinline__ void enter_child(const SceneView &sc, const Ray8 &r, 
     const unsigned slot = (unsigned)(bit - 24) ^ (r.oct4 & 7u);
     const int ni = (int)ng.x + __popc(hits & 0xffu & ~(0xffffffffu << slot));
     unsigned cb, tb, im;
-    const unsigned hm = node8_visit(sc.nodes, ni, r, tmax, cb, tb, im);
+    const unsigned hm = node8_visit(sc.nodes, sc.one_bits, ni, r, tmax, cb, tb, im);
     if (COUNT) ++n_nodes;
     ng = make_uint2(cb, (hm & 0xff000000u) | im);
     tg = make_uint2(tb, hm & 0x00ffffffu);

@@ -286,24 +286,71 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
 #define PT_TRAV_MIN_BLOCKS 10  // resident blocks of 128 threads per SM the traversal kernel is compiled for
 #endif
 #ifndef PT_REFILL_MIN
-#define PT_REFILL_MIN 4        // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
+#define PT_REFILL_MIN 8        // idle lanes a warp waits for before it fetches new rays (unless no lane has work left)
 #endif
 #ifndef PT_EXACT_LANES
-#define PT_EXACT_LANES 6       // lanes with a candidate for the exact test before the warp runs it (see below)
+#define PT_EXACT_LANES 4       // lanes with candidates for the exact test before the warp runs it (see k_wf_traverse)
 #endif
 
-// persistent warps over queue `set`: one ray per lane, refilled as lanes finish (dynamic fetch).
-// Every round of the loop a lane does ONE unit of its ray's work, and the warp runs each kind of unit once for all the
-// lanes that are up to it:
-//   exact   the reference's exact test (IEEE division, three IEEE square roots) on the lane's pending candidate — run
-//           when PT_EXACT_LANES lanes have one (or nothing else is left to do): a lane with a candidate waits, because
-//           its ray's t must be settled before it goes on (front to back);
-//   scan    the scan record of one triangle of the lane's triangle group; a marked triangle becomes the candidate;
-//   node    one wide node (node8_visit), when the lane has no triangles left.
-// The first version tested a node's triangles in a per-lane loop right after the visit: ncu's source view put 31 % of
-// the kernel's warp instructions in that loop at 3.0 active lanes and 23 % in the exact test at 1.0 — a node hands a
-// lane 0..6 triangles, so the loop ran for the unluckiest lane.  One unit per round keeps the scan at whatever share of
-// the lanes has triangles at all, and the exact test at >= PT_EXACT_LANES lanes.
+// position of the k-th set bit of m, from bit 0 (k < popc(m) <= 24; __fns is a long software sequence)
+__device__ __forceinline__ int kth_set_bit(unsigned m, int k) {
+    for (int i = 0; i < k; ++i) m &= m - 1u;
+    return __ffs(m) - 1;
+}
+
+// Cooperative scan: the triangle groups the lanes hold after a node round (0..6 triangles each, ~0.65 on average) are
+// numbered through the warp by a prefix sum, and lane i runs the scan record of pair i with the owner's ray fetched by
+// shuffles — one pass of the scan code at ~20 lanes instead of a per-lane loop that runs as long as the unluckiest lane
+// has triangles (ncu's source view of the per-lane version: 31 % of the kernel's warp instructions at 3.0 lanes).  The
+// pairs of one owner sit on consecutive lanes, so a ballot brings the verdicts back.  Must be reached by all 32 lanes.
+// On return tg is consumed and `passed` has bit k set when the owner's k-th triangle (k-th set bit of tg.y from below)
+// has to go through the exact test.
+__device__ __forceinline__ unsigned coop_scan(const SceneView &sc, const Ray8 &r, float eps, float ht, uint2 tg) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int cnt = __popc(tg.y);
+    int incl = cnt;  // inclusive prefix sum of the triangle counts
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(full, incl, off);
+        if (lane >= off) incl += v;
+    }
+    const int total = __shfl_sync(full, incl, 31), start = incl - cnt;
+    unsigned passed = 0u;
+    for (int base = 0; base < total; base += 32) {  // the same trip count for every lane; one trip unless > 32 triangles
+        const int pair = base + lane;
+        int owner = 0;  // the first lane whose inclusive sum exceeds the pair's number
+#pragma unroll
+        for (int step = 16; step; step >>= 1) {
+            const int v = __shfl_sync(full, incl, owner + step - 1);
+            if (v <= pair) owner += step;
+        }
+        owner = min(owner, 31);
+        const int k = pair - __shfl_sync(full, start, owner);
+        const unsigned obits = __shfl_sync(full, tg.y, owner);
+        const unsigned obase = __shfl_sync(full, tg.x, owner);
+        const V3 oo = mk(__shfl_sync(full, r.o.x, owner), __shfl_sync(full, r.o.y, owner), __shfl_sync(full, r.o.z, owner));
+        const V3 dd = mk(__shfl_sync(full, r.d.x, owner), __shfl_sync(full, r.d.y, owner), __shfl_sync(full, r.d.z, owner));
+        Hit hh;
+        hh.t = __shfl_sync(full, ht, owner);
+        bool pass = false;
+        if (pair < total) pass = scan_pass(sc, (int)obase + kth_set_bit(obits, k), oo, dd, eps, hh);
+        const unsigned pm = __ballot_sync(full, pass);
+        const int shift = start - base;  // my pair k was tested by lane k + shift of this trip
+        if (shift > -32 && shift < 32) passed |= shift >= 0 ? pm >> shift : pm << -shift;
+    }
+    return cnt ? passed & ((1u << cnt) - 1u) : 0u;
+}
+
+// persistent warps over queue `set`: one ray per lane, refilled as lanes finish (dynamic fetch).  A round of the loop:
+//   exact   the reference's exact test (IEEE division, three IEEE square roots) on the candidates the scans left — run
+//           when PT_EXACT_LANES lanes hold some (or nothing else is left to do); a lane with candidates sits out the
+//           node phase, because its ray's t must be settled before it walks on (front to back);
+//   node    every other lane enters one wide node (node8_visit): ~29 of 32 lanes;
+//   scan    the triangles those nodes handed out, shared out over the warp (coop_scan).
+// History (profiles/r02_*): the first 8-wide version looped over a node's triangles per lane right after the visit —
+// 31 % of the warp instructions at 3.0 lanes, 23 % in the exact test at 1.0; "one unit per lane per round" cured that
+// but put the 286-instruction node visit at 17 lanes.
 template <bool COUNT>
 __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
@@ -312,16 +359,17 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     int *head = &wf.counters[2 * set + 1];
     const int *queue = wf.queue + (size_t)set * wf.cap;
     const int lane = threadIdx.x & 31;
-    uint2 stack[kStackDepth];
-    int sp = 0, slot = -1, pend = -1;  // pend: record that passed its scan and waits for the exact test
-    uint2 ng = make_uint2(0u, 0u), tg = make_uint2(0u, 0u);
+    uint2 stack[kStackDepth];  // node groups only: triangle groups are consumed in the round that produced them
+    int sp = 0, slot = -1;
+    int pend0 = -1, pend1 = -1;  // records that passed their scan and wait for the exact test
+    uint2 ng = make_uint2(0u, 0u);
     bool done = false;
     Ray8 r;
     ray8_setup(mk(0, 0, 0), mk(0, 0, 1), r);
     Hit h = no_hit();
     unsigned long long n_nodes = 0, n_tris = 0, n_exact = 0, ray_nodes0 = 0;
     while (true) {
-        const bool need = !done && !has_inner(ng) && tg.y == 0u && sp == 0 && pend < 0;
+        const bool need = !done && !has_inner(ng) && sp == 0 && pend0 < 0;
         if (need && slot >= 0) {  // retire the finished ray
             if (COUNT && stats) {
                 atomicAdd(&stats[4], 1ull);
@@ -356,33 +404,41 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             }
         }
         if (__all_sync(0xffffffffu, done)) break;
-        // ---- pop: a lane with nothing in hand takes the top of its stack
-        if (!has_inner(ng) && tg.y == 0u && pend < 0 && sp > 0) {
-            const uint2 e = stack[--sp];
-            if (has_inner(e)) ng = e; else tg = e;
-        }
         // ---- exact phase
-        const unsigned me = __ballot_sync(0xffffffffu, pend >= 0);
+        const unsigned me = __ballot_sync(0xffffffffu, pend0 >= 0);
         if (me) {
-            const unsigned other = __ballot_sync(0xffffffffu, pend < 0 && (tg.y != 0u || has_inner(ng)));
+            const unsigned other = __ballot_sync(0xffffffffu, pend0 < 0 && (has_inner(ng) || sp > 0));
             if (__popc(me) >= PT_EXACT_LANES || other == 0u) {
-                if (pend >= 0) {
-                    tri_intersect_ref(sc.tris + 4 * (size_t)pend, pend, r.o, r.d, eps, h);
-                    pend = -1;
+                if (pend0 >= 0) {
+                    tri_intersect_ref(sc.tris + 4 * (size_t)pend0, pend0, r.o, r.d, eps, h);
+                    if (pend1 >= 0) tri_intersect_ref(sc.tris + 4 * (size_t)pend1, pend1, r.o, r.d, eps, h);
+                    if (COUNT) n_exact += pend1 >= 0 ? 2u : 1u;
+                    pend0 = pend1 = -1;
+                }
+            }
+        }
+        // ---- node phase: one wide node per lane that is not waiting for an exact test
+        uint2 tg = make_uint2(0u, 0u);
+        if (pend0 < 0) {
+            if (!has_inner(ng) && sp > 0) ng = stack[--sp];
+            if (has_inner(ng)) enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
+        }
+        // ---- scan phase: all triangles of this round, shared out over the warp
+        if (__any_sync(0xffffffffu, tg.y != 0u)) {
+            unsigned passed = coop_scan(sc, r, eps, h.t, tg);
+            if (COUNT) n_tris += __popc(tg.y);
+            while (passed) {  // the k-th triangle of my group is a candidate
+                const int k = __ffs(passed) - 1;
+                passed &= passed - 1u;
+                const int rec = (int)tg.x + kth_set_bit(tg.y, k);
+                if (pend0 < 0) pend0 = rec;
+                else if (pend1 < 0) pend1 = rec;
+                else {  // a third candidate from one node (rare): at once
+                    tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, r.o, r.d, eps, h);
                     if (COUNT) ++n_exact;
                 }
             }
         }
-        // ---- scan phase: one triangle of the lane's group
-        if (pend < 0 && tg.y != 0u) {
-            const int j = 31 - __clz((int)tg.y);
-            tg.y &= ~(1u << j);
-            const int rec = (int)tg.x + j;
-            if (scan_pass(sc, rec, r.o, r.d, eps, h)) pend = rec;
-            if (COUNT) ++n_tris;
-        }
-        // ---- node phase: one wide node
-        if (pend < 0 && tg.y == 0u && has_inner(ng)) enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
     }
     if (COUNT && stats) {
         for (int o2 = 16; o2; o2 >>= 1) {
