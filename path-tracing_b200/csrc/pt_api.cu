@@ -182,7 +182,8 @@ static int validate_config(const PtConfig *c) {
     if ((long long)c->width * c->height > 0x7fffffffLL) return fail(PT_EINVAL, "image too large");
     if (c->rays_per_pixel < 0 || c->max_ray_reflections < 0) return fail(PT_EINVAL, "negative spp / depth");
     if (c->sample_begin < 0 || c->sample_step < 0) return fail(PT_EINVAL, "negative sample partition");
-    if (c->intersector != PT_ISECT_REFERENCE) return fail(PT_EINVAL, "intersector %d not available", c->intersector);
+    if (c->intersector != PT_ISECT_REFERENCE && c->intersector != PT_ISECT_WATERTIGHT)
+        return fail(PT_EINVAL, "intersector %d unknown", c->intersector);
     if (c->rr_depth < 0) return fail(PT_EINVAL, "negative rr_depth");
     if ((c->row_begin != 0 || c->row_end != 0) && (c->row_begin < 0 || c->row_end > c->height || c->row_begin > c->row_end))
         return fail(PT_EINVAL, "row range [%d, %d) outside the image (height %d)", c->row_begin, c->row_end, c->height);
@@ -682,7 +683,7 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx, size_t npx_traced, int q_sh
     if (!ds->h_counters) CK(pool_alloc_pinned((void **)&ds->h_counters));
     if (!ds->traverse_blocks) {
         int per_sm = 0, sms = 0;
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false>, 128, 0));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false, false>, 128, 0));
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds->device));
         ds->traverse_blocks = std::max(1, per_sm) * std::max(1, sms);
     }
@@ -736,6 +737,25 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
         ev_used = 0;
         return PT_OK;
     };
+    // the kernel instantiation for (alive lists, intersector)
+    auto launch_begin = [&](int blocks, int pix0, int npix) {
+        if (rp.use_alive) {
+            if (sc.isect) k_wf_begin<COUNT, true, true><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix);
+            else k_wf_begin<COUNT, true, false><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix);
+        } else {
+            if (sc.isect) k_wf_begin<COUNT, false, true><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix);
+            else k_wf_begin<COUNT, false, false><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix);
+        }
+    };
+    auto launch_bounce = [&](int blocks, int pix0, int npix, int b) {
+        if (rp.use_alive) {
+            if (sc.isect) k_wf_bounce<COUNT, true, true><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix, b);
+            else k_wf_bounce<COUNT, true, false><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix, b);
+        } else {
+            if (sc.isect) k_wf_bounce<COUNT, false, true><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix, b);
+            else k_wf_bounce<COUNT, false, false><<<blocks, kWfBlock, 0, st>>>(sc, rp, wf, pix0, npix, b);
+        }
+    };
     CK(cudaMemsetAsync(wf.counters, 0, (kWfCounters + 3 * kAliveLists) * sizeof(int), st));
     const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
     const size_t pix_end = (size_t)rp.row1 * rp.W;  // the rows this call traces (PtConfig::row_begin / row_end)
@@ -747,19 +767,18 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
             const int steps = (remaining + Q - 1) / Q;
             for (int i = 0; i < steps; ++i) {
                 if ((rc = tick(0))) return rc;
-                if (rp.use_alive) k_wf_begin<COUNT, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
-                else k_wf_begin<COUNT, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                launch_begin(slot_blocks, (int)pix0, npix);
                 if ((rc = tock())) return rc;
                 for (int b = 0; b < rp.max_depth; ++b) {
                     if (!sc.brute && sc.root != kRefEmpty) {
                         if ((rc = tick(1))) return rc;
-                        k_wf_traverse<COUNT><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                        if (sc.isect) k_wf_traverse<COUNT, true><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                        else k_wf_traverse<COUNT, false><<<ds->traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
                         if ((rc = tock())) return rc;
                         ++n;
                     }
                     if ((rc = tick(2))) return rc;
-                    if (rp.use_alive) k_wf_bounce<COUNT, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
-                    else k_wf_bounce<COUNT, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    launch_bounce(slot_blocks, (int)pix0, npix, b);
                     if ((rc = tock())) return rc;
                     ++n;
                 }
@@ -799,12 +818,18 @@ extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, 
     CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
     RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
     if (cfg->reserved[3] == 0 && ds->view.sky) rp.use_alive = 1;  // an open scene: every miss ends a path
+    ds->view.isect = cfg->intersector == PT_ISECT_WATERTIGHT ? 1 : 0;  // the kernels take the view by value
     CK(cudaEventRecord(ds->ev0, st));
     int launches = 1;
     if (cfg->reserved[0] == 1) {  // megakernel variant
         const int tiles = ((rp.W + kTileW - 1) / kTileW) * ((rp.H + kTileH - 1) / kTileH);
-        if (ds->counters) k_render_mega<true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
-        else k_render_mega<false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+        if (ds->view.isect) {
+            if (ds->counters) k_render_mega<true, true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+            else k_render_mega<false, true><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+        } else {
+            if (ds->counters) k_render_mega<true, false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+            else k_render_mega<false, false><<<tiles, kBlockThreads, 0, st>>>(ds->view, rp);
+        }
         CK(cudaGetLastError());
     } else {
         rc = ds->counters ? render_wavefront<true>(ds, rp, st, &launches) : render_wavefront<false>(ds, rp, st, &launches);
@@ -857,6 +882,7 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
     if (!ds || !rays6 || !tri_id || !t || n < 0) return fail(PT_EINVAL, "bad intersect arguments");
     if (n == 0) return PT_OK;
     const float eps = cfg ? cfg->eps : 1e-4f;
+    ds->view.isect = cfg && cfg->intersector == PT_ISECT_WATERTIGHT ? 1 : 0;
     DevBuf<float> d_rays, d_t;
     DevBuf<int> d_ids;
     CK(d_rays.alloc(6 * (size_t)n)); CK(d_t.alloc(n)); CK(d_ids.alloc(n));
@@ -864,8 +890,13 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
     CK(cudaMemset(ds->stats, 0, kStatWords * sizeof(unsigned long long)));
     const int grid = (int)std::min<long long>((n + 255) / 256, 148 * 32);
     CK(cudaEventRecord(ds->ev0));
-    if (ds->counters) k_intersect<true><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
-    else k_intersect<false><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+    if (ds->view.isect) {
+        if (ds->counters) k_intersect<true, true><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+        else k_intersect<false, true><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+    } else {
+        if (ds->counters) k_intersect<true, false><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+        else k_intersect<false, false><<<grid, 256>>>(ds->view, d_rays.p, n, eps, d_ids.p, d_t.p, ds->stats);
+    }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ds->ev1));
     ds->timed = true;

@@ -193,7 +193,7 @@ constexpr int kBlockThreads = kTileW * kTileH * kQuad;  // 256
 // ---- megakernel variant: one thread carries one path through all its bounces (PtConfig::reserved[0] == 1) -------
 // Kept as the second, independent implementation of the loop (the wavefront pipeline in pt_wavefront.cuh is the
 // default): simplest possible control flow, no global path state, best for tiny frames.
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __global__ void __launch_bounds__(kBlockThreads)
 k_render_mega(SceneView sc, RenderParams rp) {
     __shared__ float4 s_large[kLargeRowsMax];
@@ -238,7 +238,7 @@ k_render_mega(SceneView sc, RenderParams rp) {
             int depth = 0;
             bool alive = true;
             while (alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f)) {  // ray.h:52-54
-                const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
+                const Hit h = nearest_hit<COUNT, WT>(sc, s_large, o, d, rp.eps, n_nodes, n_tris);
                 ++nseg;
                 alive = shade(sc, s_large, rp, h, pixel, (uint32_t)s, o, d, T, depth, wgt, &c, &contrib);
             }
@@ -304,7 +304,7 @@ k_render_mega(SceneView sc, RenderParams rp) {
 }
 
 // ---- pt_intersect: nearest hit on an explicit ray set ------------------------------------------------------
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __global__ void __launch_bounds__(256)
 k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float eps, int *__restrict__ ids,
             float *__restrict__ ts, unsigned long long *stats) {
@@ -316,7 +316,7 @@ k_intersect(SceneView sc, const float *__restrict__ rays6, long long n, float ep
         const float *r = rays6 + 6 * i;
         const V3 o = mk(r[0], r[1], r[2]);
         const V3 d = normalize4w0(mk(r[3], r[4], r[5]));  // Ray's constructor, ray.h:21-25
-        const Hit h = nearest_hit<COUNT>(sc, s_large, o, d, eps, n_nodes, n_tris);
+        const Hit h = nearest_hit<COUNT, WT>(sc, s_large, o, d, eps, n_nodes, n_tris);
         ids[i] = h.idx;
         ts[i] = h.t;
     }

@@ -72,6 +72,8 @@ struct SceneView {
     int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
     int n_quads;  // of which the first 2 n_quads form quad scan units
     int root;     // 0 = wide node 0 is the root; kRefEmpty if n_bvh == 0
+    int isect;    // host side only — picks the kernel instantiation: 0 the reference's plane + area-sum test (parity
+                  // mode), 1 the watertight test of the geometric triangle
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)
     const float4 *lrecs;     // shared-memory image of the large triangles (layout above), large_rows() float4
     float4 root_lo, root_hi; // box of the BVH root

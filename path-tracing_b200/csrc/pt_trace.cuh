@@ -96,6 +96,74 @@ __device__ __forceinline__ void tri_intersect_ref(const float4 *r, int rec, V3 o
     h.rec = rec;
 }
 
+// ---- the throughput intersector (PtConfig.intersector = PT_ISECT_WATERTIGHT; north_star's "watertight
+// Moller-Trumbore") -------------------------------------------------------------------------------------------------
+// Woop, Benthin, Wald 2013, "Watertight ray/triangle intersection": the ray is sheared so that it runs along +z of its
+// dominant axis, and the triangle is tested with three 2D edge functions whose shared-edge values are exactly
+// antisymmetric between neighbours (plain products and differences — this TU never contracts to FMA), so a ray cannot
+// slip between two triangles that share an edge.  Edge functions that come out exactly 0 are re-evaluated in double,
+// as in the paper.  No IEEE division or square root: one MUFU.RCP for the shear, one for T / det.
+// This is NOT the reference's test (triangles.h:48-73): it hits the geometric triangle — no eps dilation, no `vn`
+// plane — so hit IDs can differ from the reference's on edge-grazing rays and differ wholesale where the stored plane
+// is not the geometric one (Tor.obj); DESIGN.md carries the measured mismatch rates.  Nearest-hit rule, eps and the
+// tie-break on the caller's index are the same; shading still uses the stored plane's normal (scene.cpp:123).
+__device__ __forceinline__ float pick3(V3 v, int k) { return k == 0 ? v.x : (k == 1 ? v.y : v.z); }
+
+__device__ __forceinline__ bool watertight_test(float4 a, float4 b, float4 c, V3 o, V3 d, float *t_out) {
+    const float ax = fabsf(d.x), ay = fabsf(d.y), az = fabsf(d.z);
+    const int kz = ax > ay ? (ax > az ? 0 : 2) : (ay > az ? 1 : 2);
+    int kx = kz == 2 ? 0 : kz + 1, ky = kx == 2 ? 0 : kx + 1;
+    const float dz = pick3(d, kz);
+    if (dz < 0.0f) { const int tmp = kx; kx = ky; ky = tmp; }  // keeps the winding
+    const float Sz = rcp_approx(dz), Sx = pick3(d, kx) * Sz, Sy = pick3(d, ky) * Sz;
+    const V3 A = mk(a.x, a.y, a.z) - o, B = mk(b.x, b.y, b.z) - o, C = mk(c.x, c.y, c.z) - o;
+    const float Akz = pick3(A, kz), Bkz = pick3(B, kz), Ckz = pick3(C, kz);
+    const float Ax = pick3(A, kx) - Sx * Akz, Ay = pick3(A, ky) - Sy * Akz;
+    const float Bx = pick3(B, kx) - Sx * Bkz, By = pick3(B, ky) - Sy * Bkz;
+    const float Cx = pick3(C, kx) - Sx * Ckz, Cy = pick3(C, ky) - Sy * Ckz;
+    float U = Cx * By - Cy * Bx, V = Ax * Cy - Ay * Cx, W = Bx * Ay - By * Ax;
+    if (U == 0.0f || V == 0.0f || W == 0.0f) {
+        U = (float)((double)Cx * (double)By - (double)Cy * (double)Bx);
+        V = (float)((double)Ax * (double)Cy - (double)Ay * (double)Cx);
+        W = (float)((double)Bx * (double)Ay - (double)By * (double)Ax);
+    }
+    if ((U < 0.0f || V < 0.0f || W < 0.0f) && (U > 0.0f || V > 0.0f || W > 0.0f)) return false;  // two-sided
+    const float det = U + V + W;
+    if (det == 0.0f) return false;
+    const float T = U * (Sz * Akz) + V * (Sz * Bkz) + W * (Sz * Ckz);
+    *t_out = T * rcp_approx(det);
+    return true;
+}
+
+__device__ __forceinline__ void tri_intersect_wt(float4 a, float4 b, float4 c, int rec, const float4 *tris, V3 o, V3 d,
+                                                 float eps, Hit &h) {
+    float t;
+    if (!watertight_test(a, b, c, o, d, &t)) return;
+    if (!(t <= h.t) || t < eps) return;
+    const int idx = __float_as_int(b.w);
+    if (t == h.t) {
+        if (h.idx == kIdxLazy) h.idx = __float_as_int(__ldg(tris + 4 * (size_t)h.rec + 2).w);
+        if (!(idx < h.idx)) return;
+    }
+    h.t = t;
+    h.idx = idx;
+    h.rec = rec;
+}
+
+// the intersector the kernel was instantiated for (WT = watertight), on global record `rec`
+template <bool WT>
+__device__ __forceinline__ void tri_intersect(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
+    const float4 *r = sc.tris + 4 * (size_t)rec;
+    if (WT) {
+        float4 pl, a, b, c;
+        ldg256(r, pl, a);
+        ldg256(r + 2, b, c);
+        tri_intersect_wt(a, b, c, rec, sc.tris, o, d, eps, h);
+    } else {
+        tri_intersect_ref(r, rec, o, d, eps, h);
+    }
+}
+
 // ---- large triangles from shared memory (image layout: pt_scene.cuh, built by k_large_pack) ------------------
 __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large) {
     const int rows = large_rows(sc.n_large, sc.n_quads);
@@ -175,12 +243,17 @@ __device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, in
 }
 
 // exact test on the marked records k0 + bit of the shared-memory record rows
+template <bool WT>
 __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, unsigned mask, int rec_base, V3 o, V3 d,
                                                 float eps, Hit &h) {
     while (mask) {
         const int k = k0 + __ffs(mask) - 1;
         mask &= mask - 1u;
         const float4 *r = s_large + 4 * k;
+        if (WT) {  // h.idx is never lazy here (the shared-memory phase starts every query)
+            tri_intersect_wt(r[1], r[2], r[3], rec_base + k, nullptr, o, d, eps, h);
+            continue;
+        }
         const float nd = plane_distance(r[0], o, d);
         if (!(nd <= h.t) || nd < eps) continue;
         const float4 a = r[1], b = r[2], c = r[3];
@@ -193,6 +266,7 @@ __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, u
     }
 }
 
+template <bool WT>
 __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int n_quads, int rec_base, V3 o, V3 d,
                                             float eps, Hit &h) {
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
@@ -221,12 +295,12 @@ __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, 
             bits = 1u;
             m &= ~(1u << (k & 31));
         }
-        large_resolve32(s_large, rnear, bits, rec_base, o, d, eps, h);
+        large_resolve32<WT>(s_large, rnear, bits, rec_base, o, d, eps, h);
     }
-    large_resolve32(s_large, 0, q0, rec_base, o, d, eps, h);
-    if (q1) large_resolve32(s_large, 32, q1, rec_base, o, d, eps, h);
-    large_resolve32(s_large, 2 * n_quads, s0, rec_base, o, d, eps, h);
-    if (s1) large_resolve32(s_large, 2 * n_quads + 32, s1, rec_base, o, d, eps, h);
+    large_resolve32<WT>(s_large, 0, q0, rec_base, o, d, eps, h);
+    if (q1) large_resolve32<WT>(s_large, 32, q1, rec_base, o, d, eps, h);
+    large_resolve32<WT>(s_large, 2 * n_quads, s0, rec_base, o, d, eps, h);
+    if (s1) large_resolve32<WT>(s_large, 2 * n_quads + 32, s1, rec_base, o, d, eps, h);
 }
 
 // Slab test of one child box: entry distance, or +inf when the ray [0, tmax] misses the box.  fminf/fmaxf drop a
@@ -360,7 +434,17 @@ __device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes
 // The scan record of one BVH triangle (plane + three edge planes): the conservative test of scan_singles with the same
 // tolerances — approximate reciprocal, range widened by 2e-6 relative, edge planes already dilated by the builder; a
 // NaN anywhere marks.  true = the reference's exact test has to decide.
+template <bool WT>
 __device__ __forceinline__ bool scan_pass(const SceneView &sc, int rec, V3 o, V3 d, float eps, const Hit &h) {
+    if (WT) {  // watertight mode: the scan record bounds the REFERENCE's acceptance set around the stored plane, which
+                     // need not contain the geometric hit; the test itself is cheap enough to stand in for its own filter
+        const float4 *r = sc.tris + 4 * (size_t)rec;
+        float4 pl, a, b, c;
+        ldg256(r, pl, a);
+        ldg256(r + 2, b, c);
+        float t;
+        return watertight_test(a, b, c, o, d, &t) && t <= h.t && !(t < eps);
+    }
     const float4 *s = sc.scans + 4 * (size_t)rec;
     float4 p, e0, e1, e2;
     ldg256(s, p, e0);
@@ -379,9 +463,10 @@ __device__ __forceinline__ bool scan_pass(const SceneView &sc, int rec, V3 o, V3
 }
 
 // One BVH triangle: scan record first, the reference's exact test if that marks it.  Returns whether the exact test ran.
+template <bool WT>
 __device__ __forceinline__ bool tri_test(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
-    if (!scan_pass(sc, rec, o, d, eps, h)) return false;
-    tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, o, d, eps, h);
+    if (!scan_pass<WT>(sc, rec, o, d, eps, h)) return false;
+    tri_intersect<WT>(sc, rec, o, d, eps, h);
     return true;
 }
 
@@ -408,19 +493,19 @@ __device__ __forceinline__ void enter_child(const SceneView &sc, const Ray8 &r, 
 }
 
 // all triangles of group tg
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __device__ __forceinline__ void test_group(const SceneView &sc, const Ray8 &r, float eps, Hit &h, uint2 &tg,
                                            unsigned long long &n_tris, unsigned long long &n_exact) {
     while (tg.y) {
         const int j = 31 - __clz((int)tg.y);
         tg.y &= ~(1u << j);
-        const bool exact = tri_test(sc, (int)tg.x + j, r.o, r.d, eps, h);
+        const bool exact = tri_test<WT>(sc, (int)tg.x + j, r.o, r.d, eps, h);
         if (COUNT) { ++n_tris; n_exact += exact ? 1u : 0u; }
     }
 }
 
 // the whole walk in one thread (pt_intersect, the megakernel)
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __device__ __forceinline__ void bvh8_traverse(const SceneView &sc, V3 o, V3 d, float eps, Hit &h,
                                               unsigned long long &n_nodes, unsigned long long &n_tris) {
     Ray8 r;
@@ -436,7 +521,7 @@ __device__ __forceinline__ void bvh8_traverse(const SceneView &sc, V3 o, V3 d, f
             tg = ng;
             ng = make_uint2(0u, 0u);
         }
-        test_group<COUNT>(sc, r, eps, h, tg, n_tris, n_exact);
+        test_group<COUNT, WT>(sc, r, eps, h, tg, n_tris, n_exact);
         if (!has_inner(ng)) {
             if (sp == 0) break;
             ng = stack[--sp];
@@ -445,24 +530,24 @@ __device__ __forceinline__ void bvh8_traverse(const SceneView &sc, V3 o, V3 d, f
 }
 
 // scene.cpp:114-120 as written: every triangle, in order (the checker mode, PT_ACCEL_BRUTE)
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __device__ __forceinline__ Hit brute_hit(const SceneView &sc, V3 o, V3 d, float eps, unsigned long long &n_tris) {
     Hit h = no_hit();
-    for (int k = 0; k < sc.n_tri; ++k) tri_intersect_ref(sc.tris + 4 * (size_t)k, k, o, d, eps, h);
+    for (int k = 0; k < sc.n_tri; ++k) tri_intersect<WT>(sc, k, o, d, eps, h);
     if (COUNT) n_tris += sc.n_tri;
     return h;
 }
 
 // Whole nearest-hit query in one thread (pt_intersect, the megakernel).
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_large, V3 o, V3 d, float eps,
                                            unsigned long long &n_nodes, unsigned long long &n_tris) {
-    if (sc.brute) return brute_hit<COUNT>(sc, o, d, eps, n_tris);
+    if (sc.brute) return brute_hit<COUNT, WT>(sc, o, d, eps, n_tris);
     Hit h = no_hit();
-    large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
+    large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
     if (COUNT) n_tris += sc.n_large;
     if (!reaches_root(sc, o, d, h.t)) return h;
-    bvh8_traverse<COUNT>(sc, o, d, eps, h, n_nodes, n_tris);
+    bvh8_traverse<COUNT, WT>(sc, o, d, eps, h, n_nodes, n_tris);
     return h;
 }
 

@@ -129,7 +129,7 @@ __device__ __forceinline__ void alive_store(const WfState &wf, int list, int slo
                          __popc(ma & ((1u << lane) - 1u))], slot);
 }
 
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large, const WfState &wf, int set, int slot,
                                       bool active, V3 o, V3 d, float eps, unsigned long long &n_nodes,
                                       unsigned long long &n_tris) {
@@ -137,9 +137,9 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
     if (active) {
         Hit h = no_hit();
         if (sc.brute) {
-            h = brute_hit<COUNT>(sc, o, d, eps, n_tris);  // (not nearest_hit: its traversal stack would become this kernel's frame)
+            h = brute_hit<COUNT, WT>(sc, o, d, eps, n_tris);  // (not nearest_hit: its traversal stack would become this kernel's frame)
         } else {
-            large_phase(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
+            large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
             if (COUNT) n_tris += sc.n_large;
             need = reaches_root(sc, o, d, h.t);
         }
@@ -156,7 +156,9 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
     }
 }
 
-template <bool COUNT, bool ALIVE>
+// WT (here and in the kernels below): the intersector, PT_ISECT_WATERTIGHT or the reference's — a template parameter, so
+// that each instantiation carries only its own test (as a run-time branch the second test cost the parity path 5 %)
+template <bool COUNT, bool ALIVE, bool WT>
 __global__ void __launch_bounds__(kWfBlock)
 k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     __shared__ float4 s_large[kLargeRowsMax];
@@ -190,7 +192,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     }
     unsigned ma = 0u;
     const int abase = ALIVE ? alive_reserve(wf, 0, traced, ma) : 0;
-    front<COUNT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
+    front<COUNT, WT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
     if (ALIVE) alive_store(wf, 0, slot, traced, ma, abase);
     if (COUNT && rp.stats) {  // one atomic per warp per counter
         for (int o2 = 16; o2; o2 >>= 1) {
@@ -205,7 +207,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
 }
 
 // bounce `b` (0-based): shades segment b of every live path and starts segment b+1; writes queue (b+1)&1
-template <bool COUNT, bool ALIVE>
+template <bool COUNT, bool ALIVE, bool WT>
 __global__ void __launch_bounds__(kWfBlock)
 k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
     __shared__ float4 s_large[kLargeRowsMax];
@@ -268,7 +270,7 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
     }
     unsigned ma = 0u;
     const int abase = ALIVE ? alive_reserve(wf, (b + 1) % 3, alive, ma) : 0;
-    front<COUNT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
+    front<COUNT, WT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
     if (ALIVE) alive_store(wf, set, slot, alive, ma, abase);
     if (COUNT && rp.stats) {  // one atomic per warp per counter
         for (int o2 = 16; o2; o2 >>= 1) {
@@ -305,6 +307,7 @@ __device__ __forceinline__ int kth_set_bit(unsigned m, int k) {
 // pairs of one owner sit on consecutive lanes, so a ballot brings the verdicts back.  Must be reached by all 32 lanes.
 // On return tg is consumed and `passed` has bit k set when the owner's k-th triangle (k-th set bit of tg.y from below)
 // has to go through the exact test.
+template <bool WT>
 __device__ __forceinline__ unsigned coop_scan(const SceneView &sc, const Ray8 &r, float eps, float ht, uint2 tg) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -334,7 +337,7 @@ __device__ __forceinline__ unsigned coop_scan(const SceneView &sc, const Ray8 &r
         Hit hh;
         hh.t = __shfl_sync(full, ht, owner);
         bool pass = false;
-        if (pair < total) pass = scan_pass(sc, (int)obase + kth_set_bit(obits, k), oo, dd, eps, hh);
+        if (pair < total) pass = scan_pass<WT>(sc, (int)obase + kth_set_bit(obits, k), oo, dd, eps, hh);
         const unsigned pm = __ballot_sync(full, pass);
         const int shift = start - base;  // my pair k was tested by lane k + shift of this trip
         if (shift > -32 && shift < 32) passed |= shift >= 0 ? pm >> shift : pm << -shift;
@@ -351,7 +354,7 @@ __device__ __forceinline__ unsigned coop_scan(const SceneView &sc, const Ray8 &r
 // History (profiles/r02_*): the first 8-wide version looped over a node's triangles per lane right after the visit —
 // 31 % of the warp instructions at 3.0 lanes, 23 % in the exact test at 1.0; "one unit per lane per round" cured that
 // but put the 286-instruction node visit at 17 lanes.
-template <bool COUNT>
+template <bool COUNT, bool WT>
 __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
     const int count = wf.counters[2 * set];
@@ -410,8 +413,8 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             const unsigned other = __ballot_sync(0xffffffffu, pend0 < 0 && (has_inner(ng) || sp > 0));
             if (__popc(me) >= PT_EXACT_LANES || other == 0u) {
                 if (pend0 >= 0) {
-                    tri_intersect_ref(sc.tris + 4 * (size_t)pend0, pend0, r.o, r.d, eps, h);
-                    if (pend1 >= 0) tri_intersect_ref(sc.tris + 4 * (size_t)pend1, pend1, r.o, r.d, eps, h);
+                    tri_intersect<WT>(sc, pend0, r.o, r.d, eps, h);
+                    if (pend1 >= 0) tri_intersect<WT>(sc, pend1, r.o, r.d, eps, h);
                     if (COUNT) n_exact += pend1 >= 0 ? 2u : 1u;
                     pend0 = pend1 = -1;
                 }
@@ -425,7 +428,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         }
         // ---- scan phase: all triangles of this round, shared out over the warp
         if (__any_sync(0xffffffffu, tg.y != 0u)) {
-            unsigned passed = coop_scan(sc, r, eps, h.t, tg);
+            unsigned passed = coop_scan<WT>(sc, r, eps, h.t, tg);
             if (COUNT) n_tris += __popc(tg.y);
             while (passed) {  // the k-th triangle of my group is a candidate
                 const int k = __ffs(passed) - 1;
@@ -434,7 +437,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
                 if (pend0 < 0) pend0 = rec;
                 else if (pend1 < 0) pend1 = rec;
                 else {  // a third candidate from one node (rare): at once
-                    tri_intersect_ref(sc.tris + 4 * (size_t)rec, rec, r.o, r.d, eps, h);
+                    tri_intersect<WT>(sc, rec, r.o, r.d, eps, h);
                     if (COUNT) ++n_exact;
                 }
             }

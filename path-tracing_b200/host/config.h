@@ -35,6 +35,7 @@ public:
     // extensions of the B200 build (defaults = reference behaviour)
     int gpus = 1;
     int accel = PT_ACCEL_AUTO;
+    int isect = PT_ISECT_REFERENCE;  // -ISECT 1: the watertight throughput intersector (not the reference's test)
     int rr = 0;  // -RR <depth>: Russian roulette once a path's depth reaches <depth> (0 = off)
     std::string cache = "";  // -CACHE <dir>: keep a binary image of the parsed model there (scene.cpp, LoadModel)
 
@@ -67,6 +68,7 @@ public:
             else if (is("-GPUS")) gpus = std::atoi(val);
             else if (is("-ACCEL")) accel = std::atoi(val);
             else if (is("-RR")) rr = std::atoi(val);
+            else if (is("-ISECT")) isect = std::atoi(val);
             else if (is("-CACHE")) cache = val;
         }
     }
@@ -85,7 +87,7 @@ public:
         c.eps = eps; c.error = error;
         c.seed = getSeed();
         c.sample_begin = 0; c.sample_step = 1;
-        c.intersector = PT_ISECT_REFERENCE;
+        c.intersector = isect;
         c.accel = accel;
         c.n_gpus = gpus;
         c.rr_depth = rr;

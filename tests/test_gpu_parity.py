@@ -568,6 +568,42 @@ def test_scene_cache_is_keyed_by_content(lib, tor):
         assert_bits_equal(x, y)
 
 
+def test_watertight_intersector_mode(lib, oracle):
+    """PtConfig.intersector = PT_ISECT_WATERTIGHT, north_star's throughput intersector (Woop-style test of the geometric
+    triangle; NOT the reference's test, so no bit-exact claim against it).  What must hold: the 8-wide BVH and the
+    brute-force scan agree bit for bit in this mode too; both pipelines give the same accumulators; on scenes whose
+    stored planes are the geometric ones the nearest-hit IDs are the reference's except on edge-grazing rays (measured
+    rates: profiles/r02_watertight_report.txt) with t within 1e-3 relative; and the converged Cornell image meets the
+    north_star's RMSE bar of 1e-3 against the reference's."""
+    WT = ptb200.PT_ISECT_WATERTIGHT
+    for name, make, max_rate in (("cornell", scenes.cornell, 0.002), ("glossy", scenes.glossy_mix, 0.002),
+                                 ("torus40", lambda: scenes.torus_room(40, 20), 0.05)):
+        sc = make()
+        ids, t = lib.intersect(sc, G[name + "_rays"], ptb200.config(intersector=WT))
+        bids, bt = lib.intersect(sc, G[name + "_rays"], ptb200.config(intersector=WT, accel=BRUTE))
+        assert_bits_equal(ids, bids, name + " ids, BVH vs brute force")
+        assert_bits_equal(t, bt, name + " t, BVH vs brute force")
+        bad = ids != G[name + "_ids"]
+        assert bad.mean() <= max_rate, (name, bad.mean())
+        same = ~bad & (ids >= 0)
+        np.testing.assert_allclose(t[same], G[name + "_t"][same], rtol=1e-3)
+    sc = scenes.torus_room(40, 20)
+    a = lib.render_accum(sc, ptb200.config(64, 48, 16, 8, 1e-4, -1.0, seed=4, intersector=WT))
+    b = lib.render_accum(sc, ptb200.config(64, 48, 16, 8, 1e-4, -1.0, seed=4, intersector=WT, mode=1))
+    c = lib.render_accum(sc, ptb200.config(64, 48, 16, 8, 1e-4, -1.0, seed=4, intersector=WT, accel=BRUTE))
+    for x, y, z in zip(a, b, c):
+        assert_bits_equal(x, y, "wavefront vs megakernel")
+        assert_bits_equal(x, z, "BVH vs brute force")
+    assert a[2].sum() > 0
+    from test_oracle import CONVERGED_RMSE_TOL, converged_image
+    CV, img = converged_image("cornell")
+    W, H, spp, depth, seed = map(int, CV["cornell_cfg"])
+    rgb = lib.render(scenes.cornell(), ptb200.config(W, H, spp, depth, 1e-4, -1.0, seed=seed, intersector=WT))
+    assert float(np.sqrt(np.mean((rgb.astype(np.float64) - img) ** 2))) <= CONVERGED_RMSE_TOL
+    with pytest.raises(ptb200.PtError):
+        lib.intersect(sc, G["torus40_rays"], ptb200.config(intersector=7))
+
+
 def test_read_bandwidth_probe(lib):
     """pt_probe_read_bandwidth (bench.py's L2 peak): an L2-resident footprint reads faster than one that
     has to come from HBM, and both are plausible for a B200."""
