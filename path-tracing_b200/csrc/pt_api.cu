@@ -341,6 +341,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         CK(cudaMemcpy(&scr, d_scr.p, sizeof scr, cudaMemcpyDeviceToHost));
         const int n_large = std::min(scr.n_large, kMaxLarge);
         const int nb = n - n_large;
+        const bool too_many_unbounded = scr.n_unbounded > kMaxLarge;  // slivers no box can hold (pt_bvh.cuh robust_eps)
         v.brute = 0; v.n_bvh = nb; v.n_large = n_large;
         if (n_large) {  // pairs the large triangles into quad scan units and reorders the tail of vals2 accordingly
             k_large_pack<<<1, kMaxLarge>>>(vals2.p, d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb, n_large, eps, d_scr.p, ds->lrecs);
@@ -402,11 +403,16 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         }
         k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nb ? order.p : vals2.p, n, ds->tris);
         ++launches;
-        if (levels > kMaxLevels) {
+        int max_levels = kMaxLevels;
+        if (const char *e = getenv("PT_MAX_BVH_LEVELS")) max_levels = std::max(1, std::min(kMaxLevels, atoi(e)));  // test hook: a lower limit
+        if (too_many_unbounded && want == PT_ACCEL_LBVH)
+            return fail(PT_EINVAL, "%d degenerate triangles whose acceptance set is unbounded (max %d): use PT_ACCEL_AUTO or PT_ACCEL_BRUTE",
+                        scr.n_unbounded, kMaxLarge);
+        if (levels > max_levels || too_many_unbounded) {
             // the traversal stack holds two entries per level: a deeper tree (adversarial centroid spacing) is not walked.
             // PT_ACCEL_AUTO renders it with the brute-force scan instead (correct, slow); an explicit LBVH request fails.
-            if (want == PT_ACCEL_LBVH)
-                return fail(PT_EINVAL, "the scene needs a %d-level BVH (max %d): use PT_ACCEL_AUTO or PT_ACCEL_BRUTE", levels, kMaxLevels);
+            if (want == PT_ACCEL_LBVH && levels > max_levels)
+                return fail(PT_EINVAL, "the scene needs a %d-level BVH (max %d): use PT_ACCEL_AUTO or PT_ACCEL_BRUTE", levels, max_levels);
             CK(cudaDeviceSynchronize());
             k_pack_tris<<<blocks_for(n, 256), 256>>>(d_verts.p, d_planes.p, d_squares.p, d_matid.p, nullptr, n, ds->tris);
             ++launches;
@@ -882,6 +888,8 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
     if (!ds || !rays6 || !tri_id || !t || n < 0) return fail(PT_EINVAL, "bad intersect arguments");
     if (n == 0) return PT_OK;
     const float eps = cfg ? cfg->eps : 1e-4f;
+    if (cfg && cfg->intersector != PT_ISECT_REFERENCE && cfg->intersector != PT_ISECT_WATERTIGHT)
+        return fail(PT_EINVAL, "intersector %d unknown", cfg->intersector);
     ds->view.isect = cfg && cfg->intersector == PT_ISECT_WATERTIGHT ? 1 : 0;
     DevBuf<float> d_rays, d_t;
     DevBuf<int> d_ids;

@@ -49,8 +49,8 @@ __device__ __forceinline__ int f2ord(float f) {
 }
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
-struct BuildScratch {  // 8 ints: scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, quad units
-    int lo[3], hi[3], n_large, n_quads;
+struct BuildScratch {  // scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, quad units, unbounded count
+    int lo[3], hi[3], n_large, n_quads, n_unbounded, pad;
 };
 
 __global__ void k_init_scratch(BuildScratch *s) {
@@ -58,6 +58,8 @@ __global__ void k_init_scratch(BuildScratch *s) {
     s->hi[0] = s->hi[1] = s->hi[2] = f2ord(-FLT_MAX);
     s->n_large = 0;
     s->n_quads = 0;
+    s->n_unbounded = 0;
+    s->pad = 0;
 }
 
 __global__ void k_vertex_bounds(const float *__restrict__ verts, int n, BuildScratch *s) {
@@ -86,15 +88,51 @@ __global__ void k_vertex_bounds(const float *__restrict__ verts, int n, BuildScr
     }
 }
 
+// Effective eps of the bounds: what the reference's area-sum test can accept in fp32, not in exact arithmetic.
+//  * the sums carry rounding proportional to S (4e-6 (S + eps));
+//  * the hit point P and the differences P - v_k carry a few ulp of the scene's largest coordinate (amax), so each
+//    cross product of two such differences of length r is off by up to ~ r (4 amax + 2 r) 2^-23.  For a triangle of
+//    ordinary size this is nothing: the accepted points lie within eps / (2 L) of it.  For a SLIVER (shortest edge L of
+//    1e-4 and below in a 30-unit scene) that distance is units, the noise approaches eps itself, and beyond it the three
+//    differences become the same float and the computed areas vanish: the reference then accepts the whole plane.
+//    robust_eps finds the reach by iteration.  A triangle whose reach runs away is UNBOUNDED: no box, no edge plane — it is tested exactly against every ray (it joins the
+//    shared-memory list; a scene with more than kMaxLarge of them is rendered by brute force).
+// (Found by test_deep_and_degenerate_trees: clusters of 1e-6-sized triangles, 292 of 40,000 hit IDs off.)
+__device__ __forceinline__ float robust_eps(float S, float l_min, float l_max, float eps, float amax, bool *unbounded) {
+    const float e0 = eps * 1.01f + 4e-6f * (S + eps);
+    // reach r of the accepted set beyond the triangle and the noise at that reach feed each other: iterate
+    // r = 1.05 (e0 + 2 noise(r)) / (2 l_min), noise(r) = 3 * 2^-22 * (r + l_max) (4 amax + 2 (r + l_max)); for an ordinary
+    // triangle this settles after a step or two, for a sliver it runs away
+    float r = 0.0f, noise = 0.0f;
+    bool grows = false;
+#pragma unroll 1
+    for (int it = 0; it < 8; ++it) {
+        const float f = r + l_max;
+        noise = 3.0f * 2.4e-7f * f * (4.0f * amax + 2.0f * f);
+        const float rn = 1.05f * (e0 + 2.0f * noise) / (2.0f * l_min);
+        grows = !(rn <= 1.1f * r + 1e-7f);  // still growing by more than 10 % (or NaN / inf)
+        r = rn;
+        if (!(r <= 8.0f * amax)) break;
+    }
+    *unbounded = !(r <= 8.0f * amax) || grows;
+    return e0 + 2.0f * noise;
+}
+
 // Conservative box of everything the reference's Intersect can accept for this triangle (see header comment).
-__device__ __forceinline__ void tri_bounds(V3 v0, V3 v1, V3 v2, float4 plane, float S, float eps, float pad, V3 *lo,
-                                           V3 *hi) {
+// *unbounded: no finite box holds that set (a sliver, robust_eps): lo / hi are then the vertex box.
+__device__ __forceinline__ void tri_bounds(V3 v0, V3 v1, V3 v2, float4 plane, float S, float eps, float pad, float amax,
+                                           V3 *lo, V3 *hi, bool *unbounded) {
     const V3 v[3] = {v0, v1, v2};
-    // effective eps: the reference's sums carry fp32 rounding proportional to S
-    const float e = eps * 1.01f + 4e-6f * (S + eps);
+    const float l0 = length3(v1 - v0), l1 = length3(v2 - v1), l2 = length3(v0 - v2);
+    *unbounded = false;
     V3 l = mk(fminf(v0.x, fminf(v1.x, v2.x)), fminf(v0.y, fminf(v1.y, v2.y)), fminf(v0.z, fminf(v1.z, v2.z)));
     V3 h = mk(fmaxf(v0.x, fmaxf(v1.x, v2.x)), fmaxf(v0.y, fmaxf(v1.y, v2.y)), fmaxf(v0.z, fmaxf(v1.z, v2.z)));
     if (!(S > 0.0f) || !(S <= FLT_MAX) || !(plane.x == plane.x)) {  // degenerate: NaN plane, never accepted here
+        *lo = l; *hi = h;
+        return;
+    }
+    const float e = robust_eps(S, fminf(l0, fminf(l1, l2)), fmaxf(l0, fmaxf(l1, l2)), eps, amax, unbounded);
+    if (*unbounded) {
         *lo = l; *hi = h;
         return;
     }
@@ -115,7 +153,7 @@ __device__ __forceinline__ void tri_bounds(V3 v0, V3 v1, V3 v2, float4 plane, fl
             const float z = fabsf((dot3(ns, q) + plane.w) / nsng);
             zmax = fmaxf(zmax, z == z ? z : FLT_MAX);
         }
-    const float per = length3(v1 - v0) + length3(v2 - v1) + length3(v0 - v2);
+    const float per = l0 + l1 + l2;
     const float zlens = sqrtf(2.0f * S * e + e * e) / per;
     const float zp = fminf(zmax * 1.001f + 1e-7f, zlens * 1.001f);
     const V3 ex = mk(fabsf(ng.x) * zp + pad, fabsf(ng.y) * zp + pad, fabsf(ng.z) * zp + pad);
@@ -133,7 +171,8 @@ __device__ __forceinline__ uint64_t spread21(uint32_t v) {  // 21 bits -> every 
     return x;
 }
 
-// per triangle: dilated box, 63-bit Morton key of its centre; bit 63 marks a "large" triangle (sorted last)
+// per triangle: dilated box, 63-bit Morton key of its centre; bit 63 marks a "large" triangle (sorted last), the all-ones
+// key an unbounded one (last of all)
 __global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *__restrict__ planes,
                                  const float *__restrict__ squares, int n, float eps, BuildScratch *s,
                                  float4 *__restrict__ box_lo, float4 *__restrict__ box_hi,
@@ -147,8 +186,9 @@ __global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *
     const float pad = amax * (32.0f * 1.1920929e-7f);  // 32 ulp of the largest coordinate in play
     const float *v = verts + 9 * (size_t)i;
     V3 lo, hi;
-    tri_bounds(mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8]), planes[i], squares[i], eps, pad, &lo,
-               &hi);
+    bool unbounded;
+    tri_bounds(mk(v[0], v[1], v[2]), mk(v[3], v[4], v[5]), mk(v[6], v[7], v[8]), planes[i], squares[i], eps, pad, amax, &lo,
+               &hi, &unbounded);
     box_lo[i] = make_float4(lo.x, lo.y, lo.z, 0.0f);
     box_hi[i] = make_float4(hi.x, hi.y, hi.z, 0.0f);
     const V3 ext = shi - slo;
@@ -160,10 +200,14 @@ __global__ void k_tri_boxes_keys(const float *__restrict__ verts, const float4 *
     const uint32_t qz = (uint32_t)fminf(fmaxf((c.z - slo.z) * sc, 0.0f), 2097151.0f);
     uint64_t key = (spread21(qx) << 2) | (spread21(qy) << 1) | spread21(qz);
     const V3 be = hi - lo;
-    const bool large = all_large || fmaxf(be.x, fmaxf(be.y, be.z)) > 0.25f * emax;
+    const bool large = all_large || unbounded || fmaxf(be.x, fmaxf(be.y, be.z)) > 0.25f * emax;
     if (large) {
         key |= 1ull << 63;
         atomicAdd(&s->n_large, 1);
+    }
+    if (unbounded) {  // sorted behind every other large triangle: the shared-memory list takes the LAST kMaxLarge
+        key = ~0ull;
+        atomicAdd(&s->n_unbounded, 1);
     }
     keys[i] = key;
     vals[i] = i;
@@ -280,11 +324,17 @@ __device__ __forceinline__ int shared_edge(const LargeTri &t, const LargeTri &u)
     if (n != 2) return -1;
     return in[0] && in[1] ? 0 : in[1] && in[2] ? 1 : 2;
 }
-__device__ __forceinline__ float tri_e(const LargeTri &t, float eps) { return eps * 1.01f + 4e-6f * (t.S + eps); }
+// effective eps of triangle t (robust_eps); *unbounded: its edge planes must accept everything
+__device__ __forceinline__ float tri_e(const LargeTri &t, float eps, float amax, bool *unbounded) {
+    const float l0 = length3(t.p[1] - t.p[0]), l1 = length3(t.p[2] - t.p[1]), l2 = length3(t.p[0] - t.p[2]);
+    return robust_eps(t.S, fminf(l0, fminf(l1, l2)), fmaxf(l0, fmaxf(l1, l2)), eps, amax, unbounded);
+}
 // largest value of the plane function f over the region of t's plane the reference can accept (the dilated hexagon
 // v_k + (v_k - v_j) e / (2 S)); with `absolute`, of |f|
-__device__ __forceinline__ float max_over_hexagon(const LargeTri &t, float eps, float4 f, bool absolute) {
-    const float lam = 1.05f * tri_e(t, eps) / (2.0f * t.S);
+__device__ __forceinline__ float max_over_hexagon(const LargeTri &t, float eps, float amax, float4 f, bool absolute) {
+    bool unb;
+    const float lam = 1.05f * tri_e(t, eps, amax, &unb) / (2.0f * t.S);
+    if (unb) return FLT_MAX;
     float best = -FLT_MAX;
     for (int k = 0; k < 3; ++k)
         for (int j = 0; j < 3; ++j) {
@@ -306,7 +356,7 @@ __device__ bool quad_eligible(const LargeTri &a, const LargeTri &b, float eps, f
     const V3 nga = normalize3(cross3(a.p[1] - a.p[0], a.p[2] - a.p[0])), ngb = normalize3(cross3(b.p[1] - b.p[0], b.p[2] - b.p[0]));
     const V3 nsa = mk(a.plane.x, a.plane.y, a.plane.z), nsb = mk(b.plane.x, b.plane.y, b.plane.z);
     if (!(fabsf(dot3(nsa, nga)) >= 0.999999f && fabsf(dot3(nsb, ngb)) >= 0.999999f && dot3(nsa, nsb) >= 0.999999f)) return false;
-    if (!(max_over_hexagon(b, eps, a.plane, true) <= 1e-4f && max_over_hexagon(a, eps, b.plane, true) <= 1e-4f)) return false;
+    if (!(max_over_hexagon(b, eps, amax, a.plane, true) <= 1e-4f && max_over_hexagon(a, eps, amax, b.plane, true) <= 1e-4f)) return false;
     // convex: the far vertex of each lies strictly inside the two outer edges of the other
     const V3 fa = a.p[(ja + 2) % 3], fb = b.p[(jb + 2) % 3];
     const float margin = 1e-5f * amax;
@@ -377,7 +427,8 @@ k_large_pack(int *__restrict__ vals, const float *__restrict__ verts, const floa
         const LargeTri &a = tri[order[2 * k]], &b = tri[order[2 * k + 1]];
         const int ja = shared_edge(a, b), jb = shared_edge(b, a);
         const V3 nga = normalize3(cross3(a.p[1] - a.p[0], a.p[2] - a.p[0])), ngb = normalize3(cross3(b.p[1] - b.p[0], b.p[2] - b.p[0]));
-        const float ea = tri_e(a, eps), eb = tri_e(b, eps);
+        bool ua, ub;  // (an unbounded triangle never pairs: quad_eligible, max_over_hexagon)
+        const float ea = tri_e(a, eps, amax, &ua), eb = tri_e(b, eps, amax, &ub);
         float4 *o = lrecs + 4 * (size_t)n_large + kQuadRows * (size_t)k;
         o[0] = a.plane;
         o[1] = edge_plane(a, (ja + 1) % 3, nga, true, ea, slack);
@@ -388,14 +439,15 @@ k_large_pack(int *__restrict__ vals, const float *__restrict__ verts, const floa
         o[5] = diag;
         // B is scanned with A's plane: its own hit distance differs by at most (distance of B's hit point from A's
         // plane + the rounding of both numerators) / |d . n| and by |t| times the rounding of the denominators
-        const float dev = max_over_hexagon(b, eps, a.plane, true);
-        o[6] = make_float4(1.5f * dev + amax * 1e-6f, 1e-6f, max_over_hexagon(b, eps, diag, false) + slack, 0.0f);
+        const float dev = max_over_hexagon(b, eps, amax, a.plane, true);
+        o[6] = make_float4(1.5f * dev + amax * 1e-6f, 1e-6f, max_over_hexagon(b, eps, amax, diag, false) + slack, 0.0f);
     }
     if (k < n_single) {
         const LargeTri &t = tri[order[2 * nq + k]];
         const V3 ng = normalize3(cross3(t.p[1] - t.p[0], t.p[2] - t.p[0]));
-        const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x;
-        const float e = tri_e(t, eps);
+        bool unb;
+        const float e = tri_e(t, eps, amax, &unb);
+        const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x && !unb;
         float4 *o = lrecs + 4 * (size_t)n_large + kQuadRows * (size_t)nq + kSingleRows * (size_t)k;
         o[0] = t.plane;
         for (int j = 0; j < 3; ++j) o[1 + j] = edge_plane(t, j, ng, ok, e, slack);
@@ -598,8 +650,9 @@ __global__ void k_pack_scans(const float *__restrict__ verts, const float4 *__re
     t.idx = i;
     t.mat = 0;
     const V3 ng = normalize3(cross3(t.p[1] - t.p[0], t.p[2] - t.p[0]));
-    const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x;
-    const float e = tri_e(t, eps);
+    bool unb;  // (cannot be set for a triangle inside the BVH: pt_scene_create keeps unbounded ones out or goes brute force)
+    const float e = tri_e(t, eps, amax, &unb);
+    const bool ok = t.S > 0.0f && t.S <= FLT_MAX && ng.x == ng.x && !unb;
     float4 *o = scans + 4 * (size_t)k;
     o[0] = t.plane;
     for (int j = 0; j < 3; ++j) o[1 + j] = edge_plane(t, j, ng, ok, e, slack);

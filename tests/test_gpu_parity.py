@@ -391,6 +391,72 @@ def test_lbvh_equals_brute_force_100k_triangles(lib, oracle):
     assert_bits_equal(bt[sel], ot)
 
 
+def test_deep_and_degenerate_trees(lib, monkeypatch):
+    """The traversal stack is sized from the tree the builder made (two entries per level of the 8-wide BVH, at most
+    kMaxLevels = 24 levels): nothing is ever dropped silently.  (a) 100,000 triangles with ONE common centroid (equal
+    Morton keys: Karras falls back to the index bits) and (b) clusters at exponentially shrinking distances (a chain
+    in the key bits) give the brute-force answer bit for bit; (c) with the level limit lowered through the test hook
+    PT_MAX_BVH_LEVELS an explicit BVH request fails with PT_EINVAL and PT_ACCEL_AUTO renders by brute force."""
+    rng = np.random.default_rng(3)
+    n = 100000
+    d = rng.normal(size=(n, 3, 3)) * np.array([3.0, 3.0, 3.0])
+    d -= d.mean(axis=1, keepdims=True)                        # every centroid at the same point
+    tris = (d + np.array([0.0, 0.0, 2.0])).reshape(n, 9).astype(np.float32)
+    base = scenes.cornell()
+    sc = {"verts": np.concatenate([tris[:, :9], base["verts"]]), "planes": None, "squares": None,
+          "mat_ids": np.concatenate([np.zeros(n, np.int32), base["mat_ids"]]), "mats": base["mats"]}
+    rays = scenes.random_rays(20000, seed=5)
+    bi, bt = lib.intersect(sc, rays, ptb200.config(accel=BRUTE))
+    li, lt = lib.intersect(sc, rays, ptb200.config(accel=LBVH))
+    assert_bits_equal(li, bi, "coincident centroids: ids")
+    assert_bits_equal(lt, bt, "coincident centroids: t")
+    # (b) clusters of ever smaller triangles at 16 * 2^-k from a corner: a chain in the Morton bits.  Down to k = 12
+    # (triangles of 4e-4) every triangle has a finite acceptance set; 40 more of size 1e-6 are slivers whose set is the
+    # whole plane (pt_bvh.cuh robust_eps): they must be kept out of the tree and tested against every ray.
+    parts = []
+    for k in range(13):
+        c = np.array([-9.0, -9.0, -9.0]) + 16.0 * 2.0 ** -k
+        t = rng.normal(size=(64, 3, 3)) * (1.5 * 2.0 ** -k) + c
+        parts.append(t.reshape(-1, 9))
+    slivers = (rng.normal(size=(40, 3, 3)) * 1e-6 + rng.uniform(-8, 8, (40, 1, 3))).reshape(-1, 9)
+    chain = np.concatenate(parts + [slivers]).astype(np.float32)
+    sc2 = {"verts": np.concatenate([chain, base["verts"]]), "planes": None, "squares": None,
+           "mat_ids": np.concatenate([np.zeros(len(chain), np.int32), base["mat_ids"]]), "mats": base["mats"]}
+    corner = np.tile(np.array([[0, 0, 0, -9, -9, -9]], np.float32), (20000, 1)) + rng.normal(size=(20000, 6)).astype(np.float32) * 0.5
+    rays2 = np.concatenate([rays, corner])
+    bi, bt = lib.intersect(sc2, rays2, ptb200.config(accel=BRUTE))
+    ds = lib.scene_create(sc2, ptb200.config(accel=LBVH))
+    li, lt = ds.intersect(rays2, ptb200.config(accel=LBVH))
+    levels = ds.stats()["n_levels"]
+    ds.close()
+    assert_bits_equal(li, bi, "chain: ids")
+    assert_bits_equal(lt, bt, "chain: t")
+    assert 2 <= levels <= 24 and (bi[len(rays):] < len(chain)).mean() > 0.05, levels
+    sliver_hits = int(((bi >= len(chain) - 40) & (bi < len(chain))).sum())
+    assert sliver_hits > 0, "the slivers' planes are hit far away from them: the case the bounds must not cut off"
+    # more slivers than the shared-memory list holds: an explicit BVH request says so, automatic mode goes brute force
+    many = (rng.normal(size=(200, 3, 3)) * 1e-6 + rng.uniform(-8, 8, (200, 1, 3))).reshape(-1, 9).astype(np.float32)
+    sc3 = {"verts": np.concatenate([many, base["verts"]]), "planes": None, "squares": None,
+           "mat_ids": np.concatenate([np.zeros(200, np.int32), base["mat_ids"]]), "mats": base["mats"]}
+    with pytest.raises(ptb200.PtError) as e:
+        lib.scene_create(sc3, ptb200.config(accel=LBVH))
+    assert e.value.code == 1 and "unbounded" in str(e.value)
+    ds = lib.scene_create(sc3, ptb200.config(accel=ptb200.PT_ACCEL_AUTO))
+    assert ds.stats()["accel"] == BRUTE
+    ds.close()
+    # (c) the limit, lowered: explicit request fails loudly, automatic mode falls back to the brute-force scan
+    monkeypatch.setenv("PT_MAX_BVH_LEVELS", "2")
+    with pytest.raises(ptb200.PtError) as e:
+        lib.scene_create(sc2, ptb200.config(accel=LBVH))
+    assert e.value.code == 1 and "level" in str(e.value)
+    ds = lib.scene_create(sc2, ptb200.config(accel=ptb200.PT_ACCEL_AUTO))
+    ai, at = ds.intersect(rays2[:4000], ptb200.config())
+    assert ds.stats()["accel"] == BRUTE
+    ds.close()
+    assert_bits_equal(ai, bi[:4000])
+    assert_bits_equal(at, bt[:4000])
+
+
 def test_full_size_properties_1m_triangles(lib):
     """BASELINE config 3's scene (1,000,014 triangles) at reduced image size: properties that need no oracle.
     (a) LBVH == GPU brute force on a ray set; (b) determinism; (c) spp partitions add up: counts exactly, sums to
