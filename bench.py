@@ -448,7 +448,7 @@ def main():
                  "algorithmic_gbs": algo_bytes[i] / sec / 1e9, "frac_of_hbm": algo_bytes[i] / sec / 1e9 / hbm_peak,
                  "fp32_tflops": flops[i] / sec / 1e12, "frac_of_fp32": flops[i] / sec / 1e12 / fp32_peak}
             m = tr.get(nm)
-            if m:  # measured by ncu on a launch of this shape (profiles/traffic.json says which capture)
+            if m and m.get("dram_bytes_per_launch") and m.get("paths_per_launch"):  # measured by ncu on a launch of this shape (profiles/traffic.json says which capture)
                 scale = paths_c / max(1.0, m["paths_per_launch"])
                 e.update({"dram_bytes_per_launch": m["dram_bytes_per_launch"] * scale,
                           "dram_gbs": m["dram_bytes_per_launch"] * scale / (class_ms[i] / class_n[i] * 1e-3) / 1e9,

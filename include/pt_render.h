@@ -245,6 +245,13 @@ int pt_powf(const float *x, int64_t n, float y, float *out); /* the device's res
 int pt_probe_read_bandwidth(size_t footprint_bytes, int passes, double *gb_per_s);
 int pt_primary_rays(const PtConfig *cfg, const int32_t *xys3, int64_t n, float *rays6); /* (x,y,sample) -> (o,d) */
 
+/* The CHECKED build of the library (path-tracing_b200/lib/libptrender_checked.so, -DPT_CHECKED=1) compares every index
+ * its kernels compute into a queue, list, stack, node or record array with its bound and counts the violations; this
+ * reads (and resets) the counters: out8 = {queue, alive list, traversal stack, node, record, slot, pixel, checks run}.
+ * The regular build returns PT_EINVAL.  The project's own memcheck: compute-sanitizer is closed on the development
+ * GPU pool. */
+int pt_debug_checks(uint64_t *out8);
+
 /* pt_render / pt_scene_destroy keep the last path-state workspace (up to 10.8 GB of HBM) for the next call on the same
  * device; this frees it. */
 void pt_release_workspace(void);

@@ -386,6 +386,7 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             }
             if (ctr.tri_cursor != nb) return fail(PT_ECUDA, "BVH collapse placed %d of %d triangles", ctr.tri_cursor, nb);
             ds->n_nodes = ctr.n_nodes;
+            v.n_nodes = ctr.n_nodes;
             ds->n_levels = levels;
             v.root = 0;
             k_root_box<<<1, 1>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, node_lo.p, node_hi.p, d_root.p);
@@ -1400,6 +1401,24 @@ extern "C" int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, 
     CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));
     if (samples_done) *samples_done = std::min(done, spp);
     return PT_OK;
+}
+
+// the checked build's violation counters (pt_scene.cuh PT_CHK); reading resets them
+extern "C" int pt_debug_checks(uint64_t *out8) {
+    if (!out8) return fail(PT_EINVAL, "out8 is NULL");
+#if PT_CHECKED
+    int rc;
+    if ((rc = check_device())) return rc;
+    unsigned long long h[CHK_WORDS], zero[CHK_WORDS] = {0};
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpyFromSymbol(h, g_chk, sizeof h));
+    CK(cudaMemcpyToSymbol(g_chk, zero, sizeof zero));
+    for (int i = 0; i < CHK_WORDS; ++i) out8[i] = h[i];
+    return PT_OK;
+#else
+    for (int i = 0; i < 8; ++i) out8[i] = 0;
+    return fail(PT_EINVAL, "not a checked build (compile with -DPT_CHECKED=1: make -C path-tracing_b200 checked)");
+#endif
 }
 
 extern "C" int pt_powf(const float *x, int64_t n, float y, float *out) {

@@ -57,6 +57,27 @@ constexpr int kRefEmpty = 0x7fffffff;  // child ref of an empty subtree / stack 
 // MAT_MULTI (extension): a material with the refractive lobe; its lobe set is the mask in row 2 (1 mirror, 2 diffuse, 4 refract)
 enum : int { MAT_EMISSIVE = 0, MAT_NONE = 1, MAT_MIRROR = 2, MAT_DIFFUSE = 3, MAT_BOTH = 4, MAT_MULTI = 5 };
 
+// ---- checked build (-DPT_CHECKED=1, lib/libptrender_checked.so): every index the kernels compute into a queue, list,
+// stack, node or record array is compared with its bound and violations are counted (pt_debug_checks); nothing is
+// skipped or clamped.  compute-sanitizer is closed on the GPU pool this was developed on, so this is the project's own
+// memcheck: tests run the sanitizer case (tools/sanitize_case.py) on the checked library and expect all zeros.
+#ifndef PT_CHECKED
+#define PT_CHECKED 0
+#endif
+enum { CHK_QUEUE = 0, CHK_ALIVE = 1, CHK_STACK = 2, CHK_NODE = 3, CHK_RECORD = 4, CHK_SLOT = 5, CHK_PIXEL = 6, CHK_CHECKS = 7, CHK_WORDS = 8 };
+#if PT_CHECKED
+__device__ unsigned long long g_chk[CHK_WORDS];
+#define PT_CHK(cond, what)                                   \
+    do {                                                     \
+        atomicAdd(&ptd::g_chk[ptd::CHK_CHECKS], 1ull);       \
+        if (!(cond)) atomicAdd(&ptd::g_chk[what], 1ull);     \
+    } while (0)
+#else
+#define PT_CHK(cond, what) \
+    do {                   \
+    } while (0)
+#endif
+
 struct SceneView;
 __host__ __device__ __forceinline__ int large_rows(int n_large, int n_quads) {
     return 4 * n_large + kQuadRows * n_quads + kSingleRows * (n_large - 2 * n_quads);
@@ -72,6 +93,7 @@ struct SceneView {
     int n_large;  // records [n_bvh, n_bvh + n_large) are tested first, from shared memory
     int n_quads;  // of which the first 2 n_quads form quad scan units
     int root;     // 0 = wide node 0 is the root; kRefEmpty if n_bvh == 0
+    int n_nodes;  // wide nodes in use
     int isect;    // host side only — picks the kernel instantiation: 0 the reference's plane + area-sum test (parity
                   // mode), 1 the watertight test of the geometric triangle
     int brute;    // 1: test records [0, n_tri) in order from global memory, no LBVH (checker mode, PT_ACCEL_BRUTE)

@@ -153,6 +153,7 @@ __device__ __forceinline__ void tri_intersect_wt(float4 a, float4 b, float4 c, i
 // the intersector the kernel was instantiated for (WT = watertight), on global record `rec`
 template <bool WT>
 __device__ __forceinline__ void tri_intersect(const SceneView &sc, int rec, V3 o, V3 d, float eps, Hit &h) {
+    PT_CHK(rec >= 0 && rec < sc.n_tri, CHK_RECORD);
     const float4 *r = sc.tris + 4 * (size_t)rec;
     if (WT) {
         float4 pl, a, b, c;
@@ -436,6 +437,7 @@ __device__ __forceinline__ unsigned node8_visit(const float4 *__restrict__ nodes
 // NaN anywhere marks.  true = the reference's exact test has to decide.
 template <bool WT>
 __device__ __forceinline__ bool scan_pass(const SceneView &sc, int rec, V3 o, V3 d, float eps, const Hit &h) {
+    PT_CHK(rec >= 0 && rec < sc.n_bvh, CHK_RECORD);
     if (WT) {  // watertight mode: the scan record bounds the REFERENCE's acceptance set around the stored plane, which
                      // need not contain the geometric hit; the test itself is cheap enough to stand in for its own filter
         const float4 *r = sc.tris + 4 * (size_t)rec;
@@ -482,9 +484,13 @@ __device__ __forceinline__ void enter_child(const SceneView &sc, const Ray8 &r, 
     const unsigned hits = ng.y;
     const int bit = 31 - __clz((int)hits);
     ng.y &= ~(1u << bit);
-    if (has_inner(ng)) stack[sp++] = ng;
+    if (has_inner(ng)) {
+        PT_CHK(sp < kStackDepth, CHK_STACK);
+        stack[sp++] = ng;
+    }
     const unsigned slot = (unsigned)(bit - 24) ^ (r.oct4 & 7u);
     const int ni = (int)ng.x + __popc(hits & 0xffu & ~(0xffffffffu << slot));
+    PT_CHK(ni >= 0 && ni < sc.n_nodes, CHK_NODE);
     unsigned cb, tb, im;
     const unsigned hm = node8_visit(sc.nodes, sc.one_bits, ni, r, tmax, cb, tb, im);
     if (COUNT) ++n_nodes;

@@ -124,9 +124,11 @@ __device__ __forceinline__ void alive_store(const WfState &wf, int list, int slo
     if (ma == 0u) return;
     const int lane = threadIdx.x & 31;
     base = __shfl_sync(0xffffffffu, base, __ffs(ma) - 1);
-    if (active)
+    if (active) {
+        PT_CHK(base + __popc(ma & ((1u << lane) - 1u)) < wf.alive_seg, CHK_ALIVE);
         __stcs(&wf.alive[(size_t)list * wf.alive_cap + (size_t)(blockIdx.x % kAliveLists) * wf.alive_seg + base +
                          __popc(ma & ((1u << lane) - 1u))], slot);
+    }
 }
 
 template <bool COUNT, bool WT>
@@ -152,7 +154,10 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
         int base = 0;
         if (lane == leader) base = atomicAdd(&wf.counters[2 * set], __popc(m));
         base = __shfl_sync(0xffffffffu, base, leader);
-        if (need) __stcs(&wf.queue[(size_t)set * wf.cap + base + __popc(m & ((1u << lane) - 1u))], slot);
+        if (need) {
+            PT_CHK(base + __popc(m & ((1u << lane) - 1u)) < wf.cap, CHK_QUEUE);
+            __stcs(&wf.queue[(size_t)set * wf.cap + base + __popc(m & ((1u << lane) - 1u))], slot);
+        }
     }
 }
 
@@ -224,6 +229,7 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
         if (chunk0 >= n_sub) return;
         in_range = chunk0 + (int)threadIdx.x < n_sub;
         slot = in_range ? __ldcs(&wf.alive[(size_t)(b & 1) * wf.alive_cap + (size_t)sub * wf.alive_seg + chunk0 + threadIdx.x]) : 0;
+        PT_CHK(slot >= 0 && slot < wf.cap, CHK_SLOT);
     }
     // this thread's path state first: the loads are in flight while the block stages the shared-memory image
     float4 tn = make_float4(0.f, 0.f, 0.f, 0.f), ot = tn, dr = tn;
@@ -394,6 +400,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
                 const int qi = base + __popc(m & ((1u << lane) - 1u));
                 if (qi < count) {
                     slot = __ldcs(&queue[qi]);
+                    PT_CHK(slot >= 0 && slot < wf.cap, CHK_SLOT);
                     const float4 ot = __ldcs(&wf.oT[slot]), dr = __ldcs(&wf.dR[slot]);
                     ray8_setup(mk(ot.x, ot.y, ot.z), mk(dr.x, dr.y, dr.z), r);
                     h.t = ot.w;
@@ -462,6 +469,7 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
     int remaining = 0;
     if (i < npix) {
         const int p = pix0 + i;
+        PT_CHK(p >= 0 && p < rp.W * rp.H, CHK_PIXEL);
         const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
         V3 sum = mk(a1.x, a1.y, a1.z), sum2 = mk(a2.x, a2.y, a2.z);
         int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
@@ -473,6 +481,7 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
 #pragma unroll 4
         for (int j = 0; j < Q; ++j) {
             const int slot = slot0 + j * stride;
+            PT_CHK(slot >= 0 && slot < wf.cap, CHK_SLOT);
             const int flags = __float_as_int(__ldcs(&wf.Tn[slot].w));
             const float4 c = __ldcs(&wf.cS[slot]);
             const int nseg = (flags & 0xffff) + ((flags & WF_SHADE_END) ? 1 : 0);

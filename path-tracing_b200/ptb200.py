@@ -21,7 +21,7 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth", "pt_render_progressive"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth", "pt_render_progressive", "pt_debug_checks"]
 
 
 class PtScene(C.Structure):
@@ -158,6 +158,12 @@ class Library:
     def check(self, rc):
         if rc != 0:
             raise PtError(rc, self.lib.pt_last_error().decode())
+
+    def debug_checks(self):
+        """violation counters of the checked build: dict name -> count (reading resets them)"""
+        out = (C.c_uint64 * 8)()
+        self.check(self.lib.pt_debug_checks(out))
+        return dict(zip(("queue", "alive", "stack", "node", "record", "slot", "pixel", "checks_run"), [int(v) for v in out]))
 
     def device_count(self):
         return int(self.lib.pt_device_count())

@@ -670,6 +670,26 @@ def test_watertight_intersector_mode(lib, oracle):
         lib.intersect(sc, G["torus40_rays"], ptb200.config(intersector=7))
 
 
+def test_checked_build_finds_no_out_of_bounds_index(tmp_path):
+    """The project's own memcheck (compute-sanitizer is closed on the development pool): lib/libptrender_checked.so
+    counts every queue / alive-list / stack / node / record / slot / pixel index that leaves its bounds
+    (pt_scene.cuh PT_CHK, pt_debug_checks).  The sanitizer case — both pipelines, alive lists on and off, adaptive rule,
+    roulette, bands, resume, watertight mode, a 100k-triangle tree — must run clean."""
+    import ast
+    import subprocess
+    import sys
+    from util import ROOT
+    so = os.path.join(ROOT, "path-tracing_b200", "lib", "libptrender_checked.so")
+    assert os.path.exists(so), "build with: make -C path-tracing_b200 checked (python __graft_entry__.py does)"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "sanitize_case.py")], capture_output=True, text=True,
+                       timeout=900, env=dict(os.environ, PTB200_RENDER_SO=so))
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("bounds checks:")][0]
+    counts = ast.literal_eval(line.split(":", 1)[1].strip())
+    assert counts["checks_run"] > 10 ** 6, counts
+    assert all(v == 0 for k, v in counts.items() if k != "checks_run"), counts
+
+
 def test_read_bandwidth_probe(lib):
     """pt_probe_read_bandwidth (bench.py's L2 peak): an L2-resident footprint reads faster than one that
     has to come from HBM, and both are plausible for a B200."""

@@ -33,8 +33,15 @@ def main():
     ids, t = lib.intersect(mesh, scenes.random_rays(20000, seed=1))
     img, stats = lib.render_image(tor, ptb200.config(64, 64, 8, 8, 1e-4, 0.001), lib.post_config(64, 64, gauss=1))
     img, stats = lib.postprocess(sm, s2, cnt, lib.post_config(48, 32, median=1), weight=wt)
+    big = scenes.torus_room(250, 200)  # 100k triangles: a tree of several levels
+    lib.render_accum(big, ptb200.config(160, 90, 16, 8, 1e-4, -1.0))
+    lib.render_accum(big, ptb200.config(160, 90, 40, 8, 1e-4, 0.001, q_shift=3, alive=1))
     lib.lib.pt_release_workspace()
     print(f"sanitize case done: {n} contributing paths, {int((ids >= 0).sum())} hits")
+    try:
+        print("bounds checks:", lib.debug_checks())
+    except ptb200.PtError as e:
+        print("bounds checks: not a checked build:", e)
 
 
 if __name__ == "__main__":
