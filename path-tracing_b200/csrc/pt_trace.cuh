@@ -184,6 +184,11 @@ __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large
 // marks between A and B (both near the diagonal).
 // The RESOLVE runs the reference's exact test (IEEE division, area sums, tie rule) on each lane's marked triangles;
 // lanes whose candidates sit at different indices execute it together.
+// (Measured alternative, round 2, profiles/r02_sweep_bounce.txt: a range-only first pass (14 instructions per unit) with
+// edge planes and exact tests only for the units in range, nearest first.  On the convex 12-wall room it saves 6 % of
+// k_wf_bounce, but the per-lane loops over "my in-range units" diverge: Cornell, where the nearest plane is often not
+// the hit, fell from 15.1 to 7.7 Grays/s, and with the exact tests gathered behind the loop still to 10.9.  The
+// branch-free scan of every unit, 60 instructions each, wins because all 32 lanes run it together.)
 // (tnear, rnear): smallest scanned distance among the marked units so far and the first record of that unit
 __device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int n, V3 o, V3 d, float t_lo, float t_hi,
                                                float &tnear, int &rnear) {
@@ -270,6 +275,12 @@ __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, u
 template <bool WT>
 __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int n_quads, int rec_base, V3 o, V3 d,
                                             float eps, Hit &h) {
+    if (WT) {  // the scan units bound the REFERENCE's acceptance sets around the stored planes, which need not hold the
+               // geometric hit (a `vn` plane): the watertight mode tests every shared-memory triangle directly
+        large_resolve32<true>(s_large, 0, n_large >= 32 ? 0xffffffffu : (1u << n_large) - 1u, rec_base, o, d, eps, h);
+        if (n_large > 32) large_resolve32<true>(s_large, 32, n_large >= 64 ? 0xffffffffu : (1u << (n_large - 32)) - 1u, rec_base, o, d, eps, h);
+        return;
+    }
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
     const float4 *quads = s_large + 4 * n_large, *singles = quads + kQuadRows * n_quads;
     const int n_single = n_large - 2 * n_quads;
@@ -323,7 +334,9 @@ __device__ __forceinline__ float box_entry(float lox, float hix, float loy, floa
 __device__ __forceinline__ bool reaches_root(const SceneView &sc, V3 o, V3 d, float tmax) {
     if (sc.root == kRefEmpty) return false;
     const float inf = __int_as_float(0x7f800000);
-    const V3 inv = mk(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+    // MUFU.RCP (within 2^-22 of 1 / d, +-inf for d == 0 like the division): the boxes are padded by 32 ulp of the scene's
+    // largest coordinate and the exit distance is widened below
+    const V3 inv = mk(rcp_approx(d.x), rcp_approx(d.y), rcp_approx(d.z));
     const float4 n0 = sc.root_n0, n1 = sc.root_n1, n2 = sc.root_n2;
     return box_entry(n0.x, n0.y, n0.z, n0.w, n2.x, n2.y, o, inv, tmax) < inf ||
            box_entry(n1.x, n1.y, n1.z, n1.w, n2.z, n2.w, o, inv, tmax) < inf;
