@@ -55,12 +55,17 @@ __device__ __forceinline__ int slot_of(int i, int q, int npix, int q_shift, bool
     return sample_major ? q * npix + i : (i << q_shift) + q;
 }
 
-// threads per block of the per-slot kernels (begin, bounce): with the 55 registers ptxas gives k_wf_bounce, blocks of
-// 256 fit 4 to an SM (32 warps), blocks of 128 fit 9 (36 warps)
+// threads per block of the per-slot kernels (begin, bounce) and the resident blocks per SM they are compiled for:
+// 128 x 9 (56 registers, 36 warps per SM).  Measured on C3 / Cornell, profiles/r02_sweep_bounce.txt: 256 threads without a
+// block count (55 registers, 32 warps) 85.8 ms / 15.0 Grays/s, 128 x 9 84.6 / 15.2, 128 x 10 (48 registers, 104 B
+// spilled) 84.8 / 14.8, 256 x 5 84.7 / 14.8, 128 x 12 85.9 / 14.2, 512 x 2 90.5 / 14.5.
 #ifndef PT_WF_BLOCK
-#define PT_WF_BLOCK 256
+#define PT_WF_BLOCK 128
 #endif
 constexpr int kWfBlock = PT_WF_BLOCK;
+#ifndef PT_WF_MIN_BLOCKS
+#define PT_WF_MIN_BLOCKS 9
+#endif
 
 // The alive lists (RenderParams::use_alive).  A bounce launch works on the paths that are still alive, not on all slots: paths that ended
 // (Russian roulette, emitters, misses) and samples the adaptive rule skipped cost nothing afterwards (depth 32 with
@@ -164,7 +169,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
 // WT (here and in the kernels below): the intersector, PT_ISECT_WATERTIGHT or the reference's — a template parameter, so
 // that each instantiation carries only its own test (as a run-time branch the second test cost the parity path 5 %)
 template <bool COUNT, bool ALIVE, bool WT>
-__global__ void __launch_bounds__(kWfBlock)
+__global__ void __launch_bounds__(kWfBlock, PT_WF_MIN_BLOCKS)
 k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     __shared__ float4 s_large[kLargeRowsMax];
     if (!sc.brute) stage_large(sc, s_large);
@@ -213,7 +218,7 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
 
 // bounce `b` (0-based): shades segment b of every live path and starts segment b+1; writes queue (b+1)&1
 template <bool COUNT, bool ALIVE, bool WT>
-__global__ void __launch_bounds__(kWfBlock)
+__global__ void __launch_bounds__(kWfBlock, PT_WF_MIN_BLOCKS)
 k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b) {
     __shared__ float4 s_large[kLargeRowsMax];
     if (blockIdx.x == 0) {

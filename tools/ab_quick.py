@@ -38,9 +38,20 @@ def run_variant(name, big, small, state):
             cls += np.array(st["class_ms"][:4])
     segs = st["segments"]
     ds.close()
+    # C2 (Cornell, every triangle in shared memory): the per-slot kernels alone
+    cfg2 = ptb200.config(1920, 1080, 128, 8, 1e-4, -1.0, seed=42)
+    ds2 = lib.scene_create(state["cornell"], cfg2)
+    ms2 = []
+    for i in range(3):
+        ds2.render_device(cfg2)
+        st2 = ds2.stats()
+        if i:
+            ms2.append(st2["kernel_ms"])
+    ds2.close()
     lib.lib.pt_release_workspace()
     return (f"{name:8s} parity {parity:9s} frame {np.mean(ms):7.2f} ms (min {min(ms):.2f})  "
-            f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " + "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)))
+            f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " + "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)) +
+            f"  | cornell {st2['segments'] / np.mean(ms2) / 1e3:7.0f} Mrays/s")
 
 
 def main():
@@ -48,7 +59,7 @@ def main():
     t00 = time.time()
     big, small = scenes.torus_room(1000, 500), scenes.torus_room(40, 20)
     print(f"scenes built in {time.time() - t00:.1f} s", flush=True)
-    state = {"ref": None}
+    state = {"ref": None, "cornell": scenes.cornell()}
     lines = []
     for name in names:
         try:
