@@ -69,14 +69,16 @@ __device__ __forceinline__ float u01(uint32_t w) {
 // degree-8 minimax polynomial in double, one final rounding to float.  Restated here so that the diffuse direction
 // matches the CPU reference bit for bit; tests compare it with the host libm over all 2^24 inputs the renderer can
 // produce.  Valid for |y| < 120 (the renderer's argument is 2*pi*xi2 < 6.29).
-__device__ __forceinline__ float sincos_poly(double x, double x2, bool neg, int n) {
-    if ((n & 1) == 0) {
-        const double x3 = x * x2;
-        const double s1 = 0x1.1107605230bc4p-7 + x2 * -0x1.994eb3774cf24p-13;
-        const double x7 = x3 * x2;
-        const double s = x + x3 * -0x1.555545995a603p-3;
-        return (float)(s + x7 * s1);
-    }
+// The two polynomial forms of glibc's sinf_poly: the sine form for an even quadrant count n, the cosine form (all
+// coefficients times -1 when `neg`) for an odd one.
+__device__ __forceinline__ float sin_form(double x, double x2) {
+    const double x3 = x * x2;
+    const double s1 = 0x1.1107605230bc4p-7 + x2 * -0x1.994eb3774cf24p-13;
+    const double x7 = x3 * x2;
+    const double s = x + x3 * -0x1.555545995a603p-3;
+    return (float)(s + x7 * s1);
+}
+__device__ __forceinline__ float cos_form(double x2, bool neg) {
     const double sg = neg ? -1.0 : 1.0;
     const double x4 = x2 * x2;
     const double c2 = sg * -0x1.6c087e89a359dp-10 + x2 * (sg * 0x1.99343027bf8c3p-16);
@@ -85,28 +87,24 @@ __device__ __forceinline__ float sincos_poly(double x, double x2, bool neg, int 
     const double c = c1 + x4 * (sg * 0x1.55553e1068f19p-5);
     return (float)(c + x6 * c2);
 }
+// Branch-free: glibc takes |y| < pi/4 through the same two polynomials with n = 0 (its fast reduction gives exactly
+// n = 0 and x unchanged there), and picks sine / cosine form by the parity of n — here both forms are evaluated once
+// for all lanes and swapped by parity.  (As three nested branches the 32 lanes of a warp split 3 / 27 and then 15 / 12:
+// ncu's source view of k_wf_bounce, profiles/r02_ncu_bounce_before.txt.)  Same operations, same bits: checked against
+// the host libm on all 2^24 inputs the renderer can produce.
 __device__ __forceinline__ void ref_sincosf(float y, float *sp, float *cp) {
     const uint32_t top = (__float_as_uint(y) >> 20) & 0x7ffu;
     double x = (double)y;
-    if (top < ((0x3f490fdbu >> 20) & 0x7ffu)) {  // |y| < pi/4
-        const double x2 = x * x;
-        if (top < ((0x39800000u >> 20) & 0x7ffu)) {  // |y| < 2^-12
-            *sp = y;
-            *cp = 1.0f;
-            return;
-        }
-        *sp = sincos_poly(x, x2, false, 0);
-        *cp = sincos_poly(x, x2, false, 1);
-        return;
-    }
     const double r = x * 0x1.45F306DC9C883p+23;
     const int n = ((int)r + 0x800000) >> 24;
     x = x - (double)n * 0x1.921FB54442D18p0;
     const double sgn = ((n & 3) == 1 || (n & 3) == 2) ? -1.0 : 1.0;
     const bool neg = (n & 2) != 0;
-    const double xs = x * sgn, x2 = x * x;
-    *sp = sincos_poly(xs, x2, neg, n);
-    *cp = sincos_poly(xs, x2, neg, n ^ 1);
+    const float S = sin_form(x * sgn, x * x), C = cos_form(x * x, neg);
+    const bool even = (n & 1) == 0;
+    const bool tiny = top < ((0x39800000u >> 20) & 0x7ffu);  // |y| < 2^-12: glibc returns (y, 1)
+    *sp = tiny ? y : (even ? S : C);
+    *cp = tiny ? 1.0f : (even ? C : S);
 }
 
 // primary ray, main.cpp:126-129 + Ray's constructor ray.h:21-25.  The x / y expressions are evaluated in double
