@@ -323,6 +323,8 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
         DevBuf<float4> d_root;
         DevBuf<WideItem> items_a, items_b;
         DevBuf<CollapseCounters> d_ctr;
+        DevBuf<float> dp_cost;
+        DevBuf<unsigned char> dp_dec;
         CK(d_root.alloc(5));
         CK(pool_alloc((void **)&ds->lrecs, (size_t)kLargeRowsMax * sizeof(float4)));
         CK(d_scr.alloc(1)); CK(box_lo.alloc(n)); CK(box_hi.alloc(n)); CK(keys.alloc(n)); CK(keys2.alloc(n));
@@ -354,23 +356,25 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             v.root = kRefEmpty;
         } else {
             CK(children.alloc(nb)); CK(range.alloc(nb)); CK(node_lo.alloc(nb)); CK(node_hi.alloc(nb));
+            CK(dp_cost.alloc(7 * (size_t)nb)); CK(dp_dec.alloc(8 * (size_t)nb));
             if (nb >= 2) {
                 CK(parent.alloc(2 * (size_t)nb)); CK(flags.alloc(nb));
                 CK(cudaMemsetAsync(flags.p, 0, (size_t)nb * sizeof(int)));
                 k_karras<<<blocks_for(nb - 1, 256), 256>>>(keys2.p, nb, children.p, parent.p, range.p);
-                k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, parent.p, flags.p, node_lo.p, node_hi.p);
+                k_fit<<<blocks_for(nb, 256), 256>>>(vals2.p, box_lo.p, box_hi.p, nb, children.p, range.p, parent.p, flags.p, node_lo.p,
+                                                    node_hi.p, CollapseDP{dp_cost.p, dp_dec.p});
                 launches += 2;
             }
             // every wide node has at least two children (k_collapse), every leaf child a triangle
             const size_t max_nodes = (size_t)nb + 2;
-            const size_t max_items = (size_t)nb / (kLeafMax + 1) + 2;
+            const size_t max_items = (size_t)nb / 2 + 2;  // an inner child holds at least two triangles
             CK(pool_alloc((void **)&ds->nodes, kNodeRows * max_nodes * sizeof(float4)));
             CK(items_a.alloc(max_items)); CK(items_b.alloc(max_items)); CK(d_ctr.alloc(1)); CK(perm.alloc(nb)); CK(order.alloc(n));
             const WideItem root_item{0, nb >= 2 ? 0 : ~0};
             CollapseCounters ctr{1, 0, 0, 0};
             CK(cudaMemcpy(items_a.p, &root_item, sizeof root_item, cudaMemcpyHostToDevice));
             CK(cudaMemcpy(d_ctr.p, &ctr, sizeof ctr, cudaMemcpyHostToDevice));
-            const BinTree bt{children.p, range.p, vals2.p, box_lo.p, box_hi.p, node_lo.p, node_hi.p};
+            const BinTree bt{children.p, range.p, dp_dec.p, vals2.p, box_lo.p, box_hi.p, node_lo.p, node_hi.p};
             WideItem *in = items_a.p, *out_items = items_b.p;
             int n_in = 1;
             while (n_in > 0) {

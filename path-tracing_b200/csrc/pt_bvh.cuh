@@ -251,11 +251,33 @@ __global__ void k_karras(const uint64_t *__restrict__ keys, int n, int2 *__restr
     if (i == 0) parent[0] = -1;
 }
 
-// bottom-up fit: the second thread to reach a node merges its children's boxes
+// ---- which subtrees become the children of a wide node: the cost-optimal collapse of Ylitie, Karras, Laine 2017 ------
+// C(n, i) = smallest SAH cost of the binary subtree n represented as at most i roots of the wide tree (i = 1..7):
+//   C(n, 1) = min( leaf: A_n P_n c_prim  (P_n <= kLeafMax triangles),  inner: A_n c_node + D(n, 8) )
+//   C(n, i) = min( D(n, i), C(n, i - 1) ),   D(n, j) = min over 0 < k < j of C(left, k) + C(right, j - k)
+// A = half surface area of the (dilated, padded) box.  Filled bottom-up together with the boxes; k_collapse reads the
+// decisions back top-down.  dec[8 n + i]: i = 1: 0xff leaf, else the k of D(n, 8); i = 2..7: 0 = "as with i - 1", else
+// the k of D(n, i); dec[8 n + 0]: the k of D(n, 8) whatever C(n, 1) chose (a root must be an inner node).
+#ifndef PT_SAH_NODE
+#define PT_SAH_NODE 1.0f   // cost of entering a wide node ...
+#endif
+#ifndef PT_SAH_PRIM
+#define PT_SAH_PRIM 0.3f   // ... against scanning one triangle
+#endif
+struct CollapseDP {
+    float *cost;         // 7 per inner binary node: C(n, 1..7)
+    unsigned char *dec;  // 8 per inner binary node
+};
+__device__ __forceinline__ float half_area(float4 lo, float4 hi) {
+    const float ex = hi.x - lo.x, ey = hi.y - lo.y, ez = hi.z - lo.z;
+    return ex * ey + ey * ez + ez * ex;
+}
+
+// bottom-up fit: the second thread to reach a node merges its children's boxes and fills the node's cost table
 __global__ void k_fit(const int *__restrict__ vals, const float4 *__restrict__ box_lo,
                       const float4 *__restrict__ box_hi, int n, const int2 *__restrict__ children,
-                      const int *__restrict__ parent, int *__restrict__ flags, float4 *__restrict__ node_lo,
-                      float4 *__restrict__ node_hi) {
+                      const int2 *__restrict__ range, const int *__restrict__ parent, int *__restrict__ flags,
+                      float4 *__restrict__ node_lo, float4 *__restrict__ node_hi, CollapseDP dp) {
     const int k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     // leaf k's box is box_*[vals[k]]
@@ -268,8 +290,47 @@ __global__ void k_fit(const int *__restrict__ vals, const float4 *__restrict__ b
         const float4 h0 = c.x >= 0 ? __ldcg(&node_hi[c.x]) : box_hi[vals[~c.x]];
         const float4 l1 = c.y >= 0 ? __ldcg(&node_lo[c.y]) : box_lo[vals[~c.y]];
         const float4 h1 = c.y >= 0 ? __ldcg(&node_hi[c.y]) : box_hi[vals[~c.y]];
-        node_lo[p] = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
-        node_hi[p] = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        const float4 lo = make_float4(fminf(l0.x, l1.x), fminf(l0.y, l1.y), fminf(l0.z, l1.z), 0.0f);
+        const float4 hi = make_float4(fmaxf(h0.x, h1.x), fmaxf(h0.y, h1.y), fmaxf(h0.z, h1.z), 0.0f);
+        node_lo[p] = lo;
+        node_hi[p] = hi;
+        {   // cost table of p from its children's (a single triangle costs its box times c_prim, whatever the budget)
+            float cl[8], cr[8];
+            const float al = half_area(l0, h0) * PT_SAH_PRIM, ar = half_area(l1, h1) * PT_SAH_PRIM;
+            for (int i = 1; i <= 7; ++i) {
+                cl[i] = c.x >= 0 ? __ldcg(&dp.cost[7 * (size_t)c.x + i - 1]) : al;
+                cr[i] = c.y >= 0 ? __ldcg(&dp.cost[7 * (size_t)c.y + i - 1]) : ar;
+            }
+            float D[9];
+            unsigned char K[9];
+            for (int j = 2; j <= 8; ++j) {
+                float best = FLT_MAX;
+                int bk = 1;
+                for (int kk = 1; kk < j; ++kk) {
+                    if (kk > 7 || j - kk > 7) continue;
+                    const float v = cl[kk] + cr[j - kk];
+                    if (v < best) { best = v; bk = kk; }
+                }
+                D[j] = best;
+                K[j] = (unsigned char)bk;
+            }
+            const float A = half_area(lo, hi);
+            const int cnt = range[p].y - range[p].x + 1;
+            const float c_leaf = cnt <= kLeafMax ? A * (float)cnt * PT_SAH_PRIM : FLT_MAX;
+            const float c_inner = A * PT_SAH_NODE + D[8];
+            unsigned char *dec = dp.dec + 8 * (size_t)p;
+            float *cost = dp.cost + 7 * (size_t)p;
+            dec[0] = K[8];
+            float cprev = fminf(c_leaf, c_inner);
+            dec[1] = c_leaf <= c_inner ? 0xff : K[8];
+            cost[0] = cprev;
+            for (int i = 2; i <= 7; ++i) {
+                const bool split = D[i] < cprev;
+                dec[i] = split ? K[i] : 0;
+                cprev = split ? D[i] : cprev;
+                cost[i - 1] = cprev;
+            }
+        }
         __threadfence();
         p = parent[p];
     }
@@ -468,9 +529,12 @@ struct CollapseCounters {
 
 struct BinTree {
     const int2 *children, *range;
+    const unsigned char *dec;  // CollapseDP::dec
     const int *vals;
     const float4 *box_lo, *box_hi, *node_lo, *node_hi;
     __device__ __forceinline__ int count(int ref) const { return ref >= 0 ? range[ref].y - range[ref].x + 1 : 1; }
+    // does the subtree become a wide node of its own (the cost table's choice for one root), or a leaf child?
+    __device__ __forceinline__ bool is_inner(int ref) const { return ref >= 0 && dec[8 * (size_t)ref + 1] != 0xff; }
     __device__ __forceinline__ int first(int ref) const { return ref >= 0 ? range[ref].x : ~ref; }
     __device__ __forceinline__ void box(int ref, V3 *lo, V3 *hi) const {
         const float4 l = ref >= 0 ? node_lo[ref] : box_lo[vals[~ref]], h = ref >= 0 ? node_hi[ref] : box_hi[vals[~ref]];
@@ -488,10 +552,10 @@ struct BinTree {
 // decode of a quantised plane as the builder checks it: p + q s with one rounding
 __device__ __forceinline__ float q_decode(int q, float s, float p) { return __fmaf_rn((float)q, s, p); }
 
-// One thread per wide node of the current level.  Its children: start from the subtree's two binary children and keep
-// replacing a child by its own two children until there are 8 or nothing is left to open (largest box first).
-// Subtrees of <= kLeafMax triangles become leaf children (their triangles are contiguous in the sorted order), the
-// others inner children, numbered in slot order from child_base and queued for the next level.  Quantisation: q_lo = floor, q_hi = ceil on the grid p + q s, s = extent / 255, pushed outwards until
+// One thread per wide node of the current level.  Its children are the cost-optimal cut of the binary subtree into at
+// most 8 roots (the decision table k_fit filled); those the table made leaves (<= kLeafMax triangles, contiguous in the
+// sorted order) become leaf children, the others inner children, numbered in slot order from child_base and queued for
+// the next level.  Quantisation: q_lo = floor, q_hi = ceil on the grid p + q s, s = extent / 255, pushed outwards until
 // the DECODED plane (q_decode) encloses the child box with a margin of 2^-7 of a grid step: node8_visit
 // (pt_trace.cuh) evaluates (p + q s - o) / d in a different association (one FMA on a 2^15-scaled grid) whose rounding
 // stays below 2^-9 of a step plus a few ulp of |p - o| / |d|; the latter are covered by the 32-ulp padding every
@@ -502,36 +566,30 @@ k_collapse(const WideItem *__restrict__ in, int n_in, WideItem *__restrict__ out
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_in) return;
     const WideItem item = in[t];
+    // The children: read the cost-optimal cut below item.ref off the decision table (k_fit).  A work list of
+    // (subtree, budget of roots) starts with the two binary children sharing 8 slots as D(n, 8) found best.
     int refs[8];
-    float area[8];
-    int n;
+    int n = 0;
     if (item.ref >= 0) {
-        const int2 c = bt.children[item.ref];
-        refs[0] = c.x; refs[1] = c.y;
-        n = 2;
-    } else {  // a one-triangle tree
-        refs[0] = item.ref;
-        n = 1;
-    }
-    for (int i = 0; i < n; ++i) area[i] = bt.area(refs[i]);
-    // Which children are opened up: largest box first, among the subtrees that are too big for a leaf (> kLeafMax
-    // triangles); then, while slots are free — a slot costs the same whether it is used or not — among the leaves
-    // themselves.  (Measured alternative, profiles/r02_sweep_bvh8.txt: opening only children above a size target
-    // kLeafMax 8^k, which makes a BALANCED tree divide by exactly 8 per level, gave 13 levels and 13.1 node visits per
-    // ray on the torus instead of 9 and 11.5 — the Karras tree over a curved surface is not balanced in counts.)
-    for (int phase = 0; phase < 2 && n < 8; ++phase) {
-        const int min_cnt = phase == 0 ? kLeafMax + 1 : 2;
-        while (n < 8) {
-            int best = -1;
-            float best_a = -1.0f;
-            for (int i = 0; i < n; ++i)
-                if (refs[i] >= 0 && bt.count(refs[i]) >= min_cnt && area[i] > best_a) { best = i; best_a = area[i]; }
-            if (best < 0) break;
-            const int2 c = bt.children[refs[best]];
-            refs[best] = c.x; area[best] = bt.area(c.x);
-            refs[n] = c.y; area[n] = bt.area(c.y);
-            ++n;
+        int st_ref[16], st_bud[16], sp = 0;
+        const int2 c0 = bt.children[item.ref];
+        const int k0 = bt.dec[8 * (size_t)item.ref];
+        st_ref[sp] = c0.y; st_bud[sp++] = 8 - k0;
+        st_ref[sp] = c0.x; st_bud[sp++] = k0;
+        while (sp > 0 && n < 8) {
+            const int m = st_ref[--sp];
+            int j = st_bud[sp];
+            if (m < 0) { refs[n++] = m; continue; }  // a single triangle
+            const unsigned char *dec = bt.dec + 8 * (size_t)m;
+            while (j > 1 && dec[j] == 0) --j;        // "as with one root fewer"
+            if (j == 1) { refs[n++] = m; continue; } // m itself is a child: a leaf or an inner node (dec[1])
+            const int2 c = bt.children[m];
+            const int k = dec[j];
+            st_ref[sp] = c.y; st_bud[sp++] = j - k;
+            st_ref[sp] = c.x; st_bud[sp++] = k;
         }
+    } else {  // a one-triangle tree
+        refs[n++] = item.ref;
     }
     // child boxes, node box
     V3 clo[8], chi[8];
@@ -576,7 +634,7 @@ k_collapse(const WideItem *__restrict__ in, int n_in, WideItem *__restrict__ out
         const int i = child_in_slot[sl];
         if (i < 0) continue;
         const int c = bt.count(refs[i]);
-        if (c > kLeafMax) ++n_inner; else n_tri += c;
+        if (bt.is_inner(refs[i])) ++n_inner; else n_tri += c;
     }
     const int child_base = n_inner ? atomicAdd(&ctr->n_nodes, n_inner) : 0;
     const int out_base = n_inner ? atomicAdd(&ctr->n_out, n_inner) : 0;
@@ -592,7 +650,7 @@ k_collapse(const WideItem *__restrict__ in, int n_in, WideItem *__restrict__ out
             continue;
         }
         const int c = bt.count(refs[i]);
-        if (c > kLeafMax) {
+        if (bt.is_inner(refs[i])) {
             meta[w] |= (0x38u + (unsigned)sl) << sh;
             imask |= 1u << sl;
             out[out_base + k_inner] = WideItem{child_base + k_inner, refs[i]};
