@@ -27,7 +27,7 @@ def launches(path):
         rd = f("dram__bytes_read.sum") * scale.get(unit("dram__bytes_read.sum"), 1.0)
         wr = f("dram__bytes_write.sum") * scale.get(unit("dram__bytes_write.sum"), 1.0)
         dur = f("gpu__time_duration.sum") * {"ms": 1.0, "us": 1e-3, "ns": 1e-6, "s": 1e3}.get(unit("gpu__time_duration.sum"), 1.0)
-        out.append({"kernel": r[col["Kernel Name"]].split("<")[0].replace("void ", "").replace("ptd::", "").strip(), "id": r[col["ID"]],
+        out.append({"kernel": r[col["Kernel Name"]].split("<")[0].split("(")[0].replace("void ", "").replace("ptd::", "").strip(), "id": r[col["ID"]],
                     "ms": dur, "dram": rd + wr, "issue": f("smsp__issue_active.avg.pct_of_peak_sustained_active"),
                     "lanes": f("smsp__thread_inst_executed_per_inst_executed.ratio"), "l2": f("lts__t_sector_hit_rate.pct"),
                     "l1": f("l1tex__t_sector_hit_rate.pct"), "alu": f("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
