@@ -184,6 +184,20 @@ int pt_resolve_device_w(const float *d_sum3, const int32_t *d_count, const float
                         float *d_rgb, void *stream);
 /* Statistics of the last render on this handle (synchronises the device). */
 int pt_scene_stats(PtDeviceScene *ds, PtStats *out);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * device memory (stream capture, tight serving loops, harnesses that forbid cudaMalloc).
+ * pt_scene_render_device_w for a SMALL frame, with the wavefront pipeline's whole workspace (path state, ray queues,
+ * alive lists, per-pixel accumulators, counters) in a 6 MiB file-scope device array of the library instead of the
+ * handle's pooled allocation: the call allocates nothing on the host or the device.  Every GPU that loads the library
+ * holds the array until exit.  Limits: width * height <= 16384 pixels (PT_EINVAL beyond; at most 65536 path slots are
+ * in flight, larger pixel x samples-per-step products run in pixel chunks), flat-spp renders only (error < 0), no resume,
+ * wavefront pipeline only, and the scene's device must be the current device.  Same arguments and same results, bit
+ * for bit, as pt_scene_render_device_w; asynchronous on `stream` (it never waits).  Every call shares the array and
+ * finds the previous call's contents (what must start at zero is cleared by the call): calls that overlap on the GPU
+ * — two streams, two handles, two host threads — race; serialise them on one stream.  Traversal counters
+ * (pt_scene_create flags bit 0) and per-class timing are not kept by this entry point. */
+int pt_scene_render_device_static(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                                  int32_t *d_count, float *d_weight, void *stream);
 
 /* ---- after the loop: main.cpp:162-201 on the device ---------------------------------------------------------
  * Dispersion statistics + gamma resolve (main.cpp:162-185), optional GaussBlur (main.cpp:11-33) or MedianFilter

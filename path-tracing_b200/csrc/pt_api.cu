@@ -852,6 +852,131 @@ extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, 
     return PT_OK;
 }
 
+// ---- pt_scene_render_device_static: the wavefront render of a small frame that allocates nothing -----------------------
+// For callers that cannot allocate (stream capture, tight serving loops, harnesses that forbid cudaMalloc): the
+// pipeline's whole workspace — path state, ray queues, alive lists, per-pixel accumulators, counters — is carved out of
+// ONE file-scope device array instead of the handle's pooled allocation.  Every GPU that loads the library holds the
+// array until exit.  Every call shares it and finds the previous call's contents: the counters are cleared and the
+// accumulators initialised at the start of the call, everything else is written before it is read.  Two calls that
+// overlap on the GPU (different streams, different handles) race.
+constexpr size_t kStaticMaxPixels = 16384;  // pixels of the frame (accumulators), e.g. 128 x 128
+constexpr size_t kStaticMaxSlots = 65536;   // path slots in flight; larger frame x samples-per-step products run in pixel chunks
+constexpr size_t static_alive_cap(size_t slots) {
+    return ((slots + kWfBlock - 1) / kWfBlock + kAliveLists - 1) / kAliveLists * kWfBlock * kAliveLists;
+}
+constexpr size_t static_ws_bytes(size_t slots, size_t npx) {
+    return slots * 4 * sizeof(float4) + 2 * slots * sizeof(int) + 2 * static_alive_cap(slots) * sizeof(int) +
+           2 * npx * sizeof(float4) + ((npx + 3) & ~(size_t)3) * sizeof(float) + (kWfCounters + 3 * kAliveLists) * sizeof(int);
+}
+constexpr size_t kStaticWsBytes = (size_t)6 << 20;  // 6 MiB
+static_assert(static_ws_bytes(kStaticMaxSlots, kStaticMaxPixels) <= kStaticWsBytes, "static workspace too small for its stated maxima");
+static __device__ __align__(256) unsigned char g_static_ws[kStaticWsBytes];
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_m;
+void *g_static_ptr[kStaticMaxDevices] = {};      // device address of g_static_ws, per device (the name itself is a host-side stand-in)
+int g_static_traverse_blocks[kStaticMaxDevices] = {};
+}  // namespace
+
+extern "C" int pt_scene_render_device_static(PtDeviceScene *ds, const PtConfig *cfg, float *d_sum3, float *d_sum2_3,
+                                             int32_t *d_count, float *d_weight, void *stream) {
+    if (!ds) return fail(PT_EINVAL, "scene handle is NULL");
+    int rc;
+    if ((rc = validate_config(cfg))) return rc;
+    if (cfg->reserved[0] == 1) return fail(PT_EINVAL, "static workspace: the megakernel variant has no workspace; use pt_scene_render_device");
+    if (cfg->error >= 0.0f)
+        return fail(PT_EINVAL, "static workspace: flat-spp renders only (error < 0): the adaptive rule's progress check reads back "
+                               "through a pinned buffer this entry point may not allocate");
+    if (cfg->reserved[2] == 1) return fail(PT_EINVAL, "static workspace: resume is not supported");
+    const size_t npx = (size_t)cfg->width * cfg->height;
+    if (npx > kStaticMaxPixels)
+        return fail(PT_EINVAL, "static workspace: frame of %zu pixels exceeds the maximum of %zu (use pt_scene_render_device)",
+                    npx, kStaticMaxPixels);
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev != ds->device || dev < 0 || dev >= kStaticMaxDevices)
+        return fail(PT_EINVAL, "static workspace: current device %d is not the scene's device %d", dev, ds->device);
+    char *base = nullptr;
+    int traverse_blocks = 0;
+    {   // once per device, with that device current: the array's device address and the persistent grid
+        std::lock_guard<std::mutex> lk(g_static_m);
+        if (!g_static_ptr[dev]) {
+            void *p = nullptr;
+            CK(cudaGetSymbolAddress(&p, g_static_ws));
+            int per_sm = 0, sms = 0;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false, false>, 128, 0));
+            CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            g_static_traverse_blocks[dev] = std::max(1, per_sm) * std::max(1, sms);
+            g_static_ptr[dev] = p;
+        }
+        base = (char *)g_static_ptr[dev];
+        traverse_blocks = g_static_traverse_blocks[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    CK(cudaMemsetAsync(ds->stats, 0, kStatWords * sizeof(unsigned long long), st));
+    RenderParams rp = make_params(cfg, d_sum3, d_sum2_3, d_count, d_weight, ds->stats);
+    if (cfg->reserved[3] == 0 && ds->view.sky) rp.use_alive = 1;
+    SceneView sc = ds->view;  // the kernels take the view by value; the handle is left as it is
+    sc.isect = cfg->intersector == PT_ISECT_WATERTIGHT ? 1 : 0;
+    // the workspace, in wf_reserve's order, for this call's (slots, pixels)
+    const size_t npx_traced = (size_t)(rp.row1 - rp.row0) * rp.W;
+    const size_t npc = std::min(std::max<size_t>(npx_traced, 1), kStaticMaxSlots >> rp.q_shift), slots = npc << rp.q_shift;
+    const size_t alive_cap = static_alive_cap(slots), npx4 = (npx + 3) & ~(size_t)3;
+    if (static_ws_bytes(slots, npx) > kStaticWsBytes) return fail(PT_ENOMEM, "static workspace: layout exceeds the array");
+    WfState wf{};
+    char *p = base;
+    wf.oT = (float4 *)p; p += slots * sizeof(float4);
+    wf.dR = (float4 *)p; p += slots * sizeof(float4);
+    wf.Tn = (float4 *)p; p += slots * sizeof(float4);
+    wf.cS = (float4 *)p; p += slots * sizeof(float4);
+    wf.acc1 = (float4 *)p; p += npx * sizeof(float4);
+    wf.acc2 = (float4 *)p; p += npx * sizeof(float4);
+    wf.accw = (float *)p; p += npx4 * sizeof(float);
+    wf.queue = (int *)p; p += 2 * slots * sizeof(int);
+    wf.alive = (int *)p; p += 2 * alive_cap * sizeof(int);
+    wf.alive_seg = (int)(alive_cap / kAliveLists);
+    wf.alive_cap = (int)alive_cap;
+    wf.counters = (int *)p;
+    wf.cap = (int)slots;
+    // the launch sequence of render_wavefront for a flat-spp render (no readback: nothing is ever deferred)
+    CK(cudaMemsetAsync(wf.counters, 0, (kWfCounters + 3 * kAliveLists) * sizeof(int), st));
+    k_wf_init<<<blocks_for((long long)npx, 256), 256, 0, st>>>(wf, (int)npx, rp);
+    const int Q = 1 << rp.q_shift;
+    const int total = rp.spp > rp.s_begin ? (rp.spp - rp.s_begin + rp.s_step - 1) / rp.s_step : 0;
+    const int steps = (total + Q - 1) / Q;
+    const size_t pix_end = (size_t)rp.row1 * rp.W;
+    for (size_t pix0 = (size_t)rp.row0 * rp.W; pix0 < pix_end && total > 0; pix0 += npc) {
+        const int npix = (int)std::min<size_t>(npc, pix_end - pix0);
+        const int slot_blocks = blocks_for((long long)npix << rp.q_shift, kWfBlock);
+        for (int i = 0; i < steps; ++i) {
+            if (rp.use_alive) {
+                if (sc.isect) k_wf_begin<false, true, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                else k_wf_begin<false, true, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+            } else {
+                if (sc.isect) k_wf_begin<false, false, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+                else k_wf_begin<false, false, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix);
+            }
+            for (int b = 0; b < rp.max_depth; ++b) {
+                if (!sc.brute && sc.root != kRefEmpty) {
+                    if (sc.isect) k_wf_traverse<false, true><<<traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                    else k_wf_traverse<false, false><<<traverse_blocks, 128, 0, st>>>(sc, wf, b & 1, rp.eps, rp.stats);
+                }
+                if (rp.use_alive) {
+                    if (sc.isect) k_wf_bounce<false, true, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    else k_wf_bounce<false, true, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                } else {
+                    if (sc.isect) k_wf_bounce<false, false, true><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                    else k_wf_bounce<false, false, false><<<slot_blocks, kWfBlock, 0, st>>>(sc, rp, wf, (int)pix0, npix, b);
+                }
+            }
+            k_wf_commit<<<blocks_for(npix, 256), 256, 0, st>>>(rp, wf, (int)pix0, npix, i == steps - 1);
+        }
+    }
+    k_wf_finish<<<blocks_for((long long)npx, 256), 256, 0, st>>>(rp, wf, (int)npx);
+    CK(cudaGetLastError());
+    return PT_OK;
+}
+
 extern "C" int pt_resolve_device(const float *d_sum3, const int32_t *d_count, int64_t n_pixels, float *d_rgb,
                                  void *stream) {
     return pt_resolve_device_w(d_sum3, d_count, nullptr, n_pixels, d_rgb, stream);

@@ -21,7 +21,8 @@ ERRORS = {0: "PT_OK", 1: "PT_EINVAL", 2: "PT_ENODEVICE", 3: "PT_ECUDA", 4: "PT_E
 ABI_SYMBOLS = ["pt_render", "pt_render_accum", "pt_scene_create", "pt_scene_destroy", "pt_scene_render_device",
                "pt_resolve_device", "pt_scene_stats", "pt_intersect", "pt_scene_intersect", "pt_triangle_setup",
                "pt_philox", "pt_sincos", "pt_primary_rays", "pt_last_error", "pt_device_count", "pt_version",
-               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth", "pt_render_progressive", "pt_debug_checks"]
+               "pt_render_accum_w", "pt_scene_render_device_w", "pt_resolve_device_w", "pt_release_workspace", "pt_postprocess", "pt_postprocess_device", "pt_render_image", "pt_powf", "pt_last_phases", "pt_probe_read_bandwidth", "pt_render_progressive", "pt_debug_checks",
+               "pt_scene_render_device_static"]
 
 
 class PtScene(C.Structure):
@@ -127,6 +128,8 @@ class Library:
         L.pt_scene_render_device_w.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                                C.c_void_p, C.c_void_p]
         L.pt_resolve_device_w.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p]
+        L.pt_scene_render_device_static.argtypes = [C.c_void_p, C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
+                                                    C.c_void_p, C.c_void_p]
         L.pt_render_accum_w.argtypes = [C.POINTER(PtScene), C.POINTER(PtConfig), C.c_void_p, C.c_void_p, C.c_void_p,
                                         C.c_void_p]
         L.pt_scene_stats.argtypes = [C.c_void_p, C.POINTER(PtStats)]
@@ -347,6 +350,12 @@ class DeviceScene:
         """Device pointers (ints, e.g. torch.Tensor.data_ptr()); asynchronous on `stream`."""
         self.L.check(self.L.lib.pt_scene_render_device_w(self.h, C.byref(cfg), d_sum3 or None, d_sum2 or None,
                                                          d_count or None, d_weight or None, stream or None))
+
+    def render_device_static(self, cfg, d_sum3=0, d_sum2=0, d_count=0, stream=0, d_weight=0):
+        """pt_scene_render_device_static: the same render out of the library's static device workspace (small frames,
+        flat spp; allocates nothing).  Calls must not overlap on the GPU."""
+        self.L.check(self.L.lib.pt_scene_render_device_static(self.h, C.byref(cfg), d_sum3 or None, d_sum2 or None,
+                                                              d_count or None, d_weight or None, stream or None))
 
     def resolve_device(self, d_sum3, d_count, n_pixels, d_rgb, stream=0, d_weight=0):
         self.L.check(self.L.lib.pt_resolve_device_w(d_sum3, d_count, d_weight or None, n_pixels, d_rgb, stream or None))
