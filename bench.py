@@ -349,7 +349,8 @@ def main():
             if fresh:
                 nudge(sc_pinned)
             return lib.render(sc_pinned, cfg, out=rgb_pinned)
-        h = lib.scene_create(sc, cfg)
+        nudge(sc_pinned)  # every rank moves the same coordinate: the ranks keep rendering one scene
+        h = lib.scene_create(sc_pinned, cfg)
         h.render_device(cfg, d_sum.data_ptr(), 0, d_cnt_i.data_ptr(), stream, d_wt)
         acc[3 * n_px:].copy_(d_wt_t if rr else d_cnt_i)
         dist.reduce(acc, 0, op=dist.ReduceOp.SUM)
@@ -367,8 +368,8 @@ def main():
     # frame after frame would keep them (and as the bench contract words it)
     sc_pinned, rgb_pinned = sc, None
     pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    sc_pinned = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in sc.items()}
     if world == 1:
-        sc_pinned = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in sc.items()}
         rgb_pinned = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory().numpy()
 
     def timed_calls(fn, n):

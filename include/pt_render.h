@@ -167,6 +167,8 @@ int pt_render_accum_w(const PtScene *scene, const PtConfig *cfg, float *sum3, fl
 /* Upload + SoA repack + LBVH build on the current device.  `flags` bit 0: keep traversal counters; bit 1: time
  * every kernel class with CUDA events (instrumented runs only: it serialises the launches). */
 int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_t flags, PtDeviceScene **out);
+/* The handle belongs to the device that was current at pt_scene_create: pt_scene_render_device*, pt_scene_intersect
+ * and pt_scene_stats return PT_EINVAL when another device is current; pt_scene_destroy may be called from any. */
 void pt_scene_destroy(PtDeviceScene *ds);
 /* Render into DEVICE buffers (float sum3[H*W*3], float sum2_3[H*W*3], int32 count[H*W]; NULL allowed) on
  * `stream` (a cudaStream_t, 0 = default stream).  All work is issued on `stream`; the call waits on the stream once

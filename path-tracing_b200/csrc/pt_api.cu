@@ -658,6 +658,16 @@ static RenderParams make_params(const PtConfig *cfg, float *d_sum3, float *d_sum
     return rp;
 }
 
+// The device-resident entry points launch on the caller's stream and hand blocks of the scene's device around: they
+// insist on that device being current instead of guessing.
+static int require_scene_device(const PtDeviceScene *ds, const char *who) {
+    int cur = -1;
+    CK(cudaGetDevice(&cur));
+    if (cur != ds->device)
+        return fail(PT_EINVAL, "%s: the scene lives on device %d but device %d is current (cudaSetDevice first)", who, ds->device, cur);
+    return PT_OK;
+}
+
 constexpr size_t kMaxSlots = (size_t)1 << 27;  // path slots in flight (64 B of state + 16 B of queues each: <= 10.8 GB)
 
 // npx: pixels of the frame (accumulators), npx_traced: pixels of the rows this call traces (path slots)
@@ -822,7 +832,7 @@ extern "C" int pt_scene_render_device_w(PtDeviceScene *ds, const PtConfig *cfg, 
                                         int32_t *d_count, float *d_weight, void *stream) {
     if (!ds) return fail(PT_EINVAL, "scene handle is NULL");
     int rc;
-    if ((rc = validate_config(cfg))) return rc;
+    if ((rc = validate_config(cfg)) || (rc = require_scene_device(ds, "pt_scene_render_device"))) return rc;
     cudaStream_t st = (cudaStream_t)stream;
     if (cfg->reserved[2] == 1 && (!d_sum3 || !d_sum2_3 || !d_count || (cfg->rr_depth > 0 && !d_weight)))
         return fail(PT_EINVAL, "resume needs every accumulator (sum, sum2, count; weight under Russian roulette)");
@@ -994,6 +1004,7 @@ extern "C" int pt_resolve_device_w(const float *d_sum3, const int32_t *d_count, 
 extern "C" int pt_scene_stats(PtDeviceScene *ds, PtStats *out) {
     if (!ds || !out) return fail(PT_EINVAL, "NULL argument");
     memset(out, 0, sizeof *out);
+    if (int rc = require_scene_device(ds, "pt_scene_stats")) return rc;
     unsigned long long st[kStatWords] = {0};
     if (ds->timed) {
         CK(cudaEventSynchronize(ds->ev1));
@@ -1017,6 +1028,7 @@ extern "C" int pt_scene_intersect(PtDeviceScene *ds, const PtConfig *cfg, const 
                                   int32_t *tri_id, float *t) {
     if (!ds || !rays6 || !tri_id || !t || n < 0) return fail(PT_EINVAL, "bad intersect arguments");
     if (n == 0) return PT_OK;
+    if (int rc = require_scene_device(ds, "pt_scene_intersect")) return rc;
     const float eps = cfg ? cfg->eps : 1e-4f;
     if (cfg && cfg->intersector != PT_ISECT_REFERENCE && cfg->intersector != PT_ISECT_WATERTIGHT)
         return fail(PT_EINVAL, "intersector %d unknown", cfg->intersector);
@@ -1480,7 +1492,7 @@ extern "C" int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, 
     if (update < 0 || time_limit_ms < 0) return fail(PT_EINVAL, "update and time_limit_ms must be >= 0");
     if ((rc = validate_config(cfg)) || (rc = validate_scene(scene)) || (rc = validate_post(post))) return rc;
     if (post->width != cfg->width || post->height != cfg->height) return fail(PT_EINVAL, "post and render sizes differ");
-    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "in-process multi-GPU not available in this build");
+    if (cfg->n_gpus > 1) return fail(PT_EINVAL, "pt_render_progressive renders on one device (n_gpus = 1)");
     if (cfg->reserved[2]) return fail(PT_EINVAL, "pt_render_progressive manages the resume state itself");
     if ((rc = check_device())) return rc;
     CK(cudaSetDevice(cfg->device));
@@ -1496,25 +1508,39 @@ extern "C" int pt_render_progressive(const PtScene *scene, const PtConfig *cfg, 
     const bool rr = cfg->rr_depth > 0;
     PtPostConfig preview = *post;  // main.cpp:144-150: gamma only
     preview.gauss = 0; preview.median = 0;
-    const int step = cfg->sample_step > 0 ? cfg->sample_step : 1, spp = cfg->rays_per_pixel;
-    const int stride = (update > 0 ? update : 64) * step;  // samples of this partition per block
-    int done = cfg->sample_begin;                           // first sample index not yet rendered
+    const int step = cfg->sample_step > 0 ? cfg->sample_step : 1, spp = cfg->rays_per_pixel, begin = cfg->sample_begin;
+    const int k_total = spp > begin ? (spp - begin + step - 1) / step : 0;  // samples of this partition
+    int k_done = 0;              // of them rendered; the next one is sample begin + k_done * step
+    int done = begin;
+    double ms_per_sample = 0.0;  // measured on the last block (time-limited runs only)
     bool first = true, stopped = false;
-    while (done < spp && !stopped) {
+    while (k_done < k_total && !stopped) {
+        // blocks end where the reference refreshes: after sample 0, update, 2 update, ... (64 samples without -UPDATE)
+        int k_next = update > 0 ? (k_done == 0 ? 1 : ((k_done - 1) / update + 1) * update + 1) : k_done + 64;
+        std::chrono::steady_clock::time_point tb;
         if (time_limit_ms > 0) {
-            const auto ms = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
-            if (ms >= time_limit_ms) break;
+            // the reference looks at the clock before every sample (main.cpp:111-114): a block is only as long as the
+            // measured time per sample says will fit into what is left (one sample until there is a measurement)
+            tb = std::chrono::steady_clock::now();
+            const double left = (double)time_limit_ms - std::chrono::duration<double, std::milli>(tb - t0).count();
+            if (left <= 0.0) break;
+            const int fit = ms_per_sample > 0.0 ? (int)std::min(left / ms_per_sample, 1e6) : 1;
+            k_next = std::min(k_next, k_done + std::max(1, fit));
         }
-        // the reference refreshes after sample 0, update, 2 update, ...: the first block is one sample long
+        k_next = std::min(k_next, k_total);
         PtConfig c = *cfg;
-        c.sample_begin = done;
-        c.rays_per_pixel = std::min(spp, first && update > 0 ? done + step : done + stride);
+        c.sample_begin = begin + k_done * step;
+        c.rays_per_pixel = std::min(spp, begin + k_next * step);
         c.reserved[2] = first ? 0 : 1;
         if ((rc = pt_scene_render_device_w(ds, &c, d_sum.p, d_sum2.p, d_cnt.p, d_wt.p, nullptr))) return rc;
-        // next sample of the partition at or after the block's end
-        done += ((c.rays_per_pixel - done + step - 1) / step) * step;
-        const int k_done = (std::min(done, spp + step - 1) - cfg->sample_begin) / step;  // samples of the partition so far
-        if (update > 0 && on_update && (k_done - 1) % update == 0) {  // main.cpp:143: rays_count % update == 0
+        if (time_limit_ms > 0) {
+            CK(cudaStreamSynchronize(nullptr));
+            ms_per_sample = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - tb).count() / (k_next - k_done);
+        }
+        const bool refresh = update > 0 && (k_next - 1) % update == 0;  // main.cpp:143: rays_count % update == 0
+        k_done = k_next;
+        done = begin + k_done * step;
+        if (refresh && on_update) {
             if ((rc = pt_postprocess_device(d_sum.p, d_sum2.p, d_cnt.p, rr ? d_wt.p : nullptr, &preview, d_img.p, nullptr, nullptr)))
                 return rc;
             CK(cudaMemcpy(rgb8, d_img.p, 3 * px, cudaMemcpyDeviceToHost));

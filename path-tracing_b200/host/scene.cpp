@@ -338,6 +338,17 @@ bool Scene::LoadCache(const std::string &cache_file, const std::string &obj_path
     }
     if (!ok) { std::fclose(f); return false; }
     const size_t n = static_cast<size_t>(h.n_triangles), m = static_cast<size_t>(h.n_materials);
+    {   // the payload the header promises must be exactly what is left of the file: checked BEFORE anything is sized
+        // from the header (a damaged cache with the right magic and stamp is ignored, not a bad_alloc)
+        const long at = std::ftell(f);
+        const bool seek_ok = at >= 0 && std::fseek(f, 0, SEEK_END) == 0;
+        const long end = seek_ok ? std::ftell(f) : -1;
+        const unsigned long long payload = 4ull * (9 * n + 4 * n + n + n + 10 * m + 2 * m);
+        if (!seek_ok || end < at || static_cast<unsigned long long>(end - at) != payload || std::fseek(f, at, SEEK_SET) != 0) {
+            std::fclose(f);
+            return false;
+        }
+    }
     std::vector<float> v(9 * n), p(4 * n), sq(n), mt(10 * m), ext(2 * m);
     std::vector<int32_t> ids(n);
     ok = get(f, v.data(), v.size()) && get(f, p.data(), p.size()) && get(f, sq.data(), n) && get(f, ids.data(), n) &&

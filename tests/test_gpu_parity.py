@@ -549,6 +549,25 @@ def test_progressive_render(lib, oracle, tor):
     assert_bits_equal(img, want, "update = 0")
 
 
+@pytest.mark.parametrize("update", [0, 16])
+def test_progressive_render_time_limit(lib, tor, update):
+    """-TL (main.cpp:111-114 looks at the clock before every sample): blocks are sized from the measured time per
+    sample, so the loop stops within about a sample of the limit, and what it returns is the render of exactly the
+    samples it reports."""
+    import time
+    W, H, spp, limit = 640, 480, 100000, 250
+    cfg = ptb200.config(W, H, spp, 8, 1e-4, -1.0, seed=4)
+    post = lib.post_config(W, H, 1 / 2.2)
+    lib.render_image(tor, ptb200.config(W, H, 2, 8, 1e-4, -1.0, seed=4), post)  # scene cached, workspace allocated
+    t0 = time.perf_counter()
+    img, _, done = lib.render_progressive(tor, cfg, post, update=update, time_limit_ms=limit, on_update=(lambda im, n: False) if update else None)
+    ms = (time.perf_counter() - t0) * 1e3
+    assert 2 <= done < spp
+    assert ms < limit + 150, f"{ms:.0f} ms for a limit of {limit} ms ({done} samples)"
+    ref, _ = lib.render_image(tor, ptb200.config(W, H, done, 8, 1e-4, -1.0, seed=4), post)
+    assert_bits_equal(img, ref, f"time-limited render of {done} samples")
+
+
 @pytest.mark.parametrize("mode", [0, 1], ids=["wavefront", "megakernel"])
 def test_row_bands_are_the_frame(lib, tor, mode):
     """PtConfig.row_begin / row_end: a band render is the rows of the whole-frame render (pixels are independent given

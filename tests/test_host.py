@@ -234,6 +234,11 @@ def test_binary_scene_cache(loader, tmp_path):
     assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
     open(img, "wb").write(b"not a cache")
     assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    # right magic and stamps, absurd triangle count (header: magic[8], then int64 n_triangles): the payload size is
+    # checked against the file before anything is allocated from the header
+    open(img, "wb").write(blob[:8] + (2**31 - 1).to_bytes(8, "little") + blob[16:])
+    assert not loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
+    assert open(img, "rb").read() == blob
     assert loader.load_obj(d, "awk.obj", cache_dir=cache)["from_cache"]
     # the MTL changes: stale
     with open(os.path.join(d, "awk.mtl"), "a") as f:
