@@ -214,10 +214,30 @@ def run_reference_arm(args):
                             "release_threads": last["release_threads"], "host_cpus": last["host_cpus"]},
            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
-    print(json.dumps(out))
+    emit(out)
+
+
+_JSON_FD = None
+
+
+def quiet_stdout():
+    """The contract is ONE JSON line on stdout, but native libraries write there too (NCCL prints its version on the
+    first communicator when NCCL_DEBUG is set): from here on fd 1 is stderr, and emit() writes to the real stdout."""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    sys.stdout.flush()
+    line = (json.dumps(obj) + "\n").encode()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, line)
 
 
 def main():
+    quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -543,7 +563,7 @@ def main():
                        "what": "every timed call gets a scene the library has not seen: hash + upload + BVH build + render + resolve + download"},
                "e2e_cached": e2e_cached, "e2e_inproc": e2e_inproc,
                "gpu_launches": launches_per_step * args.steps, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
-        print(json.dumps(out))
+        emit(out)
     ds.close()
 
 

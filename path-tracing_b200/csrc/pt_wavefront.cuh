@@ -394,7 +394,10 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
             slot = -1;
         }
         const unsigned m = __ballot_sync(0xffffffffu, need);
-        // a refill is a chain of dependent fetches (queue head, queue entry, ray state) the whole warp sits through
+        // a refill is a chain of dependent fetches (queue head, queue entry, ray state) the whole warp sits through.
+        // Measured and rejected (profiles/r02_sweep_bvh8.txt): the warp reserving 32 entries at a time, one chunk ahead,
+        // with the ray state prefetched into L2 — the chain shrinks to two shuffles and two L2 hits, and the kernel is 10 %
+        // SLOWER (three more live registers in a kernel that already spills)
         const unsigned busy = __ballot_sync(0xffffffffu, !need && !done);
         if (m && (__popc(m) >= PT_REFILL_MIN || busy == 0u)) {
             const int leader = __ffs(m) - 1;
