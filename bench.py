@@ -230,6 +230,9 @@ def quiet_stdout():
         os.dup2(2, 1)
 
 
+INPROC_TIMEOUT_S = 240  # the in-process N-GPU leg of a --gpus N run (an extra beside the line's own numbers)
+
+
 def emit(obj):
     sys.stdout.flush()
     line = (json.dumps(obj) + "\n").encode()
@@ -519,31 +522,42 @@ def main():
     # ---- N GPUs inside ONE pt_render call (PtConfig.n_gpus = N: one host thread per device, NCCL reduce inside the
     # library), timed by rank 0 once the other ranks are done with their devices
     e2e_inproc = None
+    inproc_hung = False
     if world > 1:
         barrier()
         dist.destroy_process_group()  # every rank together; rank 0 then has the devices to itself
         if rank == 0:
             time.sleep(2.0)
-            try:
-                icfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, device=0, n_gpus=world, accel=args.accel,
-                                     mode=args.mode, q_shift=args.q_shift, rr_depth=rr)
-                isc = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in sc.items()}
-                irgb = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory().numpy()
-                lib.render(isc, icfg, out=irgb)                       # communicators, workspaces, scene cache
-                runs = {}
-                for kind in ("fresh", "cached"):
-                    t0 = time.perf_counter()
-                    for _ in range(e2e_steps):
-                        if kind == "fresh":
-                            nudge(isc)
-                        lib.render(isc, icfg, out=irgb)
-                    runs[kind] = (time.perf_counter() - t0) / e2e_steps
-                e2e_inproc = {"api": f"pt_render with PtConfig.n_gpus = {world} (one process, NCCL reduce inside the library)",
-                              "value": segments_per_step / runs["fresh"] / 1e6, "unit": "Mrays/s", "frame_ms": runs["fresh"] * 1e3,
-                              "cached": {"value": segments_per_step / runs["cached"] / 1e6, "frame_ms": runs["cached"] * 1e3},
-                              "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h}
-            except ptb200.PtError as e:
-                e2e_inproc = {"error": str(e)}
+
+            def inproc_leg(res):
+                try:
+                    icfg = ptb200.config(W, H, spp, depth, 1e-4, error, seed=42, device=0, n_gpus=world, accel=args.accel,
+                                         mode=args.mode, q_shift=args.q_shift, rr_depth=rr)
+                    isc = {k: (pin(v) if isinstance(v, np.ndarray) else v) for k, v in sc.items()}
+                    irgb = torch.zeros((H, W, 3), dtype=torch.float32).pin_memory().numpy()
+                    lib.render(isc, icfg, out=irgb)                       # communicators, workspaces, scene cache
+                    runs = {}
+                    for kind in ("fresh", "cached"):
+                        t0 = time.perf_counter()
+                        for _ in range(e2e_steps):
+                            if kind == "fresh":
+                                nudge(isc)
+                            lib.render(isc, icfg, out=irgb)
+                        runs[kind] = (time.perf_counter() - t0) / e2e_steps
+                    res["out"] = {"api": f"pt_render with PtConfig.n_gpus = {world} (one process, NCCL reduce inside the library)",
+                                  "value": segments_per_step / runs["fresh"] / 1e6, "unit": "Mrays/s", "frame_ms": runs["fresh"] * 1e3,
+                                  "cached": {"value": segments_per_step / runs["cached"] / 1e6, "frame_ms": runs["cached"] * 1e3},
+                                  "h2d_bytes_per_step": h2d * world, "d2h_bytes_per_step": d2h}
+                except Exception as e:  # noqa: BLE001 — the line of the torchrun leg must be printed whatever happens here
+                    res["out"] = {"error": f"{type(e).__name__}: {e}"}
+
+            # this leg is an extra: if it hangs (a collective that never completes) the line is printed without it
+            res = {}
+            th = threading.Thread(target=inproc_leg, args=(res,), daemon=True)
+            th.start()
+            th.join(INPROC_TIMEOUT_S)
+            inproc_hung = th.is_alive()
+            e2e_inproc = {"error": f"no answer within {INPROC_TIMEOUT_S} s"} if inproc_hung else res.get("out")
 
     if rank == 0:
         st = ds.stats()
@@ -564,6 +578,9 @@ def main():
                "e2e_cached": e2e_cached, "e2e_inproc": e2e_inproc,
                "gpu_launches": launches_per_step * args.steps, "clocks": clocks, "roofline": roof, "cpu_baseline": cpu}
         emit(out)
+        if world > 1 and inproc_hung:
+            sys.stdout.flush()
+            os._exit(0)  # the hung leg holds device handles: no orderly teardown
     ds.close()
 
 
