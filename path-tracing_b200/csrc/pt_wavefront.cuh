@@ -364,7 +364,10 @@ __device__ __forceinline__ unsigned coop_scan(const SceneView &sc, const Ray8 &r
 //   scan    the triangles those nodes handed out, shared out over the warp (coop_scan).
 // History (profiles/r02_*): the first 8-wide version looped over a node's triangles per lane right after the visit —
 // 31 % of the warp instructions at 3.0 lanes, 23 % in the exact test at 1.0; "one unit per lane per round" cured that
-// but put the 286-instruction node visit at 17 lanes.
+// but put the 286-instruction node visit at 17 lanes.  Candidates wait as (record base, bit mask of the node's
+// triangles): every candidate of a node goes to the exact phase — with two waiting slots a third candidate (a ray near
+// a shared vertex passes the scan of up to six dilated neighbours) was tested on the spot at 1.1 lanes, 6.5 % of the
+// kernel's warp instructions (profiles/r02_sweep_session2_kernels.txt: traverse -3.5 %).
 template <bool COUNT, bool WT>
 __global__ void __launch_bounds__(128, PT_TRAV_MIN_BLOCKS)
 k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *stats) {
@@ -375,7 +378,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     const int lane = threadIdx.x & 31;
     uint2 stack[kStackDepth];  // node groups only: triangle groups are consumed in the round that produced them
     int sp = 0, slot = -1;
-    int pend0 = -1, pend1 = -1;  // records that passed their scan and wait for the exact test
+    unsigned pbase = 0u, pmask = 0u;  // records pbase + (set bits of pmask) passed their scan and wait for the exact test
     uint2 ng = make_uint2(0u, 0u);
     bool done = false;
     Ray8 r;
@@ -383,7 +386,7 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
     Hit h = no_hit();
     unsigned long long n_nodes = 0, n_tris = 0, n_exact = 0, ray_nodes0 = 0;
     while (true) {
-        const bool need = !done && !has_inner(ng) && sp == 0 && pend0 < 0;
+        const bool need = !done && !has_inner(ng) && sp == 0 && pmask == 0u;
         if (need && slot >= 0) {  // retire the finished ray
             if (COUNT && stats) {
                 atomicAdd(&stats[4], 1ull);
@@ -423,21 +426,22 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         }
         if (__all_sync(0xffffffffu, done)) break;
         // ---- exact phase
-        const unsigned me = __ballot_sync(0xffffffffu, pend0 >= 0);
+        const unsigned me = __ballot_sync(0xffffffffu, pmask != 0u);
         if (me) {
-            const unsigned other = __ballot_sync(0xffffffffu, pend0 < 0 && (has_inner(ng) || sp > 0));
+            const unsigned other = __ballot_sync(0xffffffffu, pmask == 0u && (has_inner(ng) || sp > 0));
             if (__popc(me) >= PT_EXACT_LANES || other == 0u) {
-                if (pend0 >= 0) {
-                    tri_intersect<WT>(sc, pend0, r.o, r.d, eps, h);
-                    if (pend1 >= 0) tri_intersect<WT>(sc, pend1, r.o, r.d, eps, h);
-                    if (COUNT) n_exact += pend1 >= 0 ? 2u : 1u;
-                    pend0 = pend1 = -1;
+                while (pmask) {  // the first pass runs with every waiting lane; further candidates of one node (a ray
+                                 // near a shared vertex passes the scan of up to six dilated neighbours) follow
+                    const int j = 31 - __clz((int)pmask);
+                    pmask &= ~(1u << j);
+                    tri_intersect<WT>(sc, (int)pbase + j, r.o, r.d, eps, h);
+                    if (COUNT) ++n_exact;
                 }
             }
         }
         // ---- node phase: one wide node per lane that is not waiting for an exact test
         uint2 tg = make_uint2(0u, 0u);
-        if (pend0 < 0) {
+        if (pmask == 0u) {
             if (!has_inner(ng) && sp > 0) ng = stack[--sp];
             if (has_inner(ng)) enter_child<COUNT>(sc, r, h.t, ng, tg, stack, sp, n_nodes);
         }
@@ -445,16 +449,11 @@ k_wf_traverse(SceneView sc, WfState wf, int set, float eps, unsigned long long *
         if (__any_sync(0xffffffffu, tg.y != 0u)) {
             unsigned passed = coop_scan<WT>(sc, r, eps, h.t, tg);
             if (COUNT) n_tris += __popc(tg.y);
-            while (passed) {  // the k-th triangle of my group is a candidate
+            if (passed) pbase = tg.x;  // (a lane that walked a node this round had nothing pending)
+            while (passed) {  // the k-th triangle of my group is a candidate: all of them wait for the exact phase
                 const int k = __ffs(passed) - 1;
                 passed &= passed - 1u;
-                const int rec = (int)tg.x + kth_set_bit(tg.y, k);
-                if (pend0 < 0) pend0 = rec;
-                else if (pend1 < 0) pend1 = rec;
-                else {  // a third candidate from one node (rare): at once
-                    tri_intersect<WT>(sc, rec, r.o, r.d, eps, h);
-                    if (COUNT) ++n_exact;
-                }
+                pmask |= 1u << kth_set_bit(tg.y, k);
             }
         }
     }
