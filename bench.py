@@ -410,7 +410,7 @@ def main():
 
     if args.warmup > 0:
         for _ in range(2):  # untimed: the library keeps two built scenes per device, each with its path-state workspace
-            e2e_call()      # (GBs of HBM); the third new scene is the first to evict one and reuse its blocks
+            e2e_call()      # (GBs of HBM); from the third new scene on the oldest one leaves first and its blocks are reused
     e2e_sec, e2e_calls = timed_calls(e2e_call, e2e_steps)
     e2e_mrays = segments_per_step / e2e_sec / 1e6
     e2e_cached = None

@@ -158,7 +158,7 @@ struct PtDeviceScene {
     void *wf_mem = nullptr;
     size_t wf_slots = 0, wf_pixels = 0, wf_bytes = 0;
     int *h_counters = nullptr;  // pinned, 6 ints
-    int traverse_blocks = 0;
+    int traverse_blocks = 0, sms = 0;
 };
 
 static int validate_scene(const PtScene *s) {
@@ -561,15 +561,16 @@ int acquire_scene(const PtScene *scene, const PtConfig *cfg, const SceneKey &key
                 return PT_OK;
             }
     }
-    PtDeviceScene *ds = nullptr;
-    int rc = pt_scene_create(scene, cfg, 0, &ds);
-    if (rc) return rc;
+    // Room first: the least recently used idle entries of this device leave BEFORE the new scene is built, so that its
+    // arrays and its path-state workspace (GBs) come out of the blocks they hand back to the pool — built first, every
+    // new scene would go to cudaMalloc for all of it (measured: up to 400 ms on a shared box) and the device would hold
+    // one scene more than the cache's size at the peak.
     std::vector<PtDeviceScene *> evict;
     {
         std::lock_guard<std::mutex> lock(g_cache_m);
         int n_dev = 0;
         for (const CachedScene &c : g_cache) n_dev += c.device == dev;
-        while (n_dev >= kCachePerDevice) {  // drop the least recently used idle entry of this device
+        while (n_dev >= kCachePerDevice) {
             int victim = -1;
             for (size_t i = 0; i < g_cache.size(); ++i)
                 if (g_cache[i].device == dev && !g_cache[i].in_use && (victim < 0 || g_cache[i].stamp < g_cache[victim].stamp)) victim = (int)i;
@@ -578,11 +579,17 @@ int acquire_scene(const PtScene *scene, const PtConfig *cfg, const SceneKey &key
             g_cache.erase(g_cache.begin() + victim);
             --n_dev;
         }
+    }
+    for (PtDeviceScene *e : evict) pt_scene_destroy(e);
+    PtDeviceScene *ds = nullptr;
+    int rc = pt_scene_create(scene, cfg, 0, &ds);
+    if (rc) return rc;
+    {
+        std::lock_guard<std::mutex> lock(g_cache_m);
         CachedScene c;
         c.key = key; c.ds = ds; c.device = dev; c.in_use = true; c.stamp = ++g_cache_clock;
         g_cache.push_back(c);
     }
-    for (PtDeviceScene *e : evict) pt_scene_destroy(e);
     *out = ds;
     return PT_OK;
 }
@@ -707,6 +714,7 @@ static int wf_reserve(PtDeviceScene *ds, size_t npx, size_t npx_traced, int q_sh
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_traverse<false, false>, 128, 0));
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ds->device));
         ds->traverse_blocks = std::max(1, per_sm) * std::max(1, sms);
+        ds->sms = std::max(1, sms);
     }
     return PT_OK;
 }
@@ -782,7 +790,7 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     const size_t pix_end = (size_t)rp.row1 * rp.W;  // the rows this call traces (PtConfig::row_begin / row_end)
     for (size_t pix0 = (size_t)rp.row0 * rp.W; pix0 < pix_end && total > 0; pix0 += npc_max) {
         const int npix = (int)std::min<size_t>(npc_max, pix_end - pix0);
-        const int slot_blocks = blocks_for((long long)npix << rp.q_shift, kWfBlock);
+        const int slot_blocks = wf_grid(blocks_for((long long)npix << rp.q_shift, kWfBlock), ds->sms);  // the kernels stride over the rest
         int remaining = total;
         while (remaining > 0) {
             const int steps = (remaining + Q - 1) / Q;

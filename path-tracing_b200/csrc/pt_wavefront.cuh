@@ -168,6 +168,20 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
 
 // WT (here and in the kernels below): the intersector, PT_ISECT_WATERTIGHT or the reference's — a template parameter, so
 // that each instantiation carries only its own test (as a run-time branch the second test cost the parity path 5 %)
+// Grid of the per-slot kernels.  A step has up to 2^27 path slots = 1 M blocks of 128 threads; launched as such, every
+// block stages the shared-memory image again, and a launch over alive lists (ALIVE) pays for a million blocks that look
+// at an empty list and leave (depth 32 under roulette: 28 of 32 bounce launches).  So the kernels take a grid of at most
+// kWfGridWaves resident waves and stride over the virtual blocks; the stride is a multiple of kAliveLists, which keeps
+// a virtual block's sub-list (virtual block % kAliveLists) equal to its real block's.
+#ifndef PT_WF_GRID_WAVES
+#define PT_WF_GRID_WAVES 32
+#endif
+constexpr int kWfGridWaves = PT_WF_GRID_WAVES;
+__host__ __device__ inline int wf_grid(int virtual_blocks, int sms) {
+    const int cap = (sms * PT_WF_MIN_BLOCKS * kWfGridWaves + kAliveLists - 1) / kAliveLists * kAliveLists;
+    return kWfGridWaves > 0 && virtual_blocks > cap ? cap : virtual_blocks;
+}
+
 template <bool COUNT, bool ALIVE, bool WT>
 __global__ void __launch_bounds__(kWfBlock, PT_WF_MIN_BLOCKS)
 k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
@@ -175,35 +189,38 @@ k_wf_begin(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix) {
     if (!sc.brute) stage_large(sc, s_large);
     if (blockIdx.x == 0 && threadIdx.x == 0) { wf.counters[2] = 0; wf.counters[3] = 0; }  // the other queue
     __syncthreads();
-    const int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool in_range = slot < (npix << rp.q_shift);
     unsigned long long n_nodes = 0, n_tris = 0;
-    bool traced = false;
-    V3 o = mk(0.0f, 0.0f, -20.0f), d = mk(0.0f, 0.0f, 1.0f);
-    if (in_range) {
-        int pi, q;
-        slot_split(slot, npix, rp.q_shift, rp.sample_major != 0, pi, q);
-        const int p = pix0 + pi;
-        const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
-        const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
-        const int s = s_next + q * rp.s_step;
-        const bool live = s_next < rp.spp && s < rp.spp;
-        const float fn = rp.rr_depth > 0 ? __ldcs(&wf.accw[p]) : (float)cnt;
-        traced = live && !adaptive_skip(s, fn, mk(a1.x, a1.y, a1.z), mk(a2.x, a2.y, a2.z), rp.error);
-        int flags = (live ? WF_LIVE : 0) | (traced ? WF_TRACED : 0);
-        if (traced) {
-            const int x = p % rp.W, y = p / rp.W;
-            d = primary_dir(x, y, rp.W, rp.H, (uint32_t)p, (uint32_t)s, rp.seed);
-            if (rp.max_depth > 0) flags |= WF_ALIVE;  // Ray::IsValid with depth 0, colour 1 (ray.h:52-54)
+    const int n_slots = npix << rp.q_shift, n_vblocks = (n_slots + (int)blockDim.x - 1) / (int)blockDim.x;
+    for (int vb = blockIdx.x; vb < n_vblocks; vb += gridDim.x) {
+        const int slot = vb * blockDim.x + threadIdx.x;
+        const bool in_range = slot < n_slots;
+        bool traced = false;
+        V3 o = mk(0.0f, 0.0f, -20.0f), d = mk(0.0f, 0.0f, 1.0f);
+        if (in_range) {
+            int pi, q;
+            slot_split(slot, npix, rp.q_shift, rp.sample_major != 0, pi, q);
+            const int p = pix0 + pi;
+            const float4 a1 = __ldcs(&wf.acc1[p]), a2 = __ldcs(&wf.acc2[p]);
+            const int cnt = __float_as_int(a1.w), s_next = __float_as_int(a2.w);
+            const int s = s_next + q * rp.s_step;
+            const bool live = s_next < rp.spp && s < rp.spp;
+            const float fn = rp.rr_depth > 0 ? __ldcs(&wf.accw[p]) : (float)cnt;
+            traced = live && !adaptive_skip(s, fn, mk(a1.x, a1.y, a1.z), mk(a2.x, a2.y, a2.z), rp.error);
+            int flags = (live ? WF_LIVE : 0) | (traced ? WF_TRACED : 0);
+            if (traced) {
+                const int x = p % rp.W, y = p / rp.W;
+                d = primary_dir(x, y, rp.W, rp.H, (uint32_t)p, (uint32_t)s, rp.seed);
+                if (rp.max_depth > 0) flags |= WF_ALIVE;  // Ray::IsValid with depth 0, colour 1 (ray.h:52-54)
+            }
+            traced = (flags & WF_ALIVE) != 0;
+            __stcs(&wf.Tn[slot], make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags)));
+            __stcs(&wf.cS[slot], make_float4(0.0f, 0.0f, 0.0f, 1.0f));
         }
-        traced = (flags & WF_ALIVE) != 0;
-        __stcs(&wf.Tn[slot], make_float4(1.0f, 1.0f, 1.0f, __int_as_float(flags)));
-        __stcs(&wf.cS[slot], make_float4(0.0f, 0.0f, 0.0f, 1.0f));
+        unsigned ma = 0u;
+        const int abase = ALIVE ? alive_reserve(wf, 0, traced, ma) : 0;
+        front<COUNT, WT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
+        if (ALIVE) alive_store(wf, 0, slot, traced, ma, abase);
     }
-    unsigned ma = 0u;
-    const int abase = ALIVE ? alive_reserve(wf, 0, traced, ma) : 0;
-    front<COUNT, WT>(sc, s_large, wf, 0, slot, traced, o, d, rp.eps, n_nodes, n_tris);
-    if (ALIVE) alive_store(wf, 0, slot, traced, ma, abase);
     if (COUNT && rp.stats) {  // one atomic per warp per counter
         for (int o2 = 16; o2; o2 >>= 1) {
             n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);
@@ -226,63 +243,70 @@ k_wf_bounce(SceneView sc, RenderParams rp, WfState wf, int pix0, int npix, int b
         if (ALIVE && threadIdx.x < kAliveLists)
             wf.counters[kWfCounters + ((b + 2) % 3) * kAliveLists + threadIdx.x] = 0;  // the set the next bounce appends to
     }
-    int slot = blockIdx.x * blockDim.x + threadIdx.x;
-    bool in_range = slot < (npix << rp.q_shift);
-    if (ALIVE) {  // this block's share of the alive paths: chunk blockIdx / kAliveLists of sub-list blockIdx % kAliveLists
-        const int sub = blockIdx.x % kAliveLists, chunk0 = (blockIdx.x / kAliveLists) * blockDim.x;
-        const int n_sub = wf.counters[kWfCounters + (b % 3) * kAliveLists + sub];
-        if (chunk0 >= n_sub) return;
-        in_range = chunk0 + (int)threadIdx.x < n_sub;
-        slot = in_range ? __ldcs(&wf.alive[(size_t)(b & 1) * wf.alive_cap + (size_t)sub * wf.alive_seg + chunk0 + threadIdx.x]) : 0;
-        PT_CHK(slot >= 0 && slot < wf.cap, CHK_SLOT);
-    }
-    // this thread's path state first: the loads are in flight while the block stages the shared-memory image
-    float4 tn = make_float4(0.f, 0.f, 0.f, 0.f), ot = tn, dr = tn;
-    int s_base = 0, pi = 0, q = 0;
-    if (in_range) {
-        tn = __ldcs(&wf.Tn[slot]);
-        ot = __ldcs(&wf.oT[slot]);
-        dr = __ldcs(&wf.dR[slot]);
-        slot_split(slot, npix, rp.q_shift, rp.sample_major != 0, pi, q);
-        s_base = __float_as_int(__ldcs(&wf.acc2[pix0 + pi].w));
-    }
+    const int n_slots = npix << rp.q_shift;
+    // The work of this block (wf_grid).  Direct: virtual blocks blockIdx, blockIdx + gridDim, ... of the slot range.  Over
+    // alive lists: chunks of sub-list (blockIdx % kAliveLists), shared among the blocks that serve that sub-list.
+    const int sub = blockIdx.x % kAliveLists;
+    const int n_sub = ALIVE ? wf.counters[kWfCounters + (b % 3) * kAliveLists + sub] : 0;
+    const int first = ALIVE ? blockIdx.x / kAliveLists : blockIdx.x;
+    const int stride = ALIVE ? ((int)gridDim.x - sub + kAliveLists - 1) / kAliveLists : (int)gridDim.x;
+    const int n_work = ((ALIVE ? n_sub : n_slots) + (int)blockDim.x - 1) / (int)blockDim.x;
+    if (first >= n_work) return;  // (the whole block: no barrier is left behind)
     if (!sc.brute) stage_large(sc, s_large);
     const int set = (b + 1) & 1;
     __syncthreads();
     unsigned long long n_nodes = 0, n_tris = 0;
-    bool alive = false;
-    V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
-    if (in_range) {
-        int flags = __float_as_int(tn.w);
-        if (flags & WF_ALIVE) {
-            o = mk(ot.x, ot.y, ot.z);
-            d = mk(dr.x, dr.y, dr.z);
-            V3 T = mk(tn.x, tn.y, tn.z), c = mk(0, 0, 0);
-            int depth = flags & 0xffff;
-            Hit h;
-            h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
-            const int p = pix0 + pi;
-            const int s = s_base + q * rp.s_step;
-            bool contrib = false;
-            const bool rr_on = rp.rr_depth > 0;  // the path weight lives in cS.w; it is 1 unless roulette has been played
-            float wgt = rr_on && depth + 1 > rp.rr_depth ? __ldcs(&wf.cS[slot].w) : 1.0f;
-            const float wgt0 = wgt;
-            const int depth0 = depth;
-            alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, wgt, &c, &contrib);
-            const bool shade_end = !alive && depth == depth0;
-            // Ray::IsValid before the next TraceRay (ray.h:52-54)
-            alive = alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f);
-            flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0) |
-                    (shade_end ? WF_SHADE_END : 0);
-            __stcs(&wf.Tn[slot], make_float4(T.x, T.y, T.z, __int_as_float(flags)));
-            if (contrib) __stcs(&wf.cS[slot], make_float4(c.x, c.y, c.z, wgt));
-            else if (wgt != wgt0) __stcs(&wf.cS[slot].w, wgt);
+    for (int w = first; w < n_work; w += stride) {
+        int slot = w * blockDim.x + threadIdx.x;
+        bool in_range = slot < n_slots;
+        if (ALIVE) {
+            in_range = slot < n_sub;  // (position in the sub-list so far)
+            slot = in_range ? __ldcs(&wf.alive[(size_t)(b & 1) * wf.alive_cap + (size_t)sub * wf.alive_seg + slot]) : 0;
+            PT_CHK(slot >= 0 && slot < wf.cap, CHK_SLOT);
         }
+        float4 tn = make_float4(0.f, 0.f, 0.f, 0.f), ot = tn, dr = tn;
+        int s_base = 0, pi = 0, q = 0;
+        if (in_range) {
+            tn = __ldcs(&wf.Tn[slot]);
+            ot = __ldcs(&wf.oT[slot]);
+            dr = __ldcs(&wf.dR[slot]);
+            slot_split(slot, npix, rp.q_shift, rp.sample_major != 0, pi, q);
+            s_base = __float_as_int(__ldcs(&wf.acc2[pix0 + pi].w));
+        }
+        bool alive = false;
+        V3 o = mk(0, 0, 0), d = mk(0, 0, 1);
+        if (in_range) {
+            int flags = __float_as_int(tn.w);
+            if (flags & WF_ALIVE) {
+                o = mk(ot.x, ot.y, ot.z);
+                d = mk(dr.x, dr.y, dr.z);
+                V3 T = mk(tn.x, tn.y, tn.z), c = mk(0, 0, 0);
+                int depth = flags & 0xffff;
+                Hit h;
+                h.t = ot.w; h.rec = __float_as_int(dr.w); h.idx = 0;  // shade() does not read idx
+                const int p = pix0 + pi;
+                const int s = s_base + q * rp.s_step;
+                bool contrib = false;
+                const bool rr_on = rp.rr_depth > 0;  // the path weight lives in cS.w; it is 1 unless roulette has been played
+                float wgt = rr_on && depth + 1 > rp.rr_depth ? __ldcs(&wf.cS[slot].w) : 1.0f;
+                const float wgt0 = wgt;
+                const int depth0 = depth;
+                alive = shade(sc, s_large, rp, h, (uint32_t)p, (uint32_t)s, o, d, T, depth, wgt, &c, &contrib);
+                const bool shade_end = !alive && depth == depth0;
+                // Ray::IsValid before the next TraceRay (ray.h:52-54)
+                alive = alive && depth < rp.max_depth && (T.x != 0.0f || T.y != 0.0f || T.z != 0.0f);
+                flags = (flags & ~(0xffff | WF_ALIVE)) | depth | (alive ? WF_ALIVE : 0) | (contrib ? WF_CONTRIB : 0) |
+                        (shade_end ? WF_SHADE_END : 0);
+                __stcs(&wf.Tn[slot], make_float4(T.x, T.y, T.z, __int_as_float(flags)));
+                if (contrib) __stcs(&wf.cS[slot], make_float4(c.x, c.y, c.z, wgt));
+                else if (wgt != wgt0) __stcs(&wf.cS[slot].w, wgt);
+            }
+        }
+        unsigned ma = 0u;
+        const int abase = ALIVE ? alive_reserve(wf, (b + 1) % 3, alive, ma) : 0;
+        front<COUNT, WT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
+        if (ALIVE) alive_store(wf, set, slot, alive, ma, abase);
     }
-    unsigned ma = 0u;
-    const int abase = ALIVE ? alive_reserve(wf, (b + 1) % 3, alive, ma) : 0;
-    front<COUNT, WT>(sc, s_large, wf, set, slot, alive, o, d, rp.eps, n_nodes, n_tris);
-    if (ALIVE) alive_store(wf, set, slot, alive, ma, abase);
     if (COUNT && rp.stats) {  // one atomic per warp per counter
         for (int o2 = 16; o2; o2 >>= 1) {
             n_nodes += __shfl_xor_sync(0xffffffffu, n_nodes, o2);

@@ -48,10 +48,24 @@ def run_variant(name, big, small, state):
         if i:
             ms2.append(st2["kernel_ms"])
     ds2.close()
+    # C5 as BASELINE names it (glass_mix, depth 32, roulette from bounce 3): alive lists, most launches nearly empty; and the
+    # reference's default frame (Tor.obj-like small frame: launch-bound)
+    extra = ""
+    for tag, sc3, cfg3 in (("glossy_rr", state["glass"], ptb200.config(1920, 1080, 128, 32, 1e-4, -1.0, seed=42, rr_depth=3)),
+                           ("small512", small, ptb200.config(512, 512, 20, 8, 1e-4, 0.001, seed=42))):
+        ds3 = lib.scene_create(sc3, cfg3)
+        ms3 = []
+        for i in range(3):
+            ds3.render_device(cfg3)
+            st3 = ds3.stats()
+            if i:
+                ms3.append(st3["kernel_ms"])
+        ds3.close()
+        extra += f"  | {tag} {np.mean(ms3):.2f} ms"
     lib.lib.pt_release_workspace()
     return (f"{name:8s} parity {parity:9s} frame {np.mean(ms):7.2f} ms (min {min(ms):.2f})  "
             f"{segs / np.mean(ms) / 1e3:7.0f} Mrays/s  " + "  ".join(f"{c} {v / 3:.2f}" for c, v in zip(CLASSES, cls)) +
-            f"  | cornell {st2['segments'] / np.mean(ms2) / 1e3:7.0f} Mrays/s")
+            f"  | cornell {st2['segments'] / np.mean(ms2) / 1e3:7.0f} Mrays/s" + extra)
 
 
 def main():
@@ -59,7 +73,7 @@ def main():
     t00 = time.time()
     big, small = scenes.torus_room(1000, 500), scenes.torus_room(40, 20)
     print(f"scenes built in {time.time() - t00:.1f} s", flush=True)
-    state = {"ref": None, "cornell": scenes.cornell()}
+    state = {"ref": None, "cornell": scenes.cornell(), "glass": scenes.glass_mix()}
     lines = []
     for name in names:
         try:
