@@ -790,7 +790,9 @@ static int render_wavefront(PtDeviceScene *ds, const RenderParams &rp, cudaStrea
     const size_t pix_end = (size_t)rp.row1 * rp.W;  // the rows this call traces (PtConfig::row_begin / row_end)
     for (size_t pix0 = (size_t)rp.row0 * rp.W; pix0 < pix_end && total > 0; pix0 += npc_max) {
         const int npix = (int)std::min<size_t>(npc_max, pix_end - pix0);
-        const int slot_blocks = wf_grid(blocks_for((long long)npix << rp.q_shift, kWfBlock), ds->sms);  // the kernels stride over the rest
+        int slot_blocks = wf_grid(blocks_for((long long)npix << rp.q_shift, kWfBlock), ds->sms);  // the kernels stride over the rest
+        if (const char *e = getenv("PT_WF_GRID_CAP"))  // test hook: a small grid makes small frames stride too (multiple of the sub-lists)
+            slot_blocks = std::min(slot_blocks, std::max(1, atoi(e) / kAliveLists) * kAliveLists);
         int remaining = total;
         while (remaining > 0) {
             const int steps = (remaining + Q - 1) / Q;

@@ -779,3 +779,28 @@ def test_alive_lists_do_not_change_the_result(lib, tor, case):
     for x, y, what in zip(out[0], out[1], ("sum", "sum2", "count", "weight")):
         assert_bits_equal(x, y, f"{case} {what}")
     assert out[0][2].sum() > 0
+
+
+@pytest.mark.parametrize("case", ["tor_flat", "tor_adapt", "roulette", "sky", "torus40"])
+def test_strided_grid_is_the_one_block_per_chunk_grid(lib, tor, case, monkeypatch):
+    """k_wf_begin / k_wf_bounce run on a bounded grid that strides over the step's blocks of 128 slots (wf_grid); small
+    frames stay below the bound.  PT_WF_GRID_CAP (test hook) forces 64 and 128 blocks, so that every block makes
+    many passes — directly and over the alive lists' chunks: the same accumulators bit for bit."""
+    kw, sc, size, spp, depth = dict(error=-1.0), tor, (96, 64), 24, 8
+    if case == "tor_adapt":
+        kw = dict(error=0.002, alive=1)
+    elif case == "roulette":
+        kw, sc, depth = dict(error=-1.0, rr_depth=2), scenes.glass_mix(), 24
+    elif case == "sky":
+        sc = dict(scenes.open_scene(), sky=scenes.sky_image())
+    elif case == "torus40":
+        sc, size = scenes.torus_room(40, 20), (128, 72)
+    cfg = ptb200.config(size[0], size[1], spp, depth, 1e-4, seed=3, **kw)
+    monkeypatch.delenv("PT_WF_GRID_CAP", raising=False)
+    ref = lib.render_accum_w(sc, cfg)
+    for cap in ("64", "128"):
+        monkeypatch.setenv("PT_WF_GRID_CAP", cap)
+        out = lib.render_accum_w(sc, cfg)
+        for x, y, what in zip(out, ref, ("sum", "sum2", "count", "weight")):
+            assert_bits_equal(x, y, f"{case} cap {cap} {what}")
+    assert ref[2].sum() > 0

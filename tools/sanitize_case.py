@@ -1,6 +1,7 @@
 """The small case run under compute-sanitizer (one --tool per gpurun call: memcheck, racecheck, initcheck):
 Tor.obj 64x64x16 with the adaptive rule on, both pipelines, alive lists on and off, 8-wide BVH and brute force, a
-Russian-roulette render, a row band, a resumed render, the watertight intersector, pt_intersect and the post stage.
+Russian-roulette render, a row band, a resumed render, the watertight intersector, pt_intersect, the post stage, and
+renders on a strided grid of the per-slot kernels.
   compute-sanitizer --tool memcheck python tools/sanitize_case.py"""
 import os
 import sys
@@ -36,6 +37,11 @@ def main():
     big = scenes.torus_room(250, 200)  # 100k triangles: a tree of several levels
     lib.render_accum(big, ptb200.config(160, 90, 16, 8, 1e-4, -1.0))
     lib.render_accum(big, ptb200.config(160, 90, 40, 8, 1e-4, 0.001, q_shift=3, alive=1))
+    os.environ["PT_WF_GRID_CAP"] = "64"  # the per-slot kernels stride over the step's blocks (many passes per block)
+    lib.render_accum(big, ptb200.config(160, 90, 16, 8, 1e-4, -1.0))
+    lib.render_accum(big, ptb200.config(160, 90, 40, 8, 1e-4, 0.001, q_shift=3, alive=1))
+    lib.render_accum_w(scenes.glass_mix(), ptb200.config(48, 32, 8, 16, 1e-4, -1.0, seed=3, rr_depth=2))
+    del os.environ["PT_WF_GRID_CAP"]
     lib.lib.pt_release_workspace()
     print(f"sanitize case done: {n} contributing paths, {int((ids >= 0).sum())} hits")
     try:
