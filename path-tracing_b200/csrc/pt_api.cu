@@ -350,6 +350,8 @@ extern "C" int pt_scene_create(const PtScene *scene, const PtConfig *cfg, int32_
             ++launches;
             CK(cudaMemcpy(&scr, d_scr.p, sizeof scr, cudaMemcpyDeviceToHost));
             v.n_quads = scr.n_quads;
+            v.direct_lo = scr.direct_lo; v.direct_hi = scr.direct_hi;
+            v.wt_cabs = 1.2e-5f * scr.amax;
         }
         int levels = 0;
         if (nb == 0) {

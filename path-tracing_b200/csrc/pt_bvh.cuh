@@ -50,7 +50,9 @@ __device__ __forceinline__ int f2ord(float f) {
 __device__ __forceinline__ float ord2f(int i) { return __int_as_float(i >= 0 ? i : i ^ 0x7fffffff); }
 
 struct BuildScratch {  // scene vertex bounds (ordered ints) lo xyz, hi xyz, large-triangle count, quad units, unbounded count
-    int lo[3], hi[3], n_large, n_quads, n_unbounded, pad;
+    int lo[3], hi[3], n_large, n_quads, n_unbounded;
+    unsigned direct_lo, direct_hi;  // k_large_pack: large records the watertight mode must test without the scan (SceneView)
+    float amax;                     // k_large_pack: largest |coordinate| of the scene (at least 20)
 };
 
 __global__ void k_init_scratch(BuildScratch *s) {
@@ -59,7 +61,8 @@ __global__ void k_init_scratch(BuildScratch *s) {
     s->n_large = 0;
     s->n_quads = 0;
     s->n_unbounded = 0;
-    s->pad = 0;
+    s->direct_lo = s->direct_hi = 0u;
+    s->amax = 20.0f;
 }
 
 __global__ void k_vertex_bounds(const float *__restrict__ verts, int n, BuildScratch *s) {
@@ -475,8 +478,21 @@ k_large_pack(int *__restrict__ vals, const float *__restrict__ verts, const floa
     __syncthreads();
     const int nq = n_quads_s, n_single = n_large - 2 * nq;
     const float slack = amax * (64.0f * 1.1920929e-7f);
+    if (k == 0) s->amax = amax;
     if (k < n_large) {  // record rows in the new order
         const LargeTri &t = tri[order[k]];
+        {   // Watertight mode (pt_trace.cuh large_phase): the scan units bound what the REFERENCE accepts around the STORED
+            // plane.  They also bound the geometric triangle (the region is a dilation of it) when the stored plane is
+            // the geometric one: unit normals agree and every vertex lies within 1e-5 amax of the plane.  Otherwise
+            // (a `vn` plane, a degenerate triangle) the record is tested directly.
+            const V3 ng = normalize3(cross3(t.p[1] - t.p[0], t.p[2] - t.p[0])), ns = mk(t.plane.x, t.plane.y, t.plane.z);
+            float dev = 0.0f;
+            for (int j = 0; j < 3; ++j) dev = fmaxf(dev, fabsf(ns.x * t.p[j].x + ns.y * t.p[j].y + ns.z * t.p[j].z + t.plane.w));
+            bool unb;
+            tri_e(t, eps, amax, &unb);
+            const bool geometric = t.S > 0.0f && t.S <= FLT_MAX && !unb && fabsf(dot3(ns, ng)) >= 0.999999f && dev <= 1e-5f * amax;
+            if (!geometric) atomicOr(k < 32 ? &s->direct_lo : &s->direct_hi, 1u << (k & 31));
+        }
         float4 *o = lrecs + 4 * (size_t)k;
         o[0] = t.plane;
         o[1] = make_float4(t.p[0].x, t.p[0].y, t.p[0].z, t.S);

@@ -106,6 +106,10 @@ struct SceneView {
     int sky_w, sky_h;
     unsigned long long *counters;  // [0] nodes visited, [1] triangles tested; nullptr = off
     unsigned one_bits;  // 0x3f800000, deliberately a run-time value: see qfloat (pt_trace.cuh)
+    // watertight mode: bit k = large record k is tested directly, not through its scan unit (its stored plane is not the
+    // geometric one); wt_cabs = the absolute part of the scan's extra tolerance in that mode (pt_trace.cuh large_phase)
+    unsigned direct_lo, direct_hi;
+    float wt_cabs;
 };
 
 }  // namespace ptd

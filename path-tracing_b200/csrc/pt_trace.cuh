@@ -190,8 +190,12 @@ __device__ __forceinline__ void stage_large(const SceneView &sc, float4 *s_large
 // the hit, fell from 15.1 to 7.7 Grays/s, and with the exact tests gathered behind the loop still to 10.9.  The
 // branch-free scan of every unit, 60 instructions each, wins because all 32 lanes run it together.)
 // (tnear, rnear): smallest scanned distance among the marked units so far and the first record of that unit
+// WT (the watertight mode's use of the scan, large_phase): the tolerance grows by (wt_c + 2e-6 |t|) / |d . n| — the
+// watertight test decides at the TRUE hit point, which the scanned one misses by the rounding of numerator and
+// denominator and by the distance between the stored plane and the geometric triangle (<= 1e-5 amax, k_large_pack).
+template <bool WT>
 __device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int n, V3 o, V3 d, float t_lo, float t_hi,
-                                               float &tnear, int &rnear) {
+                                               float wt_c, float &tnear, int &rnear) {
     unsigned mask = 0u;  // bit 2 (u - u0) = A of unit u, bit 2 (u - u0) + 1 = B
     for (int u = 0; u < n; ++u) {
         const float4 *r = units + kQuadRows * (u0 + u);
@@ -202,7 +206,7 @@ __device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int 
         const float num = -__fmaf_rn(o.x, p.x, __fmaf_rn(o.y, p.y, __fmaf_rn(o.z, p.z, p.w)));
         const float rc = rcp_approx(sd);
         const float t = num * rc;
-        const float tau = __fmaf_rn(fabsf(t), meta.y, meta.x) * fabsf(rc);
+        const float tau = __fmaf_rn(fabsf(t), WT ? meta.y + 2e-6f : meta.y, WT ? meta.x + wt_c : meta.x) * fabsf(rc);
         const float tol = __fmaf_rn(fabsf(t), 2e-6f, tau);
         const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
         const float4 e0 = r[1], e1 = r[2], e2 = r[3], e3 = r[4], e4 = r[5];
@@ -223,23 +227,26 @@ __device__ __forceinline__ unsigned scan_quads(const float4 *units, int u0, int 
 }
 
 // one 32-triangle chunk of single units [s0, s0 + n): returns their candidate mask
+template <bool WT>
 __device__ __forceinline__ unsigned scan_singles(const float4 *units, int s0, int n, int rec0, V3 o, V3 d, float t_lo,
-                                                 float t_hi, float &tnear, int &rnear) {
+                                                 float t_hi, float wt_c, float &tnear, int &rnear) {
     unsigned mask = 0u;
     for (int k = 0; k < n; ++k) {
         const float4 *r = units + kSingleRows * (s0 + k);
         const float4 p = r[0];
         const float sd = d.x * p.x + d.y * p.y + d.z * p.z;
         const float num = -(o.x * p.x + o.y * p.y + o.z * p.z + p.w);
-        const float t = num * rcp_approx(sd);
-        const float tol = fabsf(t) * 2e-6f;
+        const float rc = rcp_approx(sd);
+        const float t = num * rc;
+        const float tau = WT ? __fmaf_rn(fabsf(t), 2e-6f, wt_c) * fabsf(rc) : 0.0f;
+        const float tol = WT ? __fmaf_rn(fabsf(t), 2e-6f, tau) : fabsf(t) * 2e-6f;
         const float Px = __fmaf_rn(d.x, t, o.x), Py = __fmaf_rn(d.y, t, o.y), Pz = __fmaf_rn(d.z, t, o.z);
         const float4 e0 = r[1], e1 = r[2], e2 = r[3];
         const float g0 = __fmaf_rn(e0.x, Px, __fmaf_rn(e0.y, Py, __fmaf_rn(e0.z, Pz, e0.w)));
         const float g1 = __fmaf_rn(e1.x, Px, __fmaf_rn(e1.y, Py, __fmaf_rn(e1.z, Pz, e1.w)));
         const float g2 = __fmaf_rn(e2.x, Px, __fmaf_rn(e2.y, Py, __fmaf_rn(e2.z, Pz, e2.w)));
         // written so that a NaN anywhere (sd == 0, infinities) marks the triangle: the resolve decides
-        const bool out = (t > t_hi) | (t < t_lo) | (fminf(fminf(g0, g1), g2) < -tol);
+        const bool out = (WT ? (t - tau > t_hi) | (t + tau < t_lo) : (t > t_hi) | (t < t_lo)) | (fminf(fminf(g0, g1), g2) < -tol);
         mask |= (out ? 0u : 1u) << k;
         const bool nearer = !out && t < tnear;
         tnear = nearer ? t : tnear;
@@ -272,25 +279,30 @@ __device__ __forceinline__ void large_resolve32(const float4 *s_large, int k0, u
     }
 }
 
+// direct: bit k = large record k goes to the watertight test whatever its scan unit says (SceneView::direct_lo / hi)
 template <bool WT>
 __device__ __forceinline__ void large_phase(const float4 *s_large, int n_large, int n_quads, int rec_base, V3 o, V3 d,
-                                            float eps, Hit &h) {
-    if (WT) {  // the scan units bound the REFERENCE's acceptance sets around the stored planes, which need not hold the
-               // geometric hit (a `vn` plane): the watertight mode tests every shared-memory triangle directly
-        large_resolve32<true>(s_large, 0, n_large >= 32 ? 0xffffffffu : (1u << n_large) - 1u, rec_base, o, d, eps, h);
-        if (n_large > 32) large_resolve32<true>(s_large, 32, n_large >= 64 ? 0xffffffffu : (1u << (n_large - 32)) - 1u, rec_base, o, d, eps, h);
-        return;
-    }
+                                            float eps, Hit &h, unsigned long long direct = 0ull, float wt_c = 0.0f) {
+    // Watertight mode: the same scan in front of the watertight test.  The units bound what the reference accepts
+    // around the stored plane — a dilation of the geometric triangle when that plane is the geometric one; records whose
+    // plane is not (`vn`) are in `direct`.  The tolerances grow as scan_quads describes; a false mark costs one test.
+    // (Round 2 tested every shared-memory triangle directly in this mode: k_wf_bounce took twice the parity mode's time.)
     const float t_hi = h.t + fabsf(h.t) * 2e-6f, t_lo = eps - fabsf(eps) * 2e-6f;
     const float4 *quads = s_large + 4 * n_large, *singles = quads + kQuadRows * n_quads;
     const int n_single = n_large - 2 * n_quads;
     // records 2u, 2u + 1 belong to quad u; record 2 n_quads + s to single s
     float tnear = __int_as_float(0x7f800000);
     int rnear = -1;
-    unsigned q0 = scan_quads(quads, 0, min(n_quads, 16), o, d, t_lo, t_hi, tnear, rnear);
-    unsigned q1 = n_quads > 16 ? scan_quads(quads, 16, n_quads - 16, o, d, t_lo, t_hi, tnear, rnear) : 0u;
-    unsigned s0 = scan_singles(singles, 0, min(n_single, 32), 2 * n_quads, o, d, t_lo, t_hi, tnear, rnear);
-    unsigned s1 = n_single > 32 ? scan_singles(singles, 32, n_single - 32, 2 * n_quads, o, d, t_lo, t_hi, tnear, rnear) : 0u;
+    unsigned q0 = scan_quads<WT>(quads, 0, min(n_quads, 16), o, d, t_lo, t_hi, wt_c, tnear, rnear);
+    unsigned q1 = n_quads > 16 ? scan_quads<WT>(quads, 16, n_quads - 16, o, d, t_lo, t_hi, wt_c, tnear, rnear) : 0u;
+    unsigned s0 = scan_singles<WT>(singles, 0, min(n_single, 32), 2 * n_quads, o, d, t_lo, t_hi, wt_c, tnear, rnear);
+    unsigned s1 = n_single > 32 ? scan_singles<WT>(singles, 32, n_single - 32, 2 * n_quads, o, d, t_lo, t_hi, wt_c, tnear, rnear) : 0u;
+    if (WT && direct) {
+        const int nq2 = 2 * n_quads;
+        const unsigned long long dq = nq2 >= 64 ? direct : direct & ((1ull << nq2) - 1ull), dsg = nq2 >= 64 ? 0ull : direct >> nq2;
+        q0 |= (unsigned)dq; q1 |= (unsigned)(dq >> 32);
+        s0 |= (unsigned)dsg; s1 |= (unsigned)(dsg >> 32);
+    }
     // The unit with the smallest scanned distance first, all lanes together: it is the hit for most rays, and once
     // h.t is set the other candidates leave the exact test at its range check.  Any order gives the same answer
     // (header comment).
@@ -563,7 +575,7 @@ __device__ __forceinline__ Hit nearest_hit(const SceneView &sc, const float4 *s_
                                            unsigned long long &n_nodes, unsigned long long &n_tris) {
     if (sc.brute) return brute_hit<COUNT, WT>(sc, o, d, eps, n_tris);
     Hit h = no_hit();
-    large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
+    large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h, ((unsigned long long)sc.direct_hi << 32) | sc.direct_lo, sc.wt_cabs);
     if (COUNT) n_tris += sc.n_large;
     if (!reaches_root(sc, o, d, h.t)) return h;
     bvh8_traverse<COUNT, WT>(sc, o, d, eps, h, n_nodes, n_tris);

@@ -146,7 +146,7 @@ __device__ __forceinline__ void front(const SceneView &sc, const float4 *s_large
         if (sc.brute) {
             h = brute_hit<COUNT, WT>(sc, o, d, eps, n_tris);  // (not nearest_hit: its traversal stack would become this kernel's frame)
         } else {
-            large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h);
+            large_phase<WT>(s_large, sc.n_large, sc.n_quads, sc.n_bvh, o, d, eps, h, ((unsigned long long)sc.direct_hi << 32) | sc.direct_lo, sc.wt_cabs);
             if (COUNT) n_tris += sc.n_large;
             need = reaches_root(sc, o, d, h.t);
         }
