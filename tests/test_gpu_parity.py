@@ -265,15 +265,18 @@ def _stress_rays(sc, n, seed):
     return np.concatenate([org, d], 1).astype(np.float32)
 
 
+@pytest.mark.parametrize("isect", [0, 1], ids=["reference", "watertight"])
 @pytest.mark.parametrize("name", ["cornell", "glossy", "tor", "torus40", "composite"])
-def test_shared_memory_scan_never_misses(lib, tor, name):
+def test_shared_memory_scan_never_misses(lib, tor, name, isect):
     """The scan of the shared-memory triangles (single and quad units, pt_trace.cuh) is conservative by construction;
     here it is checked against the brute-force mode (scene.cpp:114-120 as written) on 600k rays per scene, most of
-    them aimed at edges, vertices and grazing directions."""
+    them aimed at edges, vertices and grazing directions.  The watertight mode puts the same scan (with a tolerance grown
+    for the true hit point, records with a `vn` plane tested directly: Tor.obj, the composite) in front of its own
+    test: same check against its own brute-force mode."""
     sc = {"cornell": scenes.cornell, "glossy": scenes.glossy_mix, "tor": lambda: tor,
           "torus40": lambda: scenes.torus_room(40, 20), "composite": lambda: scenes.composite(tor)}[name]()
     rays = np.concatenate([_stress_rays(sc, 400000, 11), scenes.random_rays(200000, seed=3)])
-    cfg_b, cfg_l = ptb200.config(accel=BRUTE), ptb200.config(accel=LBVH)
+    cfg_b, cfg_l = ptb200.config(accel=BRUTE, intersector=isect), ptb200.config(accel=LBVH, intersector=isect)
     db, dl = lib.scene_create(sc, cfg_b), lib.scene_create(sc, cfg_l)
     ib, tb = db.intersect(rays, cfg_b)
     il, tl = dl.intersect(rays, cfg_l)
